@@ -1,0 +1,388 @@
+// cbp_batch_kernels.cuh — B bound vectors over one matrix.
+//
+// Layout in HBM: bounds are [column][vector] (Bnd = {lb, ub}, 16 B), the
+// vector count padded to a multiple of 32, so the 32 lanes of a warp read the
+// 32 vectors of one column as one contiguous 512-byte line.  A warp owns
+// (row, group of 32 vectors); the row's (a, j) pairs are warp-uniform, so the
+// matrix is fetched once per warp while every lane accumulates its own
+// vector's activities sequentially in CSR order — bit-for-bit the order of the
+// CPU restatement.  Two bound buffers give Jacobi rounds; accepted candidates
+// are atomic min/max on the other buffer plus a dirty bit per (column, vector).
+#pragma once
+#include "cbp_device.cuh"
+
+namespace cbp {
+
+struct BtParams {
+  const double *val;
+  const int *col;
+  const int *rowNz;   // packed offset of each kept row
+  const int *rowCnt;  // nonzeros of each kept row
+  const double *rowLB, *rowUB;
+  const int *rowOrig;
+  const signed char *colType;
+  int mKept, n, Bp, G;  // Bp = padded vector count, G = Bp / 32
+  Bnd *X[2];
+  unsigned *dirty[2];   // [n][G]
+  unsigned *ever;       // [n][G] union of the dirty marks of applied rounds
+  unsigned *active;     // [G]
+  int *vecInfRow, *vecInfCol;  // [Bp] min violating row / crossing column (INT_MAX none)
+  int *vecChanged;             // [Bp] changed columns in the running round
+  int *vecRounds, *vecTotal, *vecStop, *vecFinal;  // [Bp]
+  int *anyActive;
+  Scal s;
+};
+
+struct BtSink {
+  Bnd *dst;         // already offset to this lane's vector: dst[j * Bp]
+  unsigned *dirty;  // already offset to this warp's group: dirty[j * G]
+  size_t Bp;
+  int G;
+  unsigned bit;
+  __device__ __forceinline__ void ub(int j, double v)
+  {
+    atomic_min_f64(&dst[static_cast<size_t>(j) * Bp].ub, v);
+    atomicOr(&dirty[static_cast<size_t>(j) * G], bit);
+  }
+  __device__ __forceinline__ void lb(int j, double v)
+  {
+    atomic_max_f64(&dst[static_cast<size_t>(j) * Bp].lb, v);
+    atomicOr(&dirty[static_cast<size_t>(j) * G], bit);
+  }
+};
+
+// One round, rows phase.  grid.x * 8 warps cover G * mKept (group-major, so
+// warps that run together share a vector group and its bounds stay in L2).
+__global__ void __launch_bounds__(kThreads) bt_rows_kernel(const BtParams p, int cur)
+{
+  const long long W = static_cast<long long>(blockIdx.x) * kWarps + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (W >= static_cast<long long>(p.G) * p.mKept)
+    return;
+  const int g = static_cast<int>(W / p.mKept), r = static_cast<int>(W % p.mKept);
+  const unsigned act = __ldg(&p.active[g]);
+  if (act == 0u)
+    return;
+  const bool mine = (act >> lane) & 1u;
+  const size_t Bp = static_cast<size_t>(p.Bp);
+  const int b = g * 32 + lane;
+  const Bnd *__restrict__ src = p.X[cur] + b;
+  const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
+
+  RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+#pragma unroll 4
+  for (int k = kb; k < ke; ++k) {
+    const double a = __ldg(&p.val[k]);
+    const int j = __ldg(&p.col[k]);
+    const Bnd x = ldcg_bnd(&src[static_cast<size_t>(j) * Bp]);
+    accumulate(ra, a, a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s.inf);
+  }
+  RowPlan pl = plan_row(ra, __ldg(&p.rowLB[r]), __ldg(&p.rowUB[r]), p.s);
+  if (!mine) {
+    pl.infeasible = false;
+    pl.sideU = false;
+    pl.sideL = false;
+  }
+  if (pl.infeasible)
+    atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
+  if (!__any_sync(0xffffffffu, pl.sideU || pl.sideL))
+    return;
+  BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, Bp, p.G, 1u << lane };
+  for (int k = kb; k < ke; ++k) {
+    const double a = __ldg(&p.val[k]);
+    const int j = __ldg(&p.col[k]);
+    if (pl.sideU || pl.sideL) {
+      const Bnd x = ldcg_bnd(&src[static_cast<size_t>(j) * Bp]);
+      tighten_nz(sink, pl, a, j, a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.colType, p.s);
+    }
+  }
+}
+
+// After the rows phase: settle every (column, vector) marked in this round
+// (R9), count changed columns per vector.  One thread per dirty word.
+__global__ void bt_settle_kernel(const BtParams p, int cur)
+{
+  const size_t nW = static_cast<size_t>(p.n) * p.G;
+  const size_t w = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (w >= nW)
+    return;
+  unsigned bits = p.dirty[cur][w];
+  if (!bits)
+    return;
+  const int j = static_cast<int>(w / p.G), g = static_cast<int>(w % p.G);
+  const size_t base = static_cast<size_t>(j) * p.Bp + static_cast<size_t>(g) * 32;
+  const Bnd *src = p.X[cur] + base;
+  Bnd *dst = p.X[cur ^ 1] + base;
+  while (bits) {
+    const int l = __ffs(bits) - 1;
+    bits &= bits - 1;
+    Bnd x = dst[l];
+    const double L0 = x.lb, U0 = x.ub;
+    const int b = g * 32 + l;
+    if (settle(x.lb, x.ub, src[l].ub, p.s))
+      atomicMin(&p.vecInfCol[b], j);
+    else if (x.lb != L0 || x.ub != U0)
+      dst[l] = x;
+    atomicAdd(&p.vecChanged[b], 1);
+  }
+}
+
+// Per-vector bookkeeping of src/CbcBoundPropagation.cpp:129-189 after a round.
+__global__ void bt_state_kernel(const BtParams p, int cur, int round, int limit, int timeUp)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  bool on = false;
+  if (b < p.Bp) {
+    on = (p.active[b >> 5] >> lane) & 1u;
+    if (on) {
+      const int chg = p.vecChanged[b];
+      p.vecChanged[b] = 0;
+      p.vecRounds[b] = round + 1;
+      int stop = 0, fin = cur;
+      if (p.vecInfRow[b] != 0x7fffffff || p.vecInfCol[b] != 0x7fffffff)
+        stop = 4;
+      else if (chg == 0)
+        stop = 1;
+      else {
+        p.vecTotal[b] += chg;
+        if (round + 1 >= limit) {
+          stop = 2;
+          fin = cur ^ 1;
+        } else if (timeUp) {
+          stop = 3;
+          fin = cur ^ 1;
+        }
+      }
+      if (stop) {
+        p.vecStop[b] = stop;
+        p.vecFinal[b] = fin;
+        on = false;
+      }
+    }
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, on);
+  if (lane == 0 && b < p.Bp) {
+    p.active[b >> 5] = m;
+    if (m)
+      atomicOr(p.anyActive, 1);
+  }
+}
+
+// Start of the next round: copy this round's settled values into the buffer
+// that becomes the atomics target (it was the source, so it is stale exactly
+// at the marked entries), only for vectors that go on; fold the marks of
+// applied rounds into `ever`; clear the marks.
+__global__ void bt_carry_kernel(const BtParams p, int cur)
+{
+  const size_t nW = static_cast<size_t>(p.n) * p.G;
+  const size_t w = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (w >= nW)
+    return;
+  const unsigned bits0 = p.dirty[cur][w];
+  if (!bits0)
+    return;
+  p.dirty[cur][w] = 0u;
+  const int j = static_cast<int>(w / p.G), g = static_cast<int>(w % p.G);
+  const size_t base = static_cast<size_t>(j) * p.Bp + static_cast<size_t>(g) * 32;
+  Bnd *stale = p.X[cur] + base;
+  const Bnd *fresh = p.X[cur ^ 1] + base;
+  // a vector's round was applied iff it is still running or stopped with the
+  // new buffer as its answer
+  unsigned applied = 0u;
+  unsigned bits = bits0;
+  const unsigned act = p.active[g];
+  while (bits) {
+    const int l = __ffs(bits) - 1;
+    bits &= bits - 1;
+    const int b = g * 32 + l;
+    const bool running = (act >> l) & 1u;
+    if (running)
+      stale[l] = fresh[l];
+    if (running || p.vecFinal[b] == (cur ^ 1))
+      applied |= 1u << l;
+  }
+  if (applied)
+    p.ever[w] |= applied;
+}
+
+// ---- loading ------------------------------------------------------------------
+
+// every vector starts from the base bounds (R11 applied per vector later)
+__global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double *__restrict__ baseUb,
+  int n, size_t Bp, Bnd *X0)
+{
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<size_t>(n) * Bp)
+    return;
+  const int j = static_cast<int>(i / Bp);
+  Bnd x;
+  x.lb = __ldg(&baseLb[j]);
+  x.ub = __ldg(&baseUb[j]);
+  X0[i] = x;
+}
+
+// node bound diffs, applied in order inside a vector (one thread per vector)
+__global__ void bt_delta_kernel(const long long *__restrict__ start, const unsigned *__restrict__ var,
+  const double *__restrict__ bnd, int B, size_t Bp, Bnd *X0)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B)
+    return;
+  for (long long k = start[b]; k < start[b + 1]; ++k) {
+    const unsigned v = var[k];
+    Bnd *x = &X0[static_cast<size_t>(v & 0x7fffffffu) * Bp + b];
+    if (v & 0x80000000u)
+      x->ub = bnd[k];
+    else
+      x->lb = bnd[k];
+  }
+}
+
+// dense input, B x n row-major per vector -> [column][vector]; 32x32 tiles
+__global__ void bt_transpose_in_kernel(const double *__restrict__ lb, const double *__restrict__ ub,
+  int B, int n, size_t Bp, Bnd *X0, double padLb, double padUb)
+{
+  __shared__ double tl[32][33], tu[32][33];
+  const int j0 = blockIdx.x * 32, b0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int b = b0 + i, j = j0 + threadIdx.x;
+    const bool ok = b < B && j < n;
+    tl[i][threadIdx.x] = ok ? lb[static_cast<size_t>(b) * n + j] : padLb;
+    tu[i][threadIdx.x] = ok ? ub[static_cast<size_t>(b) * n + j] : padUb;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int j = j0 + i, b = b0 + threadIdx.x;
+    if (j < n) {
+      Bnd x;
+      x.lb = tl[threadIdx.x][i];
+      x.ub = tu[threadIdx.x][i];
+      X0[static_cast<size_t>(j) * Bp + b] = x;
+    }
+  }
+}
+
+// R11 per (column, vector); copies X0 into X1; seeds round 0's marks
+__global__ void bt_prepass_kernel(const BtParams p, int B)
+{
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const size_t Bp = static_cast<size_t>(p.Bp);
+  if (i >= static_cast<size_t>(p.n) * Bp)
+    return;
+  const int j = static_cast<int>(i / Bp), b = static_cast<int>(i % Bp);
+  Bnd x = p.X[0][i];
+  if (b < B) {
+    const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);
+    if (r == 2)
+      atomicMin(&p.vecInfCol[b], j);
+    else if (r == 1) {
+      atomicOr(&p.dirty[0][static_cast<size_t>(j) * p.G + (b >> 5)], 1u << (b & 31));
+      p.X[0][i] = x;
+    }
+  }
+  p.X[1][i] = x;
+}
+
+// a vector whose input already crosses (R11) stops before its first round
+__global__ void bt_prepass_state_kernel(const BtParams p)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  bool on = false;
+  if (b < p.Bp) {
+    on = (p.active[b >> 5] >> lane) & 1u;
+    if (on && p.vecInfCol[b] != 0x7fffffff) {
+      p.vecStop[b] = 4;
+      p.vecRounds[b] = 1;
+      p.vecFinal[b] = 0;
+      on = false;
+    }
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, on);
+  if (lane == 0 && b < p.Bp)
+    p.active[b >> 5] = m;
+}
+
+__global__ void bt_init_state_kernel(const BtParams p, int B)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= p.Bp)
+    return;
+  p.vecInfRow[b] = 0x7fffffff;
+  p.vecInfCol[b] = 0x7fffffff;
+  p.vecChanged[b] = 0;
+  p.vecRounds[b] = 0;
+  p.vecTotal[b] = 0;
+  p.vecStop[b] = 0;
+  p.vecFinal[b] = 0;
+  const unsigned m = __ballot_sync(0xffffffffu, b < B);
+  if ((threadIdx.x & 31) == 0)
+    p.active[b >> 5] = m;
+}
+
+// ---- fetching -------------------------------------------------------------------
+
+// dense answer: [column][vector] of each vector's final buffer -> B x n row-major
+__global__ void bt_transpose_out_kernel(const BtParams p, int B, double *lb, double *ub)
+{
+  __shared__ double tl[32][33], tu[32][33];
+  const int j0 = blockIdx.x * 32, b0 = blockIdx.y * 32;
+  const size_t Bp = static_cast<size_t>(p.Bp);
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int j = j0 + i, b = b0 + threadIdx.x;
+    if (j < p.n && b < B) {
+      const Bnd x = p.X[p.vecFinal[b]][static_cast<size_t>(j) * Bp + b];
+      tl[i][threadIdx.x] = x.lb;
+      tu[i][threadIdx.x] = x.ub;
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int b = b0 + i, j = j0 + threadIdx.x;
+    if (b < B && j < p.n) {
+      lb[static_cast<size_t>(b) * p.n + j] = tl[threadIdx.x][i];
+      ub[static_cast<size_t>(b) * p.n + j] = tu[threadIdx.x][i];
+    }
+  }
+}
+
+// sparse answer, pass 1: how many columns each feasible vector changed
+__global__ void bt_count_updates_kernel(const BtParams p, int B, long long *count)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B)
+    return;
+  long long c = 0;
+  if (p.vecStop[b] != 4) {
+    const unsigned *e = p.ever + (b >> 5);
+    const unsigned bit = 1u << (b & 31);
+    for (int j = 0; j < p.n; ++j)
+      c += (e[static_cast<size_t>(j) * p.G] & bit) ? 1 : 0;
+  }
+  count[b] = c;
+}
+
+// pass 2: columns in ascending order, as updatedBounds() pairs (col, (lb, ub))
+__global__ void bt_fill_updates_kernel(const BtParams p, int B, const long long *__restrict__ start,
+  int *updCol, double *updLb, double *updUb)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B || p.vecStop[b] == 4)
+    return;
+  const unsigned *e = p.ever + (b >> 5);
+  const unsigned bit = 1u << (b & 31);
+  const Bnd *X = p.X[p.vecFinal[b]] + b;
+  long long at = start[b];
+  for (int j = 0; j < p.n; ++j) {
+    if (e[static_cast<size_t>(j) * p.G] & bit) {
+      const Bnd x = X[static_cast<size_t>(j) * p.Bp];
+      updCol[at] = j;
+      updLb[at] = x.lb;
+      updUb[at] = x.ub;
+      ++at;
+    }
+  }
+}
+
+}  // namespace cbp

@@ -1,0 +1,356 @@
+// cbp_device.cuh — device-side building blocks shared by the single-vector
+// and the batched kernels (sm_100a).  Compiled with -fmad=false: every
+// multiply-add that the rules want fused is written as fma(); nothing else
+// may contract, so the arithmetic is operation-for-operation the one frozen
+// in DESIGN.md §3 (rules R1-R12).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cbp {
+
+constexpr int kThreads = 256;      // threads per CTA of the streaming kernels
+constexpr int kWarps = kThreads / 32;
+constexpr int kTileNnz = 2048;     // nonzeros staged per tile (24 KB of val+col)
+constexpr int kTileRows = 256;     // rows per tile (one per thread)
+constexpr int kShortLen = 32;      // rows up to this length: one thread per row
+constexpr int kAlign = 16;         // tile starts are multiples of 16 entries (128 B of val)
+constexpr int kRoundCap = 1024;    // per-round counts kept on the device
+
+constexpr double kContRelThr = 1.0e-3;  // R8
+constexpr double kIntThr = 0.5;         // R8
+
+enum TileKind { kShort = 0, kMedium = 1, kLong = 2 };
+
+// One unit of streaming work: a run of whole rows (kShort / kMedium) or one
+// chunk of a long row (kLong).  nzBegin indexes the packed val/col arrays.
+struct Tile {
+  int nzBegin;   // multiple of kAlign
+  int nzCount;   // real entries
+  int rowBegin;  // first row (kept order)
+  int rowCount;
+  int rpOff;     // offset of this tile's rowCount+1 local row pointers
+  int kind;
+  int longIdx;   // kLong: index into LongRow[]
+  int chunkIdx;  // kLong: chunk number inside the row
+};
+
+struct LongRow {
+  int row;        // kept-order row index
+  int firstPart;  // index of chunk 0's partial
+  int nChunks;
+  int pad;
+};
+
+// Partial (or whole) row activity: R3 plus the largest |a|*(ub-lb).
+struct __align__(16) RowAct {
+  double minAct, maxAct, maxRange;
+  int infMin, infMax;
+};
+static_assert(sizeof(RowAct) == 32, "RowAct is read back as two 16-byte words");
+
+struct __align__(16) Bnd {  // one column's bounds
+  double lb, ub;
+};
+
+// ---- scalars every kernel needs ----------------------------------------
+struct Scal {
+  double inf;      // solver infinity
+  double tol;      // primal tolerance
+  double feasTol;  // 100 * tol (R4, R9)
+};
+
+__device__ __forceinline__ bool is_inf(double x, double INF) { return !(fabs(x) < INF); }
+
+// atomic max / min on doubles through the integer atomics (no -0.0 is ever
+// stored: R7 adds +0.0).  For v >= 0 signed-int order equals double order and
+// any negative double is a negative int; for v < 0 unsigned order is reversed
+// double order among negatives and every non-negative double is smaller.
+__device__ __forceinline__ void atomic_max_f64(double *addr, double v)
+{
+  if (v >= 0.0)
+    atomicMax(reinterpret_cast<long long *>(addr), __double_as_longlong(v));
+  else
+    atomicMin(reinterpret_cast<unsigned long long *>(addr),
+      static_cast<unsigned long long>(__double_as_longlong(v)));
+}
+__device__ __forceinline__ void atomic_min_f64(double *addr, double v)
+{
+  if (v >= 0.0)
+    atomicMin(reinterpret_cast<long long *>(addr), __double_as_longlong(v));
+  else
+    atomicMax(reinterpret_cast<unsigned long long *>(addr),
+      static_cast<unsigned long long>(__double_as_longlong(v)));
+}
+
+__device__ __forceinline__ Bnd ldcg_bnd(const Bnd *p)
+{
+  const double2 v = __ldcg(reinterpret_cast<const double2 *>(p));
+  Bnd b;
+  b.lb = v.x;
+  b.ub = v.y;
+  return b;
+}
+
+// ---- R4 / R5: what a finished row activity allows ------------------------
+struct RowPlan {
+  double slackU, slackL;
+  int infMin, infMax;
+  bool sideU, sideL, infeasible;
+};
+
+__device__ __forceinline__ RowPlan plan_row(const RowAct &a, double rl, double ru, const Scal &s)
+{
+  RowPlan p;
+  const bool ruFin = ru < s.inf, rlFin = rl > -s.inf;
+  p.infeasible = (ruFin && a.infMin == 0 && a.minAct > ru + s.feasTol)
+    || (rlFin && a.infMax == 0 && a.maxAct < rl - s.feasTol);
+  p.sideU = ruFin && a.infMin <= 1 && !(a.infMax == 0 && a.maxAct <= ru + s.tol);
+  p.sideL = rlFin && a.infMax <= 1 && !(a.infMin == 0 && a.minAct >= rl - s.tol);
+  p.slackU = ru - a.minAct;
+  p.slackL = a.maxAct - rl;
+  p.infMin = a.infMin;
+  p.infMax = a.infMax;
+  // Row-level shortcut, exact: with only finite ranges a candidate passes the
+  // per-nonzero pre-check of R6 only if slack < |a|(ub-lb) <= maxRange.
+  if (a.infMin + a.infMax == 0) {
+    p.sideU = p.sideU && p.slackU < a.maxRange;
+    p.sideL = p.sideL && p.slackL < a.maxRange;
+  }
+  if (p.infeasible) {
+    p.sideU = false;
+    p.sideL = false;
+  }
+  return p;
+}
+
+// ---- R3 for one nonzero --------------------------------------------------
+__device__ __forceinline__ void accumulate(RowAct &r, double a, double lo, double hi, double INF)
+{
+  const bool loInf = is_inf(lo, INF), hiInf = is_inf(hi, INF);
+  if (loInf)
+    ++r.infMin;
+  else
+    r.minAct = fma(a, lo, r.minAct);
+  if (hiInf)
+    ++r.infMax;
+  else
+    r.maxAct = fma(a, hi, r.maxAct);
+  if (!loInf && !hiInf) {
+    const double w = fabs(a) * (a > 0.0 ? hi - lo : lo - hi);
+    r.maxRange = fmax(r.maxRange, w);
+  }
+}
+
+__device__ __forceinline__ void combine(RowAct &r, const RowAct &o)
+{
+  r.minAct += o.minAct;
+  r.maxAct += o.maxAct;
+  r.maxRange = fmax(r.maxRange, o.maxRange);
+  r.infMin += o.infMin;
+  r.infMax += o.infMax;
+}
+
+// ---- R6-R8: candidates of one nonzero ------------------------------------
+// Sink must provide  void ub(int j, double v)  and  void lb(int j, double v)
+// which publish an ACCEPTED candidate (atomic min / max + dirty mark).
+template <class Sink>
+__device__ __forceinline__ void offer_ub(Sink &sink, int j, double v, double old, bool isInt, const Scal &s)
+{
+  if (isInt)
+    v = floor(v + s.tol);
+  v += 0.0;
+  if (!(fabs(v) < s.inf))
+    return;
+  if (fabs(old) < s.inf) {
+    const double thr = isInt ? kIntThr : kContRelThr * fmax(1.0, fabs(old));
+    if (!(v < old - thr))
+      return;
+  } else if (!(v < old)) {
+    return;
+  }
+  sink.ub(j, v);
+}
+
+template <class Sink>
+__device__ __forceinline__ void offer_lb(Sink &sink, int j, double v, double old, bool isInt, const Scal &s)
+{
+  if (isInt)
+    v = ceil(v - s.tol);
+  v += 0.0;
+  if (!(fabs(v) < s.inf))
+    return;
+  if (fabs(old) < s.inf) {
+    const double thr = isInt ? kIntThr : kContRelThr * fmax(1.0, fabs(old));
+    if (!(v > old + thr))
+      return;
+  } else if (!(v > old)) {
+    return;
+  }
+  sink.lb(j, v);
+}
+
+template <class Sink>
+__device__ __forceinline__ void tighten_nz(Sink &sink, const RowPlan &p, double a, int j, double lo,
+  double hi, const signed char *__restrict__ colType, const Scal &s)
+{
+  const bool loInf = is_inf(lo, s.inf), hiInf = is_inf(hi, s.inf);
+  const bool finite = !loInf && !hiInf;
+  const double l = a > 0.0 ? lo : hi, u = a > 0.0 ? hi : lo;
+  const double w = finite ? fabs(a) * (u - l) : 0.0;
+  bool wantU = false, wantL = false;
+  double vU = 0.0, vL = 0.0;
+  if (p.sideU) {
+    if (p.infMin == 0) {
+      if (!finite || p.slackU < w) {
+        vU = lo + p.slackU / a;
+        wantU = true;
+      }
+    } else if (loInf) {
+      vU = p.slackU / a;
+      wantU = true;
+    }
+  }
+  if (p.sideL) {
+    if (p.infMax == 0) {
+      if (!finite || p.slackL < w) {
+        vL = hi - p.slackL / a;
+        wantL = true;
+      }
+    } else if (hiInf) {
+      vL = -p.slackL / a;
+      wantL = true;
+    }
+  }
+  if (!wantU && !wantL)
+    return;
+  const bool isInt = colType[j] != 0;
+  if (wantU) {  // rowUB side: a>0 bounds x from above, a<0 from below
+    if (a > 0.0)
+      offer_ub(sink, j, vU, u, isInt, s);
+    else
+      offer_lb(sink, j, vU, l, isInt, s);
+  }
+  if (wantL) {
+    if (a > 0.0)
+      offer_lb(sink, j, vL, l, isInt, s);
+    else
+      offer_ub(sink, j, vL, u, isInt, s);
+  }
+}
+
+// ---- R9 for one changed column --------------------------------------------
+// returns true if the bounds cross beyond tolerance
+__device__ __forceinline__ bool settle(double &L, double &U, double oldUb, const Scal &s)
+{
+  if (L > U) {
+    if (L > U + s.feasTol)
+      return true;
+    if (U < oldUb) {
+      const double x = L < oldUb ? L : oldUb;
+      U = x;
+      L = x;
+    } else {
+      L = U;
+    }
+  }
+  return false;
+}
+
+// ---- R11 for one column ---------------------------------------------------
+// returns 0 untouched, 1 changed, 2 crossing (bounds left as they were)
+__device__ __forceinline__ int prepass_col(double &l, double &u, bool isInt, const Scal &s)
+{
+  const double l0 = l, u0 = u;
+  int touched = 0;
+  if (isInt) {
+    if (fabs(l) < s.inf) {
+      const double t = ceil(l - s.tol) + 0.0;
+      if (t != l) {
+        l = t;
+        touched = 1;
+      }
+    }
+    if (fabs(u) < s.inf) {
+      const double t = floor(u + s.tol) + 0.0;
+      if (t != u) {
+        u = t;
+        touched = 1;
+      }
+    }
+  }
+  if (l > u) {
+    if (settle(l, u, u0, s)) {
+      l = l0;
+      u = u0;
+      return 2;
+    }
+    touched = 1;
+  }
+  return touched;
+}
+
+// ---- warp / block reductions with a fixed shape ---------------------------
+__device__ __forceinline__ double shfl_xor_f64(double v, int m)
+{
+  return __shfl_xor_sync(0xffffffffu, v, m);
+}
+
+__device__ __forceinline__ void warp_reduce(RowAct &r)
+{
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1) {
+    RowAct o;
+    o.minAct = shfl_xor_f64(r.minAct, m);
+    o.maxAct = shfl_xor_f64(r.maxAct, m);
+    o.maxRange = shfl_xor_f64(r.maxRange, m);
+    const int packed = __shfl_xor_sync(0xffffffffu, (r.infMax << 16) | r.infMin, m);
+    o.infMin = packed & 0xffff;
+    o.infMax = packed >> 16;
+    combine(r, o);
+  }
+}
+
+// ---- TMA (bulk async copy) + mbarrier wrappers ------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+  asm volatile(
+    "{\n"
+    ".reg .pred p;\n"
+    "WAIT_%=:\n"
+    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+    "@p bra DONE_%=;\n"
+    "bra WAIT_%=;\n"
+    "DONE_%=:\n"
+    "}\n" ::"r"(smem_u32(bar)),
+    "r"(parity)
+    : "memory");
+}
+// contiguous global -> shared copy done by the TMA unit; completes on `bar`
+__device__ __forceinline__ void bulk_g2s(void *sdst, const void *gsrc, uint32_t bytes, uint64_t *bar)
+{
+  asm volatile(
+    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+      smem_u32(sdst)),
+    "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+    : "memory");
+}
+
+}  // namespace cbp

@@ -1,0 +1,1127 @@
+// cbp_engine.cu — host side of libcbp.so: context, matrix re-tiling and upload,
+// and the C ABI declared in include/cbp_capi.h.  The kernels live in
+// cbp_sv_kernels.cuh (single vector, persistent cooperative loop) and
+// cbp_batch_kernels.cuh (B vectors).  No CPU fallback anywhere: every entry
+// point either runs on the device or reports an error.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/cbp_capi.h"
+#include "cbp_batch_kernels.cuh"
+#include "cbp_sv_kernels.cuh"
+
+using namespace cbp;
+
+// ----------------------------------------------------------------------------
+struct cbp_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool ownsStream = false;
+  int numSMs = 0;
+  int svBlocksPerSM = 0;
+  std::string err;
+  cbp_stats stats {};
+  cudaEvent_t evA = nullptr, evB = nullptr;
+  std::vector<cudaEvent_t> evPool;  // pairs, batch rounds
+};
+
+struct BatchState {
+  int B = 0, Bp = 0, G = 0;
+  size_t cells = 0;  // n * Bp
+  Bnd *X[2] = { nullptr, nullptr };
+  unsigned *dirty[2] = { nullptr, nullptr };
+  unsigned *ever = nullptr, *active = nullptr;
+  int *ints = nullptr;  // 7 arrays of Bp ints + anyActive
+  long long *counts = nullptr;  // B+1
+  // loaded input (device copies) so the batch can be re-expanded
+  double *baseLb = nullptr, *baseUb = nullptr;
+  long long *dStart = nullptr;
+  unsigned *dVar = nullptr;
+  double *dBnd = nullptr;
+  long long nDelta = 0;
+  bool loaded = false, denseLoaded = false;
+  size_t capCells = 0, capDelta = 0;
+  int capBp = 0;
+};
+
+struct cbp_matrix {
+  cbp_ctx *ctx = nullptr;
+  int m = 0, n = 0, mKept = 0;
+  long long nnz = 0, nnzPacked = 0;
+  double inf = 1e30;
+  // device, matrix
+  double *val = nullptr;
+  int *col = nullptr;
+  Tile *tiles = nullptr;
+  int *rp = nullptr;
+  double *rowLB = nullptr, *rowUB = nullptr;
+  int *rowOrig = nullptr, *rowNz = nullptr, *rowCnt = nullptr;
+  LongRow *longRows = nullptr;
+  signed char *colType = nullptr;
+  int *singRows = nullptr;
+  int nTiles = 0, firstLongTile = 0, nLong = 0, nParts = 0, nSing = 0;
+  // device, single-vector workspace
+  RowAct *longPart = nullptr;
+  Bnd *X[2] = { nullptr, nullptr };
+  unsigned *dirty[2] = { nullptr, nullptr };
+  int nWords = 0;
+  SvStatus *st = nullptr;
+  double *dLb = nullptr, *dUb = nullptr;  // staging for host-pointer calls
+  int *dRes = nullptr;                    // small int scratch
+  double *dAct = nullptr;                 // row-activity staging (2m doubles + 2m ints)
+  BatchState bt;
+};
+
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) {                                                             \
+      ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                     \
+      return CBP_ERR_CUDA;                                                               \
+    }                                                                                    \
+  } while (0)
+
+static thread_local std::string g_createErr;
+
+template <class T>
+static cudaError_t dalloc(T **p, size_t count)
+{
+  return cudaMalloc(reinterpret_cast<void **>(p), std::max<size_t>(count, 1) * sizeof(T));
+}
+
+static Scal make_scal(const cbp_matrix *mat, double tol)
+{
+  Scal s;
+  s.inf = mat->inf;
+  s.tol = tol;
+  s.feasTol = 100.0 * tol;
+  return s;
+}
+
+static inline int cdiv(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
+
+// ----------------------------------------------------------------------------
+extern "C" {
+
+cbp_ctx *cbp_create(int device)
+{
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    g_createErr = std::string("no CUDA device: ") + cudaGetErrorString(e);
+    fprintf(stderr, "cbp_create: %s\n", g_createErr.c_str());
+    return nullptr;
+  }
+  if (device < 0)
+    cudaGetDevice(&device);
+  if (cudaSetDevice(device) != cudaSuccess)
+    return nullptr;
+  cbp_ctx *ctx = new cbp_ctx();
+  ctx->device = device;
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  ctx->numSMs = prop.multiProcessorCount;
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete ctx;
+    return nullptr;
+  }
+  ctx->ownsStream = true;
+  cudaEventCreate(&ctx->evA);
+  cudaEventCreate(&ctx->evB);
+  cudaFuncSetAttribute(sv_fixpoint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    static_cast<int>(sizeof(SvSmem)));
+  int perSM = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, sv_fixpoint_kernel, kThreads, sizeof(SvSmem));
+  ctx->svBlocksPerSM = perSM;
+  if (perSM < 1) {
+    fprintf(stderr, "cbp_create: persistent kernel does not fit on this device\n");
+    cbp_destroy(ctx);
+    return nullptr;
+  }
+  return ctx;
+}
+
+void cbp_destroy(cbp_ctx *ctx)
+{
+  if (!ctx)
+    return;
+  cudaSetDevice(ctx->device);
+  if (ctx->evA)
+    cudaEventDestroy(ctx->evA);
+  if (ctx->evB)
+    cudaEventDestroy(ctx->evB);
+  for (cudaEvent_t e : ctx->evPool)
+    cudaEventDestroy(e);
+  if (ctx->ownsStream && ctx->stream)
+    cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int cbp_set_stream(cbp_ctx *ctx, void *cudaStream)
+{
+  if (!ctx)
+    return CBP_ERR_ARG;
+  if (ctx->ownsStream && ctx->stream)
+    cudaStreamDestroy(ctx->stream);
+  ctx->stream = static_cast<cudaStream_t>(cudaStream);
+  ctx->ownsStream = false;
+  return CBP_OK;
+}
+
+const char *cbp_last_error(const cbp_ctx *ctx) { return ctx ? ctx->err.c_str() : g_createErr.c_str(); }
+
+int cbp_get_stats(const cbp_ctx *ctx, cbp_stats *out)
+{
+  if (!ctx || !out)
+    return CBP_ERR_ARG;
+  *out = ctx->stats;
+  return CBP_OK;
+}
+
+int cbp_synchronize(cbp_ctx *ctx)
+{
+  if (!ctx)
+    return CBP_ERR_ARG;
+  CK(cudaStreamSynchronize(ctx->stream));
+  return CBP_OK;
+}
+
+// ----------------------------------------------------------------------------
+// Matrix upload.  Rows are split into three classes by nonzero count and laid
+// out class by class; inside a class the caller's row order is kept.  Zero
+// coefficients, 'N' rows and empty rows are dropped (R1, R3).
+// ----------------------------------------------------------------------------
+void cbp_matrix_free(cbp_matrix *mat)
+{
+  if (!mat)
+    return;
+  cudaSetDevice(mat->ctx->device);
+  void *ptrs[] = { mat->val, mat->col, mat->tiles, mat->rp, mat->rowLB, mat->rowUB, mat->rowOrig,
+    mat->rowNz, mat->rowCnt, mat->longRows, mat->colType, mat->singRows, mat->longPart, mat->X[0],
+    mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
+    mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
+    mat->bt.ints, mat->bt.counts, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
+    mat->bt.dBnd };
+  for (void *p : ptrs)
+    if (p)
+      cudaFree(p);
+  delete mat;
+}
+
+cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStart, const int *rowLen,
+  const int *colIdx, const double *val, const char *rowSense, const double *rhs, const double *range,
+  const char *colType, double infinity)
+{
+  if (!ctx)
+    return nullptr;
+  if (m < 0 || n <= 0 || !rowStart || !rowSense || !rhs || (m > 0 && (!colIdx || !val))) {
+    ctx->err = "cbp_matrix_upload: bad argument";
+    return nullptr;
+  }
+  cudaSetDevice(ctx->device);
+  const double INF = infinity;
+  struct KRow {
+    int orig, cnt;
+    double rl, ru;
+  };
+  std::vector<KRow> cls[3];
+  long long nnzKept = 0;
+  for (int i = 0; i < m; ++i) {
+    double rl, ru;
+    const double r = rhs[i];
+    switch (rowSense[i]) {
+    case 'L': rl = -INF; ru = r; break;
+    case 'G': rl = r; ru = INF; break;
+    case 'E': rl = r; ru = r; break;
+    case 'R': rl = r - std::fabs(range ? range[i] : 0.0); ru = r; break;
+    default: continue;
+    }
+    const int64_t s = rowStart[i], e = rowLen ? s + rowLen[i] : rowStart[i + 1];
+    int cnt = 0;
+    for (int64_t k = s; k < e; ++k) {
+      if (val[k] != 0.0) {
+        if (colIdx[k] < 0 || colIdx[k] >= n) {
+          ctx->err = "cbp_matrix_upload: column index out of range";
+          return nullptr;
+        }
+        ++cnt;
+      }
+    }
+    if (cnt == 0)
+      continue;
+    const int c = cnt <= kShortLen ? kShort : (cnt <= kTileNnz ? kMedium : kLong);
+    cls[c].push_back({ i, cnt, rl, ru });
+    nnzKept += cnt;
+  }
+  const size_t mKept = cls[0].size() + cls[1].size() + cls[2].size();
+  if (nnzKept + static_cast<long long>(kAlign) * (static_cast<long long>(mKept) + 8) > INT_MAX) {
+    ctx->err = "cbp_matrix_upload: more than 2^31 nonzeros are not supported";
+    return nullptr;
+  }
+  std::vector<double> hVal, hRl(mKept), hRu(mKept);
+  std::vector<int> hCol, hRp, hOrig(mKept), hNz(mKept), hCnt(mKept), hSing;
+  std::vector<Tile> hTiles;
+  std::vector<LongRow> hLong;
+  hVal.reserve(nnzKept + nnzKept / 64 + 64);
+  hCol.reserve(nnzKept + nnzKept / 64 + 64);
+  auto pad_to_align = [&]() {
+    while (hVal.size() % kAlign) {
+      hVal.push_back(0.0);
+      hCol.push_back(0);
+    }
+  };
+  auto emit_row = [&](const KRow &kr, int keptIdx) {
+    hOrig[keptIdx] = kr.orig;
+    hRl[keptIdx] = kr.rl;
+    hRu[keptIdx] = kr.ru;
+    hNz[keptIdx] = static_cast<int>(hVal.size());
+    hCnt[keptIdx] = kr.cnt;
+    const int64_t s = rowStart[kr.orig], e = rowLen ? s + rowLen[kr.orig] : rowStart[kr.orig + 1];
+    for (int64_t k = s; k < e; ++k)
+      if (val[k] != 0.0) {
+        hVal.push_back(val[k]);
+        hCol.push_back(colIdx[k]);
+      }
+    if (kr.cnt == 1)
+      hSing.push_back(keptIdx);
+  };
+  int kept = 0;
+  for (int c = 0; c < 2; ++c) {  // short, then medium rows: greedy tiles of whole rows
+    size_t i = 0;
+    const std::vector<KRow> &rows = cls[c];
+    while (i < rows.size()) {
+      pad_to_align();
+      Tile T {};
+      T.nzBegin = static_cast<int>(hVal.size());
+      T.rowBegin = kept;
+      T.rpOff = static_cast<int>(hRp.size());
+      T.kind = c;
+      int nz = 0, nr = 0;
+      while (i < rows.size() && nr < kTileRows && nz + rows[i].cnt <= kTileNnz) {
+        hRp.push_back(nz);
+        emit_row(rows[i], kept);
+        nz += rows[i].cnt;
+        ++nr;
+        ++kept;
+        ++i;
+      }
+      hRp.push_back(nz);
+      T.nzCount = nz;
+      T.rowCount = nr;
+      hTiles.push_back(T);
+    }
+  }
+  const int firstLongTile = static_cast<int>(hTiles.size());
+  int nParts = 0;
+  for (const KRow &kr : cls[2]) {  // long rows: chunks of kTileNnz
+    pad_to_align();
+    const int begin = static_cast<int>(hVal.size());
+    emit_row(kr, kept);
+    LongRow lr {};
+    lr.row = kept;
+    lr.firstPart = nParts;
+    lr.nChunks = (kr.cnt + kTileNnz - 1) / kTileNnz;
+    for (int ch = 0; ch < lr.nChunks; ++ch) {
+      Tile T {};
+      T.nzBegin = begin + ch * kTileNnz;
+      T.nzCount = std::min(kTileNnz, kr.cnt - ch * kTileNnz);
+      T.rowBegin = kept;
+      T.rowCount = 1;
+      T.rpOff = 0;
+      T.kind = kLong;
+      T.longIdx = static_cast<int>(hLong.size());
+      T.chunkIdx = ch;
+      hTiles.push_back(T);
+    }
+    nParts += lr.nChunks;
+    hLong.push_back(lr);
+    ++kept;
+  }
+  for (int i = 0; i < 2 * kAlign; ++i) {  // slack for the 16-byte rounding of the last copy
+    hVal.push_back(0.0);
+    hCol.push_back(0);
+  }
+
+  cbp_matrix *mat = new cbp_matrix();
+  mat->ctx = ctx;
+  mat->m = m;
+  mat->n = n;
+  mat->mKept = static_cast<int>(mKept);
+  mat->nnz = nnzKept;
+  mat->nnzPacked = static_cast<long long>(hVal.size());
+  mat->inf = INF;
+  mat->nTiles = static_cast<int>(hTiles.size());
+  mat->firstLongTile = firstLongTile;
+  mat->nLong = static_cast<int>(hLong.size());
+  mat->nParts = nParts;
+  mat->nSing = static_cast<int>(hSing.size());
+  mat->nWords = (n + 31) / 32;
+  std::vector<signed char> hType(n, 0);
+  if (colType)
+    for (int j = 0; j < n; ++j)
+      hType[j] = static_cast<signed char>(colType[j]);
+
+  bool ok = true;
+  auto up = [&](auto **dptr, const auto &h) {
+    using T = typename std::remove_reference<decltype(h)>::type::value_type;
+    if (!ok)
+      return;
+    if (dalloc(reinterpret_cast<T **>(dptr), h.size()) != cudaSuccess) {
+      ok = false;
+      return;
+    }
+    if (!h.empty()
+      && cudaMemcpyAsync(*dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream)
+        != cudaSuccess)
+      ok = false;
+  };
+  up(&mat->val, hVal);
+  up(&mat->col, hCol);
+  up(&mat->tiles, hTiles);
+  up(&mat->rp, hRp);
+  up(&mat->rowLB, hRl);
+  up(&mat->rowUB, hRu);
+  up(&mat->rowOrig, hOrig);
+  up(&mat->rowNz, hNz);
+  up(&mat->rowCnt, hCnt);
+  up(&mat->longRows, hLong);
+  up(&mat->colType, hType);
+  up(&mat->singRows, hSing);
+  ok = ok && dalloc(&mat->longPart, nParts) == cudaSuccess;
+  ok = ok && dalloc(&mat->X[0], n) == cudaSuccess && dalloc(&mat->X[1], n) == cudaSuccess;
+  ok = ok && dalloc(&mat->dirty[0], mat->nWords) == cudaSuccess
+    && dalloc(&mat->dirty[1], mat->nWords) == cudaSuccess;
+  ok = ok && dalloc(&mat->st, 1) == cudaSuccess;
+  ok = ok && dalloc(&mat->dLb, n) == cudaSuccess && dalloc(&mat->dUb, n) == cudaSuccess;
+  ok = ok && dalloc(&mat->dRes, 16) == cudaSuccess;
+  ok = ok && dalloc(&mat->dAct, 3 * static_cast<size_t>(std::max(m, 1))) == cudaSuccess;
+  ok = ok && cudaStreamSynchronize(ctx->stream) == cudaSuccess;
+  if (!ok) {
+    ctx->err = std::string("cbp_matrix_upload: ") + cudaGetErrorString(cudaGetLastError());
+    cbp_matrix_free(mat);
+    return nullptr;
+  }
+  return mat;
+}
+
+// ----------------------------------------------------------------------------
+// single vector
+// ----------------------------------------------------------------------------
+static int sv_stage_in(cbp_matrix *mat, const double *lb, const double *ub, int flags,
+  const double **dl, const double **du)
+{
+  cbp_ctx *ctx = mat->ctx;
+  if (flags & CBP_FLAG_DEVICE_PTRS) {
+    *dl = lb;
+    *du = ub;
+    return CBP_OK;
+  }
+  CK(cudaMemcpyAsync(mat->dLb, lb, sizeof(double) * mat->n, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(mat->dUb, ub, sizeof(double) * mat->n, cudaMemcpyHostToDevice, ctx->stream));
+  *dl = mat->dLb;
+  *du = mat->dUb;
+  return CBP_OK;
+}
+
+static int sv_stage_out(cbp_matrix *mat, const Bnd *X, double *lb, double *ub, int flags)
+{
+  cbp_ctx *ctx = mat->ctx;
+  const int n = mat->n;
+  const bool dev = flags & CBP_FLAG_DEVICE_PTRS;
+  sv_finish_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(X, n, dev ? lb : mat->dLb, dev ? ub : mat->dUb);
+  ++ctx->stats.kernelLaunches;
+  CK(cudaGetLastError());
+  if (!dev) {
+    CK(cudaMemcpyAsync(lb, mat->dLb, sizeof(double) * n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(ub, mat->dUb, sizeof(double) * n, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  return CBP_OK;
+}
+
+static int sv_reset_state(cbp_matrix *mat)
+{
+  cbp_ctx *ctx = mat->ctx;
+  SvStatus init;
+  memset(&init, 0, sizeof(init));
+  init.infeasRow = INT_MAX;
+  init.infeasCol = INT_MAX;
+  // only the head of the status block needs initial values
+  CK(cudaMemsetAsync(mat->st, 0, sizeof(SvStatus), ctx->stream));
+  CK(cudaMemcpyAsync(mat->st, &init, offsetof(SvStatus, roundChanged), cudaMemcpyHostToDevice,
+    ctx->stream));
+  CK(cudaMemsetAsync(mat->dirty[0], 0, sizeof(unsigned) * mat->nWords, ctx->stream));
+  CK(cudaMemsetAsync(mat->dirty[1], 0, sizeof(unsigned) * mat->nWords, ctx->stream));
+  return CBP_OK;
+}
+
+int cbp_singletons(cbp_matrix *mat, double *lb, double *ub, double primalTol, int *nTightened,
+  int *nFixed, int flags)
+{
+  if (!mat || !lb || !ub || !nTightened)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  const Scal s = make_scal(mat, primalTol);
+  const int n = mat->n;
+  const double *dl, *du;
+  int rc = sv_stage_in(mat, lb, ub, flags, &dl, &du);
+  if (rc)
+    return rc;
+  if ((rc = sv_reset_state(mat)))
+    return rc;
+  CK(cudaMemsetAsync(mat->dRes, 0, sizeof(int) * 4, ctx->stream));
+  sv_prepare_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(dl, du, mat->colType, n, mat->X[0], mat->X[1],
+    mat->dirty[0], mat->st, s, 0);
+  ++ctx->stats.kernelLaunches;
+  if (mat->nSing > 0) {
+    sv_singleton_kernel<<<cdiv(mat->nSing, 256), 256, 0, ctx->stream>>>(mat->singRows, mat->nSing,
+      mat->rowNz, mat->val, mat->col, mat->rowLB, mat->rowUB, mat->colType, mat->X[0], mat->X[1],
+      mat->dirty[0], s);
+    sv_singleton_settle_kernel<<<cdiv(mat->nWords, 256), 256, 0, ctx->stream>>>(mat->X[0], mat->X[1],
+      mat->dirty[0], mat->nWords, mat->dRes, s);
+    ctx->stats.kernelLaunches += 2;
+  }
+  CK(cudaGetLastError());
+  int res[4] = { 0, 0, 0, 0 };
+  CK(cudaMemcpyAsync(res, mat->dRes, sizeof(int) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (res[2] > 0) {  // bounds cross: infeasible, bounds left untouched
+    *nTightened = -1;
+    if (nFixed)
+      *nFixed = 0;
+    return CBP_OK;
+  }
+  *nTightened = res[0];
+  if (nFixed)
+    *nFixed = res[1];
+  if (res[0] > 0) {
+    if ((rc = sv_stage_out(mat, mat->X[1], lb, ub, flags)))
+      return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  return CBP_OK;
+}
+
+int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int maxRounds,
+  double timeLimitSec, cbp_result *out, int *roundChanged, int roundCap, int flags)
+{
+  if (!mat || !lb || !ub || !out)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  memset(out, 0, sizeof(*out));
+  out->feasible = 1;
+  out->infeasibleRow = -1;
+  out->infeasibleCol = -1;
+  if (!(timeLimitSec > 0.0)) {  // the reference tests the clock before every round (:109-121)
+    out->stopReason = CBP_STOP_TIME_LIMIT;
+    return CBP_OK;
+  }
+  const Scal s = make_scal(mat, primalTol);
+  const int n = mat->n;
+  const double *dl, *du;
+  int rc = sv_stage_in(mat, lb, ub, flags, &dl, &du);
+  if (rc)
+    return rc;
+  CK(cudaEventRecord(ctx->evA, ctx->stream));
+  if ((rc = sv_reset_state(mat)))
+    return rc;
+  sv_prepare_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(dl, du, mat->colType, n, mat->X[0], mat->X[1],
+    mat->dirty[0], mat->st, s, 1);
+  ++ctx->stats.kernelLaunches;
+  CK(cudaGetLastError());
+
+  SvParams p;
+  p.val = mat->val;
+  p.col = mat->col;
+  p.tiles = mat->tiles;
+  p.rp = mat->rp;
+  p.rowLB = mat->rowLB;
+  p.rowUB = mat->rowUB;
+  p.rowOrig = mat->rowOrig;
+  p.longRows = mat->longRows;
+  p.colType = mat->colType;
+  p.longPart = mat->longPart;
+  p.nTiles = mat->nTiles;
+  p.firstLongTile = mat->firstLongTile;
+  p.nLong = mat->nLong;
+  p.n = n;
+  p.X[0] = mat->X[0];
+  p.X[1] = mat->X[1];
+  p.dirty[0] = mat->dirty[0];
+  p.dirty[1] = mat->dirty[1];
+  p.nWords = mat->nWords;
+  p.st = mat->st;
+  p.s = s;
+  p.maxRounds = maxRounds;
+  p.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
+  const int maxGrid = ctx->svBlocksPerSM * ctx->numSMs;
+  const int want = std::max(mat->nTiles, cdiv(mat->nWords, kThreads));
+  const int grid = std::max(1, std::min(maxGrid, want));
+  void *args[] = { &p };
+  cudaEvent_t k0, k1;
+  if (ctx->evPool.size() < 2) {
+    cudaEvent_t e;
+    while (ctx->evPool.size() < 2) {
+      CK(cudaEventCreate(&e));
+      ctx->evPool.push_back(e);
+    }
+  }
+  k0 = ctx->evPool[0];
+  k1 = ctx->evPool[1];
+  CK(cudaEventRecord(k0, ctx->stream));
+  CK(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(sv_fixpoint_kernel), dim3(grid), dim3(kThreads),
+    args, sizeof(SvSmem), ctx->stream));
+  CK(cudaEventRecord(k1, ctx->stream));
+  ++ctx->stats.kernelLaunches;
+
+  SvStatus head;
+  CK(cudaMemcpyAsync(&head, mat->st, offsetof(SvStatus, roundChanged), cudaMemcpyDeviceToHost,
+    ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  out->rounds = head.rounds;
+  out->stopReason = head.stopReason;
+  out->nChanged = head.nChangedTotal;
+  if (head.stopReason == CBP_STOP_INFEASIBLE) {
+    out->feasible = 0;
+    if (head.infeasRow != INT_MAX)
+      out->infeasibleRow = head.infeasRow;
+    else if (head.infeasCol != INT_MAX)
+      out->infeasibleCol = head.infeasCol;
+  }
+  if ((rc = sv_stage_out(mat, mat->X[head.finalBuf & 1], lb, ub, flags)))
+    return rc;
+  if (roundChanged && roundCap > 0) {
+    const int cnt = std::min(std::min(roundCap, head.rounds), kRoundCap);
+    if (cnt > 0)
+      CK(cudaMemcpyAsync(roundChanged, mat->st->roundChanged, sizeof(int) * cnt, cudaMemcpyDeviceToHost,
+        ctx->stream));
+  }
+  CK(cudaEventRecord(ctx->evB, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  float ms = 0.f, kms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->evA, ctx->evB);
+  cudaEventElapsedTime(&kms, k0, k1);
+  out->seconds = ms * 1.0e-3;
+  ctx->stats.lastRunMs = ms;
+  ctx->stats.lastRoundKernelMs = kms;
+  ctx->stats.lastRoundKernelLaunches = 1;
+  ctx->stats.lastRoundsTotal = head.rounds;
+  return CBP_OK;
+}
+
+int cbp_row_activity(cbp_matrix *mat, const double *lb, const double *ub, double *minAct,
+  double *maxAct, int *infMin, int *infMax, int flags)
+{
+  if (!mat || !lb || !ub || !minAct || !maxAct || !infMin || !infMax)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  const double *dl, *du;
+  int rc = sv_stage_in(mat, lb, ub, flags, &dl, &du);
+  if (rc)
+    return rc;
+  const int m = mat->m;
+  const bool dev = flags & CBP_FLAG_DEVICE_PTRS;
+  double *dMin = dev ? minAct : mat->dAct, *dMax = dev ? maxAct : mat->dAct + m;
+  int *dIm = dev ? infMin : reinterpret_cast<int *>(mat->dAct + 2 * static_cast<size_t>(m));
+  int *dIx = dev ? infMax : dIm + m;
+  CK(cudaMemsetAsync(dMin, 0, sizeof(double) * m, ctx->stream));
+  CK(cudaMemsetAsync(dMax, 0, sizeof(double) * m, ctx->stream));
+  CK(cudaMemsetAsync(dIm, 0, sizeof(int) * m, ctx->stream));
+  CK(cudaMemsetAsync(dIx, 0, sizeof(int) * m, ctx->stream));
+  if (mat->mKept > 0) {
+    row_activity_kernel<<<cdiv(static_cast<long long>(mat->mKept) * 32, 256), 256, 0, ctx->stream>>>(
+      mat->rowNz, mat->rowCnt, mat->rowOrig, mat->mKept, mat->val, mat->col, dl, du, mat->inf, dMin, dMax,
+      dIm, dIx);
+    ++ctx->stats.kernelLaunches;
+  }
+  CK(cudaGetLastError());
+  if (!dev) {
+    CK(cudaMemcpyAsync(minAct, dMin, sizeof(double) * m, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(maxAct, dMax, sizeof(double) * m, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(infMin, dIm, sizeof(int) * m, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(infMax, dIx, sizeof(int) * m, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  CK(cudaStreamSynchronize(ctx->stream));
+  return CBP_OK;
+}
+
+// ----------------------------------------------------------------------------
+// batch
+// ----------------------------------------------------------------------------
+static int bt_reserve(cbp_matrix *mat, int B)
+{
+  cbp_ctx *ctx = mat->ctx;
+  BatchState &bt = mat->bt;
+  const int Bp = (B + 31) / 32 * 32;
+  const size_t cells = static_cast<size_t>(mat->n) * Bp;
+  if (cells > bt.capCells || Bp > bt.capBp) {
+    void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts };
+    for (void *p : old)
+      if (p)
+        cudaFree(p);
+    bt.X[0] = bt.X[1] = nullptr;
+    bt.dirty[0] = bt.dirty[1] = bt.ever = bt.active = nullptr;
+    bt.ints = nullptr;
+    bt.counts = nullptr;
+    bt.capCells = 0;
+    bt.capBp = 0;
+    const size_t words = cells / 32;
+    if (dalloc(&bt.X[0], cells) != cudaSuccess || dalloc(&bt.X[1], cells) != cudaSuccess
+      || dalloc(&bt.dirty[0], words) != cudaSuccess || dalloc(&bt.dirty[1], words) != cudaSuccess
+      || dalloc(&bt.ever, words) != cudaSuccess || dalloc(&bt.active, Bp / 32) != cudaSuccess
+      || dalloc(&bt.ints, static_cast<size_t>(Bp) * 7 + 8) != cudaSuccess
+      || dalloc(&bt.counts, static_cast<size_t>(Bp) + 1) != cudaSuccess) {
+      ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
+      return CBP_ERR_NOMEM;
+    }
+    bt.capCells = cells;
+    bt.capBp = Bp;
+  }
+  if (!bt.baseLb) {
+    if (dalloc(&bt.baseLb, mat->n) != cudaSuccess || dalloc(&bt.baseUb, mat->n) != cudaSuccess) {
+      ctx->err = "batch workspace: base bounds";
+      return CBP_ERR_NOMEM;
+    }
+  }
+  bt.B = B;
+  bt.Bp = Bp;
+  bt.G = Bp / 32;
+  bt.cells = cells;
+  return CBP_OK;
+}
+
+static BtParams bt_params(cbp_matrix *mat, double tol)
+{
+  BatchState &bt = mat->bt;
+  BtParams p;
+  p.val = mat->val;
+  p.col = mat->col;
+  p.rowNz = mat->rowNz;
+  p.rowCnt = mat->rowCnt;
+  p.rowLB = mat->rowLB;
+  p.rowUB = mat->rowUB;
+  p.rowOrig = mat->rowOrig;
+  p.colType = mat->colType;
+  p.mKept = mat->mKept;
+  p.n = mat->n;
+  p.Bp = bt.Bp;
+  p.G = bt.G;
+  p.X[0] = bt.X[0];
+  p.X[1] = bt.X[1];
+  p.dirty[0] = bt.dirty[0];
+  p.dirty[1] = bt.dirty[1];
+  p.ever = bt.ever;
+  p.active = bt.active;
+  int *q = bt.ints;
+  p.vecInfRow = q;
+  p.vecInfCol = q + bt.Bp;
+  p.vecChanged = q + 2 * bt.Bp;
+  p.vecRounds = q + 3 * bt.Bp;
+  p.vecTotal = q + 4 * bt.Bp;
+  p.vecStop = q + 5 * bt.Bp;
+  p.vecFinal = q + 6 * bt.Bp;
+  p.anyActive = q + 7 * bt.Bp;
+  p.s = make_scal(mat, tol);
+  return p;
+}
+
+// (re)build X[0] from the loaded input; everything else is set up by run
+static int bt_expand(cbp_matrix *mat)
+{
+  cbp_ctx *ctx = mat->ctx;
+  BatchState &bt = mat->bt;
+  if (!bt.loaded) {
+    ctx->err = "no batch loaded";
+    return CBP_ERR_ARG;
+  }
+  if (bt.denseLoaded)
+    return CBP_OK;  // a dense batch is consumed in place; it cannot be re-expanded
+  bt_expand_kernel<<<cdiv(static_cast<long long>(bt.cells), 256), 256, 0, ctx->stream>>>(bt.baseLb,
+    bt.baseUb, mat->n, bt.Bp, bt.X[0]);
+  ++ctx->stats.kernelLaunches;
+  if (bt.nDelta > 0) {
+    bt_delta_kernel<<<cdiv(bt.B, 128), 128, 0, ctx->stream>>>(bt.dStart, bt.dVar, bt.dBnd, bt.B, bt.Bp,
+      bt.X[0]);
+    ++ctx->stats.kernelLaunches;
+  }
+  CK(cudaGetLastError());
+  return CBP_OK;
+}
+
+int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *baseUb, int B,
+  const int64_t *deltaStart, const uint32_t *deltaVar, const double *deltaBound, int flags)
+{
+  if (!mat || !baseLb || !baseUb || B <= 0 || !deltaStart)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  int rc = bt_reserve(mat, B);
+  if (rc)
+    return rc;
+  BatchState &bt = mat->bt;
+  const cudaMemcpyKind kind = (flags & CBP_FLAG_DEVICE_PTRS) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  long long nDelta = 0;
+  if (flags & CBP_FLAG_DEVICE_PTRS) {
+    CK(cudaMemcpyAsync(&nDelta, deltaStart + B, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  } else {
+    nDelta = deltaStart[B];
+  }
+  if (nDelta < 0 || (nDelta > 0 && (!deltaVar || !deltaBound)))
+    return CBP_ERR_ARG;
+  if (static_cast<size_t>(nDelta) > bt.capDelta || !bt.dStart) {
+    void *old[] = { bt.dVar, bt.dBnd };
+    for (void *p : old)
+      if (p)
+        cudaFree(p);
+    bt.dVar = nullptr;
+    bt.dBnd = nullptr;
+    if (dalloc(&bt.dVar, nDelta) != cudaSuccess || dalloc(&bt.dBnd, nDelta) != cudaSuccess) {
+      ctx->err = "batch workspace: deltas";
+      return CBP_ERR_NOMEM;
+    }
+    bt.capDelta = static_cast<size_t>(nDelta);
+  }
+  if (bt.dStart)
+    cudaFree(bt.dStart);
+  bt.dStart = nullptr;
+  if (dalloc(&bt.dStart, static_cast<size_t>(B) + 1) != cudaSuccess)
+    return CBP_ERR_NOMEM;
+  CK(cudaMemcpyAsync(bt.baseLb, baseLb, sizeof(double) * mat->n, kind, ctx->stream));
+  CK(cudaMemcpyAsync(bt.baseUb, baseUb, sizeof(double) * mat->n, kind, ctx->stream));
+  CK(cudaMemcpyAsync(bt.dStart, deltaStart, sizeof(long long) * (B + 1), kind, ctx->stream));
+  if (nDelta > 0) {
+    CK(cudaMemcpyAsync(bt.dVar, deltaVar, sizeof(unsigned) * nDelta, kind, ctx->stream));
+    CK(cudaMemcpyAsync(bt.dBnd, deltaBound, sizeof(double) * nDelta, kind, ctx->stream));
+  }
+  bt.nDelta = nDelta;
+  bt.loaded = true;
+  bt.denseLoaded = false;
+  return bt_expand(mat);
+}
+
+int cbp_batch_reset(cbp_matrix *mat)
+{
+  if (!mat)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  if (mat->bt.denseLoaded) {
+    ctx->err = "cbp_batch_reset: a dense batch cannot be re-expanded";
+    return CBP_ERR_ARG;
+  }
+  return bt_expand(mat);
+}
+
+int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeLimitSec)
+{
+  if (!mat || !mat->bt.loaded)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  BatchState &bt = mat->bt;
+  const BtParams p = bt_params(mat, primalTol);
+  const int limit = maxRounds > 0 ? maxRounds : INT_MAX;
+  const size_t words = bt.cells / 32;
+  cudaStream_t st = ctx->stream;
+  CK(cudaEventRecord(ctx->evA, st));
+  CK(cudaMemsetAsync(bt.dirty[0], 0, sizeof(unsigned) * words, st));
+  CK(cudaMemsetAsync(bt.dirty[1], 0, sizeof(unsigned) * words, st));
+  CK(cudaMemsetAsync(bt.ever, 0, sizeof(unsigned) * words, st));
+  bt_init_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, bt.B);
+  bt_prepass_kernel<<<cdiv(static_cast<long long>(bt.cells), 256), 256, 0, st>>>(p, bt.B);
+  bt_prepass_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p);
+  ctx->stats.kernelLaunches += 3;
+  CK(cudaGetLastError());
+  const long long warps = static_cast<long long>(bt.G) * mat->mKept;
+  const int rowsGrid = cdiv(warps, kWarps);
+  const int wordGrid = cdiv(static_cast<long long>(words), 256);
+  double roundKernelMs = 0.0;
+  int roundKernelLaunches = 0;
+  int any = 1;
+  while (ctx->evPool.size() < 2) {
+    cudaEvent_t e;
+    CK(cudaEventCreate(&e));
+    ctx->evPool.push_back(e);
+  }
+  for (int round = 0; any && !(timeLimitSec <= 0.0); ++round) {
+    const int cur = round & 1;
+    CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
+    CK(cudaEventRecord(ctx->evPool[0], st));
+    if (warps > 0) {
+      bt_rows_kernel<<<rowsGrid, kThreads, 0, st>>>(p, cur);
+      ++ctx->stats.kernelLaunches;
+    }
+    CK(cudaEventRecord(ctx->evPool[1], st));
+    bt_settle_kernel<<<wordGrid, 256, 0, st>>>(p, cur);
+    int timeUp = 0;
+    if (timeLimitSec < 1.0e9) {  // a real limit: look at the clock between rounds
+      CK(cudaEventRecord(ctx->evB, st));
+      CK(cudaEventSynchronize(ctx->evB));
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, ctx->evA, ctx->evB);
+      timeUp = ms * 1.0e-3 >= timeLimitSec;
+    }
+    bt_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, cur, round, limit, timeUp);
+    bt_carry_kernel<<<wordGrid, 256, 0, st>>>(p, cur);
+    ctx->stats.kernelLaunches += 3;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(&any, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->evPool[0], ctx->evPool[1]);
+    roundKernelMs += ms;
+    ++roundKernelLaunches;
+  }
+  CK(cudaEventRecord(ctx->evB, st));
+  CK(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->evA, ctx->evB);
+  ctx->stats.lastRunMs = ms;
+  ctx->stats.lastRoundKernelMs = roundKernelMs;
+  ctx->stats.lastRoundKernelLaunches = roundKernelLaunches;
+  // rounds summed over vectors (for throughput accounting)
+  std::vector<int> rounds(bt.Bp);
+  CK(cudaMemcpy(rounds.data(), p.vecRounds, sizeof(int) * bt.Bp, cudaMemcpyDeviceToHost));
+  long long tot = 0;
+  for (int b = 0; b < bt.B; ++b)
+    tot += rounds[b];
+  ctx->stats.lastRoundsTotal = tot;
+  return CBP_OK;
+}
+
+static int bt_fetch_results(cbp_matrix *mat, cbp_result *out, bool devOut)
+{
+  cbp_ctx *ctx = mat->ctx;
+  BatchState &bt = mat->bt;
+  std::vector<int> h(static_cast<size_t>(bt.Bp) * 7);
+  CK(cudaMemcpyAsync(h.data(), bt.ints, sizeof(int) * h.size(), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  std::vector<cbp_result> tmp;
+  cbp_result *dstp = out;
+  if (devOut) {
+    tmp.resize(bt.B);
+    dstp = tmp.data();
+  }
+  const int Bp = bt.Bp;
+  for (int b = 0; b < bt.B; ++b) {
+    cbp_result r;
+    memset(&r, 0, sizeof(r));
+    const int ir = h[b], ic = h[Bp + b];
+    r.rounds = h[3 * Bp + b];
+    r.nChanged = h[4 * Bp + b];
+    r.stopReason = h[5 * Bp + b];
+    r.feasible = r.stopReason != CBP_STOP_INFEASIBLE;
+    r.infeasibleRow = -1;
+    r.infeasibleCol = -1;
+    if (!r.feasible) {
+      if (ir != INT_MAX)
+        r.infeasibleRow = ir;
+      else if (ic != INT_MAX)
+        r.infeasibleCol = ic;
+    }
+    if (r.stopReason == CBP_STOP_NOT_RUN && r.rounds == 0)
+      r.stopReason = CBP_STOP_TIME_LIMIT;
+    r.seconds = ctx->stats.lastRunMs * 1.0e-3;
+    dstp[b] = r;
+  }
+  if (devOut)
+    CK(cudaMemcpy(out, tmp.data(), sizeof(cbp_result) * bt.B, cudaMemcpyHostToDevice));
+  return CBP_OK;
+}
+
+int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *updStart, int *updCol,
+  double *updLb, double *updUb, int flags)
+{
+  if (!mat || !mat->bt.loaded || !out)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  BatchState &bt = mat->bt;
+  const bool dev = flags & CBP_FLAG_DEVICE_PTRS;
+  int rc = bt_fetch_results(mat, out, dev);
+  if (rc)
+    return rc;
+  if (!updStart)
+    return CBP_OK;
+  const BtParams p = bt_params(mat, 0.0);
+  bt_count_updates_kernel<<<cdiv(bt.B, 64), 64, 0, ctx->stream>>>(p, bt.B, bt.counts);
+  ++ctx->stats.kernelLaunches;
+  std::vector<long long> cnt(bt.B + 1);
+  CK(cudaMemcpyAsync(cnt.data(), bt.counts, sizeof(long long) * bt.B, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  long long run = 0;
+  for (int b = 0; b < bt.B; ++b) {
+    const long long c = cnt[b];
+    cnt[b] = run;
+    run += c;
+  }
+  cnt[bt.B] = run;
+  if (dev)
+    CK(cudaMemcpy(updStart, cnt.data(), sizeof(long long) * (bt.B + 1), cudaMemcpyHostToDevice));
+  else
+    memcpy(updStart, cnt.data(), sizeof(long long) * (bt.B + 1));
+  if (run > updCap || (run > 0 && (!updCol || !updLb || !updUb))) {
+    ctx->err = "cbp_batch_fetch: update buffers too small";
+    return CBP_ERR_CAPACITY;
+  }
+  if (run == 0)
+    return CBP_OK;
+  CK(cudaMemcpyAsync(bt.counts, cnt.data(), sizeof(long long) * (bt.B + 1), cudaMemcpyHostToDevice,
+    ctx->stream));
+  int *dCol = updCol;
+  double *dLb = updLb, *dUb = updUb;
+  if (!dev) {
+    CK(dalloc(&dCol, run));
+    CK(dalloc(&dLb, run));
+    CK(dalloc(&dUb, run));
+  }
+  bt_fill_updates_kernel<<<cdiv(bt.B, 64), 64, 0, ctx->stream>>>(p, bt.B, bt.counts, dCol, dLb, dUb);
+  ++ctx->stats.kernelLaunches;
+  cudaError_t e = cudaGetLastError();
+  if (!dev) {
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(updCol, dCol, sizeof(int) * run, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(updLb, dLb, sizeof(double) * run, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(updUb, dUb, sizeof(double) * run, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(dCol);
+    cudaFree(dLb);
+    cudaFree(dUb);
+  } else if (e == cudaSuccess) {
+    e = cudaStreamSynchronize(ctx->stream);
+  }
+  CK(e);
+  return CBP_OK;
+}
+
+int cbp_batch_fetch_dense(cbp_matrix *mat, double *lb, double *ub, int flags)
+{
+  if (!mat || !mat->bt.loaded || !lb || !ub)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  BatchState &bt = mat->bt;
+  const bool dev = flags & CBP_FLAG_DEVICE_PTRS;
+  const BtParams p = bt_params(mat, 0.0);
+  const size_t total = static_cast<size_t>(bt.B) * mat->n;
+  double *dl = lb, *du = ub;
+  if (!dev) {
+    CK(dalloc(&dl, total));
+    if (dalloc(&du, total) != cudaSuccess) {
+      cudaFree(dl);
+      ctx->err = "cbp_batch_fetch_dense: staging";
+      return CBP_ERR_NOMEM;
+    }
+  }
+  dim3 grid(cdiv(mat->n, 32), cdiv(bt.B, 32)), block(32, 8);
+  bt_transpose_out_kernel<<<grid, block, 0, ctx->stream>>>(p, bt.B, dl, du);
+  ++ctx->stats.kernelLaunches;
+  cudaError_t e = cudaGetLastError();
+  if (!dev) {
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(lb, dl, sizeof(double) * total, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(ub, du, sizeof(double) * total, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(dl);
+    cudaFree(du);
+  } else if (e == cudaSuccess) {
+    e = cudaStreamSynchronize(ctx->stream);
+  }
+  CK(e);
+  return CBP_OK;
+}
+
+int cbp_propagate_batch(cbp_matrix *mat, int B, double *lb, double *ub, double primalTol,
+  int maxRounds, double timeLimitSec, cbp_result *out, int flags)
+{
+  if (!mat || B <= 0 || !lb || !ub || !out)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  int rc = bt_reserve(mat, B);
+  if (rc)
+    return rc;
+  BatchState &bt = mat->bt;
+  const bool dev = flags & CBP_FLAG_DEVICE_PTRS;
+  const size_t total = static_cast<size_t>(B) * mat->n;
+  double *dl = lb, *du = ub;
+  if (!dev) {
+    CK(dalloc(&dl, total));
+    if (dalloc(&du, total) != cudaSuccess) {
+      cudaFree(dl);
+      ctx->err = "cbp_propagate_batch: staging";
+      return CBP_ERR_NOMEM;
+    }
+    cudaError_t e = cudaMemcpyAsync(dl, lb, sizeof(double) * total, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(du, ub, sizeof(double) * total, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) {
+      cudaFree(dl);
+      cudaFree(du);
+      CK(e);
+    }
+  }
+  dim3 grid(cdiv(mat->n, 32), bt.Bp / 32), block(32, 8);
+  bt_transpose_in_kernel<<<grid, block, 0, ctx->stream>>>(dl, du, B, mat->n, bt.Bp, bt.X[0], 0.0, 0.0);
+  ++ctx->stats.kernelLaunches;
+  bt.loaded = true;
+  bt.denseLoaded = true;
+  rc = cbp_batch_run(mat, primalTol, maxRounds, timeLimitSec);
+  if (rc == CBP_OK)
+    rc = bt_fetch_results(mat, out, dev);
+  if (rc == CBP_OK) {
+    const BtParams p = bt_params(mat, 0.0);
+    dim3 g2(cdiv(mat->n, 32), cdiv(B, 32));
+    bt_transpose_out_kernel<<<g2, block, 0, ctx->stream>>>(p, B, dl, du);
+    ++ctx->stats.kernelLaunches;
+    cudaError_t e = cudaGetLastError();
+    if (!dev) {
+      if (e == cudaSuccess)
+        e = cudaMemcpyAsync(lb, dl, sizeof(double) * total, cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess)
+        e = cudaMemcpyAsync(ub, du, sizeof(double) * total, cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    if (e == cudaSuccess)
+      e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) {
+      ctx->err = std::string("cbp_propagate_batch: ") + cudaGetErrorString(e);
+      rc = CBP_ERR_CUDA;
+    }
+  }
+  if (!dev) {
+    cudaFree(dl);
+    cudaFree(du);
+  }
+  bt.loaded = rc == CBP_OK;
+  return rc;
+}
+
+int cbp_propagate_batch_delta(cbp_matrix *mat, const double *baseLb, const double *baseUb, int B,
+  const int64_t *deltaStart, const uint32_t *deltaVar, const double *deltaBound, double primalTol,
+  int maxRounds, double timeLimitSec, cbp_result *out, int64_t updCap, int64_t *updStart, int *updCol,
+  double *updLb, double *updUb, int flags)
+{
+  int rc = cbp_batch_load_delta(mat, baseLb, baseUb, B, deltaStart, deltaVar, deltaBound, flags);
+  if (rc)
+    return rc;
+  if ((rc = cbp_batch_run(mat, primalTol, maxRounds, timeLimitSec)))
+    return rc;
+  return cbp_batch_fetch(mat, out, updCap, updStart, updCol, updLb, updUb, flags);
+}
+
+}  // extern "C"

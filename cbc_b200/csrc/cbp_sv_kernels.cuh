@@ -1,0 +1,487 @@
+// cbp_sv_kernels.cuh — single bound vector: the whole round loop of
+// /root/reference/src/CbcBoundPropagation.cpp:107-195 as ONE persistent
+// cooperative kernel.  Per round the matrix is streamed once: tiles of val/col
+// are brought into shared memory by the TMA unit (cp.async.bulk + mbarrier,
+// double buffered), the column bounds are gathered per nonzero, row
+// activities are formed, and candidate bounds go out as atomic min/max on the
+// *other* bound buffer (Jacobi).  Two grid-wide barriers per round (three when
+// the matrix has rows longer than a tile); the host is not involved until the
+// loop has stopped.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "cbp_device.cuh"
+
+namespace cbp {
+namespace cg = cooperative_groups;
+
+struct SvStatus {
+  int rounds;
+  int stopReason;
+  int infeasRow;  // min original row index over violators (INT_MAX if none)
+  int infeasCol;  // min crossing column (INT_MAX if none)
+  int finalBuf;   // which of X[0], X[1] holds the answer
+  int nChangedTotal;
+  int timeUp;
+  int chg[2];  // changed-column count of the running round (slot = round & 1)
+  int pad;
+  unsigned long long t0;  // globaltimer at kernel start
+  int roundChanged[kRoundCap];
+};
+
+struct SvParams {
+  // matrix (device)
+  const double *val;
+  const int *col;
+  const Tile *tiles;
+  const int *rp;
+  const double *rowLB, *rowUB;
+  const int *rowOrig;
+  const LongRow *longRows;
+  const signed char *colType;
+  RowAct *longPart;  // scratch: one partial per long-row chunk
+  int nTiles, firstLongTile, nLong, n;
+  // state
+  Bnd *X[2];
+  unsigned *dirty[2];
+  int nWords;
+  SvStatus *st;
+  Scal s;
+  int maxRounds;  // <=0: no limit
+  unsigned long long budgetNs;  // time limit measured from kernel start
+};
+
+struct SvSmem {
+  alignas(128) double val[2][kTileNnz];
+  alignas(128) int col[2][kTileNnz];
+  alignas(16) double2 lohi[kTileNnz];
+  int rp[kTileRows + 1];
+  alignas(8) uint64_t bar[2];
+  RowAct red[kWarps];
+  int cnt[kWarps];
+};
+
+// publishes accepted candidates into the round's target buffer
+struct SvSink {
+  Bnd *dst;
+  unsigned *dirty;
+  __device__ __forceinline__ void mark(int j) { atomicOr(&dirty[j >> 5], 1u << (j & 31)); }
+  __device__ __forceinline__ void ub(int j, double v)
+  {
+    atomic_min_f64(&dst[j].ub, v);
+    mark(j);
+  }
+  __device__ __forceinline__ void lb(int j, double v)
+  {
+    atomic_max_f64(&dst[j].lb, v);
+    mark(j);
+  }
+};
+
+__device__ __forceinline__ void sv_issue(const SvParams &p, SvSmem &sm, int t, int stage)
+{
+  const Tile T = p.tiles[t];
+  const uint32_t cnt = (static_cast<uint32_t>(T.nzCount) + 3u) & ~3u;  // 16-byte multiples
+  mbar_expect_tx(&sm.bar[stage], cnt * 12u);
+  bulk_g2s(sm.val[stage], p.val + T.nzBegin, cnt * 8u, &sm.bar[stage]);
+  bulk_g2s(sm.col[stage], p.col + T.nzBegin, cnt * 4u, &sm.bar[stage]);
+}
+
+// gather: one thread per staged nonzero; writes (lo, hi) = the bounds that
+// enter minAct / maxAct for that nonzero (R3)
+__device__ __forceinline__ void sv_gather(const SvSmem &sm, double2 *lohi, int stage, int nz,
+  const Bnd *__restrict__ src)
+{
+  for (int k = threadIdx.x; k < nz; k += kThreads) {
+    const double a = sm.val[stage][k];
+    const Bnd b = ldcg_bnd(&src[sm.col[stage][k]]);
+    lohi[k] = a > 0.0 ? make_double2(b.lb, b.ub) : make_double2(b.ub, b.lb);
+  }
+}
+
+__device__ __forceinline__ RowAct ldcg_rowact(const RowAct *q)
+{
+  const double2 a = __ldcg(reinterpret_cast<const double2 *>(q));
+  const double2 b = __ldcg(reinterpret_cast<const double2 *>(q) + 1);
+  RowAct r;
+  r.minAct = a.x;
+  r.maxAct = a.y;
+  r.maxRange = b.x;
+  const long long pk = __double_as_longlong(b.y);
+  r.infMin = static_cast<int>(pk & 0xffffffffll);
+  r.infMax = static_cast<int>(pk >> 32);
+  return r;
+}
+
+__device__ __forceinline__ void sv_flag_row(const SvParams &p, int row)
+{
+  atomicMin(&p.st->infeasRow, p.rowOrig[row]);
+}
+
+// One pass over tiles [tBegin, tEnd) for this CTA.  phaseL=false: round phase A
+// (short / medium rows completely, long-row chunks: partial sums only).
+// phaseL=true: long-row chunks again, now with the whole row's activity known.
+template <bool phaseL>
+__device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_t (&parity)[2],
+  int tBegin, int tEnd, const Bnd *__restrict__ src, SvSink &sink)
+{
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int t = tBegin + blockIdx.x;
+  if (t < tEnd && tid == 0)
+    sv_issue(p, sm, t, 0);
+  for (int stage = 0; t < tEnd; t += gridDim.x, stage ^= 1) {
+    const int tn = t + gridDim.x;
+    if (tid == 0 && tn < tEnd)
+      sv_issue(p, sm, tn, stage ^ 1);
+    const Tile T = p.tiles[t];
+    if (T.kind != kLong)
+      for (int i = tid; i <= T.rowCount; i += kThreads)
+        sm.rp[i] = p.rp[T.rpOff + i];
+    mbar_wait(&sm.bar[stage], parity[stage]);
+    parity[stage] ^= 1u;
+    sv_gather(sm, sm.lohi, stage, T.nzCount, src);
+    __syncthreads();
+    const double *val = sm.val[stage];
+    const int *col = sm.col[stage];
+    if (T.kind == kShort) {
+      if (tid < T.rowCount) {
+        const int kb = sm.rp[tid], ke = sm.rp[tid + 1];
+        RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+        for (int k = kb; k < ke; ++k) {
+          const double2 lh = sm.lohi[k];
+          accumulate(ra, val[k], lh.x, lh.y, p.s.inf);
+        }
+        const int row = T.rowBegin + tid;
+        const RowPlan pl = plan_row(ra, p.rowLB[row], p.rowUB[row], p.s);
+        if (pl.infeasible)
+          sv_flag_row(p, row);
+        if (pl.sideU || pl.sideL) {
+          for (int k = kb; k < ke; ++k) {
+            const double2 lh = sm.lohi[k];
+            tighten_nz(sink, pl, val[k], col[k], lh.x, lh.y, p.colType, p.s);
+          }
+        }
+      }
+    } else if (T.kind == kMedium) {
+      for (int r = warp; r < T.rowCount; r += kWarps) {
+        const int kb = sm.rp[r], ke = sm.rp[r + 1];
+        RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+        for (int k = kb + lane; k < ke; k += 32) {
+          const double2 lh = sm.lohi[k];
+          accumulate(ra, val[k], lh.x, lh.y, p.s.inf);
+        }
+        warp_reduce(ra);
+        const int row = T.rowBegin + r;
+        const RowPlan pl = plan_row(ra, p.rowLB[row], p.rowUB[row], p.s);
+        if (pl.infeasible && lane == 0)
+          sv_flag_row(p, row);
+        if (pl.sideU || pl.sideL) {
+          for (int k = kb + lane; k < ke; k += 32) {
+            const double2 lh = sm.lohi[k];
+            tighten_nz(sink, pl, val[k], col[k], lh.x, lh.y, p.colType, p.s);
+          }
+        }
+      }
+    } else {  // one chunk of a long row
+      const LongRow lr = p.longRows[T.longIdx];
+      if (!phaseL) {
+        RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+        for (int k = tid; k < T.nzCount; k += kThreads) {
+          const double2 lh = sm.lohi[k];
+          accumulate(ra, val[k], lh.x, lh.y, p.s.inf);
+        }
+        warp_reduce(ra);
+        if (lane == 0)
+          sm.red[warp] = ra;
+        __syncthreads();
+        if (tid == 0) {
+          RowAct tot = sm.red[0];
+          for (int w = 1; w < kWarps; ++w)
+            combine(tot, sm.red[w]);
+          p.longPart[lr.firstPart + T.chunkIdx] = tot;
+        }
+      } else {
+        RowAct tot = ldcg_rowact(&p.longPart[lr.firstPart]);
+        for (int c = 1; c < lr.nChunks; ++c)
+          combine(tot, ldcg_rowact(&p.longPart[lr.firstPart + c]));
+        const RowPlan pl = plan_row(tot, p.rowLB[lr.row], p.rowUB[lr.row], p.s);
+        if (pl.infeasible && tid == 0 && T.chunkIdx == 0)
+          sv_flag_row(p, lr.row);
+        if (pl.sideU || pl.sideL) {
+          for (int k = tid; k < T.nzCount; k += kThreads) {
+            const double2 lh = sm.lohi[k];
+            tighten_nz(sink, pl, val[k], col[k], lh.x, lh.y, p.colType, p.s);
+          }
+        }
+      }
+    }
+    __syncthreads();  // everyone is done with this stage and with lohi
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) sv_fixpoint_kernel(const SvParams p)
+{
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SvSmem &sm = *reinterpret_cast<SvSmem *>(smem_raw);
+  cg::grid_group grid = cg::this_grid();
+  const int tid = threadIdx.x;
+  const int gtid = blockIdx.x * kThreads + tid, gsize = gridDim.x * kThreads;
+  uint32_t parity[2] = { 0u, 0u };
+  if (tid == 0) {
+    mbar_init(&sm.bar[0], 1);
+    mbar_init(&sm.bar[1], 1);
+    mbar_fence_init();
+    if (blockIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      p.st->t0 = t;
+    }
+  }
+  __syncthreads();
+  // R11 failed in the prepare kernel: infeasible before the first round
+  if (__ldcg(&p.st->infeasCol) != 0x7fffffff) {
+    if (gtid == 0) {
+      p.st->rounds = 1;
+      p.st->stopReason = 4;
+      p.st->finalBuf = 0;
+    }
+    return;
+  }
+
+  const int limit = p.maxRounds > 0 ? p.maxRounds : 0x7fffffff;
+  for (int round = 0;; ++round) {
+    const int cur = round & 1;
+    const Bnd *src = p.X[cur];
+    Bnd *dst = p.X[cur ^ 1];
+    SvSink sink = { dst, p.dirty[cur] };
+
+    // A1: bring the target buffer up to date at the columns the previous
+    // round changed (it was that round's source, so it is stale there), and
+    // clear that round's marks.  Atomics: rows of this round may hit the same
+    // column at the same time.
+    if (round > 0) {
+      unsigned *prev = p.dirty[cur ^ 1];
+      for (int w = gtid; w < p.nWords; w += gsize) {
+        unsigned bits = __ldcg(&prev[w]);
+        if (!bits)
+          continue;
+        prev[w] = 0u;
+        while (bits) {
+          const int j = (w << 5) + __ffs(bits) - 1;
+          bits &= bits - 1;
+          const Bnd b = ldcg_bnd(&src[j]);
+          atomic_max_f64(&dst[j].lb, b.lb);
+          atomic_min_f64(&dst[j].ub, b.ub);
+        }
+      }
+    }
+    // A2: stream the matrix
+    sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
+    grid.sync();
+    if (p.nLong > 0) {
+      sv_stream<true>(p, sm, parity, p.firstLongTile, p.nTiles, src, sink);
+      grid.sync();
+    }
+    // B: settle the changed columns (R9) and count them
+    {
+      int mine = 0;
+      const unsigned *dw = p.dirty[cur];
+      for (int w = gtid; w < p.nWords; w += gsize) {
+        unsigned bits = __ldcg(&dw[w]);
+        mine += __popc(bits);
+        while (bits) {
+          const int j = (w << 5) + __ffs(bits) - 1;
+          bits &= bits - 1;
+          Bnd b = ldcg_bnd(&dst[j]);
+          const double oldUb = __ldcg(&src[j].ub);
+          const double L0 = b.lb, U0 = b.ub;
+          if (settle(b.lb, b.ub, oldUb, p.s))
+            atomicMin(&p.st->infeasCol, j);
+          else if (b.lb != L0 || b.ub != U0)
+            dst[j] = b;
+        }
+      }
+#pragma unroll
+      for (int m = 16; m >= 1; m >>= 1)
+        mine += __shfl_xor_sync(0xffffffffu, mine, m);
+      if ((tid & 31) == 0)
+        sm.cnt[tid >> 5] = mine;
+      __syncthreads();
+      if (tid == 0) {
+        int tot = 0;
+        for (int w = 0; w < kWarps; ++w)
+          tot += sm.cnt[w];
+        if (tot)
+          atomicAdd(&p.st->chg[cur], tot);
+        if (blockIdx.x == 0) {
+          p.st->chg[cur ^ 1] = 0;  // next round's slot; nobody touches it in this phase
+          unsigned long long t;
+          asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+          if (t - p.st->t0 >= p.budgetNs)
+            p.st->timeUp = 1;
+        }
+      }
+    }
+    grid.sync();
+    // every thread takes the same decision from the same global words
+    const int badRow = __ldcg(&p.st->infeasRow), badCol = __ldcg(&p.st->infeasCol);
+    const int changed = __ldcg(&p.st->chg[cur]);
+    int stop = 0;
+    int fin = cur;
+    if (badRow != 0x7fffffff || badCol != 0x7fffffff)
+      stop = 4;  // InfeasibleDetected: the failing round is not applied
+    else if (changed == 0)
+      stop = 1;  // ReachedFixpoint
+    else if (round + 1 >= limit) {
+      stop = 2;  // HitMaxRounds: the last round is applied
+      fin = cur ^ 1;
+    } else if (__ldcg(&p.st->timeUp)) {
+      stop = 3;  // HitTimeLimit, checked before the next round would start
+      fin = cur ^ 1;
+    }
+    if (gtid == 0) {
+      if (round < kRoundCap)
+        p.st->roundChanged[round] = changed;
+      if (stop != 4)
+        p.st->nChangedTotal += changed;
+    }
+    if (stop) {
+      if (gtid == 0) {
+        p.st->rounds = round + 1;
+        p.st->stopReason = stop;
+        p.st->finalBuf = fin;
+      }
+      break;
+    }
+  }
+}
+
+// ---- small helper kernels ---------------------------------------------------
+
+// interleave lb/ub into both state buffers, apply R11, mark what it changed
+__global__ void sv_prepare_kernel(const double *__restrict__ lb, const double *__restrict__ ub,
+  const signed char *__restrict__ colType, int n, Bnd *X0, Bnd *X1, unsigned *dirty0, SvStatus *st,
+  Scal s, int doPrepass)
+{
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n)
+    return;
+  double l = lb[j], u = ub[j];
+  const int r = doPrepass ? prepass_col(l, u, colType[j] != 0, s) : 0;
+  if (r == 2)
+    atomicMin(&st->infeasCol, j);
+  else if (r == 1)
+    atomicOr(&dirty0[j >> 5], 1u << (j & 31));
+  Bnd b;
+  b.lb = l;
+  b.ub = u;
+  X0[j] = b;
+  X1[j] = b;
+}
+
+__global__ void sv_finish_kernel(const Bnd *__restrict__ X, int n, double *lb, double *ub)
+{
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n)
+    return;
+  const Bnd b = X[j];
+  lb[j] = b.lb;
+  ub[j] = b.ub;
+}
+
+// Phase 1 (singleton rows): one thread per row that has exactly one nonzero.
+// Candidates are rowUB/a and rowLB/a; acceptance as in R7/R8; Jacobi.
+__global__ void sv_singleton_kernel(const int *__restrict__ singRows, int nSing,
+  const int *__restrict__ rowNz, const double *__restrict__ val, const int *__restrict__ col,
+  const double *__restrict__ rowLB, const double *__restrict__ rowUB,
+  const signed char *__restrict__ colType, const Bnd *__restrict__ src, Bnd *dst, unsigned *dirty,
+  Scal s)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nSing)
+    return;
+  const int row = singRows[i];
+  const int k = rowNz[row];
+  const double a = val[k];
+  const int j = col[k];
+  const Bnd b = src[j];
+  const bool isInt = colType[j] != 0;
+  SvSink sink = { dst, dirty };
+  const double ru = rowUB[row], rl = rowLB[row];
+  if (ru < s.inf) {
+    if (a > 0.0)
+      offer_ub(sink, j, ru / a, b.ub, isInt, s);
+    else
+      offer_lb(sink, j, ru / a, b.lb, isInt, s);
+  }
+  if (rl > -s.inf) {
+    if (a > 0.0)
+      offer_lb(sink, j, rl / a, b.lb, isInt, s);
+    else
+      offer_ub(sink, j, rl / a, b.ub, isInt, s);
+  }
+}
+
+// settle + count for the singleton phase; res[0]=changed, res[1]=fixed, res[2]=crossing
+__global__ void sv_singleton_settle_kernel(const Bnd *__restrict__ src, Bnd *dst, unsigned *dirty,
+  int nWords, int *res, Scal s)
+{
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nWords)
+    return;
+  unsigned bits = dirty[w];
+  if (!bits)
+    return;
+  dirty[w] = 0u;
+  while (bits) {
+    const int j = (w << 5) + __ffs(bits) - 1;
+    bits &= bits - 1;
+    Bnd b = dst[j];
+    if (settle(b.lb, b.ub, src[j].ub, s)) {
+      atomicAdd(&res[2], 1);
+      continue;
+    }
+    dst[j] = b;
+    atomicAdd(&res[0], 1);
+    if (b.lb == b.ub)
+      atomicAdd(&res[1], 1);
+  }
+}
+
+// plain activity kernel (diagnostic API): one warp per kept row, lanes stride
+__global__ void row_activity_kernel(const int *__restrict__ rowNz, const int *__restrict__ rowCnt,
+  const int *__restrict__ rowOrig, int mKept, const double *__restrict__ val,
+  const int *__restrict__ col, const double *__restrict__ lb, const double *__restrict__ ub,
+  double INF, double *minAct, double *maxAct, int *infMin, int *infMax)
+{
+  const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= mKept)
+    return;
+  const int kb = rowNz[r], ke = kb + rowCnt[r];
+  RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+  if (rowCnt[r] <= kShortLen) {  // sequential order, as the oracle sums
+    if (lane == 0)
+      for (int k = kb; k < ke; ++k) {
+        const double a = val[k];
+        const int j = col[k];
+        accumulate(ra, a, a > 0.0 ? lb[j] : ub[j], a > 0.0 ? ub[j] : lb[j], INF);
+      }
+  } else {
+    for (int k = kb + lane; k < ke; k += 32) {
+      const double a = val[k];
+      const int j = col[k];
+      accumulate(ra, a, a > 0.0 ? lb[j] : ub[j], a > 0.0 ? ub[j] : lb[j], INF);
+    }
+    warp_reduce(ra);
+  }
+  if (lane == 0) {
+    const int o = rowOrig[r];
+    minAct[o] = ra.minAct;
+    maxAct[o] = ra.maxAct;
+    infMin[o] = ra.infMin;
+    infMax[o] = ra.infMax;
+  }
+}
+
+}  // namespace cbp

@@ -1,0 +1,167 @@
+/*
+ * cbp_capi.h — C ABI of the B200 bound-propagation engine (libcbp.so).
+ *
+ * This is the drop-in boundary for the hot path of
+ * /root/reference/src/CbcBoundPropagation.cpp: everything `run()` does between
+ * extracting the problem data (:90-105) and applying the tightened bounds
+ * (:165-194) happens behind these entry points, on the GPU.  Plain pointers
+ * and sizes only; no C++ or torch types cross.  All entry points return 0 on
+ * success and a negative CBP_ERR_* code on failure (cbp_last_error gives the
+ * text); there is no CPU fallback: without a usable CUDA device cbp_create
+ * fails.
+ *
+ * Pointer arguments are HOST pointers unless CBP_FLAG_DEVICE_PTRS is given, in
+ * which case every bound / result array of that call is a device pointer on
+ * the context's device.
+ */
+#ifndef CBP_CAPI_H
+#define CBP_CAPI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define CBP_API __attribute__((visibility("default")))
+#else
+#define CBP_API
+#endif
+
+typedef struct cbp_ctx cbp_ctx;
+typedef struct cbp_matrix cbp_matrix;
+
+enum {
+  CBP_OK = 0,
+  CBP_ERR_ARG = -1,     /* bad argument */
+  CBP_ERR_CUDA = -2,    /* a CUDA call failed; see cbp_last_error */
+  CBP_ERR_NOMEM = -3,   /* device or host allocation failed */
+  CBP_ERR_CAPACITY = -4 /* a caller-provided output buffer is too small */
+};
+
+enum {
+  CBP_FLAG_DEVICE_PTRS = 1 /* bound/result arrays are device pointers */
+};
+
+/* Stop reasons; numbering of CbcBoundPropagation::StopReason
+ * (src/CbcBoundPropagation.hpp:60-66). */
+enum {
+  CBP_STOP_NOT_RUN = 0,
+  CBP_STOP_FIXPOINT = 1,
+  CBP_STOP_MAX_ROUNDS = 2,
+  CBP_STOP_TIME_LIMIT = 3,
+  CBP_STOP_INFEASIBLE = 4
+};
+
+/* What one propagation run reports; the fields are what
+ * CbcBoundPropagation keeps after the round loop
+ * (src/CbcBoundPropagation.cpp:129-133,166-189,197-201). */
+typedef struct cbp_result {
+  int feasible;      /* 0 iff infeasibility was proved (run() returns false) */
+  int rounds;        /* nRoundsRun_: rounds executed, the empty fixpoint round included */
+  int nChanged;      /* nBoundPropFixed_: sum over rounds of changed columns */
+  int infeasibleRow; /* CoinBoundPropagation::infeasibleRow(), -1 if n/a (:132) */
+  int infeasibleCol; /* CoinBoundPropagation::infeasibleCol(), -1 if n/a (:133) */
+  int stopReason;    /* CBP_STOP_* */
+  double seconds;    /* device time of the run */
+} cbp_result;
+
+/* Counters for benchmarks: kernels launched by this context so far and the
+ * device time of the most recent run's kernels, taken with CUDA events on
+ * the context's stream. */
+typedef struct cbp_stats {
+  int64_t kernelLaunches;
+  double lastRunMs;       /* whole run (all kernels of the last propagate call) */
+  double lastRoundKernelMs; /* time spent in the round kernel(s) of the last run */
+  int lastRoundKernelLaunches;
+  int64_t lastRoundsTotal; /* rounds summed over the vectors of the last run */
+} cbp_stats;
+
+/* -- context ----------------------------------------------------------- */
+
+/* One context per calling thread / stream; device -1 = current device.
+ * Replaces nothing in the reference (it has no device); needed because
+ * run() is re-entered from Cbc worker threads on distinct solver clones
+ * (src/CbcThread.cpp:1249,1319). */
+CBP_API cbp_ctx *cbp_create(int device);
+CBP_API void cbp_destroy(cbp_ctx *ctx);
+/* Use an existing cudaStream_t (e.g. torch's current stream) for all work. */
+CBP_API int cbp_set_stream(cbp_ctx *ctx, void *cudaStream);
+CBP_API const char *cbp_last_error(const cbp_ctx *ctx);
+CBP_API int cbp_get_stats(const cbp_ctx *ctx, cbp_stats *out);
+CBP_API int cbp_synchronize(cbp_ctx *ctx);
+
+/* -- problem data -------------------------------------------------------- */
+
+/* Upload the data run() reads once per call: getMatrixByRow() (row-major
+ * CoinPackedMatrix: vectorStarts / vectorLengths / indices / elements),
+ * getRowSense(), getRightHandSide(), getRowRange(), getColType(false),
+ * getInfinity()  (src/CbcBoundPropagation.cpp:91-99).  rowLen may be NULL when
+ * the rows are stored without gaps (rowStart has m+1 entries).  The matrix is
+ * re-tiled on the host and kept in HBM until cbp_matrix_free. */
+CBP_API cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStart,
+  const int *rowLen, const int *colIdx, const double *val, const char *rowSense,
+  const double *rhs, const double *range, const char *colType, double infinity);
+CBP_API void cbp_matrix_free(cbp_matrix *mat);
+
+/* -- the path itself ------------------------------------------------------- */
+
+/* Phase 1, OsiSolverInterface::tightenBoundsFromSingletonRows(int &nFixed)
+ * as called at src/CbcBoundPropagation.cpp:51: *nTightened < 0 means
+ * infeasible, otherwise the number of columns whose bounds changed; *nFixed of
+ * them ended fixed.  lb/ub (n doubles) are updated in place. */
+CBP_API int cbp_singletons(cbp_matrix *mat, double *lb, double *ub, double primalTol,
+  int *nTightened, int *nFixed, int flags);
+
+/* Phase 2, the whole round loop of src/CbcBoundPropagation.cpp:107-195 (each
+ * round = one CoinBoundPropagation construction, :124-127) run on the device
+ * without host round trips.  maxRounds <= 0 means "until fixpoint" (Level
+ * Fixpoint, :88).  lb/ub (n doubles) are updated in place with every completed
+ * feasible round.  roundChanged (nullable, roundCap ints) receives the
+ * per-round changed-column counts that run() prints at logLevel >= 2 (:191). */
+CBP_API int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol,
+  int maxRounds, double timeLimitSec, cbp_result *out, int *roundChanged, int roundCap,
+  int flags);
+
+/* B independent runs of the same loop over one matrix (new surface; per
+ * vector it is exactly cbp_propagate).  lb/ub are B x n, row-major per vector. */
+CBP_API int cbp_propagate_batch(cbp_matrix *mat, int B, double *lb, double *ub,
+  double primalTol, int maxRounds, double timeLimitSec, cbp_result *out, int flags);
+
+/* Batch in the node bound-diff wire format of CbcPartialNodeInfo
+ * (src/CbcNode.cpp:265-273: variable | 0x80000000 = upper bound): vector b is
+ * baseLb/baseUb with deltaVar/deltaBound[deltaStart[b] .. deltaStart[b+1])
+ * applied in order.  Outputs: out[B]; and, as CoinBoundPropagation's
+ * updatedBounds() would list them (src/CbcBoundPropagation.cpp:166,181-186),
+ * for vector b the columns whose final bounds differ from its input:
+ * updCol/updLb/updUb[updStart[b] .. updStart[b+1]).  updCap is the capacity of
+ * the three upd arrays; if it is too small CBP_ERR_CAPACITY is returned and
+ * updStart[B] holds the required size.  upd* may all be NULL. */
+CBP_API int cbp_propagate_batch_delta(cbp_matrix *mat, const double *baseLb, const double *baseUb,
+  int B, const int64_t *deltaStart, const uint32_t *deltaVar, const double *deltaBound,
+  double primalTol, int maxRounds, double timeLimitSec, cbp_result *out,
+  int64_t updCap, int64_t *updStart, int *updCol, double *updLb, double *updUb, int flags);
+
+/* Device-resident batch, split into its three steps so a caller (or a
+ * benchmark) can keep the inputs in HBM: load = upload base + deltas and
+ * expand them; run = the round loop; fetch = results and changed bounds. */
+CBP_API int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *baseUb,
+  int B, const int64_t *deltaStart, const uint32_t *deltaVar, const double *deltaBound, int flags);
+CBP_API int cbp_batch_reset(cbp_matrix *mat); /* re-expand the loaded base + deltas */
+CBP_API int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeLimitSec);
+CBP_API int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *updStart,
+  int *updCol, double *updLb, double *updUb, int flags);
+/* Dense final bounds of the resident batch, B x n row-major per vector. */
+CBP_API int cbp_batch_fetch_dense(cbp_matrix *mat, double *lb, double *ub, int flags);
+
+/* Min/max row activities with exact infinite-bound counters for one bound
+ * vector (the arithmetic of src/CbcSolverHeuristics.cpp:282-318); rows in the
+ * caller's order, skipped ('N' / empty) rows report zeros. */
+CBP_API int cbp_row_activity(cbp_matrix *mat, const double *lb, const double *ub,
+  double *minAct, double *maxAct, int *infMin, int *infMax, int flags);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,195 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the
+same seeded inputs, against the golden micro-instances, and size-independent
+properties at larger sizes."""
+import numpy as np
+import pytest
+
+from cbc_b200 import capi
+from cbc_b200 import instances as I
+from helpers import assert_same_bounds, assert_same_result, golden_cases
+
+pytestmark = pytest.mark.gpu
+
+
+def _both(oracle, ctx, inst, lb=None, ub=None, **kw):
+    lb = inst.lb if lb is None else lb
+    ub = inst.ub if ub is None else ub
+    mat = capi.Matrix(ctx, inst)
+    rg, lg, ug = mat.propagate(lb, ub, **kw)
+    mat.close()
+    ro, lo, uo = oracle.propagate(oracle.Problem(inst), lb, ub, **kw)
+    return (rg, lg, ug), (ro, lo, uo)
+
+
+@pytest.mark.parametrize("case", golden_cases(), ids=lambda c: c["name"])
+def test_golden_micro(gpu_ctx, case):
+    inst = I.micro(case["instance"])
+    mat = capi.Matrix(gpu_ctx, inst)
+    r, lb, ub = mat.propagate(case["lb_in"], case["ub_in"])
+    assert r["feasible"] == case["feasible"]
+    assert r["rounds"] == case["rounds"]
+    assert r["nChanged"] == case["nChanged"]
+    assert r["infeasibleRow"] == case.get("infeasibleRow", -1)
+    assert r["infeasibleCol"] == case.get("infeasibleCol", -1)
+    assert np.array_equal(lb, np.array(case["lb"], float))
+    assert np.array_equal(ub, np.array(case["ub"], float))
+    if "singletons" in case:
+        nt, nf, _, _ = mat.singletons(case["lb_in"], case["ub_in"])
+        assert nt == case["singletons"]
+    # batch path, same vector three times
+    res, L, U = mat.propagate_batch(np.tile(case["lb_in"], (3, 1)), np.tile(case["ub_in"], (3, 1)))
+    for b in range(3):
+        assert bool(res["feasible"][b]) == case["feasible"] and res["rounds"][b] == case["rounds"]
+        assert res["infeasibleRow"][b] == case.get("infeasibleRow", -1)
+        assert np.array_equal(L[b], np.array(case["lb"], float)) and np.array_equal(U[b], np.array(case["ub"], float))
+    mat.close()
+
+
+SV_CASES = {
+    "setcover": lambda: I.set_cover(m=2000, n=4000, density=0.01, fix_frac=0.93, seed=21),
+    "fast0507": lambda: I.fast0507_shaped(m=101, n=9000, fix_frac=0.985, seed=22),
+    "knapassign": lambda: I.knapsack_assignment(m=4000, n=10000, seed=23),
+    "mixed": lambda: I.mixed_bigm(m=20000, n=20000, seed=24),
+    "mixed_loose": lambda: I.mixed_bigm(m=5000, n=3000, avg_len=20, fix_frac=0.2, seed=25),
+    "powerlaw": lambda: I.power_law(n=30000, nnz_target=200000, n_dense=3, dense_len=9000, max_len=3000, seed=26),
+    "powerlaw_bad": lambda: I.power_law(n=30000, nnz_target=200000, n_dense=3, dense_len=9000, max_len=3000,
+                                        seed=27, infeasible=True),
+}
+
+
+@pytest.mark.parametrize("name", list(SV_CASES))
+def test_single_vector_fixpoint(oracle, gpu_ctx, name):
+    inst = SV_CASES[name]()
+    (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst)
+    assert_same_result(rg, ro, name)
+    assert rg["roundChanged"] == ro["roundChanged"]
+    assert_same_bounds(inst.colType, lg, ug, lo, uo, name)
+    if inst.xstar is not None:
+        assert rg["feasible"] and inst.contains(lg, ug)
+
+
+def test_max_rounds_and_time_limit(oracle, gpu_ctx):
+    inst = I.mixed_bigm(m=20000, n=20000, seed=24)
+    for mr in (1, 2, 5):
+        (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst, max_rounds=mr)
+        assert_same_result(rg, ro, f"maxRounds={mr}")
+        assert rg["stopReason"] == 2
+        assert_same_bounds(inst.colType, lg, ug, lo, uo, f"maxRounds={mr}")
+    (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst, time_limit=0.0)
+    assert_same_result(rg, ro, "timeLimit=0")
+    assert rg["stopReason"] == 3 and np.array_equal(lg, inst.lb)
+
+
+def test_row_activity_counters_exact(oracle, gpu_ctx):
+    inst = I.mixed_bigm(m=20000, n=20000, seed=24)
+    lb = inst.lb.copy()
+    lb[::7] = -inst.inf  # plenty of infinite contributions on both sides
+    mat = capi.Matrix(gpu_ctx, inst)
+    mn, mx, im, ix = mat.row_activity(lb, inst.ub)
+    mat.close()
+    omn, omx, oim, oix = oracle.row_activity(oracle.Problem(inst), lb, inst.ub)
+    assert np.array_equal(im, oim) and np.array_equal(ix, oix)
+    assert np.allclose(mn, omn, rtol=1e-9, atol=1e-12) and np.allclose(mx, omx, rtol=1e-9, atol=1e-12)
+
+
+def test_singletons_match(oracle, gpu_ctx):
+    inst = I.mixed_bigm(m=6000, n=3000, avg_len=2.0, seed=31)
+    # cut most rows down to one nonzero so that phase 1 has work
+    keep = np.ones(inst.nnz, bool)
+    first = inst.rowStart[:-1]
+    lens = np.diff(inst.rowStart)
+    rows = np.repeat(np.arange(inst.m), lens)
+    pos = np.arange(inst.nnz) - np.repeat(first, lens)
+    keep[(pos > 0) & (rows % 3 != 0)] = False
+    inst.val = inst.val.copy()
+    inst.val[~keep] = 0.0  # zeros must be ignored by both sides
+    mat = capi.Matrix(gpu_ctx, inst)
+    nt, nf, lg, ug = mat.singletons(inst.lb, inst.ub)
+    mat.close()
+    ont, onf, lo, uo = oracle.singletons(oracle.Problem(inst), inst.lb, inst.ub)
+    assert (nt, nf) == (ont, onf) and nt > 0
+    assert_same_bounds(inst.colType, lg, ug, lo, uo, "singletons")
+
+
+def test_empty_and_ragged_inputs(oracle, gpu_ctx):
+    # no rows at all; rows that are empty, free ('N') or all-zero
+    inst = I.Instance("norows", 0, 3, np.zeros(1, np.int64), np.zeros(0, np.int32), np.zeros(0),
+                      np.zeros(0, np.uint8), np.zeros(0), np.zeros(0), np.array([1, 2, 0], np.int8),
+                      np.zeros(3), np.array([1.0, 2.5, 7.0]))
+    (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst)
+    assert_same_result(rg, ro, "norows")
+    assert np.array_equal(ug, uo) and ug[1] == 2.0
+    inst = I.Instance("ragged", 4, 3, np.array([0, 0, 2, 4, 5], np.int64), np.array([0, 1, 0, 2, 1], np.int32),
+                      np.array([1.0, 1.0, 0.0, 0.0, 3.0]), np.frombuffer(b"LNLL", np.uint8).copy(),
+                      np.array([1.0, 0.5, -1.0, 4.5]), np.zeros(4), np.array([1, 2, 0], np.int8),
+                      np.zeros(3), np.array([1.0, 9.0, 7.0]))
+    (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst)
+    assert_same_result(rg, ro, "ragged")
+    assert np.array_equal(lg, lo) and np.array_equal(ug, uo) and ug[1] == 1.0
+
+
+def _check_batch(oracle, ctx, inst, s, v, b, what, **kw):
+    mat = capi.Matrix(ctx, inst)
+    res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b, **kw)
+    Lg, Ug = mat.batch_fetch_dense()
+    ores, Lo, Uo = oracle.propagate_batch_delta(oracle.Problem(inst), inst.lb, inst.ub, s, v, b, threads=4, **kw)
+    for k in ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason"):
+        bad = np.flatnonzero(res[k] != ores[k])
+        assert bad.size == 0, f"{what}: {k} differs for vectors {bad[:8]}: {res[k][bad[:8]]} vs {ores[k][bad[:8]]}"
+    for k in range(len(s) - 1):
+        assert_same_bounds(inst.colType, Lg[k], Ug[k], Lo[k], Uo[k], f"{what} vector {k}")
+    # sparse answer == dense answer restricted to what changed (feasible vectors only)
+    L0, U0 = I.expand_deltas(inst.lb, inst.ub, s, v, b)
+    for k in range(len(s) - 1):
+        cols = uc[us[k]:us[k + 1]]
+        if not res["feasible"][k]:
+            assert cols.size == 0
+            continue
+        want = np.flatnonzero((Lg[k] != L0[k]) | (Ug[k] != U0[k]))
+        assert np.array_equal(cols, want), f"{what} vector {k}: update list"
+        assert np.array_equal(ul[us[k]:us[k + 1]], Lg[k][want]) and np.array_equal(uu[us[k]:us[k + 1]], Ug[k][want])
+    # dense entry point gives the same
+    res2, L2, U2 = mat.propagate_batch(L0, U0, **kw)
+    for k in ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason"):
+        assert np.array_equal(res2[k], res[k]), k
+    assert np.array_equal(L2, Lg) and np.array_equal(U2, Ug)
+    mat.close()
+    return res
+
+
+def test_batch_dives_knapsack_assignment(oracle, gpu_ctx):
+    inst = I.knapsack_assignment(m=3000, n=8000, seed=41)
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 70, max_depth=48, seed=42)
+    res = _check_batch(oracle, gpu_ctx, inst, s, v, b, "dives")
+    assert res["feasible"].astype(bool).any() and (~res["feasible"].astype(bool)).any()
+    assert res["rounds"].max() >= 3
+
+
+def test_batch_strong_branching_set_cover(oracle, gpu_ctx):
+    inst = I.fast0507_shaped(m=101, n=9000, fix_frac=0.985, seed=22)
+    r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    inst.lb, inst.ub = lb0, ub0  # node bounds = propagated root, as in strong branching
+    s, v, b = I.strong_branch_deltas(inst, lb0, ub0, 48, seed=43)
+    res = _check_batch(oracle, gpu_ctx, inst, s, v, b, "strong branching")
+    assert res["nChanged"].sum() > 0
+
+
+def test_batch_probe_mixed(oracle, gpu_ctx):
+    inst = I.mixed_bigm(m=6000, n=6000, seed=44)
+    s, v, b = I.probe_deltas(inst, inst.lb, inst.ub, 20, seed=45)
+    _check_batch(oracle, gpu_ctx, inst, s, v, b, "probes")
+    _check_batch(oracle, gpu_ctx, inst, s, v, b, "probes maxRounds=3", max_rounds=3)
+
+
+def test_fixpoint_is_idempotent_at_size(gpu_ctx):
+    """Size-independent property on a larger instance: propagating a fixpoint again changes nothing
+    and takes exactly one round; the planted point survives."""
+    inst = I.mixed_bigm(m=300_000, n=300_000, seed=51)
+    mat = capi.Matrix(gpu_ctx, inst)
+    r1, l1, u1 = mat.propagate(inst.lb, inst.ub)
+    assert r1["feasible"] and r1["stopReason"] == 1 and inst.contains(l1, u1)
+    assert np.all(l1 >= inst.lb) and np.all(u1 <= inst.ub)
+    r2, l2, u2 = mat.propagate(l1, u1)
+    assert r2["rounds"] == 1 and r2["nChanged"] == 0
+    assert np.array_equal(l1, l2) and np.array_equal(u1, u2)
+    mat.close()
