@@ -1,0 +1,349 @@
+#!/usr/bin/env python
+"""bench.py — bound-propagation throughput on B200 (metric of BASELINE.json:
+nnz·rounds·nodes processed per second, beside the HBM roofline and the CPU baseline).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5|c1] [--impl reference]
+
+A step is one pass of the hot path over one batch of synthetic input that is
+already resident in HBM: for the batched workloads (default c2: fast0507-shaped
+set cover, 4096 strong-branching bound vectors per GPU) the base bounds and the
+node bound diffs are resident and a step expands them and runs every vector to
+its fixpoint; for the single-vector workloads (c1, c3, c5) the bound vector is
+resident and a step runs it to its fixpoint.  Multi-GPU: the node batch is
+sharded, one process per GPU, no data-path collective (weak scaling).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from cbc_b200 import instances as I  # noqa: E402
+
+METRIC = "nnz*rounds*nodes processed/sec"
+UNIT = "nnz*rounds*nodes/s"
+
+
+# ------------------------------------------------------------------ workloads
+def make_workload(name, rank=0, scale=1.0):
+    """Returns dict(inst, kind, base lb/ub, deltas or None, description)."""
+    if name == "c2":
+        inst = I.fast0507_shaped(fix_frac=0.3)
+        B = max(64, int(4096 * scale))
+        s, v, b = I.strong_branch_deltas(inst, inst.lb, inst.ub, B // 2, seed=I.SEED0 + 100 + rank)
+        return dict(inst=inst, kind="batch", lb=inst.lb, ub=inst.ub, deltas=(s, v, b), B=B,
+                    desc=f"c2: fast0507-shaped set cover {inst.m}x{inst.n}, {inst.nnz} nnz, 30% columns fixed at 0, "
+                         f"{B} strong-branching bound vectors per GPU (base + one bound change each)")
+    if name == "c4":
+        inst = I.knapsack_assignment()
+        B = max(64, int(2048 * scale))
+        s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, B, max_depth=64, seed=I.SEED0 + 200 + rank)
+        return dict(inst=inst, kind="batch", lb=inst.lb, ub=inst.ub, deltas=(s, v, b), B=B,
+                    desc=f"c4: knapsack/assignment {inst.m}x{inst.n}, {inst.nnz} nnz, {B} dive vectors per GPU "
+                         f"(1..64 cumulative fixings)")
+    if name == "c3":
+        sz = max(1000, int(1_000_000 * scale))
+        inst = I.mixed_bigm(m=sz, n=sz)
+        return dict(inst=inst, kind="single", lb=inst.lb, ub=inst.ub, deltas=None, B=1,
+                    desc=f"c3: mixed-integer {inst.m}x{inst.n}, {inst.nnz} nnz, single-vector fixpoint")
+    if name == "c5":
+        inst = I.power_law(n=max(1000, int(1_000_000 * scale)), nnz_target=max(10000, int(5_000_000 * scale)),
+                           dense_len=max(100, int(100_000 * scale)))
+        return dict(inst=inst, kind="single", lb=inst.lb, ub=inst.ub, deltas=None, B=1,
+                    desc=f"c5: power-law rows {inst.m}x{inst.n}, {inst.nnz} nnz, 8 rows of "
+                         f"{max(100, int(100_000 * scale))} nnz, single-vector fixpoint")
+    if name == "c1":
+        inst = I.set_cover(fix_frac=0.93)
+        return dict(inst=inst, kind="single", lb=inst.lb, ub=inst.ub, deltas=None, B=1,
+                    desc=f"c1: set cover {inst.m}x{inst.n}, {inst.nnz} nnz, root bound vector")
+    raise SystemExit(f"unknown workload {name}")
+
+
+def algorithmic_bytes(inst, rounds_launched, vector_rounds, batch):
+    """per round 12*nnz + 20*m + 33*n (single vector) or
+    12*nnz + 20*m + n + 32*n*B (batch; B = vectors active in that round, so the sum over
+    rounds of B is the vector-rounds total)."""
+    if batch:
+        return rounds_launched * (12 * inst.nnz + 20 * inst.m + inst.n) + 32 * inst.n * vector_rounds
+    return rounds_launched * (12 * inst.nnz + 20 * inst.m + 33 * inst.n)
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop = index, [], False
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        sm = [int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit()]
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
+        return {"sm_mhz": int(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ CPU arms
+def cpu_run(work, threads, target_seconds, max_vectors=None):
+    """Time the CPU restatement (oracle/) on a bounded sample of the workload."""
+    from oracle import oracle_py as O
+
+    inst = work["inst"]
+    prob = O.Problem(inst)
+    if work["kind"] == "single":
+        t0 = time.perf_counter()
+        r, _, _ = O.propagate(prob, work["lb"], work["ub"])
+        dt = time.perf_counter() - t0
+        return dict(units=inst.nnz * r["rounds"], seconds=dt, sample=f"whole instance, {r['rounds']} rounds",
+                    threads=1)
+    s, v, b = work["deltas"]
+    B = len(s) - 1
+    # calibrate on a few vectors, then size the sample for ~target_seconds
+    probe = min(B, max(threads, 8))
+    t0 = time.perf_counter()
+    res, _, _ = O.propagate_batch_delta(prob, work["lb"], work["ub"], s[: probe + 1], v[: s[probe]], b[: s[probe]],
+                                        threads=threads, want_bounds=False)
+    dt = max(time.perf_counter() - t0, 1e-6)
+    k = int(min(B, max(probe, probe * target_seconds / dt)))
+    if max_vectors:
+        k = min(k, max_vectors)
+    t0 = time.perf_counter()
+    res, _, _ = O.propagate_batch_delta(prob, work["lb"], work["ub"], s[: k + 1], v[: s[k]], b[: s[k]],
+                                        threads=threads, want_bounds=False)
+    dt = time.perf_counter() - t0
+    return dict(units=inst.nnz * int(res["rounds"].sum()), seconds=dt,
+                sample=f"first {k} of {B} vectors of the same batch", threads=threads)
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path.  The reference itself cannot be built here (its
+    arithmetic lives in CoinUtils/Osi, absent), so this times the CPU restatement in oracle/ with all
+    the host threads it can use."""
+    if rank != 0:
+        return
+    from oracle import oracle_py as O
+
+    work = make_workload(args.workload, 0, args.scale)
+    threads = O.max_threads() if work["kind"] == "batch" else 1
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_run(work, threads, per_step / 4)
+    units, secs, sample = 0, 0.0, ""
+    for _ in range(args.steps):
+        r = cpu_run(work, threads, per_step)
+        units += r["units"]
+        secs += r["seconds"]
+        sample = r["sample"]
+    val = units / secs
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": work["desc"]},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------ GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cbc_b200")
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from cbc_b200 import capi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    W = max(3, args.warmup)
+
+    work = make_workload(args.workload, rank, args.scale)
+    inst = work["inst"]
+    stream = torch.cuda.current_stream().cuda_stream
+    ctx = capi.Context(local, stream=stream)
+    mat = capi.Matrix(ctx, inst)
+    batch = work["kind"] == "batch"
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # resident inputs
+    if batch:
+        s, v, b = work["deltas"]
+        mat.batch_load_delta(work["lb"], work["ub"], s, v, b)
+        ctx.synchronize()
+
+        def step():
+            mat.batch_run()
+            st = ctx.stats()
+            return st["lastRoundsTotal"], st["lastRoundKernelMs"], st["lastRoundKernelLaunches"]
+    else:
+        dlb0 = torch.tensor(work["lb"], device="cuda")
+        dub0 = torch.tensor(work["ub"], device="cuda")
+        dlb, dub = dlb0.clone(), dub0.clone()
+
+        def step():
+            dlb.copy_(dlb0)
+            dub.copy_(dub0)
+            r = mat.propagate_device(dlb.data_ptr(), dub.data_ptr())
+            st = ctx.stats()
+            return r["rounds"], st["lastRoundKernelMs"], r["rounds"]
+
+    for _ in range(W):
+        step()
+    barrier()
+    l0 = ctx.stats()["kernelLaunches"]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    vec_rounds = kernel_ms = 0.0
+    round_launches = 0
+    with ClockSampler(local) as clk:
+        ev0.record()
+        for _ in range(args.steps):
+            vr, kms, kl = step()
+            vec_rounds += vr
+            kernel_ms += kms
+            round_launches += kl
+        ev1.record()
+        barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = ctx.stats()["kernelLaunches"] - l0
+    units = float(inst.nnz) * vec_rounds
+    t = torch.tensor([ms, units, float(launches)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        ms, units, launches = float(tmax[0]), float(t[1]), float(t[2])
+    value = units / (ms * 1e-3)
+
+    # ---- end to end through the C ABI with HOST buffers (copies inside the timed region)
+    e2e_steps = max(2, min(args.steps, 5))
+    if batch:
+        def e2e_step():
+            res, us, uc, ul, uu = mat.propagate_batch_delta(work["lb"], work["ub"], s, v, b)
+            return int(res["rounds"].sum()), uc.size
+        h2d = 16 * inst.n + 8 * (len(s)) + 12 * len(v)
+    else:
+        def e2e_step():
+            r, _, _ = mat.propagate(work["lb"], work["ub"])
+            return r["rounds"], 0
+        h2d = 16 * inst.n
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    e_units, n_upd = 0, 0
+    for _ in range(e2e_steps):
+        rr, nu = e2e_step()
+        e_units += inst.nnz * rr
+        n_upd = nu
+    torch.cuda.synchronize()
+    e_dt = time.perf_counter() - t0
+    d2h = (32 * work["B"] + 8 * (work["B"] + 1) + 20 * n_upd) if batch else (16 * inst.n + 64)
+    e = torch.tensor([e_dt, float(e_units)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        emax = e.clone()
+        dist.all_reduce(emax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(e, op=dist.ReduceOp.SUM)
+        e_dt, e_units = float(emax[0]), float(e[1])
+    e2e_val = e_units / e_dt
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk_path):
+        peaks = json.load(open(pk_path))
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    alg = algorithmic_bytes(inst, round_launches, vec_rounds, batch)
+    achieved = alg / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "bt_rows_kernel" if batch else "sv_fixpoint_kernel",
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
+                "kernel_ms_per_launch": kernel_ms / max(1, round_launches),
+                "algorithmic_bytes_per_launch": alg / max(1, round_launches)}
+    prof = os.path.join(ROOT, "profiles", f"traffic_{args.workload}.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": work["desc"], "l2": "inputs larger than L2" if (alg / max(1, round_launches)) > 126e6
+                   else "working set fits L2; matrix re-read every round by design",
+                   "vectors_per_gpu": work["B"], "sharding": "node batch sharded across GPUs, no collective"},
+        "roofline": roofline,
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+        "gpu_launches": int(launches),
+        "clocks": clk.summary(),
+    }
+    if world == 1 and not args.no_cpu:
+        c = cpu_run(work, 1, 12.0)
+        line["cpu_baseline"] = {"value": c["units"] / c["seconds"], "unit": UNIT, "cores": 1, "kind": "port",
+                                "sample": c["sample"]}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

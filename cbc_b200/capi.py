@@ -36,7 +36,7 @@ class Stats(C.Structure):
 SYMBOLS = [
     "cbp_create", "cbp_destroy", "cbp_set_stream", "cbp_last_error", "cbp_get_stats", "cbp_synchronize",
     "cbp_matrix_upload", "cbp_matrix_free", "cbp_singletons", "cbp_propagate", "cbp_propagate_batch",
-    "cbp_propagate_batch_delta", "cbp_batch_load_delta", "cbp_batch_reset", "cbp_batch_run",
+    "cbp_propagate_batch_delta", "cbp_batch_load_delta", "cbp_batch_run",
     "cbp_batch_fetch", "cbp_batch_fetch_dense", "cbp_row_activity",
 ]
 
@@ -74,7 +74,6 @@ def load():
     lib.cbp_propagate_batch.argtypes = [vp, i32, vp, vp, f64, i32, f64, vp, i32]
     lib.cbp_propagate_batch_delta.argtypes = [vp, vp, vp, i32, vp, vp, vp, f64, i32, f64, vp, i64, vp, vp, vp, vp, i32]
     lib.cbp_batch_load_delta.argtypes = [vp, vp, vp, i32, vp, vp, vp, i32]
-    lib.cbp_batch_reset.argtypes = [vp]
     lib.cbp_batch_run.argtypes = [vp, f64, i32, f64]
     lib.cbp_batch_fetch.argtypes = [vp, vp, i64, vp, vp, vp, vp, i32]
     lib.cbp_batch_fetch_dense.argtypes = [vp, vp, vp, i32]
@@ -179,7 +178,8 @@ class Matrix:
         self.ctx.check(self.ctx.lib.cbp_propagate(self.h, _ptr(lb), _ptr(ub), tol, max_rounds, time_limit,
                                                   C.byref(r), _ptr(rc_arr), round_cap, 0), "cbp_propagate")
         out = _res_dict(r)
-        out["roundChanged"] = [int(x) for x in rc_arr[: min(r.rounds, round_cap)] if x >= 0]
+        done = r.rounds - (0 if r.feasible else 1)  # the failing round reports no count
+        out["roundChanged"] = [int(x) for x in rc_arr[: min(done, round_cap)] if x >= 0]
         return out, lb, ub
 
     def propagate_device(self, lb_ptr, ub_ptr, tol=1e-7, max_rounds=0, time_limit=1e100):
@@ -226,9 +226,6 @@ class Matrix:
         self._B = len(start) - 1
         self.ctx.check(self.ctx.lib.cbp_batch_load_delta(self.h, _ptr(base_lb), _ptr(base_ub), self._B, _ptr(start),
                                                          _ptr(var), _ptr(bnd), 0), "cbp_batch_load_delta")
-
-    def batch_reset(self):
-        self.ctx.check(self.ctx.lib.cbp_batch_reset(self.h), "cbp_batch_reset")
 
     def batch_run(self, tol=1e-7, max_rounds=0, time_limit=1e100):
         self.ctx.check(self.ctx.lib.cbp_batch_run(self.h, tol, max_rounds, time_limit), "cbp_batch_run")

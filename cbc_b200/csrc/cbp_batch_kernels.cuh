@@ -208,9 +208,21 @@ __global__ void bt_carry_kernel(const BtParams p, int cur)
 
 // ---- loading ------------------------------------------------------------------
 
-// every vector starts from the base bounds (R11 applied per vector later)
+// does any base column need R11 (non-integral integer bounds, crossing bounds)?
+__global__ void bt_base_check_kernel(const double *__restrict__ baseLb, const double *__restrict__ baseUb,
+  const signed char *__restrict__ colType, int n, Scal s, int *flag)
+{
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n)
+    return;
+  double l = baseLb[j], u = baseUb[j];
+  if (prepass_col(l, u, colType[j] != 0, s) != 0)
+    atomicOr(flag, 1);
+}
+
+// every vector starts from the base bounds; both buffers are written
 __global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double *__restrict__ baseUb,
-  int n, size_t Bp, Bnd *X0)
+  int n, size_t Bp, Bnd *X0, Bnd *X1)
 {
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<size_t>(n) * Bp)
@@ -220,22 +232,45 @@ __global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double
   x.lb = __ldg(&baseLb[j]);
   x.ub = __ldg(&baseUb[j]);
   X0[i] = x;
+  X1[i] = x;
 }
 
-// node bound diffs, applied in order inside a vector (one thread per vector)
+// node bound diffs, applied in order inside a vector (one thread per vector).
+// With cellPrepass the touched cells also get R11 here (the fast path, taken
+// when no base column needs R11, so untouched cells are already final).
 __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsigned *__restrict__ var,
-  const double *__restrict__ bnd, int B, size_t Bp, Bnd *X0)
+  const double *__restrict__ bnd, int B, const BtParams p, int cellPrepass)
 {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B)
     return;
-  for (long long k = start[b]; k < start[b + 1]; ++k) {
+  const size_t Bp = static_cast<size_t>(p.Bp);
+  const long long k0 = start[b], k1 = start[b + 1];
+  for (long long k = k0; k < k1; ++k) {
     const unsigned v = var[k];
-    Bnd *x = &X0[static_cast<size_t>(v & 0x7fffffffu) * Bp + b];
+    const size_t at = static_cast<size_t>(v & 0x7fffffffu) * Bp + b;
+    Bnd x = p.X[0][at];
     if (v & 0x80000000u)
-      x->ub = bnd[k];
+      x.ub = bnd[k];
     else
-      x->lb = bnd[k];
+      x.lb = bnd[k];
+    p.X[0][at] = x;
+    p.X[1][at] = x;
+  }
+  if (!cellPrepass)
+    return;
+  for (long long k = k0; k < k1; ++k) {
+    const int j = static_cast<int>(var[k] & 0x7fffffffu);
+    const size_t at = static_cast<size_t>(j) * Bp + b;
+    Bnd x = p.X[0][at];
+    const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);
+    if (r == 2)
+      atomicMin(&p.vecInfCol[b], j);
+    else if (r == 1) {
+      atomicOr(&p.dirty[0][static_cast<size_t>(j) * p.G + (b >> 5)], 1u << (b & 31));
+      p.X[0][at] = x;
+      p.X[1][at] = x;
+    }
   }
 }
 

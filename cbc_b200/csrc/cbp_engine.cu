@@ -46,7 +46,7 @@ struct BatchState {
   unsigned *dVar = nullptr;
   double *dBnd = nullptr;
   long long nDelta = 0;
-  bool loaded = false, denseLoaded = false;
+  bool loaded = false, denseLoaded = false, consumed = false;
   size_t capCells = 0, capDelta = 0;
   int capBp = 0;
 };
@@ -254,7 +254,8 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
         ++cnt;
       }
     }
-    if (cnt == 0)
+    // a row without nonzeros says rl <= 0 <= ru; keep it only if that can fail (R4)
+    if (cnt == 0 && !(ru < 0.0 || rl > 0.0))
       continue;
     const int c = cnt <= kShortLen ? kShort : (cnt <= kTileNnz ? kMedium : kLong);
     cls[c].push_back({ i, cnt, rl, ru });
@@ -599,7 +600,8 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   if ((rc = sv_stage_out(mat, mat->X[head.finalBuf & 1], lb, ub, flags)))
     return rc;
   if (roundChanged && roundCap > 0) {
-    const int cnt = std::min(std::min(roundCap, head.rounds), kRoundCap);
+    const int done = head.rounds - (head.stopReason == CBP_STOP_INFEASIBLE ? 1 : 0);
+    const int cnt = std::min(std::min(roundCap, done), kRoundCap);
     if (cnt > 0)
       CK(cudaMemcpyAsync(roundChanged, mat->st->roundChanged, sizeof(int) * cnt, cudaMemcpyDeviceToHost,
         ctx->stream));
@@ -734,29 +736,6 @@ static BtParams bt_params(cbp_matrix *mat, double tol)
   return p;
 }
 
-// (re)build X[0] from the loaded input; everything else is set up by run
-static int bt_expand(cbp_matrix *mat)
-{
-  cbp_ctx *ctx = mat->ctx;
-  BatchState &bt = mat->bt;
-  if (!bt.loaded) {
-    ctx->err = "no batch loaded";
-    return CBP_ERR_ARG;
-  }
-  if (bt.denseLoaded)
-    return CBP_OK;  // a dense batch is consumed in place; it cannot be re-expanded
-  bt_expand_kernel<<<cdiv(static_cast<long long>(bt.cells), 256), 256, 0, ctx->stream>>>(bt.baseLb,
-    bt.baseUb, mat->n, bt.Bp, bt.X[0]);
-  ++ctx->stats.kernelLaunches;
-  if (bt.nDelta > 0) {
-    bt_delta_kernel<<<cdiv(bt.B, 128), 128, 0, ctx->stream>>>(bt.dStart, bt.dVar, bt.dBnd, bt.B, bt.Bp,
-      bt.X[0]);
-    ++ctx->stats.kernelLaunches;
-  }
-  CK(cudaGetLastError());
-  return CBP_OK;
-}
-
 int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *baseUb, int B,
   const int64_t *deltaStart, const uint32_t *deltaVar, const double *deltaBound, int flags)
 {
@@ -806,20 +785,8 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
   bt.nDelta = nDelta;
   bt.loaded = true;
   bt.denseLoaded = false;
-  return bt_expand(mat);
-}
-
-int cbp_batch_reset(cbp_matrix *mat)
-{
-  if (!mat)
-    return CBP_ERR_ARG;
-  cbp_ctx *ctx = mat->ctx;
-  CK(cudaSetDevice(ctx->device));
-  if (mat->bt.denseLoaded) {
-    ctx->err = "cbp_batch_reset: a dense batch cannot be re-expanded";
-    return CBP_ERR_ARG;
-  }
-  return bt_expand(mat);
+  bt.consumed = false;
+  return CBP_OK;
 }
 
 int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeLimitSec)
@@ -838,9 +805,41 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   CK(cudaMemsetAsync(bt.dirty[1], 0, sizeof(unsigned) * words, st));
   CK(cudaMemsetAsync(bt.ever, 0, sizeof(unsigned) * words, st));
   bt_init_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, bt.B);
-  bt_prepass_kernel<<<cdiv(static_cast<long long>(bt.cells), 256), 256, 0, st>>>(p, bt.B);
+  ++ctx->stats.kernelLaunches;
+  const int cellGrid = cdiv(static_cast<long long>(bt.cells), 256);
+  bool fullPrepass = true;
+  if (!bt.denseLoaded) {
+    // base + deltas: expand here, so a loaded batch can be run any number of times
+    if (bt.consumed) {
+      ctx->err = "cbp_batch_run: this batch was loaded dense and has already been run";
+      return CBP_ERR_ARG;
+    }
+    int need = 0;
+    CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
+    bt_base_check_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->colType, mat->n, p.s,
+      p.anyActive);
+    CK(cudaMemcpyAsync(&need, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));
+    bt_expand_kernel<<<cellGrid, 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.Bp, bt.X[0], bt.X[1]);
+    ctx->stats.kernelLaunches += 2;
+    CK(cudaStreamSynchronize(st));
+    fullPrepass = need != 0;
+    if (bt.nDelta > 0) {
+      bt_delta_kernel<<<cdiv(bt.B, 128), 128, 0, st>>>(bt.dStart, bt.dVar, bt.dBnd, bt.B, p, fullPrepass ? 0 : 1);
+      ++ctx->stats.kernelLaunches;
+    }
+  } else {
+    if (bt.consumed) {
+      ctx->err = "cbp_batch_run: a dense batch can be run once";
+      return CBP_ERR_ARG;
+    }
+    bt.consumed = true;
+  }
+  if (fullPrepass) {
+    bt_prepass_kernel<<<cellGrid, 256, 0, st>>>(p, bt.B);
+    ++ctx->stats.kernelLaunches;
+  }
   bt_prepass_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p);
-  ctx->stats.kernelLaunches += 3;
+  ++ctx->stats.kernelLaunches;
   CK(cudaGetLastError());
   const long long warps = static_cast<long long>(bt.G) * mat->mKept;
   const int rowsGrid = cdiv(warps, kWarps);
@@ -1081,6 +1080,7 @@ int cbp_propagate_batch(cbp_matrix *mat, int B, double *lb, double *ub, double p
   ++ctx->stats.kernelLaunches;
   bt.loaded = true;
   bt.denseLoaded = true;
+  bt.consumed = false;
   rc = cbp_batch_run(mat, primalTol, maxRounds, timeLimitSec);
   if (rc == CBP_OK)
     rc = bt_fetch_results(mat, out, dev);

@@ -340,10 +340,11 @@ __global__ void __launch_bounds__(kThreads, 2) sv_fixpoint_kernel(const SvParams
       fin = cur ^ 1;
     }
     if (gtid == 0) {
-      if (round < kRoundCap)
-        p.st->roundChanged[round] = changed;
-      if (stop != 4)
+      if (stop != 4) {  // a failing round is not applied and not reported
+        if (round < kRoundCap)
+          p.st->roundChanged[round] = changed;
         p.st->nChangedTotal += changed;
+      }
     }
     if (stop) {
       if (gtid == 0) {

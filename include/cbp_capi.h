@@ -144,11 +144,12 @@ CBP_API int cbp_propagate_batch_delta(cbp_matrix *mat, const double *baseLb, con
   int64_t updCap, int64_t *updStart, int *updCol, double *updLb, double *updUb, int flags);
 
 /* Device-resident batch, split into its three steps so a caller (or a
- * benchmark) can keep the inputs in HBM: load = upload base + deltas and
- * expand them; run = the round loop; fetch = results and changed bounds. */
+ * benchmark) can keep the inputs in HBM: load = upload base + deltas; run =
+ * expand them into the per-vector bound arrays and do the round loop (may be
+ * repeated: every run starts again from base + deltas); fetch = results and
+ * changed bounds of the last run. */
 CBP_API int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *baseUb,
   int B, const int64_t *deltaStart, const uint32_t *deltaVar, const double *deltaBound, int flags);
-CBP_API int cbp_batch_reset(cbp_matrix *mat); /* re-expand the loaded base + deltas */
 CBP_API int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeLimitSec);
 CBP_API int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *updStart,
   int *updCol, double *updLb, double *updUb, int flags);

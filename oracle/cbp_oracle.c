@@ -214,9 +214,8 @@ static inline int process_row(round_ctx *c, int i, const double *lb, const doubl
   double rl, ru;
   if (!row_bounds(p, i, &rl, &ru))
     return 0;
+  /* an empty (or all-zero) row is the constraint rl <= 0 <= ru and is tested like any other */
   const int64_t s = p->rowStart[i], e = row_end(p, i);
-  if (e <= s)
-    return 0;
   double minAct, maxAct;
   int infMin, infMax;
   row_sums(p, i, lb, ub, &minAct, &maxAct, &infMin, &infMax);

@@ -92,23 +92,42 @@ def test_row_activity_counters_exact(oracle, gpu_ctx):
     assert np.allclose(mn, omn, rtol=1e-9, atol=1e-12) and np.allclose(mx, omx, rtol=1e-9, atol=1e-12)
 
 
+def _with_singleton_rows(inst, k, seed):
+    """Append k one-nonzero rows that the planted point satisfies (some tight, some 'E', some with zeros)."""
+    g = np.random.default_rng(seed)
+    cols = g.choice(inst.n, size=k, replace=False)
+    a = g.integers(1, 9, size=k).astype(float) * np.where(g.random(k) < 0.4, -1.0, 1.0)
+    act = a * inst.xstar[cols]
+    kind = g.integers(0, 3, size=k)  # 0: <=, 1: >=, 2: ==
+    slack = np.floor(g.random(k) * 3.0)
+    sense = np.where(kind == 0, ord("L"), np.where(kind == 1, ord("G"), ord("E"))).astype(np.uint8)
+    rhs = np.where(kind == 0, act + slack, np.where(kind == 1, act - slack, act))
+    # every appended row also carries an explicit zero entry that must be ignored
+    new_cols = np.stack([cols, (cols + 1) % inst.n], axis=1).ravel().astype(np.int32)
+    new_vals = np.stack([a, np.zeros(k)], axis=1).ravel()
+    rowStart = np.concatenate([inst.rowStart, inst.rowStart[-1] + 2 * np.arange(1, k + 1)])
+    return I.Instance(inst.name + "+sing", inst.m + k, inst.n, rowStart, np.concatenate([inst.col, new_cols]),
+                      np.concatenate([inst.val, new_vals]), np.concatenate([inst.sense, sense]),
+                      np.concatenate([inst.rhs, rhs]), np.concatenate([inst.range, np.zeros(k)]), inst.colType,
+                      inst.lb, inst.ub, inst.inf, inst.xstar)
+
+
 def test_singletons_match(oracle, gpu_ctx):
-    inst = I.mixed_bigm(m=6000, n=3000, avg_len=2.0, seed=31)
-    # cut most rows down to one nonzero so that phase 1 has work
-    keep = np.ones(inst.nnz, bool)
-    first = inst.rowStart[:-1]
-    lens = np.diff(inst.rowStart)
-    rows = np.repeat(np.arange(inst.m), lens)
-    pos = np.arange(inst.nnz) - np.repeat(first, lens)
-    keep[(pos > 0) & (rows % 3 != 0)] = False
-    inst.val = inst.val.copy()
-    inst.val[~keep] = 0.0  # zeros must be ignored by both sides
+    inst = _with_singleton_rows(I.mixed_bigm(m=3000, n=3000, seed=31), 900, 32)
     mat = capi.Matrix(gpu_ctx, inst)
     nt, nf, lg, ug = mat.singletons(inst.lb, inst.ub)
-    mat.close()
     ont, onf, lo, uo = oracle.singletons(oracle.Problem(inst), inst.lb, inst.ub)
-    assert (nt, nf) == (ont, onf) and nt > 0
+    assert (nt, nf) == (ont, onf) and nt > 100 and nf > 10
     assert_same_bounds(inst.colType, lg, ug, lo, uo, "singletons")
+    assert inst.contains(lg, ug)
+    # and an infeasible singleton: x_j <= lb_j - 1
+    j = int(np.flatnonzero(inst.colType == 1)[0])
+    bad = _with_singleton_rows(inst, 1, 33)
+    bad.col[-2], bad.val[-2], bad.sense[-1], bad.rhs[-1] = j, 1.0, ord("L"), inst.lb[j] - 1.0
+    mat2 = capi.Matrix(gpu_ctx, bad)
+    assert mat2.singletons(bad.lb, bad.ub)[0] == -1 == oracle.singletons(oracle.Problem(bad), bad.lb, bad.ub)[0]
+    mat.close()
+    mat2.close()
 
 
 def test_empty_and_ragged_inputs(oracle, gpu_ctx):
@@ -166,7 +185,7 @@ def test_batch_dives_knapsack_assignment(oracle, gpu_ctx):
 
 
 def test_batch_strong_branching_set_cover(oracle, gpu_ctx):
-    inst = I.fast0507_shaped(m=101, n=9000, fix_frac=0.985, seed=22)
+    inst = I.fast0507_shaped(m=101, n=9000, fix_frac=0.996, seed=22)
     r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
     inst.lb, inst.ub = lb0, ub0  # node bounds = propagated root, as in strong branching
     s, v, b = I.strong_branch_deltas(inst, lb0, ub0, 48, seed=43)
