@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(kThreads) bt_rows_kernel(const BtParams p, int
 #pragma unroll 4
   for (int k = kb; k < ke; ++k) {
     const double a = __ldg(&p.val[k]);
-    const int j = __ldg(&p.col[k]);
+    const int j = col_of(__ldg(&p.col[k]));
     const Bnd x = ldcg_bnd(&src[static_cast<size_t>(j) * Bp]);
     accumulate(ra, a, a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s.inf);
   }
@@ -90,10 +90,11 @@ __global__ void __launch_bounds__(kThreads) bt_rows_kernel(const BtParams p, int
   BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, Bp, p.G, 1u << lane };
   for (int k = kb; k < ke; ++k) {
     const double a = __ldg(&p.val[k]);
-    const int j = __ldg(&p.col[k]);
+    const int c = __ldg(&p.col[k]);
+    const int j = col_of(c);
     if (pl.sideU || pl.sideL) {
       const Bnd x = ldcg_bnd(&src[static_cast<size_t>(j) * Bp]);
-      tighten_nz(sink, pl, a, j, a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.colType, p.s);
+      tighten_nz(sink, pl, a, j, col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
     }
   }
 }

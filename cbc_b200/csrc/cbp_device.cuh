@@ -62,6 +62,12 @@ struct Scal {
 
 __device__ __forceinline__ bool is_inf(double x, double INF) { return !(fabs(x) < INF); }
 
+// The packed column index carries the column's integrality in bit 31 (a static
+// property, set at upload), so the tightening pass needs no colType lookup.
+constexpr int kColMask = 0x7fffffff;
+__device__ __forceinline__ int col_of(int packed) { return packed & kColMask; }
+__device__ __forceinline__ bool col_is_int(int packed) { return packed < 0; }
+
 // atomic max / min on doubles through the integer atomics (no -0.0 is ever
 // stored: R7 adds +0.0).  For v >= 0 signed-int order equals double order and
 // any negative double is a negative int; for v < 0 unsigned order is reversed
@@ -191,8 +197,8 @@ __device__ __forceinline__ void offer_lb(Sink &sink, int j, double v, double old
 }
 
 template <class Sink>
-__device__ __forceinline__ void tighten_nz(Sink &sink, const RowPlan &p, double a, int j, double lo,
-  double hi, const signed char *__restrict__ colType, const Scal &s)
+__device__ __forceinline__ void tighten_nz(Sink &sink, const RowPlan &p, double a, int j, bool isInt,
+  double lo, double hi, const Scal &s)
 {
   const bool loInf = is_inf(lo, s.inf), hiInf = is_inf(hi, s.inf);
   const bool finite = !loInf && !hiInf;
@@ -224,7 +230,6 @@ __device__ __forceinline__ void tighten_nz(Sink &sink, const RowPlan &p, double 
   }
   if (!wantU && !wantL)
     return;
-  const bool isInt = colType[j] != 0;
   if (wantU) {  // rowUB side: a>0 bounds x from above, a<0 from below
     if (a > 0.0)
       offer_ub(sink, j, vU, u, isInt, s);

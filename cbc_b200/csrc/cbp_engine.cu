@@ -288,7 +288,8 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     for (int64_t k = s; k < e; ++k)
       if (val[k] != 0.0) {
         hVal.push_back(val[k]);
-        hCol.push_back(colIdx[k]);
+        const bool isInt = colType && colType[colIdx[k]] != 0;
+        hCol.push_back(isInt ? (colIdx[k] | INT_MIN) : colIdx[k]);  // bit 31 = integer column
       }
     if (kr.cnt == 1)
       hSing.push_back(keptIdx);

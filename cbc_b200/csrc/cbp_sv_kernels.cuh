@@ -88,14 +88,26 @@ __device__ __forceinline__ void sv_issue(const SvParams &p, SvSmem &sm, int t, i
 }
 
 // gather: one thread per staged nonzero; writes (lo, hi) = the bounds that
-// enter minAct / maxAct for that nonzero (R3)
+// enter minAct / maxAct for that nonzero (R3).  All loads of a thread are
+// issued before the first use, so 8 gathers per thread are in flight.
 __device__ __forceinline__ void sv_gather(const SvSmem &sm, double2 *lohi, int stage, int nz,
   const Bnd *__restrict__ src)
 {
-  for (int k = threadIdx.x; k < nz; k += kThreads) {
-    const double a = sm.val[stage][k];
-    const Bnd b = ldcg_bnd(&src[sm.col[stage][k]]);
-    lohi[k] = a > 0.0 ? make_double2(b.lb, b.ub) : make_double2(b.ub, b.lb);
+  constexpr int kPer = kTileNnz / kThreads;
+  Bnd b[kPer];
+#pragma unroll
+  for (int i = 0; i < kPer; ++i) {
+    const int k = threadIdx.x + i * kThreads;
+    if (k < nz)
+      b[i] = ldcg_bnd(&src[col_of(sm.col[stage][k])]);
+  }
+#pragma unroll
+  for (int i = 0; i < kPer; ++i) {
+    const int k = threadIdx.x + i * kThreads;
+    if (k < nz) {
+      const double a = sm.val[stage][k];
+      lohi[k] = a > 0.0 ? make_double2(b[i].lb, b[i].ub) : make_double2(b[i].ub, b[i].lb);
+    }
   }
 }
 
@@ -137,6 +149,11 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
     if (T.kind != kLong)
       for (int i = tid; i <= T.rowCount; i += kThreads)
         sm.rp[i] = p.rp[T.rpOff + i];
+    double rl = 0.0, ru = 0.0;  // short rows: fetched now, used after the walk
+    if (T.kind == kShort && tid < T.rowCount) {
+      rl = p.rowLB[T.rowBegin + tid];
+      ru = p.rowUB[T.rowBegin + tid];
+    }
     mbar_wait(&sm.bar[stage], parity[stage]);
     parity[stage] ^= 1u;
     sv_gather(sm, sm.lohi, stage, T.nzCount, src);
@@ -152,13 +169,13 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
           accumulate(ra, val[k], lh.x, lh.y, p.s.inf);
         }
         const int row = T.rowBegin + tid;
-        const RowPlan pl = plan_row(ra, p.rowLB[row], p.rowUB[row], p.s);
+        const RowPlan pl = plan_row(ra, rl, ru, p.s);
         if (pl.infeasible)
           sv_flag_row(p, row);
         if (pl.sideU || pl.sideL) {
           for (int k = kb; k < ke; ++k) {
             const double2 lh = sm.lohi[k];
-            tighten_nz(sink, pl, val[k], col[k], lh.x, lh.y, p.colType, p.s);
+            tighten_nz(sink, pl, val[k], col_of(col[k]), col_is_int(col[k]), lh.x, lh.y, p.s);
           }
         }
       }
@@ -178,7 +195,7 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
         if (pl.sideU || pl.sideL) {
           for (int k = kb + lane; k < ke; k += 32) {
             const double2 lh = sm.lohi[k];
-            tighten_nz(sink, pl, val[k], col[k], lh.x, lh.y, p.colType, p.s);
+            tighten_nz(sink, pl, val[k], col_of(col[k]), col_is_int(col[k]), lh.x, lh.y, p.s);
           }
         }
       }
@@ -210,7 +227,7 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
         if (pl.sideU || pl.sideL) {
           for (int k = tid; k < T.nzCount; k += kThreads) {
             const double2 lh = sm.lohi[k];
-            tighten_nz(sink, pl, val[k], col[k], lh.x, lh.y, p.colType, p.s);
+            tighten_nz(sink, pl, val[k], col_of(col[k]), col_is_int(col[k]), lh.x, lh.y, p.s);
           }
         }
       }
@@ -404,9 +421,9 @@ __global__ void sv_singleton_kernel(const int *__restrict__ singRows, int nSing,
   const int row = singRows[i];
   const int k = rowNz[row];
   const double a = val[k];
-  const int j = col[k];
+  const int j = col_of(col[k]);
   const Bnd b = src[j];
-  const bool isInt = colType[j] != 0;
+  const bool isInt = col_is_int(col[k]);
   SvSink sink = { dst, dirty };
   const double ru = rowUB[row], rl = rowLB[row];
   if (ru < s.inf) {
@@ -465,13 +482,13 @@ __global__ void row_activity_kernel(const int *__restrict__ rowNz, const int *__
     if (lane == 0)
       for (int k = kb; k < ke; ++k) {
         const double a = val[k];
-        const int j = col[k];
+        const int j = col_of(col[k]);
         accumulate(ra, a, a > 0.0 ? lb[j] : ub[j], a > 0.0 ? ub[j] : lb[j], INF);
       }
   } else {
     for (int k = kb + lane; k < ke; k += 32) {
       const double a = val[k];
-      const int j = col[k];
+      const int j = col_of(col[k]);
       accumulate(ra, a, a > 0.0 ? lb[j] : ub[j], a > 0.0 ? ub[j] : lb[j], INF);
     }
     warp_reduce(ra);

@@ -138,13 +138,19 @@ def test_empty_and_ragged_inputs(oracle, gpu_ctx):
     (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst)
     assert_same_result(rg, ro, "norows")
     assert np.array_equal(ug, uo) and ug[1] == 2.0
-    inst = I.Instance("ragged", 4, 3, np.array([0, 0, 2, 4, 5], np.int64), np.array([0, 1, 0, 2, 1], np.int32),
-                      np.array([1.0, 1.0, 0.0, 0.0, 3.0]), np.frombuffer(b"LNLL", np.uint8).copy(),
-                      np.array([1.0, 0.5, -1.0, 4.5]), np.zeros(4), np.array([1, 2, 0], np.int8),
-                      np.zeros(3), np.array([1.0, 9.0, 7.0]))
+    def ragged(rhs2):
+        return I.Instance("ragged", 4, 3, np.array([0, 0, 2, 4, 5], np.int64), np.array([0, 1, 0, 2, 1], np.int32),
+                          np.array([1.0, 1.0, 0.0, 0.0, 3.0]), np.frombuffer(b"LNLL", np.uint8).copy(),
+                          np.array([1.0, 0.5, rhs2, 4.5]), np.zeros(4), np.array([1, 2, 0], np.int8),
+                          np.zeros(3), np.array([1.0, 9.0, 7.0]))
+    inst = ragged(1.0)  # row 0 empty, row 1 free, row 2 all zeros with 0 <= 1, row 3: 3 x1 <= 4.5
     (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst)
     assert_same_result(rg, ro, "ragged")
     assert np.array_equal(lg, lo) and np.array_equal(ug, uo) and ug[1] == 1.0
+    inst = ragged(-1.0)  # the all-zero row now says 0 <= -1
+    (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst)
+    assert_same_result(rg, ro, "ragged infeasible")
+    assert not rg["feasible"] and rg["infeasibleRow"] == 2 and np.array_equal(ug, inst.ub)
 
 
 def _check_batch(oracle, ctx, inst, s, v, b, what, **kw):
