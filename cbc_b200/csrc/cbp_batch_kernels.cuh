@@ -21,6 +21,8 @@ struct BtParams {
   const double *rowLB, *rowUB;
   const int *rowOrig;
   const signed char *colType;
+  const int *shortRowsBt, *longRowsBt;  // kept-row indices by batch class
+  int nShortBt, nLongBt;
   int mKept, n, Bp, G;  // Bp = padded vector count, G = Bp / 32
   Bnd *X[2];
   unsigned *dirty[2];   // [n][G]
@@ -51,15 +53,70 @@ struct BtSink {
   }
 };
 
-// One round, rows phase.  grid.x * 8 warps cover G * mKept (group-major, so
-// warps that run together share a vector group and its bounds stay in L2).
-__global__ void __launch_bounds__(kThreads) bt_rows_kernel(const BtParams p, int cur)
+// The row walk of one warp over nonzeros [kb, ke): the 32 lanes fetch 32
+// (a, j) pairs with one coalesced load each, then every pair is broadcast by
+// shuffle and each lane gathers the bounds of ITS vector for that column (the
+// 32 lanes together read one 512-byte line).  Eight gathers are issued before
+// the first one is consumed.  Each lane accumulates in CSR order.
+__device__ __forceinline__ void bt_walk_sum(const BtParams &p, const Bnd *__restrict__ src, size_t Bp,
+  int kb, int ke, int lane, RowAct &ra)
+{
+  for (int base = kb; base < ke; base += 32) {
+    const int k = base + lane;
+    const double myA = k < ke ? __ldg(&p.val[k]) : 0.0;
+    const int myC = k < ke ? __ldg(&p.col[k]) : 0;
+#pragma unroll
+    for (int i0 = 0; i0 < 32; i0 += 8) {
+      if (base + i0 >= ke)
+        break;
+      Bnd x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int c = __shfl_sync(0xffffffffu, myC, i0 + u);
+        x[u] = ldcg_bnd(&src[static_cast<size_t>(col_of(c)) * Bp]);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const double a = __shfl_sync(0xffffffffu, myA, i0 + u);
+        if (a != 0.0)  // warp-uniform: only the padding past ke is zero
+          accumulate(ra, a, a > 0.0 ? x[u].lb : x[u].ub, a > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
+      }
+    }
+  }
+}
+
+// second walk, only for warps where some lane's row can tighten something
+__device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const Bnd *__restrict__ src, size_t Bp,
+  int kb, int ke, int lane, const RowPlan &pl, BtSink &sink)
+{
+  const bool want = pl.sideU || pl.sideL;
+  for (int base = kb; base < ke; base += 32) {
+    const int k = base + lane;
+    const double myA = k < ke ? __ldg(&p.val[k]) : 0.0;
+    const int myC = k < ke ? __ldg(&p.col[k]) : 0;
+    const int cnt = min(32, ke - base);
+    for (int i = 0; i < cnt; ++i) {
+      const double a = __shfl_sync(0xffffffffu, myA, i);
+      const int c = __shfl_sync(0xffffffffu, myC, i);
+      if (want) {
+        const int j = col_of(c);
+        const Bnd x = ldcg_bnd(&src[static_cast<size_t>(j) * Bp]);
+        tighten_nz(sink, pl, a, j, col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+      }
+    }
+  }
+}
+
+// One round, rows phase, rows up to kBtLongLen nonzeros: a warp owns (row,
+// group of 32 vectors).  Work is group-major so that the warps running at the
+// same time share few vector groups and their bounds stay in L2.
+__global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, int cur)
 {
   const long long W = static_cast<long long>(blockIdx.x) * kWarps + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
-  if (W >= static_cast<long long>(p.G) * p.mKept)
+  if (W >= static_cast<long long>(p.G) * p.nShortBt)
     return;
-  const int g = static_cast<int>(W / p.mKept), r = static_cast<int>(W % p.mKept);
+  const int g = static_cast<int>(W / p.nShortBt), r = __ldg(&p.shortRowsBt[W % p.nShortBt]);
   const unsigned act = __ldg(&p.active[g]);
   if (act == 0u)
     return;
@@ -70,13 +127,7 @@ __global__ void __launch_bounds__(kThreads) bt_rows_kernel(const BtParams p, int
   const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
 
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-#pragma unroll 4
-  for (int k = kb; k < ke; ++k) {
-    const double a = __ldg(&p.val[k]);
-    const int j = col_of(__ldg(&p.col[k]));
-    const Bnd x = ldcg_bnd(&src[static_cast<size_t>(j) * Bp]);
-    accumulate(ra, a, a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s.inf);
-  }
+  bt_walk_sum(p, src, Bp, kb, ke, lane, ra);
   RowPlan pl = plan_row(ra, __ldg(&p.rowLB[r]), __ldg(&p.rowUB[r]), p.s);
   if (!mine) {
     pl.infeasible = false;
@@ -88,15 +139,50 @@ __global__ void __launch_bounds__(kThreads) bt_rows_kernel(const BtParams p, int
   if (!__any_sync(0xffffffffu, pl.sideU || pl.sideL))
     return;
   BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, Bp, p.G, 1u << lane };
-  for (int k = kb; k < ke; ++k) {
-    const double a = __ldg(&p.val[k]);
-    const int c = __ldg(&p.col[k]);
-    const int j = col_of(c);
-    if (pl.sideU || pl.sideL) {
-      const Bnd x = ldcg_bnd(&src[static_cast<size_t>(j) * Bp]);
-      tighten_nz(sink, pl, a, j, col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
-    }
+  bt_walk_tighten(p, src, Bp, kb, ke, lane, pl, sink);
+}
+
+// Rows longer than kBtLongLen: a CTA owns (row, group); its 8 warps split the
+// row into 8 contiguous pieces, the partial activities are combined in warp
+// order through shared memory.  With a whole CTA per row the CTAs in flight
+// cover only one or two vector groups, whose bounds (n x 512 B each) then fit
+// in L2 across all the rows that use them.
+__global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParams p, int cur)
+{
+  __shared__ RowAct red[kWarps][32];
+  const int g = blockIdx.x / p.nLongBt, r = __ldg(&p.longRowsBt[blockIdx.x % p.nLongBt]);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned act = __ldg(&p.active[g]);
+  if (act == 0u)
+    return;
+  const bool mine = (act >> lane) & 1u;
+  const size_t Bp = static_cast<size_t>(p.Bp);
+  const int b = g * 32 + lane;
+  const Bnd *__restrict__ src = p.X[cur] + b;
+  const int kb = __ldg(&p.rowNz[r]), cnt = __ldg(&p.rowCnt[r]);
+  const int per = ((cnt + kWarps - 1) / kWarps + 31) & ~31;  // 32-aligned pieces
+  const int wb = min(kb + warp * per, kb + cnt), we = min(wb + per, kb + cnt);
+
+  RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+  bt_walk_sum(p, src, Bp, wb, we, lane, ra);
+  red[warp][lane] = ra;
+  __syncthreads();
+  RowAct tot = red[0][lane];
+#pragma unroll
+  for (int w = 1; w < kWarps; ++w)
+    combine(tot, red[w][lane]);
+  RowPlan pl = plan_row(tot, __ldg(&p.rowLB[r]), __ldg(&p.rowUB[r]), p.s);
+  if (!mine) {
+    pl.infeasible = false;
+    pl.sideU = false;
+    pl.sideL = false;
   }
+  if (pl.infeasible && warp == 0)
+    atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
+  if (!__syncthreads_or(pl.sideU || pl.sideL))
+    return;
+  BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, Bp, p.G, 1u << lane };
+  bt_walk_tighten(p, src, Bp, wb, we, lane, pl, sink);
 }
 
 // After the rows phase: settle every (column, vector) marked in this round

@@ -16,6 +16,7 @@ constexpr int kTileRows = 256;     // rows per tile (one per thread)
 constexpr int kShortLen = 32;      // rows up to this length: one thread per row
 constexpr int kAlign = 16;         // tile starts are multiples of 16 entries (128 B of val)
 constexpr int kRoundCap = 1024;    // per-round counts kept on the device
+constexpr int kBtLongLen = 256;    // batch mode: longer rows get a whole CTA per (row, group)
 
 constexpr double kContRelThr = 1.0e-3;  // R8
 constexpr double kIntThr = 0.5;         // R8
@@ -131,21 +132,17 @@ __device__ __forceinline__ RowPlan plan_row(const RowAct &a, double rl, double r
 }
 
 // ---- R3 for one nonzero --------------------------------------------------
+// Branch-free: an infinite term enters the sum as a*0 (which leaves the sum
+// bit-for-bit unchanged, the sums never hold -0.0) and bumps its counter.
 __device__ __forceinline__ void accumulate(RowAct &r, double a, double lo, double hi, double INF)
 {
   const bool loInf = is_inf(lo, INF), hiInf = is_inf(hi, INF);
-  if (loInf)
-    ++r.infMin;
-  else
-    r.minAct = fma(a, lo, r.minAct);
-  if (hiInf)
-    ++r.infMax;
-  else
-    r.maxAct = fma(a, hi, r.maxAct);
-  if (!loInf && !hiInf) {
-    const double w = fabs(a) * (a > 0.0 ? hi - lo : lo - hi);
-    r.maxRange = fmax(r.maxRange, w);
-  }
+  r.infMin += loInf ? 1 : 0;
+  r.infMax += hiInf ? 1 : 0;
+  r.minAct = fma(a, loInf ? 0.0 : lo, r.minAct);
+  r.maxAct = fma(a, hiInf ? 0.0 : hi, r.maxAct);
+  const double w = fabs(a) * (a > 0.0 ? hi - lo : lo - hi);
+  r.maxRange = fmax(r.maxRange, (loInf || hiInf) ? 0.0 : w);
 }
 
 __device__ __forceinline__ void combine(RowAct &r, const RowAct &o)

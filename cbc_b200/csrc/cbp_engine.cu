@@ -66,6 +66,8 @@ struct cbp_matrix {
   LongRow *longRows = nullptr;
   signed char *colType = nullptr;
   int *singRows = nullptr;
+  int *shortRowsBt = nullptr, *longRowsBt = nullptr;
+  int nShortBt = 0, nLongBt = 0;
   int nTiles = 0, firstLongTile = 0, nLong = 0, nParts = 0, nSing = 0;
   // device, single-vector workspace
   RowAct *longPart = nullptr;
@@ -204,7 +206,8 @@ void cbp_matrix_free(cbp_matrix *mat)
     return;
   cudaSetDevice(mat->ctx->device);
   void *ptrs[] = { mat->val, mat->col, mat->tiles, mat->rp, mat->rowLB, mat->rowUB, mat->rowOrig,
-    mat->rowNz, mat->rowCnt, mat->longRows, mat->colType, mat->singRows, mat->longPart, mat->X[0],
+    mat->rowNz, mat->rowCnt, mat->longRows, mat->colType, mat->singRows, mat->shortRowsBt,
+    mat->longRowsBt, mat->longPart, mat->X[0],
     mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
     mat->bt.ints, mat->bt.counts, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
@@ -396,6 +399,13 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   up(&mat->longRows, hLong);
   up(&mat->colType, hType);
   up(&mat->singRows, hSing);
+  std::vector<int> hShortBt, hLongBt;
+  for (int r = 0; r < static_cast<int>(mKept); ++r)
+    (hCnt[r] > kBtLongLen ? hLongBt : hShortBt).push_back(r);
+  mat->nShortBt = static_cast<int>(hShortBt.size());
+  mat->nLongBt = static_cast<int>(hLongBt.size());
+  up(&mat->shortRowsBt, hShortBt);
+  up(&mat->longRowsBt, hLongBt);
   ok = ok && dalloc(&mat->longPart, nParts) == cudaSuccess;
   ok = ok && dalloc(&mat->X[0], n) == cudaSuccess && dalloc(&mat->X[1], n) == cudaSuccess;
   ok = ok && dalloc(&mat->dirty[0], mat->nWords) == cudaSuccess
@@ -714,6 +724,10 @@ static BtParams bt_params(cbp_matrix *mat, double tol)
   p.rowUB = mat->rowUB;
   p.rowOrig = mat->rowOrig;
   p.colType = mat->colType;
+  p.shortRowsBt = mat->shortRowsBt;
+  p.longRowsBt = mat->longRowsBt;
+  p.nShortBt = mat->nShortBt;
+  p.nLongBt = mat->nLongBt;
   p.mKept = mat->mKept;
   p.n = mat->n;
   p.Bp = bt.Bp;
@@ -842,8 +856,13 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   bt_prepass_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p);
   ++ctx->stats.kernelLaunches;
   CK(cudaGetLastError());
-  const long long warps = static_cast<long long>(bt.G) * mat->mKept;
+  const long long warps = static_cast<long long>(bt.G) * mat->nShortBt;
   const int rowsGrid = cdiv(warps, kWarps);
+  const long long longGrid = static_cast<long long>(bt.G) * mat->nLongBt;
+  if (longGrid > INT_MAX || warps / kWarps > INT_MAX) {
+    ctx->err = "cbp_batch_run: batch too large for one launch";
+    return CBP_ERR_ARG;
+  }
   const int wordGrid = cdiv(static_cast<long long>(words), 256);
   double roundKernelMs = 0.0;
   int roundKernelLaunches = 0;
@@ -857,6 +876,10 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     const int cur = round & 1;
     CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
     CK(cudaEventRecord(ctx->evPool[0], st));
+    if (longGrid > 0) {
+      bt_rows_long_kernel<<<static_cast<int>(longGrid), kThreads, 0, st>>>(p, cur);
+      ++ctx->stats.kernelLaunches;
+    }
     if (warps > 0) {
       bt_rows_kernel<<<rowsGrid, kThreads, 0, st>>>(p, cur);
       ++ctx->stats.kernelLaunches;
