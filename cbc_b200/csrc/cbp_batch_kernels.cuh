@@ -18,6 +18,7 @@ struct BtParams {
   const int *col;
   const int *rowNz;   // packed offset of each kept row
   const int *rowCnt;  // nonzeros of each kept row
+  const int *rowPos;  // rows longer than kBtLongLen: positive coefficients come first, this many
   const double *rowLB, *rowUB;
   const int *rowOrig;
   const signed char *colType;
@@ -53,67 +54,115 @@ struct BtSink {
   }
 };
 
-// The row walk of one warp over nonzeros [kb, ke): the 32 lanes fetch 32
-// (a, j) pairs with one coalesced load each, then every pair is broadcast by
-// shuffle and each lane gathers the bounds of ITS vector for that column (the
-// 32 lanes together read one 512-byte line).  Eight gathers are issued before
-// the first one is consumed.  Each lane accumulates in CSR order.
-__device__ __forceinline__ void bt_walk_sum(const BtParams &p, const Bnd *__restrict__ src, size_t Bp,
-  int kb, int ke, int lane, RowAct &ra)
+// One staged matrix entry: coefficient, column, integrality (16 bytes).
+struct __align__(16) Stg {
+  double a;
+  int j;
+  int isInt;
+};
+
+// R3 for one (nonzero, vector).  kNoInf: no bound of this batch is infinite
+// (checked when the batch is loaded; tightening never creates infinities), so
+// the counters stay zero and the tests disappear.  kSign: +1 / -1 when the
+// caller knows the sign of every coefficient in the range, 0 when mixed.
+template <bool kNoInf, int kSign>
+__device__ __forceinline__ void bt_acc(RowAct &ra, double a, const Bnd &x, double INF)
+{
+  const bool pos = kSign > 0 ? true : (kSign < 0 ? false : a > 0.0);
+  const double lo = pos ? x.lb : x.ub, hi = pos ? x.ub : x.lb;
+  if (kNoInf) {
+    ra.minAct = fma(a, lo, ra.minAct);
+    ra.maxAct = fma(a, hi, ra.maxAct);
+    const double w = fabs(a) * (x.ub - x.lb);
+    ra.maxRange = w > ra.maxRange ? w : ra.maxRange;
+  } else {
+    accumulate(ra, a, lo, hi, INF);
+  }
+}
+
+// The row walk of one warp over nonzeros [kb, ke).  Per block of 32 nonzeros
+// the lanes stage (a, j) in shared memory with one coalesced load each; then
+// every lane walks the block in CSR order, reading (a, j) as a shared-memory
+// broadcast and gathering the bounds of ITS vector for column j (the 32 lanes
+// together read one 512-byte line of the [column][vector] array).  Eight
+// gathers are in flight before the first is consumed.
+template <bool kNoInf, int kSign>
+__device__ __forceinline__ void bt_walk_sum(const BtParams &p, const char *__restrict__ src,
+  unsigned strideB, int kb, int ke, int lane, Stg *stg, RowAct &ra)
 {
   for (int base = kb; base < ke; base += 32) {
     const int k = base + lane;
-    const double myA = k < ke ? __ldg(&p.val[k]) : 0.0;
-    const int myC = k < ke ? __ldg(&p.col[k]) : 0;
+    __syncwarp();
+    if (k < ke) {
+      const int c = __ldg(&p.col[k]);
+      Stg e;
+      e.a = __ldg(&p.val[k]);
+      e.j = col_of(c);
+      e.isInt = col_is_int(c) ? 1 : 0;
+      stg[lane] = e;
+    }
+    __syncwarp();
+    const int cnt = min(32, ke - base);
+    if (cnt == 32) {
 #pragma unroll
-    for (int i0 = 0; i0 < 32; i0 += 8) {
-      if (base + i0 >= ke)
-        break;
-      Bnd x[8];
+      for (int i0 = 0; i0 < 32; i0 += 8) {
+        Bnd x[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int c = __shfl_sync(0xffffffffu, myC, i0 + u);
-        x[u] = ldcg_bnd(&src[static_cast<size_t>(col_of(c)) * Bp]);
+        for (int u = 0; u < 8; ++u)
+          x[u] = ldcg_bnd(reinterpret_cast<const Bnd *>(
+            src + static_cast<unsigned long long>(static_cast<unsigned>(stg[i0 + u].j)) * strideB));
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          bt_acc<kNoInf, kSign>(ra, stg[i0 + u].a, x[u], p.s.inf);
       }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const double a = __shfl_sync(0xffffffffu, myA, i0 + u);
-        if (a != 0.0)  // warp-uniform: only the padding past ke is zero
-          accumulate(ra, a, a > 0.0 ? x[u].lb : x[u].ub, a > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
+    } else {
+      for (int i = 0; i < cnt; ++i) {
+        const Bnd x = ldcg_bnd(reinterpret_cast<const Bnd *>(
+          src + static_cast<unsigned long long>(static_cast<unsigned>(stg[i].j)) * strideB));
+        bt_acc<kNoInf, kSign>(ra, stg[i].a, x, p.s.inf);
       }
     }
   }
 }
 
 // second walk, only for warps where some lane's row can tighten something
-__device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const Bnd *__restrict__ src, size_t Bp,
-  int kb, int ke, int lane, const RowPlan &pl, BtSink &sink)
+__device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const char *__restrict__ src,
+  unsigned strideB, int kb, int ke, int lane, Stg *stg, const RowPlan &pl, BtSink &sink)
 {
   const bool want = pl.sideU || pl.sideL;
   for (int base = kb; base < ke; base += 32) {
     const int k = base + lane;
-    const double myA = k < ke ? __ldg(&p.val[k]) : 0.0;
-    const int myC = k < ke ? __ldg(&p.col[k]) : 0;
+    __syncwarp();
+    if (k < ke) {
+      const int c = __ldg(&p.col[k]);
+      Stg e;
+      e.a = __ldg(&p.val[k]);
+      e.j = col_of(c);
+      e.isInt = col_is_int(c) ? 1 : 0;
+      stg[lane] = e;
+    }
+    __syncwarp();
     const int cnt = min(32, ke - base);
-    for (int i = 0; i < cnt; ++i) {
-      const double a = __shfl_sync(0xffffffffu, myA, i);
-      const int c = __shfl_sync(0xffffffffu, myC, i);
-      if (want) {
-        const int j = col_of(c);
-        const Bnd x = ldcg_bnd(&src[static_cast<size_t>(j) * Bp]);
-        tighten_nz(sink, pl, a, j, col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+    if (want) {
+      for (int i = 0; i < cnt; ++i) {
+        const Stg e = stg[i];
+        const Bnd x = ldcg_bnd(reinterpret_cast<const Bnd *>(
+          src + static_cast<unsigned long long>(static_cast<unsigned>(e.j)) * strideB));
+        tighten_nz(sink, pl, e.a, e.j, e.isInt != 0, e.a > 0.0 ? x.lb : x.ub, e.a > 0.0 ? x.ub : x.lb, p.s);
       }
     }
   }
 }
 
 // One round, rows phase, rows up to kBtLongLen nonzeros: a warp owns (row,
-// group of 32 vectors).  Work is group-major so that the warps running at the
-// same time share few vector groups and their bounds stay in L2.
+// group of 32 vectors) and sums in CSR order.  Work is group-major so that the
+// warps running at the same time share few vector groups.
+template <bool kNoInf>
 __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, int cur)
 {
+  __shared__ Stg stage[kWarps][32];
   const long long W = static_cast<long long>(blockIdx.x) * kWarps + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (W >= static_cast<long long>(p.G) * p.nShortBt)
     return;
   const int g = static_cast<int>(W / p.nShortBt), r = __ldg(&p.shortRowsBt[W % p.nShortBt]);
@@ -121,13 +170,13 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
   if (act == 0u)
     return;
   const bool mine = (act >> lane) & 1u;
-  const size_t Bp = static_cast<size_t>(p.Bp);
   const int b = g * 32 + lane;
-  const Bnd *__restrict__ src = p.X[cur] + b;
+  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + b);
+  const unsigned strideB = static_cast<unsigned>(p.Bp) * static_cast<unsigned>(sizeof(Bnd));
   const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
 
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-  bt_walk_sum(p, src, Bp, kb, ke, lane, ra);
+  bt_walk_sum<kNoInf, 0>(p, src, strideB, kb, ke, lane, stage[warp], ra);
   RowPlan pl = plan_row(ra, __ldg(&p.rowLB[r]), __ldg(&p.rowUB[r]), p.s);
   if (!mine) {
     pl.infeasible = false;
@@ -138,33 +187,38 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
     atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
   if (!__any_sync(0xffffffffu, pl.sideU || pl.sideL))
     return;
-  BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, Bp, p.G, 1u << lane };
-  bt_walk_tighten(p, src, Bp, kb, ke, lane, pl, sink);
+  BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, static_cast<size_t>(p.Bp), p.G, 1u << lane };
+  bt_walk_tighten(p, src, strideB, kb, ke, lane, stage[warp], pl, sink);
 }
 
 // Rows longer than kBtLongLen: a CTA owns (row, group); its 8 warps split the
 // row into 8 contiguous pieces, the partial activities are combined in warp
 // order through shared memory.  With a whole CTA per row the CTAs in flight
-// cover only one or two vector groups, whose bounds (n x 512 B each) then fit
-// in L2 across all the rows that use them.
+// cover only one or two vector groups, whose bounds (n x 512 B each) then stay
+// in L2 across all the rows that use them.  Such rows are stored with their
+// positive coefficients first (rowPos of them), so no per-nonzero sign test.
+template <bool kNoInf>
 __global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParams p, int cur)
 {
   __shared__ RowAct red[kWarps][32];
+  __shared__ Stg stage[kWarps][32];
   const int g = blockIdx.x / p.nLongBt, r = __ldg(&p.longRowsBt[blockIdx.x % p.nLongBt]);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned act = __ldg(&p.active[g]);
   if (act == 0u)
     return;
   const bool mine = (act >> lane) & 1u;
-  const size_t Bp = static_cast<size_t>(p.Bp);
   const int b = g * 32 + lane;
-  const Bnd *__restrict__ src = p.X[cur] + b;
+  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + b);
+  const unsigned strideB = static_cast<unsigned>(p.Bp) * static_cast<unsigned>(sizeof(Bnd));
   const int kb = __ldg(&p.rowNz[r]), cnt = __ldg(&p.rowCnt[r]);
+  const int ksplit = kb + __ldg(&p.rowPos[r]);              // first negative coefficient
   const int per = ((cnt + kWarps - 1) / kWarps + 31) & ~31;  // 32-aligned pieces
   const int wb = min(kb + warp * per, kb + cnt), we = min(wb + per, kb + cnt);
 
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-  bt_walk_sum(p, src, Bp, wb, we, lane, ra);
+  bt_walk_sum<kNoInf, 1>(p, src, strideB, wb, min(we, max(wb, ksplit)), lane, stage[warp], ra);
+  bt_walk_sum<kNoInf, -1>(p, src, strideB, max(wb, min(we, ksplit)), we, lane, stage[warp], ra);
   red[warp][lane] = ra;
   __syncthreads();
   RowAct tot = red[0][lane];
@@ -181,8 +235,8 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParam
     atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
   if (!__syncthreads_or(pl.sideU || pl.sideL))
     return;
-  BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, Bp, p.G, 1u << lane };
-  bt_walk_tighten(p, src, Bp, wb, we, lane, pl, sink);
+  BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, static_cast<size_t>(p.Bp), p.G, 1u << lane };
+  bt_walk_tighten(p, src, strideB, wb, we, lane, stage[warp], pl, sink);
 }
 
 // After the rows phase: settle every (column, vector) marked in this round

@@ -11,9 +11,10 @@ namespace cbp {
 
 constexpr int kThreads = 256;      // threads per CTA of the streaming kernels
 constexpr int kWarps = kThreads / 32;
-constexpr int kTileNnz = 2048;     // nonzeros staged per tile (24 KB of val+col)
+constexpr int kTileNnz = 1024;     // nonzeros staged per tile (12 KB of val+col per stage)
 constexpr int kTileRows = 256;     // rows per tile (one per thread)
-constexpr int kShortLen = 32;      // rows up to this length: one thread per row
+constexpr int kShortLen = 32;      // rows up to this length: one thread per row (sliced-ELL)
+constexpr int kSellWindow = 4096;  // short rows are sorted by length inside windows of this many rows
 constexpr int kAlign = 16;         // tile starts are multiples of 16 entries (128 B of val)
 constexpr int kRoundCap = 1024;    // per-round counts kept on the device
 constexpr int kBtLongLen = 256;    // batch mode: longer rows get a whole CTA per (row, group)

@@ -47,6 +47,7 @@ struct BatchState {
   double *dBnd = nullptr;
   long long nDelta = 0;
   bool loaded = false, denseLoaded = false, consumed = false;
+  bool hasInf = true;  // some input bound may be infinite (false only when checked)
   size_t capCells = 0, capDelta = 0;
   int capBp = 0;
 };
@@ -62,13 +63,16 @@ struct cbp_matrix {
   Tile *tiles = nullptr;
   int *rp = nullptr;
   double *rowLB = nullptr, *rowUB = nullptr;
-  int *rowOrig = nullptr, *rowNz = nullptr, *rowCnt = nullptr;
+  int *rowOrig = nullptr, *rowNz = nullptr, *rowCnt = nullptr, *rowPos = nullptr;
   LongRow *longRows = nullptr;
   signed char *colType = nullptr;
   int *singRows = nullptr;
   int *shortRowsBt = nullptr, *longRowsBt = nullptr;
   int nShortBt = 0, nLongBt = 0;
   int nTiles = 0, firstLongTile = 0, nLong = 0, nParts = 0, nSing = 0;
+  double *sellVal = nullptr;
+  int *sellCol = nullptr, *sellOff = nullptr;
+  int nSlices = 0, mShort = 0;
   // device, single-vector workspace
   RowAct *longPart = nullptr;
   Bnd *X[2] = { nullptr, nullptr };
@@ -206,8 +210,8 @@ void cbp_matrix_free(cbp_matrix *mat)
     return;
   cudaSetDevice(mat->ctx->device);
   void *ptrs[] = { mat->val, mat->col, mat->tiles, mat->rp, mat->rowLB, mat->rowUB, mat->rowOrig,
-    mat->rowNz, mat->rowCnt, mat->longRows, mat->colType, mat->singRows, mat->shortRowsBt,
-    mat->longRowsBt, mat->longPart, mat->X[0],
+    mat->rowNz, mat->rowCnt, mat->rowPos, mat->longRows, mat->colType, mat->singRows, mat->shortRowsBt,
+    mat->longRowsBt, mat->sellVal, mat->sellCol, mat->sellOff, mat->longPart, mat->X[0],
     mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
     mat->bt.ints, mat->bt.counts, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
@@ -270,7 +274,7 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     return nullptr;
   }
   std::vector<double> hVal, hRl(mKept), hRu(mKept);
-  std::vector<int> hCol, hRp, hOrig(mKept), hNz(mKept), hCnt(mKept), hSing;
+  std::vector<int> hCol, hRp, hOrig(mKept), hNz(mKept), hCnt(mKept), hPos(mKept, 0), hSing;
   std::vector<Tile> hTiles;
   std::vector<LongRow> hLong;
   hVal.reserve(nnzKept + nnzKept / 64 + 64);
@@ -288,17 +292,59 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     hNz[keptIdx] = static_cast<int>(hVal.size());
     hCnt[keptIdx] = kr.cnt;
     const int64_t s = rowStart[kr.orig], e = rowLen ? s + rowLen[kr.orig] : rowStart[kr.orig + 1];
-    for (int64_t k = s; k < e; ++k)
-      if (val[k] != 0.0) {
+    // rows longer than kBtLongLen are summed piecewise anyway (no CSR-order
+    // promise), so they are stored positives first: two passes over the row
+    const int passes = kr.cnt > kBtLongLen ? 2 : 1;
+    for (int pass = 0; pass < passes; ++pass) {
+      for (int64_t k = s; k < e; ++k) {
+        if (val[k] == 0.0 || (passes == 2 && (val[k] > 0.0) != (pass == 0)))
+          continue;
         hVal.push_back(val[k]);
         const bool isInt = colType && colType[colIdx[k]] != 0;
         hCol.push_back(isInt ? (colIdx[k] | INT_MIN) : colIdx[k]);  // bit 31 = integer column
       }
+      if (pass == 0 && passes == 2)
+        hPos[keptIdx] = static_cast<int>(hVal.size()) - hNz[keptIdx];
+    }
     if (kr.cnt == 1)
       hSing.push_back(keptIdx);
   };
   int kept = 0;
-  for (int c = 0; c < 2; ++c) {  // short, then medium rows: greedy tiles of whole rows
+  // short rows: sorted by length inside windows (little padding in the slices,
+  // the caller's order survives at window scale), stored once in packed CSR
+  // form (batch kernels, phase 1) and once as sliced-ELL (single-vector loop)
+  std::vector<double> hSellVal;
+  std::vector<int> hSellCol, hSellOff;
+  {
+    std::vector<KRow> &rows = cls[kShort];
+    for (size_t w = 0; w < rows.size(); w += kSellWindow) {
+      const size_t e = std::min(rows.size(), w + kSellWindow);
+      std::stable_sort(rows.begin() + w, rows.begin() + e,
+        [](const KRow &a, const KRow &b) { return a.cnt > b.cnt; });
+    }
+    for (const KRow &kr : rows)
+      emit_row(kr, kept++);
+    const int mS = static_cast<int>(rows.size());
+    const int nSlices = (mS + 31) / 32;
+    hSellOff.assign(nSlices + 1, 0);
+    for (int sl = 0; sl < nSlices; ++sl) {
+      int len = 0;
+      for (int r = sl * 32; r < std::min(mS, sl * 32 + 32); ++r)
+        len = std::max(len, hCnt[r]);
+      hSellOff[sl + 1] = hSellOff[sl] + 32 * len;
+    }
+    hSellVal.assign(static_cast<size_t>(hSellOff[nSlices]) + 32, 0.0);
+    hSellCol.assign(static_cast<size_t>(hSellOff[nSlices]) + 32, 0);
+    for (int r = 0; r < mS; ++r) {
+      const size_t base = static_cast<size_t>(hSellOff[r >> 5]) + (r & 31);
+      for (int k = 0; k < hCnt[r]; ++k) {
+        hSellVal[base + 32 * static_cast<size_t>(k)] = hVal[hNz[r] + k];
+        hSellCol[base + 32 * static_cast<size_t>(k)] = hCol[hNz[r] + k];
+      }
+    }
+  }
+  {  // medium rows: greedy tiles of whole rows, staged through shared memory
+    const int c = kMedium;
     size_t i = 0;
     const std::vector<KRow> &rows = cls[c];
     while (i < rows.size()) {
@@ -396,9 +442,15 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   up(&mat->rowOrig, hOrig);
   up(&mat->rowNz, hNz);
   up(&mat->rowCnt, hCnt);
+  up(&mat->rowPos, hPos);
   up(&mat->longRows, hLong);
   up(&mat->colType, hType);
   up(&mat->singRows, hSing);
+  up(&mat->sellVal, hSellVal);
+  up(&mat->sellCol, hSellCol);
+  up(&mat->sellOff, hSellOff);
+  mat->nSlices = static_cast<int>(hSellOff.size()) - 1;
+  mat->mShort = static_cast<int>(cls[kShort].size());
   std::vector<int> hShortBt, hLongBt;
   for (int r = 0; r < static_cast<int>(mKept); ++r)
     (hCnt[r] > kBtLongLen ? hLongBt : hShortBt).push_back(r);
@@ -565,6 +617,11 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   p.firstLongTile = mat->firstLongTile;
   p.nLong = mat->nLong;
   p.n = n;
+  p.sellVal = mat->sellVal;
+  p.sellCol = mat->sellCol;
+  p.sellOff = mat->sellOff;
+  p.nSlices = mat->nSlices;
+  p.mShort = mat->mShort;
   p.X[0] = mat->X[0];
   p.X[1] = mat->X[1];
   p.dirty[0] = mat->dirty[0];
@@ -575,7 +632,7 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   p.maxRounds = maxRounds;
   p.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
   const int maxGrid = ctx->svBlocksPerSM * ctx->numSMs;
-  const int want = std::max(mat->nTiles, cdiv(mat->nWords, kThreads));
+  const int want = std::max(std::max(mat->nTiles, cdiv(mat->nSlices, kWarps)), cdiv(mat->nWords, kThreads));
   const int grid = std::max(1, std::min(maxGrid, want));
   void *args[] = { &p };
   cudaEvent_t k0, k1;
@@ -720,6 +777,7 @@ static BtParams bt_params(cbp_matrix *mat, double tol)
   p.col = mat->col;
   p.rowNz = mat->rowNz;
   p.rowCnt = mat->rowCnt;
+  p.rowPos = mat->rowPos;
   p.rowLB = mat->rowLB;
   p.rowUB = mat->rowUB;
   p.rowOrig = mat->rowOrig;
@@ -801,6 +859,16 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
   bt.loaded = true;
   bt.denseLoaded = false;
   bt.consumed = false;
+  // Are all input bounds finite?  Then the rows kernels drop their infinity tests.
+  bt.hasInf = true;
+  if (!(flags & CBP_FLAG_DEVICE_PTRS)) {
+    bool any = false;
+    for (int j = 0; j < mat->n && !any; ++j)
+      any = !(std::fabs(baseLb[j]) < mat->inf) || !(std::fabs(baseUb[j]) < mat->inf);
+    for (long long k = 0; k < nDelta && !any; ++k)
+      any = !(std::fabs(deltaBound[k]) < mat->inf);
+    bt.hasInf = any;
+  }
   return CBP_OK;
 }
 
@@ -877,11 +945,17 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
     CK(cudaEventRecord(ctx->evPool[0], st));
     if (longGrid > 0) {
-      bt_rows_long_kernel<<<static_cast<int>(longGrid), kThreads, 0, st>>>(p, cur);
+      if (bt.hasInf)
+        bt_rows_long_kernel<false><<<static_cast<int>(longGrid), kThreads, 0, st>>>(p, cur);
+      else
+        bt_rows_long_kernel<true><<<static_cast<int>(longGrid), kThreads, 0, st>>>(p, cur);
       ++ctx->stats.kernelLaunches;
     }
     if (warps > 0) {
-      bt_rows_kernel<<<rowsGrid, kThreads, 0, st>>>(p, cur);
+      if (bt.hasInf)
+        bt_rows_kernel<false><<<rowsGrid, kThreads, 0, st>>>(p, cur);
+      else
+        bt_rows_kernel<true><<<rowsGrid, kThreads, 0, st>>>(p, cur);
       ++ctx->stats.kernelLaunches;
     }
     CK(cudaEventRecord(ctx->evPool[1], st));
@@ -1105,6 +1179,7 @@ int cbp_propagate_batch(cbp_matrix *mat, int B, double *lb, double *ub, double p
   bt.loaded = true;
   bt.denseLoaded = true;
   bt.consumed = false;
+  bt.hasInf = true;
   rc = cbp_batch_run(mat, primalTol, maxRounds, timeLimitSec);
   if (rc == CBP_OK)
     rc = bt_fetch_results(mat, out, dev);

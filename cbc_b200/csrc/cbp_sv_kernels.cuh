@@ -41,6 +41,12 @@ struct SvParams {
   const signed char *colType;
   RowAct *longPart;  // scratch: one partial per long-row chunk
   int nTiles, firstLongTile, nLong, n;
+  // short rows (<= kShortLen nonzeros) in sliced-ELL form: slice s holds rows
+  // 32s .. 32s+31 (kept order), entry k of lane l at sellOff[s] + 32k + l
+  const double *sellVal;
+  const int *sellCol;
+  const int *sellOff;  // nSlices + 1
+  int nSlices, mShort;
   // state
   Bnd *X[2];
   unsigned *dirty[2];
@@ -149,37 +155,13 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
     if (T.kind != kLong)
       for (int i = tid; i <= T.rowCount; i += kThreads)
         sm.rp[i] = p.rp[T.rpOff + i];
-    double rl = 0.0, ru = 0.0;  // short rows: fetched now, used after the walk
-    if (T.kind == kShort && tid < T.rowCount) {
-      rl = p.rowLB[T.rowBegin + tid];
-      ru = p.rowUB[T.rowBegin + tid];
-    }
     mbar_wait(&sm.bar[stage], parity[stage]);
     parity[stage] ^= 1u;
     sv_gather(sm, sm.lohi, stage, T.nzCount, src);
     __syncthreads();
     const double *val = sm.val[stage];
     const int *col = sm.col[stage];
-    if (T.kind == kShort) {
-      if (tid < T.rowCount) {
-        const int kb = sm.rp[tid], ke = sm.rp[tid + 1];
-        RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-        for (int k = kb; k < ke; ++k) {
-          const double2 lh = sm.lohi[k];
-          accumulate(ra, val[k], lh.x, lh.y, p.s.inf);
-        }
-        const int row = T.rowBegin + tid;
-        const RowPlan pl = plan_row(ra, rl, ru, p.s);
-        if (pl.infeasible)
-          sv_flag_row(p, row);
-        if (pl.sideU || pl.sideL) {
-          for (int k = kb; k < ke; ++k) {
-            const double2 lh = sm.lohi[k];
-            tighten_nz(sink, pl, val[k], col_of(col[k]), col_is_int(col[k]), lh.x, lh.y, p.s);
-          }
-        }
-      }
-    } else if (T.kind == kMedium) {
+    if (T.kind == kMedium) {
       for (int r = warp; r < T.rowCount; r += kWarps) {
         const int kb = sm.rp[r], ke = sm.rp[r + 1];
         RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
@@ -236,7 +218,84 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 2) sv_fixpoint_kernel(const SvParams p)
+// Short rows: one thread per row over the sliced-ELL copy.  The 32 lanes of a
+// warp read 32 consecutive entries per step (coalesced), every lane walks ITS
+// row in CSR order with the sums in registers — the order of the CPU
+// restatement, so these rows agree with it bit for bit.  No shared memory, no
+// block barrier; four gathers per lane are in flight.
+__device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink)
+{
+  const int lane = threadIdx.x & 31;
+  const int gw = blockIdx.x * kWarps + (threadIdx.x >> 5), nw = gridDim.x * kWarps;
+  for (int s = gw; s < p.nSlices; s += nw) {
+    const int off = __ldg(&p.sellOff[s]);
+    const int len = (__ldg(&p.sellOff[s + 1]) - off) >> 5;
+    const int row = (s << 5) + lane;
+    const bool valid = row < p.mShort;
+    const double rl = valid ? __ldg(&p.rowLB[row]) : 0.0, ru = valid ? __ldg(&p.rowUB[row]) : 0.0;
+    const double *__restrict__ v = p.sellVal + off + lane;
+    const int *__restrict__ c = p.sellCol + off + lane;
+    RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+    for (int k = 0; k < len; k += 4) {
+      double a[4];
+      Bnd x[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        a[u] = 0.0;
+        int cj = 0;
+        if (k + u < len) {
+          a[u] = __ldg(&v[(k + u) << 5]);
+          cj = __ldg(&c[(k + u) << 5]);
+        }
+        x[u].lb = 0.0;
+        x[u].ub = 0.0;
+        if (a[u] != 0.0)
+          x[u] = ldcg_bnd(&src[col_of(cj)]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)  // padding has a == 0 and bounds 0: it leaves every field untouched
+        accumulate(ra, a[u], a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
+    }
+    RowPlan pl = plan_row(ra, rl, ru, p.s);
+    if (!valid) {
+      pl.infeasible = false;
+      pl.sideU = false;
+      pl.sideL = false;
+    }
+    if (pl.infeasible)
+      sv_flag_row(p, row);
+    // Second pass, one row at a time and nonzero-parallel: the lanes of the
+    // warp take the (<= 32) nonzeros of each row that may tighten something;
+    // that row's plan is broadcast by shuffle.  Rows that cannot tighten cost
+    // nothing here, however many of them share the warp.
+    unsigned todo = __ballot_sync(0xffffffffu, pl.sideU || pl.sideL);
+    const int packed = min(pl.infMin, 2) | (min(pl.infMax, 2) << 2) | (pl.sideU ? 16 : 0) | (pl.sideL ? 32 : 0);
+    while (todo) {
+      const int owner = __ffs(todo) - 1;
+      todo &= todo - 1;
+      RowPlan q;
+      q.slackU = __shfl_sync(0xffffffffu, pl.slackU, owner);
+      q.slackL = __shfl_sync(0xffffffffu, pl.slackL, owner);
+      const int pk = __shfl_sync(0xffffffffu, packed, owner);
+      q.infMin = pk & 3;
+      q.infMax = (pk >> 2) & 3;
+      q.sideU = (pk & 16) != 0;
+      q.sideL = (pk & 32) != 0;
+      q.infeasible = false;
+      if (lane < len) {
+        const int at = off + (lane << 5) + owner;
+        const double a = __ldg(&p.sellVal[at]);
+        if (a != 0.0) {
+          const int cj = __ldg(&p.sellCol[at]);
+          const Bnd x = ldcg_bnd(&src[col_of(cj)]);
+          tighten_nz(sink, q, a, col_of(cj), col_is_int(cj), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 3) sv_fixpoint_kernel(const SvParams p)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SvSmem &sm = *reinterpret_cast<SvSmem *>(smem_raw);
@@ -292,7 +351,8 @@ __global__ void __launch_bounds__(kThreads, 2) sv_fixpoint_kernel(const SvParams
         }
       }
     }
-    // A2: stream the matrix
+    // A2: stream the matrix: short rows from the sliced-ELL copy, the rest as TMA-staged tiles
+    sv_short_rows(p, src, sink);
     sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
     grid.sync();
     if (p.nLong > 0) {

@@ -206,6 +206,27 @@ def test_batch_probe_mixed(oracle, gpu_ctx):
     _check_batch(oracle, gpu_ctx, inst, s, v, b, "probes maxRounds=3", max_rounds=3)
 
 
+def test_batch_long_rows_mixed_signs(oracle, gpu_ctx):
+    # rows far longer than a warp's block, 15% negative coefficients, continuous + integer columns
+    inst = I.power_law(n=20000, nnz_target=150000, n_dense=3, dense_len=6000, max_len=2500, seed=46)
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 40, max_depth=30, seed=47)
+    res = _check_batch(oracle, gpu_ctx, inst, s, v, b, "long rows")
+    assert res["nChanged"].sum() > 0
+
+
+def test_batch_base_needs_rounding(oracle, gpu_ctx):
+    # base bounds of integer columns are fractional: every vector starts with R11 changes
+    inst = I.knapsack_assignment(m=600, n=1500, seed=48)
+    inst.colType = inst.colType.copy()
+    inst.colType[::3] = 2
+    inst.ub = inst.ub.copy()
+    inst.ub[::3] = 1.6
+    inst.lb = inst.lb.copy()
+    inst.lb[1::7] = -0.3
+    s, v, b = I.dive_deltas(inst, np.ceil(inst.lb - 1e-7), np.floor(inst.ub + 1e-7), 33, max_depth=20, seed=49)
+    _check_batch(oracle, gpu_ctx, inst, s, v, b, "fractional base")
+
+
 def test_fixpoint_is_idempotent_at_size(gpu_ctx):
     """Size-independent property on a larger instance: propagating a fixpoint again changes nothing
     and takes exactly one round; the planted point survives."""
