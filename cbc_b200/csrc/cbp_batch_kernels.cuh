@@ -63,20 +63,21 @@ struct __align__(16) Stg {
 
 // R3 for one (nonzero, vector).  kNoInf: no bound of this batch is infinite
 // (checked when the batch is loaded; tightening never creates infinities), so
-// the counters stay zero and the tests disappear.  kSign: +1 / -1 when the
+// the counters stay zero and the tests disappear.  kAllInt (walk): the matrix
+// has no continuous column, so useful_range is the plain range.  kSign: +1 / -1 when the
 // caller knows the sign of every coefficient in the range, 0 when mixed.
 template <bool kNoInf, int kSign>
-__device__ __forceinline__ void bt_acc(RowAct &ra, double a, const Bnd &x, double INF)
+__device__ __forceinline__ void bt_acc(RowAct &ra, double a, bool isInt, const Bnd &x, double INF)
 {
   const bool pos = kSign > 0 ? true : (kSign < 0 ? false : a > 0.0);
   const double lo = pos ? x.lb : x.ub, hi = pos ? x.ub : x.lb;
   if (kNoInf) {
     ra.minAct = fma(a, lo, ra.minAct);
     ra.maxAct = fma(a, hi, ra.maxAct);
-    const double w = fabs(a) * (x.ub - x.lb);
+    const double w = fabs(a) * useful_range(x.ub - x.lb, isInt);
     ra.maxRange = w > ra.maxRange ? w : ra.maxRange;
   } else {
-    accumulate(ra, a, lo, hi, INF);
+    accumulate(ra, a, isInt, lo, hi, INF);
   }
 }
 
@@ -86,7 +87,7 @@ __device__ __forceinline__ void bt_acc(RowAct &ra, double a, const Bnd &x, doubl
 // broadcast and gathering the bounds of ITS vector for column j (the 32 lanes
 // together read one 512-byte line of the [column][vector] array).  Eight
 // gathers are in flight before the first is consumed.
-template <bool kNoInf, int kSign>
+template <bool kNoInf, int kSign, bool kAllInt>
 __device__ __forceinline__ void bt_walk_sum(const BtParams &p, const char *__restrict__ src,
   unsigned strideB, int kb, int ke, int lane, Stg *stg, RowAct &ra)
 {
@@ -113,13 +114,13 @@ __device__ __forceinline__ void bt_walk_sum(const BtParams &p, const char *__res
             src + static_cast<unsigned long long>(static_cast<unsigned>(stg[i0 + u].j)) * strideB));
 #pragma unroll
         for (int u = 0; u < 8; ++u)
-          bt_acc<kNoInf, kSign>(ra, stg[i0 + u].a, x[u], p.s.inf);
+          bt_acc<kNoInf, kSign>(ra, stg[i0 + u].a, kAllInt ? true : stg[i0 + u].isInt != 0, x[u], p.s.inf);
       }
     } else {
       for (int i = 0; i < cnt; ++i) {
         const Bnd x = ldcg_bnd(reinterpret_cast<const Bnd *>(
           src + static_cast<unsigned long long>(static_cast<unsigned>(stg[i].j)) * strideB));
-        bt_acc<kNoInf, kSign>(ra, stg[i].a, x, p.s.inf);
+        bt_acc<kNoInf, kSign>(ra, stg[i].a, kAllInt ? true : stg[i].isInt != 0, x, p.s.inf);
       }
     }
   }
@@ -157,7 +158,7 @@ __device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const char *_
 // One round, rows phase, rows up to kBtLongLen nonzeros: a warp owns (row,
 // group of 32 vectors) and sums in CSR order.  Work is group-major so that the
 // warps running at the same time share few vector groups.
-template <bool kNoInf>
+template <bool kNoInf, bool kAllInt>
 __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, int cur)
 {
   __shared__ Stg stage[kWarps][32];
@@ -176,7 +177,7 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
   const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
 
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-  bt_walk_sum<kNoInf, 0>(p, src, strideB, kb, ke, lane, stage[warp], ra);
+  bt_walk_sum<kNoInf, 0, kAllInt>(p, src, strideB, kb, ke, lane, stage[warp], ra);
   RowPlan pl = plan_row(ra, __ldg(&p.rowLB[r]), __ldg(&p.rowUB[r]), p.s);
   if (!mine) {
     pl.infeasible = false;
@@ -197,7 +198,7 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
 // cover only one or two vector groups, whose bounds (n x 512 B each) then stay
 // in L2 across all the rows that use them.  Such rows are stored with their
 // positive coefficients first (rowPos of them), so no per-nonzero sign test.
-template <bool kNoInf>
+template <bool kNoInf, bool kAllInt>
 __global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParams p, int cur)
 {
   __shared__ RowAct red[kWarps][32];
@@ -217,8 +218,8 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParam
   const int wb = min(kb + warp * per, kb + cnt), we = min(wb + per, kb + cnt);
 
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-  bt_walk_sum<kNoInf, 1>(p, src, strideB, wb, min(we, max(wb, ksplit)), lane, stage[warp], ra);
-  bt_walk_sum<kNoInf, -1>(p, src, strideB, max(wb, min(we, ksplit)), we, lane, stage[warp], ra);
+  bt_walk_sum<kNoInf, 1, kAllInt>(p, src, strideB, wb, min(we, max(wb, ksplit)), lane, stage[warp], ra);
+  bt_walk_sum<kNoInf, -1, kAllInt>(p, src, strideB, max(wb, min(we, ksplit)), we, lane, stage[warp], ra);
   red[warp][lane] = ra;
   __syncthreads();
   RowAct tot = red[0][lane];

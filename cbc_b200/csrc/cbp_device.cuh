@@ -120,7 +120,7 @@ __device__ __forceinline__ RowPlan plan_row(const RowAct &a, double rl, double r
   p.infMin = a.infMin;
   p.infMax = a.infMax;
   // Row-level shortcut, exact: with only finite ranges a candidate passes the
-  // per-nonzero pre-check of R6 only if slack < |a|(ub-lb) <= maxRange.
+  // per-nonzero pre-check of R6 only if slack < |a| * useful_range <= maxRange.
   if (a.infMin + a.infMax == 0) {
     p.sideU = p.sideU && p.slackU < a.maxRange;
     p.sideL = p.sideL && p.slackL < a.maxRange;
@@ -132,18 +132,28 @@ __device__ __forceinline__ RowPlan plan_row(const RowAct &a, double rl, double r
   return p;
 }
 
+// R6: the part of a column's range that a candidate must undercut to be
+// accepted by R8 (integer: the whole range; continuous: range minus the
+// smallest accepted step).
+__device__ __forceinline__ double useful_range(double width, bool isInt)
+{
+  return isInt ? width : width - kContRelThr * fmax(1.0, width);
+}
+
 // ---- R3 for one nonzero --------------------------------------------------
 // Branch-free: an infinite term enters the sum as a*0 (which leaves the sum
 // bit-for-bit unchanged, the sums never hold -0.0) and bumps its counter.
-__device__ __forceinline__ void accumulate(RowAct &r, double a, double lo, double hi, double INF)
+// maxRange collects max |a| * useful_range for the row-level shortcut.
+__device__ __forceinline__ void accumulate(RowAct &r, double a, bool isInt, double lo, double hi, double INF)
 {
   const bool loInf = is_inf(lo, INF), hiInf = is_inf(hi, INF);
   r.infMin += loInf ? 1 : 0;
   r.infMax += hiInf ? 1 : 0;
   r.minAct = fma(a, loInf ? 0.0 : lo, r.minAct);
   r.maxAct = fma(a, hiInf ? 0.0 : hi, r.maxAct);
-  const double w = fabs(a) * (a > 0.0 ? hi - lo : lo - hi);
-  r.maxRange = fmax(r.maxRange, (loInf || hiInf) ? 0.0 : w);
+  const double w = fabs(a) * useful_range(a > 0.0 ? hi - lo : lo - hi, isInt);
+  const double wf = (loInf || hiInf) ? 0.0 : w;
+  r.maxRange = wf > r.maxRange ? wf : r.maxRange;
 }
 
 __device__ __forceinline__ void combine(RowAct &r, const RowAct &o)
@@ -159,7 +169,8 @@ __device__ __forceinline__ void combine(RowAct &r, const RowAct &o)
 // Sink must provide  void ub(int j, double v)  and  void lb(int j, double v)
 // which publish an ACCEPTED candidate (atomic min / max + dirty mark).
 template <class Sink>
-__device__ __forceinline__ void offer_ub(Sink &sink, int j, double v, double old, bool isInt, const Scal &s)
+__device__ __forceinline__ void offer_ub(Sink &sink, int j, double v, double old, double other, bool isInt,
+  const Scal &s)
 {
   if (isInt)
     v = floor(v + s.tol);
@@ -167,7 +178,7 @@ __device__ __forceinline__ void offer_ub(Sink &sink, int j, double v, double old
   if (!(fabs(v) < s.inf))
     return;
   if (fabs(old) < s.inf) {
-    const double thr = isInt ? kIntThr : kContRelThr * fmax(1.0, fabs(old));
+    const double thr = isInt ? kIntThr : kContRelThr * fmax(1.0, fabs(other) < s.inf ? old - other : fabs(old));
     if (!(v < old - thr))
       return;
   } else if (!(v < old)) {
@@ -177,7 +188,8 @@ __device__ __forceinline__ void offer_ub(Sink &sink, int j, double v, double old
 }
 
 template <class Sink>
-__device__ __forceinline__ void offer_lb(Sink &sink, int j, double v, double old, bool isInt, const Scal &s)
+__device__ __forceinline__ void offer_lb(Sink &sink, int j, double v, double old, double other, bool isInt,
+  const Scal &s)
 {
   if (isInt)
     v = ceil(v - s.tol);
@@ -185,7 +197,7 @@ __device__ __forceinline__ void offer_lb(Sink &sink, int j, double v, double old
   if (!(fabs(v) < s.inf))
     return;
   if (fabs(old) < s.inf) {
-    const double thr = isInt ? kIntThr : kContRelThr * fmax(1.0, fabs(old));
+    const double thr = isInt ? kIntThr : kContRelThr * fmax(1.0, fabs(other) < s.inf ? other - old : fabs(old));
     if (!(v > old + thr))
       return;
   } else if (!(v > old)) {
@@ -201,7 +213,7 @@ __device__ __forceinline__ void tighten_nz(Sink &sink, const RowPlan &p, double 
   const bool loInf = is_inf(lo, s.inf), hiInf = is_inf(hi, s.inf);
   const bool finite = !loInf && !hiInf;
   const double l = a > 0.0 ? lo : hi, u = a > 0.0 ? hi : lo;
-  const double w = finite ? fabs(a) * (u - l) : 0.0;
+  const double w = finite ? fabs(a) * useful_range(u - l, isInt) : 0.0;
   bool wantU = false, wantL = false;
   double vU = 0.0, vL = 0.0;
   if (p.sideU) {
@@ -230,15 +242,15 @@ __device__ __forceinline__ void tighten_nz(Sink &sink, const RowPlan &p, double 
     return;
   if (wantU) {  // rowUB side: a>0 bounds x from above, a<0 from below
     if (a > 0.0)
-      offer_ub(sink, j, vU, u, isInt, s);
+      offer_ub(sink, j, vU, u, l, isInt, s);
     else
-      offer_lb(sink, j, vU, l, isInt, s);
+      offer_lb(sink, j, vU, l, u, isInt, s);
   }
   if (wantL) {
     if (a > 0.0)
-      offer_lb(sink, j, vL, l, isInt, s);
+      offer_lb(sink, j, vL, l, u, isInt, s);
     else
-      offer_ub(sink, j, vL, u, isInt, s);
+      offer_ub(sink, j, vL, u, l, isInt, s);
   }
 }
 

@@ -25,7 +25,8 @@ struct cbp_ctx {
   cudaStream_t stream = nullptr;
   bool ownsStream = false;
   int numSMs = 0;
-  int svBlocksPerSM = 0;
+  int svBlocksPerSM = 0;       // persistent kernel with tile staging
+  int svBlocksPerSMNoTiles = 0;  // ... for matrices with short rows only
   std::string err;
   cbp_stats stats {};
   cudaEvent_t evA = nullptr, evB = nullptr;
@@ -57,6 +58,7 @@ struct cbp_matrix {
   int m = 0, n = 0, mKept = 0;
   long long nnz = 0, nnzPacked = 0;
   double inf = 1e30;
+  bool allInt = false;  // no continuous column
   // device, matrix
   double *val = nullptr;
   int *col = nullptr;
@@ -95,6 +97,8 @@ struct cbp_matrix {
   } while (0)
 
 static thread_local std::string g_createErr;
+
+static constexpr size_t kSvSmallSmem = 0;  // the short-rows-only variant needs no dynamic shared memory
 
 template <class T>
 static cudaError_t dalloc(T **p, size_t count)
@@ -141,12 +145,14 @@ cbp_ctx *cbp_create(int device)
   ctx->ownsStream = true;
   cudaEventCreate(&ctx->evA);
   cudaEventCreate(&ctx->evB);
-  cudaFuncSetAttribute(sv_fixpoint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaFuncSetAttribute(sv_fixpoint_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
     static_cast<int>(sizeof(SvSmem)));
-  int perSM = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, sv_fixpoint_kernel, kThreads, sizeof(SvSmem));
+  int perSM = 0, perSM2 = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, sv_fixpoint_kernel<true>, kThreads, sizeof(SvSmem));
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM2, sv_fixpoint_kernel<false>, kThreads, kSvSmallSmem);
   ctx->svBlocksPerSM = perSM;
-  if (perSM < 1) {
+  ctx->svBlocksPerSMNoTiles = perSM2;
+  if (perSM < 1 || perSM2 < 1) {
     fprintf(stderr, "cbp_create: persistent kernel does not fit on this device\n");
     cbp_destroy(ctx);
     return nullptr;
@@ -414,6 +420,9 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   mat->nParts = nParts;
   mat->nSing = static_cast<int>(hSing.size());
   mat->nWords = (n + 31) / 32;
+  mat->allInt = colType != nullptr;
+  for (int j = 0; j < n && mat->allInt; ++j)
+    mat->allInt = colType[j] != 0;
   std::vector<signed char> hType(n, 0);
   if (colType)
     for (int j = 0; j < n; ++j)
@@ -631,7 +640,8 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   p.s = s;
   p.maxRounds = maxRounds;
   p.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
-  const int maxGrid = ctx->svBlocksPerSM * ctx->numSMs;
+  const bool tiles = mat->nTiles > 0;
+  const int maxGrid = (tiles ? ctx->svBlocksPerSM : ctx->svBlocksPerSMNoTiles) * ctx->numSMs;
   const int want = std::max(std::max(mat->nTiles, cdiv(mat->nSlices, kWarps)), cdiv(mat->nWords, kThreads));
   const int grid = std::max(1, std::min(maxGrid, want));
   void *args[] = { &p };
@@ -646,8 +656,12 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   k0 = ctx->evPool[0];
   k1 = ctx->evPool[1];
   CK(cudaEventRecord(k0, ctx->stream));
-  CK(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(sv_fixpoint_kernel), dim3(grid), dim3(kThreads),
-    args, sizeof(SvSmem), ctx->stream));
+  if (tiles)
+    CK(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(sv_fixpoint_kernel<true>), dim3(grid),
+      dim3(kThreads), args, sizeof(SvSmem), ctx->stream));
+  else
+    CK(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(sv_fixpoint_kernel<false>), dim3(grid),
+      dim3(kThreads), args, kSvSmallSmem, ctx->stream));
   CK(cudaEventRecord(k1, ctx->stream));
   ++ctx->stats.kernelLaunches;
 
@@ -944,18 +958,25 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     const int cur = round & 1;
     CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
     CK(cudaEventRecord(ctx->evPool[0], st));
+    // kernel variants: <no infinite bound in this batch, no continuous column in this matrix>
+    const int variant = (bt.hasInf ? 0 : 2) | (mat->allInt ? 1 : 0);
     if (longGrid > 0) {
-      if (bt.hasInf)
-        bt_rows_long_kernel<false><<<static_cast<int>(longGrid), kThreads, 0, st>>>(p, cur);
-      else
-        bt_rows_long_kernel<true><<<static_cast<int>(longGrid), kThreads, 0, st>>>(p, cur);
+      const int lg = static_cast<int>(longGrid);
+      switch (variant) {
+      case 0: bt_rows_long_kernel<false, false><<<lg, kThreads, 0, st>>>(p, cur); break;
+      case 1: bt_rows_long_kernel<false, true><<<lg, kThreads, 0, st>>>(p, cur); break;
+      case 2: bt_rows_long_kernel<true, false><<<lg, kThreads, 0, st>>>(p, cur); break;
+      default: bt_rows_long_kernel<true, true><<<lg, kThreads, 0, st>>>(p, cur); break;
+      }
       ++ctx->stats.kernelLaunches;
     }
     if (warps > 0) {
-      if (bt.hasInf)
-        bt_rows_kernel<false><<<rowsGrid, kThreads, 0, st>>>(p, cur);
-      else
-        bt_rows_kernel<true><<<rowsGrid, kThreads, 0, st>>>(p, cur);
+      switch (variant) {
+      case 0: bt_rows_kernel<false, false><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+      case 1: bt_rows_kernel<false, true><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+      case 2: bt_rows_kernel<true, false><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+      default: bt_rows_kernel<true, true><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+      }
       ++ctx->stats.kernelLaunches;
     }
     CK(cudaEventRecord(ctx->evPool[1], st));

@@ -64,7 +64,6 @@ struct SvSmem {
   int rp[kTileRows + 1];
   alignas(8) uint64_t bar[2];
   RowAct red[kWarps];
-  int cnt[kWarps];
 };
 
 // publishes accepted candidates into the round's target buffer
@@ -167,7 +166,7 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
         RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
         for (int k = kb + lane; k < ke; k += 32) {
           const double2 lh = sm.lohi[k];
-          accumulate(ra, val[k], lh.x, lh.y, p.s.inf);
+          accumulate(ra, val[k], col_is_int(col[k]), lh.x, lh.y, p.s.inf);
         }
         warp_reduce(ra);
         const int row = T.rowBegin + r;
@@ -187,7 +186,7 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
         RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
         for (int k = tid; k < T.nzCount; k += kThreads) {
           const double2 lh = sm.lohi[k];
-          accumulate(ra, val[k], lh.x, lh.y, p.s.inf);
+          accumulate(ra, val[k], col_is_int(col[k]), lh.x, lh.y, p.s.inf);
         }
         warp_reduce(ra);
         if (lane == 0)
@@ -239,6 +238,7 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
     for (int k = 0; k < len; k += 4) {
       double a[4];
       Bnd x[4];
+      bool ii[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         a[u] = 0.0;
@@ -247,6 +247,7 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
           a[u] = __ldg(&v[(k + u) << 5]);
           cj = __ldg(&c[(k + u) << 5]);
         }
+        ii[u] = col_is_int(cj);
         x[u].lb = 0.0;
         x[u].ub = 0.0;
         if (a[u] != 0.0)
@@ -254,7 +255,7 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u)  // padding has a == 0 and bounds 0: it leaves every field untouched
-        accumulate(ra, a[u], a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
+        accumulate(ra, a[u], ii[u], a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
     }
     RowPlan pl = plan_row(ra, rl, ru, p.s);
     if (!valid) {
@@ -295,18 +296,24 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 3) sv_fixpoint_kernel(const SvParams p)
+// kTiles=false is the variant for matrices whose rows are all short: no
+// shared-memory staging, fewer registers, more resident warps.
+template <bool kTiles>
+__global__ void __launch_bounds__(kThreads, kTiles ? 3 : 4) sv_fixpoint_kernel(const SvParams p)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  SvSmem &sm = *reinterpret_cast<SvSmem *>(smem_raw);
+  SvSmem &sm = *reinterpret_cast<SvSmem *>(smem_raw);  // kTiles=false: launched without it, never touched
+  __shared__ int s_cnt[kWarps];
   cg::grid_group grid = cg::this_grid();
   const int tid = threadIdx.x;
   const int gtid = blockIdx.x * kThreads + tid, gsize = gridDim.x * kThreads;
   uint32_t parity[2] = { 0u, 0u };
   if (tid == 0) {
-    mbar_init(&sm.bar[0], 1);
-    mbar_init(&sm.bar[1], 1);
-    mbar_fence_init();
+    if (kTiles) {
+      mbar_init(&sm.bar[0], 1);
+      mbar_init(&sm.bar[1], 1);
+      mbar_fence_init();
+    }
     if (blockIdx.x == 0) {
       unsigned long long t;
       asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -353,9 +360,10 @@ __global__ void __launch_bounds__(kThreads, 3) sv_fixpoint_kernel(const SvParams
     }
     // A2: stream the matrix: short rows from the sliced-ELL copy, the rest as TMA-staged tiles
     sv_short_rows(p, src, sink);
-    sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
+    if (kTiles)
+      sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
     grid.sync();
-    if (p.nLong > 0) {
+    if (kTiles && p.nLong > 0) {
       sv_stream<true>(p, sm, parity, p.firstLongTile, p.nTiles, src, sink);
       grid.sync();
     }
@@ -382,12 +390,12 @@ __global__ void __launch_bounds__(kThreads, 3) sv_fixpoint_kernel(const SvParams
       for (int m = 16; m >= 1; m >>= 1)
         mine += __shfl_xor_sync(0xffffffffu, mine, m);
       if ((tid & 31) == 0)
-        sm.cnt[tid >> 5] = mine;
+        s_cnt[tid >> 5] = mine;
       __syncthreads();
       if (tid == 0) {
         int tot = 0;
         for (int w = 0; w < kWarps; ++w)
-          tot += sm.cnt[w];
+          tot += s_cnt[w];
         if (tot)
           atomicAdd(&p.st->chg[cur], tot);
         if (blockIdx.x == 0) {
@@ -488,15 +496,15 @@ __global__ void sv_singleton_kernel(const int *__restrict__ singRows, int nSing,
   const double ru = rowUB[row], rl = rowLB[row];
   if (ru < s.inf) {
     if (a > 0.0)
-      offer_ub(sink, j, ru / a, b.ub, isInt, s);
+      offer_ub(sink, j, ru / a, b.ub, b.lb, isInt, s);
     else
-      offer_lb(sink, j, ru / a, b.lb, isInt, s);
+      offer_lb(sink, j, ru / a, b.lb, b.ub, isInt, s);
   }
   if (rl > -s.inf) {
     if (a > 0.0)
-      offer_lb(sink, j, rl / a, b.lb, isInt, s);
+      offer_lb(sink, j, rl / a, b.lb, b.ub, isInt, s);
     else
-      offer_ub(sink, j, rl / a, b.ub, isInt, s);
+      offer_ub(sink, j, rl / a, b.ub, b.lb, isInt, s);
   }
 }
 
@@ -543,13 +551,13 @@ __global__ void row_activity_kernel(const int *__restrict__ rowNz, const int *__
       for (int k = kb; k < ke; ++k) {
         const double a = val[k];
         const int j = col_of(col[k]);
-        accumulate(ra, a, a > 0.0 ? lb[j] : ub[j], a > 0.0 ? ub[j] : lb[j], INF);
+        accumulate(ra, a, true, a > 0.0 ? lb[j] : ub[j], a > 0.0 ? ub[j] : lb[j], INF);
       }
   } else {
     for (int k = kb + lane; k < ke; k += 32) {
       const double a = val[k];
       const int j = col_of(col[k]);
-      accumulate(ra, a, a > 0.0 ? lb[j] : ub[j], a > 0.0 ? ub[j] : lb[j], INF);
+      accumulate(ra, a, true, a > 0.0 ? lb[j] : ub[j], a > 0.0 ? ub[j] : lb[j], INF);
     }
     warp_reduce(ra);
   }

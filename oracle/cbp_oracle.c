@@ -23,7 +23,9 @@
  *       (:324-326 redundancy test, applied per side).
  *   R6  candidates, slackU = rowUB - minAct, slackL = maxAct - rowLB:
  *         infMin==0: c = lo + slackU/a, evaluated only when the column's
- *                    range is infinite or slackU < |a|(ub-lb)
+ *                    range is infinite or slackU < |a|((ub-lb) - g), where
+ *                    g = 0 for integer columns and 1e-3*max(1, ub-lb) for
+ *                    continuous ones (the smallest step R8 would accept)
  *         infMin==1: c = slackU/a, only for the nonzero whose lo is infinite
  *         infMax==0: c = hi - slackL/a (same pre-check with slackL)
  *         infMax==1: c = -slackL/a, only for the nonzero whose hi is infinite
@@ -33,8 +35,9 @@
  *       c = ceil(c - tol); then c += 0.0 (no negative zero); a candidate with
  *       !(|c| < INF) is dropped.
  *   R8  a candidate is accepted iff it improves the ROUND-START bound by more
- *       than thr: 0.5 for integer columns, 1e-3*max(1,|old bound|) for
- *       continuous ones; an infinite old bound accepts any finite candidate.
+ *       than thr: 0.5 for integer columns; for continuous ones 1e-3*max(1,
+ *       ub-lb) when both round-start bounds are finite, else 1e-3*max(1,|old
+ *       bound|); an infinite old bound accepts any finite candidate.
  *       new lb = max of accepted candidates, new ub = min (Jacobi round).
  *   R9  after all rows, for every changed column: lb' > ub' + 100 tol means
  *       infeasible (column); a smaller crossing is snapped: if ub moved,
@@ -124,9 +127,10 @@ static inline void propose_ub(round_ctx *c, int j, double v)
   v += 0.0;
   if (!(fabs(v) < INF))
     return;
-  const double old = c->ub[j];
+  const double old = c->ub[j], other = c->lb[j];
   if (fabs(old) < INF) {
-    const double thr = isInt ? INT_THR : CONT_REL_THR * fmax(1.0, fabs(old));
+    const double thr = isInt ? INT_THR
+                             : CONT_REL_THR * fmax(1.0, fabs(other) < INF ? old - other : fabs(old));
     note_margin(c->mm, v - (old - thr), v);
     if (isInt && v - 1.0 < old - thr) /* a flipped rounding would matter */
       note_margin(c->mm, rmargin, v);
@@ -153,9 +157,10 @@ static inline void propose_lb(round_ctx *c, int j, double v)
   v += 0.0;
   if (!(fabs(v) < INF))
     return;
-  const double old = c->lb[j];
+  const double old = c->lb[j], other = c->ub[j];
   if (fabs(old) < INF) {
-    const double thr = isInt ? INT_THR : CONT_REL_THR * fmax(1.0, fabs(old));
+    const double thr = isInt ? INT_THR
+                             : CONT_REL_THR * fmax(1.0, fabs(other) < INF ? other - old : fabs(old));
     note_margin(c->mm, v - (old + thr), v);
     if (isInt && v + 1.0 > old + thr)
       note_margin(c->mm, rmargin, v);
@@ -245,7 +250,9 @@ static inline int process_row(round_ctx *c, int i, const double *lb, const doubl
     const double hi = a > 0.0 ? u : l;
     const int loInf = is_inf(lo, INF), hiInf = is_inf(hi, INF);
     const int finite = !loInf && !hiInf;
-    const double w = finite ? fabs(a) * (u - l) : 0.0;
+    const int isInt = p->colType && p->colType[j] != 0;
+    const double width = u - l;
+    const double w = finite ? fabs(a) * (isInt ? width : width - CONT_REL_THR * fmax(1.0, width)) : 0.0;
     if (sideU) {
       if (infMin == 0) {
         if (!finite || slackU < w) {
