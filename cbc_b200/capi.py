@@ -37,7 +37,7 @@ SYMBOLS = [
     "cbp_create", "cbp_destroy", "cbp_set_stream", "cbp_last_error", "cbp_get_stats", "cbp_synchronize",
     "cbp_matrix_upload", "cbp_matrix_free", "cbp_singletons", "cbp_propagate", "cbp_propagate_batch",
     "cbp_propagate_batch_delta", "cbp_batch_load_delta", "cbp_batch_run",
-    "cbp_batch_fetch", "cbp_batch_fetch_dense", "cbp_row_activity",
+    "cbp_batch_fetch", "cbp_batch_fetch_dense", "cbp_row_activity", "cbp_sv_round_stamps",
 ]
 
 _lib = None
@@ -78,6 +78,7 @@ def load():
     lib.cbp_batch_fetch.argtypes = [vp, vp, i64, vp, vp, vp, vp, i32]
     lib.cbp_batch_fetch_dense.argtypes = [vp, vp, vp, i32]
     lib.cbp_row_activity.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32]
+    lib.cbp_sv_round_stamps.argtypes = [vp, vp, i32]
     _lib = lib
     return lib
 
@@ -189,6 +190,14 @@ class Matrix:
                                                   time_limit, C.byref(r), None, 0, FLAG_DEVICE_PTRS),
                        "cbp_propagate")
         return _res_dict(r)
+
+    def round_stamps(self, max_rounds=64):
+        """(rounds, 4) ns since loop start: after rows, after long rows, after settle, after decision."""
+        out = np.zeros((max_rounds, 4), np.uint32)
+        k = self.ctx.lib.cbp_sv_round_stamps(self.h, _ptr(out), max_rounds)
+        if k < 0:
+            self.ctx.check(k, "cbp_sv_round_stamps")
+        return out[:k]
 
     def row_activity(self, lb, ub):
         lb = np.ascontiguousarray(lb, np.float64)

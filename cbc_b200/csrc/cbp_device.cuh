@@ -14,8 +14,17 @@ constexpr int kWarps = kThreads / 32;
 constexpr int kTileNnz = 1024;     // nonzeros staged per tile (12 KB of val+col per stage)
 constexpr int kTileRows = 256;     // rows per tile (one per thread)
 constexpr int kShortLen = 32;      // rows up to this length: one thread per row (sliced-ELL)
+#ifndef CBP_SV_CHUNK
+#define CBP_SV_CHUNK 8
+#endif
+#ifndef CBP_SV_NT_BLOCKS
+#define CBP_SV_NT_BLOCKS 3
+#endif
+constexpr int kSvChunk = CBP_SV_CHUNK;        // sliced-ELL steps whose loads are in flight together
+constexpr int kSvNoTileBlocks = CBP_SV_NT_BLOCKS;  // CTAs per SM of the short-rows-only variant
 constexpr int kSellWindow = 4096;  // short rows are sorted by length inside windows of this many rows
 constexpr int kAlign = 16;         // tile starts are multiples of 16 entries (128 B of val)
+constexpr int kStampRounds = 64;   // rounds whose phase timestamps are kept (diagnostic)
 constexpr int kRoundCap = 1024;    // per-round counts kept on the device
 constexpr int kBtLongLen = 256;    // batch mode: longer rows get a whole CTA per (row, group)
 

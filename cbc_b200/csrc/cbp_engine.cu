@@ -701,6 +701,18 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   return CBP_OK;
 }
 
+int cbp_sv_round_stamps(cbp_matrix *mat, unsigned *out, int maxRounds)
+{
+  if (!mat || !out || maxRounds <= 0)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  const int cnt = std::min(maxRounds, kStampRounds);
+  CK(cudaMemcpy(out, reinterpret_cast<const char *>(mat->st) + offsetof(SvStatus, stamps), sizeof(unsigned) * 4 * cnt,
+    cudaMemcpyDeviceToHost));
+  return cnt;
+}
+
 int cbp_row_activity(cbp_matrix *mat, const double *lb, const double *ub, double *minAct,
   double *maxAct, int *infMin, int *infMax, int flags)
 {

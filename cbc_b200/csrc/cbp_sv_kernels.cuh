@@ -24,8 +24,12 @@ struct SvStatus {
   int nChangedTotal;
   int timeUp;
   int chg[2];  // changed-column count of the running round (slot = round & 1)
+  int sliceCtr[2];  // next short-row slice to hand out in the running round (slot = round & 1)
   int pad;
   unsigned long long t0;  // globaltimer at kernel start
+  // diagnostic: globaltimer seen by CTA 0 after the row phase, the long-row phase, the settle
+  // phase and the decision of each of the first kStampRounds rounds (ns since t0)
+  unsigned stamps[kStampRounds][4];
   int roundChanged[kRoundCap];
 };
 
@@ -64,6 +68,7 @@ struct SvSmem {
   int rp[kTileRows + 1];
   alignas(8) uint64_t bar[2];
   RowAct red[kWarps];
+  RowAct stash[kThreads];  // a long row's chunk partials, fetched one per thread
 };
 
 // publishes accepted candidates into the round's target buffer
@@ -199,9 +204,18 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
           p.longPart[lr.firstPart + T.chunkIdx] = tot;
         }
       } else {
-        RowAct tot = ldcg_rowact(&p.longPart[lr.firstPart]);
-        for (int c = 1; c < lr.nChunks; ++c)
-          combine(tot, ldcg_rowact(&p.longPart[lr.firstPart + c]));
+        // the row's partials, combined in chunk order by every thread alike;
+        // they are fetched in parallel (one per thread) and summed from shared memory
+        RowAct tot = { 0.0, 0.0, 0.0, 0, 0 };
+        for (int c0 = 0; c0 < lr.nChunks; c0 += kThreads) {
+          const int nc = min(kThreads, lr.nChunks - c0);
+          if (tid < nc)
+            sm.stash[tid] = ldcg_rowact(&p.longPart[lr.firstPart + c0 + tid]);
+          __syncthreads();
+          for (int c = 0; c < nc; ++c)
+            combine(tot, sm.stash[c]);
+          __syncthreads();
+        }
         const RowPlan pl = plan_row(tot, p.rowLB[lr.row], p.rowUB[lr.row], p.s);
         if (pl.infeasible && tid == 0 && T.chunkIdx == 0)
           sv_flag_row(p, lr.row);
@@ -222,11 +236,21 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
 // row in CSR order with the sums in registers — the order of the CPU
 // restatement, so these rows agree with it bit for bit.  No shared memory, no
 // block barrier; four gathers per lane are in flight.
-__device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink)
+// Slices are handed out through an atomic counter (a warp asks for its next
+// slice before it starts the current one), so a round ends when the work
+// ends, not when the unluckiest statically assigned warp does.
+__device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink,
+  int *ctr)
 {
   const int lane = threadIdx.x & 31;
-  const int gw = blockIdx.x * kWarps + (threadIdx.x >> 5), nw = gridDim.x * kWarps;
-  for (int s = gw; s < p.nSlices; s += nw) {
+  int next = 0;
+  if (lane == 0)
+    next = atomicAdd(ctr, 1);
+  next = __shfl_sync(0xffffffffu, next, 0);
+  while (next < p.nSlices) {
+    const int s = next;
+    if (lane == 0)
+      next = atomicAdd(ctr, 1);
     const int off = __ldg(&p.sellOff[s]);
     const int len = (__ldg(&p.sellOff[s + 1]) - off) >> 5;
     const int row = (s << 5) + lane;
@@ -235,27 +259,29 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
     const double *__restrict__ v = p.sellVal + off + lane;
     const int *__restrict__ c = p.sellCol + off + lane;
     RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-    for (int k = 0; k < len; k += 4) {
-      double a[4];
-      Bnd x[4];
-      bool ii[4];
+    for (int k = 0; k < len; k += kSvChunk) {
+      double a[kSvChunk];
+      int cj[kSvChunk];
+      Bnd x[kSvChunk];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kSvChunk; ++u) {
         a[u] = 0.0;
-        int cj = 0;
-        if (k + u < len) {
+        cj[u] = 0;
+        if (k + u < len) {  // uniform
+          cj[u] = __ldg(&c[(k + u) << 5]);
           a[u] = __ldg(&v[(k + u) << 5]);
-          cj = __ldg(&c[(k + u) << 5]);
         }
-        ii[u] = col_is_int(cj);
-        x[u].lb = 0.0;
-        x[u].ub = 0.0;
-        if (a[u] != 0.0)
-          x[u] = ldcg_bnd(&src[col_of(cj)]);
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u)  // padding has a == 0 and bounds 0: it leaves every field untouched
-        accumulate(ra, a[u], ii[u], a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
+      for (int u = 0; u < kSvChunk; ++u)  // padding points at column 0: a harmless, shared gather
+        x[u] = ldcg_bnd(&src[col_of(cj[u])]);
+#pragma unroll
+      for (int u = 0; u < kSvChunk; ++u) {  // padding has a == 0: fma(0, x, s) == s, range 0, finite
+        const bool pad = a[u] == 0.0;
+        const double lo = pad ? 0.0 : (a[u] > 0.0 ? x[u].lb : x[u].ub);
+        const double hi = pad ? 0.0 : (a[u] > 0.0 ? x[u].ub : x[u].lb);
+        accumulate(ra, a[u], col_is_int(cj[u]), lo, hi, p.s.inf);
+      }
     }
     RowPlan pl = plan_row(ra, rl, ru, p.s);
     if (!valid) {
@@ -272,34 +298,61 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
     unsigned todo = __ballot_sync(0xffffffffu, pl.sideU || pl.sideL);
     const int packed = min(pl.infMin, 2) | (min(pl.infMax, 2) << 2) | (pl.sideU ? 16 : 0) | (pl.sideL ? 32 : 0);
     while (todo) {
-      const int owner = __ffs(todo) - 1;
-      todo &= todo - 1;
-      RowPlan q;
-      q.slackU = __shfl_sync(0xffffffffu, pl.slackU, owner);
-      q.slackL = __shfl_sync(0xffffffffu, pl.slackL, owner);
-      const int pk = __shfl_sync(0xffffffffu, packed, owner);
-      q.infMin = pk & 3;
-      q.infMax = (pk >> 2) & 3;
-      q.sideU = (pk & 16) != 0;
-      q.sideL = (pk & 32) != 0;
-      q.infeasible = false;
-      if (lane < len) {
-        const int at = off + (lane << 5) + owner;
-        const double a = __ldg(&p.sellVal[at]);
-        if (a != 0.0) {
-          const int cj = __ldg(&p.sellCol[at]);
-          const Bnd x = ldcg_bnd(&src[col_of(cj)]);
-          tighten_nz(sink, q, a, col_of(cj), col_is_int(cj), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+      // up to four rows per trip, all their loads issued before the first use
+      int owner[4];
+      double a4[4];
+      int c4[4];
+      Bnd x4[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        owner[t] = todo ? __ffs(todo) - 1 : -1;
+        todo &= todo - 1;
+        a4[t] = 0.0;
+        c4[t] = 0;
+        if (owner[t] >= 0 && lane < len) {
+          const int at = off + (lane << 5) + owner[t];
+          c4[t] = __ldg(&p.sellCol[at]);
+          a4[t] = __ldg(&p.sellVal[at]);
         }
       }
+#pragma unroll
+      for (int t = 0; t < 4; ++t)
+        x4[t] = ldcg_bnd(&src[col_of(c4[t])]);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        if (owner[t] < 0)
+          break;  // uniform
+        RowPlan q;
+        q.slackU = __shfl_sync(0xffffffffu, pl.slackU, owner[t]);
+        q.slackL = __shfl_sync(0xffffffffu, pl.slackL, owner[t]);
+        const int pk = __shfl_sync(0xffffffffu, packed, owner[t]);
+        q.infMin = pk & 3;
+        q.infMax = (pk >> 2) & 3;
+        q.sideU = (pk & 16) != 0;
+        q.sideL = (pk & 32) != 0;
+        q.infeasible = false;
+        if (a4[t] != 0.0)
+          tighten_nz(sink, q, a4[t], col_of(c4[t]), col_is_int(c4[t]), a4[t] > 0.0 ? x4[t].lb : x4[t].ub,
+            a4[t] > 0.0 ? x4[t].ub : x4[t].lb, p.s);
+      }
     }
+    next = __shfl_sync(0xffffffffu, next, 0);
+  }
+}
+
+__device__ __forceinline__ void sv_stamp(const SvParams &p, int round, int which)
+{
+  if (blockIdx.x == 0 && threadIdx.x == 0 && round < kStampRounds) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    p.st->stamps[round][which] = static_cast<unsigned>(t - p.st->t0);
   }
 }
 
 // kTiles=false is the variant for matrices whose rows are all short: no
 // shared-memory staging, fewer registers, more resident warps.
 template <bool kTiles>
-__global__ void __launch_bounds__(kThreads, kTiles ? 3 : 4) sv_fixpoint_kernel(const SvParams p)
+__global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fixpoint_kernel(const SvParams p)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SvSmem &sm = *reinterpret_cast<SvSmem *>(smem_raw);  // kTiles=false: launched without it, never touched
@@ -344,39 +397,39 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : 4) sv_fixpoint_kernel(c
     // column at the same time.
     if (round > 0) {
       unsigned *prev = p.dirty[cur ^ 1];
-      for (int w = gtid; w < p.nWords; w += gsize) {
-        unsigned bits = __ldcg(&prev[w]);
-        if (!bits)
-          continue;
-        prev[w] = 0u;
-        while (bits) {
-          const int j = (w << 5) + __ffs(bits) - 1;
-          bits &= bits - 1;
+      for (int j0 = gtid & ~31; j0 < p.n; j0 += gsize) {  // one column per thread, one word per warp
+        const int j = j0 + (tid & 31);
+        const unsigned bits = __ldcg(&prev[j0 >> 5]);
+        if ((bits >> (tid & 31)) & 1u) {
           const Bnd b = ldcg_bnd(&src[j]);
           atomic_max_f64(&dst[j].lb, b.lb);
           atomic_min_f64(&dst[j].ub, b.ub);
         }
+        __syncwarp();
+        if ((tid & 31) == 0 && bits)
+          prev[j0 >> 5] = 0u;
       }
     }
     // A2: stream the matrix: short rows from the sliced-ELL copy, the rest as TMA-staged tiles
-    sv_short_rows(p, src, sink);
+    sv_short_rows(p, src, sink, &p.st->sliceCtr[cur]);
     if (kTiles)
       sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
     grid.sync();
+    sv_stamp(p, round, 0);
     if (kTiles && p.nLong > 0) {
       sv_stream<true>(p, sm, parity, p.firstLongTile, p.nTiles, src, sink);
       grid.sync();
     }
+    sv_stamp(p, round, 1);
     // B: settle the changed columns (R9) and count them
     {
       int mine = 0;
       const unsigned *dw = p.dirty[cur];
-      for (int w = gtid; w < p.nWords; w += gsize) {
-        unsigned bits = __ldcg(&dw[w]);
-        mine += __popc(bits);
-        while (bits) {
-          const int j = (w << 5) + __ffs(bits) - 1;
-          bits &= bits - 1;
+      for (int j0 = gtid & ~31; j0 < p.n; j0 += gsize) {  // one column per thread, one word per warp
+        const int j = j0 + (tid & 31);
+        const unsigned bits = __ldcg(&dw[j0 >> 5]);
+        if ((bits >> (tid & 31)) & 1u) {
+          ++mine;
           Bnd b = ldcg_bnd(&dst[j]);
           const double oldUb = __ldcg(&src[j].ub);
           const double L0 = b.lb, U0 = b.ub;
@@ -399,7 +452,8 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : 4) sv_fixpoint_kernel(c
         if (tot)
           atomicAdd(&p.st->chg[cur], tot);
         if (blockIdx.x == 0) {
-          p.st->chg[cur ^ 1] = 0;  // next round's slot; nobody touches it in this phase
+          p.st->chg[cur ^ 1] = 0;  // next round's slots; nobody touches them in this phase
+          p.st->sliceCtr[cur ^ 1] = 0;
           unsigned long long t;
           asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
           if (t - p.st->t0 >= p.budgetNs)
@@ -408,6 +462,7 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : 4) sv_fixpoint_kernel(c
       }
     }
     grid.sync();
+    sv_stamp(p, round, 2);
     // every thread takes the same decision from the same global words
     const int badRow = __ldcg(&p.st->infeasRow), badCol = __ldcg(&p.st->infeasCol);
     const int changed = __ldcg(&p.st->chg[cur]);
@@ -424,6 +479,7 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : 4) sv_fixpoint_kernel(c
       stop = 3;  // HitTimeLimit, checked before the next round would start
       fin = cur ^ 1;
     }
+    sv_stamp(p, round, 3);
     if (gtid == 0) {
       if (stop != 4) {  // a failing round is not applied and not reported
         if (round < kRoundCap)

@@ -156,6 +156,12 @@ CBP_API int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, in
 /* Dense final bounds of the resident batch, B x n row-major per vector. */
 CBP_API int cbp_batch_fetch_dense(cbp_matrix *mat, double *lb, double *ub, int flags);
 
+/* Diagnostic: device timestamps (ns since the loop started, as seen by CTA 0) of the last
+ * cbp_propagate: for each of the first rounds, after the row phase, after the long-row phase,
+ * after the settle phase and after the stop decision; out gets 4 values per round.  Returns the
+ * number of rounds written (at most 64) or a negative error. */
+CBP_API int cbp_sv_round_stamps(cbp_matrix *mat, unsigned *out, int maxRounds);
+
 /* Min/max row activities with exact infinite-bound counters for one bound
  * vector (the arithmetic of src/CbcSolverHeuristics.cpp:282-318); rows in the
  * caller's order, skipped ('N' / empty) rows report zeros. */
