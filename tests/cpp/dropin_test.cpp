@@ -1,0 +1,207 @@
+// dropin_test.cpp — drives the C++ drop-ins the way Cbc's callers do, on top
+// of the COIN test double.  Usage:
+//   cbp_dropin_test <instance.bin> <out.bin> <level 1|2|3> <maxRounds> <logLevel> <timeLimit> [dive]
+// Prints one "RESULT {json}" line; writes the solver's final column bounds to
+// out.bin (n doubles lb, n doubles ub).  With "dive" it instead performs the
+// single-round CoinBoundPropagation step of CbcHeuristicDive
+// (/root/reference/src/CbcHeuristicDive.cpp:967-1001).
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <ctime>
+#include <string>
+#include <vector>
+
+#include "CbcBoundPropagation.hpp"
+#include "CoinBoundPropagation.hpp"
+#include "OsiSolverInterface.hpp"
+#include "cbp_capi.h"
+#include "../../cbc_b200/host/CbpDeviceCache.hpp"
+
+double CoinGetTimeOfDay()
+{
+  return std::chrono::duration<double>(std::chrono::system_clock::now().time_since_epoch()).count();
+}
+double CoinCpuTime() { return static_cast<double>(clock()) / CLOCKS_PER_SEC; }
+
+struct TestMatrix : CoinPackedMatrix {
+  std::vector<double> el;
+  std::vector<int> idx, start, len;
+  const double *getElements() const override { return el.data(); }
+  const int *getIndices() const override { return idx.data(); }
+  const CoinBigIndex *getVectorStarts() const override { return start.data(); }
+  const int *getVectorLengths() const override { return len.data(); }
+  int getNumRows() const override { return static_cast<int>(len.size()); }
+  CoinBigIndex getNumElements() const override { return static_cast<int>(el.size()); }
+};
+
+struct TestSolver : OsiSolverInterface {
+  TestMatrix mat;
+  std::vector<char> sense, ctype;
+  std::vector<double> rhs, range, lb, ub;
+  double inf = 1e30, tol = 1e-7;
+  int nSetLower = 0, nSetUpper = 0;
+
+  CbpProblemView view() const
+  {
+    CbpProblemView v;
+    v.m = mat.getNumRows();
+    v.n = static_cast<int>(lb.size());
+    v.rowStart32 = mat.start.data();
+    v.rowLen = mat.len.data();
+    v.colIdx = mat.idx.data();
+    v.val = mat.el.data();
+    v.rowSense = sense.data();
+    v.rhs = rhs.data();
+    v.range = range.data();
+    v.colType = ctype.data();
+    v.infinity = inf;
+    return v;
+  }
+  int getNumCols() const override { return static_cast<int>(lb.size()); }
+  int getNumRows() const override { return mat.getNumRows(); }
+  // what an Osi implementation would bind: phase 1 on the device (cbp_singletons)
+  int tightenBoundsFromSingletonRows(int &nFixed) override
+  {
+    nFixed = 0;
+    cbp_matrix *m = cbpAcquireMatrix(view());
+    if (!m)
+      return 0;
+    int nT = 0;
+    std::vector<double> l = lb, u = ub;
+    if (cbp_singletons(m, l.data(), u.data(), tol, &nT, &nFixed, 0) != CBP_OK)
+      return 0;
+    if (nT > 0)
+      for (size_t j = 0; j < lb.size(); ++j) {
+        if (l[j] != lb[j])
+          setColLower(static_cast<int>(j), l[j]);
+        if (u[j] != ub[j])
+          setColUpper(static_cast<int>(j), u[j]);
+      }
+    return nT;
+  }
+  const char *getColType(bool) const override { return ctype.data(); }
+  const CoinPackedMatrix *getMatrixByRow() const override { return &mat; }
+  const char *getRowSense() const override { return sense.data(); }
+  const double *getRightHandSide() const override { return rhs.data(); }
+  const double *getRowRange() const override { return range.data(); }
+  bool getDblParam(OsiDblParam key, double &value) const override
+  {
+    if (key == OsiPrimalTolerance) {
+      value = tol;
+      return true;
+    }
+    return false;
+  }
+  double getInfinity() const override { return inf; }
+  const double *getColLower() const override { return lb.data(); }
+  const double *getColUpper() const override { return ub.data(); }
+  void setColLower(int col, double value) override
+  {
+    lb[col] = value;
+    ++nSetLower;
+  }
+  void setColUpper(int col, double value) override
+  {
+    ub[col] = value;
+    ++nSetUpper;
+  }
+  std::string getRowName(int row, unsigned) const override { return "R" + std::to_string(row); }
+  std::string getColName(int col, unsigned) const override { return "C" + std::to_string(col); }
+};
+
+template <class T>
+static bool rd(FILE *f, std::vector<T> &v, size_t n)
+{
+  v.resize(n);
+  return n == 0 || fread(v.data(), sizeof(T), n, f) == n;
+}
+
+static bool load(const char *path, TestSolver &s)
+{
+  FILE *f = fopen(path, "rb");
+  if (!f)
+    return false;
+  int m = 0, n = 0;
+  long long nnz = 0;
+  bool ok = fread(&m, 4, 1, f) == 1 && fread(&n, 4, 1, f) == 1 && fread(&nnz, 8, 1, f) == 1;
+  std::vector<int> start;
+  ok = ok && rd(f, start, static_cast<size_t>(m) + 1) && rd(f, s.mat.idx, nnz) && rd(f, s.mat.el, nnz)
+    && rd(f, s.sense, m) && rd(f, s.rhs, m) && rd(f, s.range, m) && rd(f, s.ctype, n) && rd(f, s.lb, n)
+    && rd(f, s.ub, n) && fread(&s.inf, 8, 1, f) == 1;
+  fclose(f);
+  if (!ok)
+    return false;
+  s.mat.start.assign(start.begin(), start.begin() + m);
+  s.mat.len.resize(m);
+  for (int i = 0; i < m; ++i)
+    s.mat.len[i] = start[i + 1] - start[i];
+  return true;
+}
+
+int main(int argc, char **argv)
+{
+  if (argc < 7) {
+    fprintf(stderr, "usage: %s inst.bin out.bin level maxRounds logLevel timeLimit [dive]\n", argv[0]);
+    return 2;
+  }
+  TestSolver solver;
+  if (!load(argv[1], solver)) {
+    fprintf(stderr, "cannot read %s\n", argv[1]);
+    return 2;
+  }
+  const int level = atoi(argv[3]), maxRounds = atoi(argv[4]), logLevel = atoi(argv[5]);
+  const double timeLimit = atof(argv[6]);
+  const bool dive = argc > 7 && !strcmp(argv[7], "dive");
+  if (dive) {
+    // the block of CbcHeuristicDive::solution, verbatim in shape
+    const CoinPackedMatrix *matByRow = solver.getMatrixByRow();
+    int totalBoundFixed = 0, reasonToStop = 0;
+    CoinBoundPropagation bt(solver.getNumCols(), solver.getColType(false), solver.getColLower(),
+      solver.getColUpper(), matByRow, solver.getRowSense(), solver.getRightHandSide(), solver.getRowRange(),
+      solver.tol, solver.getInfinity());
+    if (bt.isInfeasible()) {
+      reasonToStop = 1;
+    } else {
+      const auto &bounds = bt.updatedBounds();
+      for (const auto &p : bounds) {
+        int col = static_cast<int>(p.first);
+        solver.setColLower(col, p.second.first);
+        solver.setColUpper(col, p.second.second);
+        totalBoundFixed++;
+      }
+    }
+    printf("RESULT {\"dive\": 1, \"ran\": %d, \"infeasible\": %d, \"infeasibleRow\": %d, \"infeasibleCol\": %d, "
+           "\"totalBoundFixed\": %d, \"reasonToStop\": %d}\n",
+      bt.ran() ? 1 : 0, bt.isInfeasible() ? 1 : 0, bt.infeasibleRow(), bt.infeasibleCol(), totalBoundFixed,
+      reasonToStop);
+  } else {
+    // the calling sequence of CbcSolver::applyLpMethod (src/CbcSolver.cpp:1092-1105)
+    CbcBoundPropagation bp;
+    const double startTime = CoinGetTimeOfDay();
+    const bool feasible = bp.run(&solver, NULL, logLevel, static_cast<CbcBoundPropagation::Level>(level), maxRounds,
+      true, timeLimit, startTime);
+    printf("RESULT {\"feasible\": %d, \"nSingletonTightened\": %d, \"nSingletonFixed\": %d, \"nBoundPropFixed\": %d, "
+           "\"nFixed\": %d, \"nRoundsRun\": %d, \"stopReason\": %d, \"infeasibleRow\": %d, \"infeasibleCol\": %d, "
+           "\"nSetLower\": %d, \"nSetUpper\": %d, \"timeUsed\": %.6f}\n",
+      feasible ? 1 : 0, bp.nSingletonTightened(), bp.nSingletonFixed(), bp.nBoundPropFixed(), bp.nFixed(),
+      bp.nRoundsRun(), static_cast<int>(bp.stopReason()), bp.infeasibleRow(), bp.infeasibleCol(), solver.nSetLower,
+      solver.nSetUpper, bp.timeUsed());
+    // a second run on the now-propagated solver: same matrix, must hit the cache and be a fixpoint
+    if (feasible && level >= 2 && timeLimit > 0) {
+      CbcBoundPropagation again;
+      const bool f2 = again.run(&solver, NULL, 0, CbcBoundPropagation::Fixpoint, 0, true, 1e100, 0.0);
+      printf("AGAIN {\"feasible\": %d, \"nRoundsRun\": %d, \"nBoundPropFixed\": %d, \"stopReason\": %d}\n", f2 ? 1 : 0,
+        again.nRoundsRun(), again.nBoundPropFixed(), static_cast<int>(again.stopReason()));
+    }
+  }
+  FILE *o = fopen(argv[2], "wb");
+  if (o) {
+    fwrite(solver.lb.data(), 8, solver.lb.size(), o);
+    fwrite(solver.ub.data(), 8, solver.ub.size(), o);
+    fclose(o);
+  }
+  cbpReleaseThreadCache();
+  return 0;
+}
