@@ -189,7 +189,7 @@ int main(int argc, char **argv)
       bp.nRoundsRun(), static_cast<int>(bp.stopReason()), bp.infeasibleRow(), bp.infeasibleCol(), solver.nSetLower,
       solver.nSetUpper, bp.timeUsed());
     // a second run on the now-propagated solver: same matrix, must hit the cache and be a fixpoint
-    if (feasible && level >= 2 && timeLimit > 0) {
+    if (feasible && bp.stopReason() == CbcBoundPropagation::ReachedFixpoint && level >= 2) {
       CbcBoundPropagation again;
       const bool f2 = again.run(&solver, NULL, 0, CbcBoundPropagation::Fixpoint, 0, true, 1e100, 0.0);
       printf("AGAIN {\"feasible\": %d, \"nRoundsRun\": %d, \"nBoundPropFixed\": %d, \"stopReason\": %d}\n", f2 ? 1 : 0,

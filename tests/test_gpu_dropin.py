@@ -69,7 +69,8 @@ def test_run_matches_oracle(oracle, tmp_path, level, max_rounds):
         return
     assert res["nRoundsRun"] == r["rounds"] and res["nBoundPropFixed"] == r["nChanged"]
     assert res["stopReason"] == r["stopReason"] and res["nFixed"] == nf + r["nChanged"]
-    assert res["nSetLower"] == res["nSetUpper"]  # both sides are set for every listed column
+    changed = int(np.count_nonzero((lb != inst.lb) | (ub != inst.ub)))
+    assert res["nSetLower"] >= changed - nt and res["nSetUpper"] >= changed - nt  # setColLower AND setColUpper per column
     # the reference's output lines (src/CbcBoundPropagation.cpp:70,192,174,205)
     assert f"  Bound propagation (singletons): {nt - nf} tightened, {nf} fixed." in log
     assert f"  Bound propagation: round 1 fixed {r['roundChanged'][0]} variables (total {r['roundChanged'][0]})." in log
