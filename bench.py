@@ -230,7 +230,7 @@ def main():
             mat.batch_run()
             st = ctx.stats()
             return st["lastRoundsTotal"], st["lastRoundKernelMs"], st["lastRoundKernelLaunches"]
-    else:
+    elif world == 1:
         dlb0 = torch.tensor(work["lb"], device="cuda")
         dub0 = torch.tensor(work["ub"], device="cuda")
         dlb, dub = dlb0.clone(), dub0.clone()
@@ -241,7 +241,25 @@ def main():
             r = mat.propagate_device(dlb.data_ptr(), dub.data_ptr())
             st = ctx.stats()
             return r["rounds"], st["lastRoundKernelMs"], r["rounds"]
+    else:
+        # single vector over a row-sharded matrix: this rank owns a block of rows (balanced by
+        # nonzeros); one max all-reduce over [lb ; -ub ; flag] per round (NCCL over NVLink)
+        from cbc_b200 import multigpu as MG
 
+        r0, r1 = MG.row_blocks(inst.rowStart, world)[rank]
+        mat.close()
+        mat = capi.Matrix(ctx, MG.sub_instance(inst, r0, r1))
+        local_round = MG.cuda_local_round(mat)
+        dlb0 = torch.tensor(work["lb"], device="cuda")
+        dub0 = torch.tensor(work["ub"], device="cuda")
+        isint = torch.tensor(inst.colType != 0, device="cuda")
+        sharded_ms = [0.0]
+
+        def step():
+            r, _, _ = MG.propagate_row_sharded(local_round, dlb0.clone(), dub0.clone(), isint, row_offset=r0,
+                                               inf=inst.inf)
+            # every rank does all rounds; count the rounds once (rank 0) so the SUM over ranks is the job's
+            return (r["rounds"] if rank == 0 else 0), 0.0, r["rounds"]
     for _ in range(W):
         step()
     barrier()
@@ -276,6 +294,15 @@ def main():
             res, us, uc, ul, uu = mat.propagate_batch_delta(work["lb"], work["ub"], s, v, b)
             return int(res["rounds"].sum()), uc.size
         h2d = 16 * inst.n + 8 * (len(s)) + 12 * len(v)
+    elif world > 1:
+        def e2e_step():
+            lb_h = torch.from_numpy(work["lb"]).pin_memory()
+            ub_h = torch.from_numpy(work["ub"]).pin_memory()
+            r, lbo, ubo = MG.propagate_row_sharded(local_round, lb_h.cuda(non_blocking=True),
+                                                   ub_h.cuda(non_blocking=True), isint, row_offset=r0, inf=inst.inf)
+            lbo.cpu(), ubo.cpu()
+            return (r["rounds"] if rank == 0 else 0), 0
+        h2d = 16 * inst.n
     else:
         def e2e_step():
             r, _, _ = mat.propagate(work["lb"], work["ub"])
@@ -326,11 +353,15 @@ def main():
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak" if batch else "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": work["desc"], "l2": "inputs larger than L2" if (alg / max(1, round_launches)) > 126e6
+        "config": {"workload": work["desc"] + (f", rows sharded over {world} GPUs, one max all-reduce of [lb;-ub] "
+                                              f"per round" if (world > 1 and not batch) else ""), "l2": "inputs larger than L2" if (alg / max(1, round_launches)) > 126e6
                    else "working set fits L2; matrix re-read every round by design",
-                   "vectors_per_gpu": work["B"], "sharding": "node batch sharded across GPUs, no collective"},
+                   "vectors_per_gpu": work["B"],
+                   "sharding": "node batch sharded across GPUs, no collective" if batch else
+                   ("rows sharded, NCCL max all-reduce per round" if world > 1 else "single GPU")},
         "roofline": roofline,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
         "gpu_launches": int(launches),

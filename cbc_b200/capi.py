@@ -11,6 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libcbp.so")
 
 FLAG_DEVICE_PTRS = 1
+FLAG_RAW_ROUND = 2
 ERR_CAPACITY = -4
 STOP_NAMES = {0: "NotRun", 1: "ReachedFixpoint", 2: "HitMaxRounds", 3: "HitTimeLimit", 4: "InfeasibleDetected"}
 
@@ -183,11 +184,13 @@ class Matrix:
         out["roundChanged"] = [int(x) for x in rc_arr[: min(done, round_cap)] if x >= 0]
         return out, lb, ub
 
-    def propagate_device(self, lb_ptr, ub_ptr, tol=1e-7, max_rounds=0, time_limit=1e100):
-        """lb/ub are device pointers (ints) to n doubles each, updated in place."""
+    def propagate_device(self, lb_ptr, ub_ptr, tol=1e-7, max_rounds=0, time_limit=1e100, raw_round=False):
+        """lb/ub are device pointers (ints) to n doubles each, updated in place.  raw_round: see
+        CBP_FLAG_RAW_ROUND (one round's unsettled proposals, for row-sharded runs)."""
         r = Result()
+        flags = FLAG_DEVICE_PTRS | (FLAG_RAW_ROUND if raw_round else 0)
         self.ctx.check(self.ctx.lib.cbp_propagate(self.h, C.c_void_p(lb_ptr), C.c_void_p(ub_ptr), tol, max_rounds,
-                                                  time_limit, C.byref(r), None, 0, FLAG_DEVICE_PTRS),
+                                                  time_limit, C.byref(r), None, 0, flags),
                        "cbp_propagate")
         return _res_dict(r)
 

@@ -91,16 +91,26 @@ template <bool kNoInf, int kSign, bool kAllInt>
 __device__ __forceinline__ void bt_walk_sum(const BtParams &p, const char *__restrict__ src,
   unsigned strideB, int kb, int ke, int lane, Stg *stg, RowAct &ra)
 {
+  // the next block's (a, j) are fetched while the current block is being walked
+  double nextA = 0.0;
+  int nextC = 0;
+  if (kb + lane < ke) {
+    nextC = __ldg(&p.col[kb + lane]);
+    nextA = __ldg(&p.val[kb + lane]);
+  }
   for (int base = kb; base < ke; base += 32) {
-    const int k = base + lane;
     __syncwarp();
-    if (k < ke) {
-      const int c = __ldg(&p.col[k]);
+    {
       Stg e;
-      e.a = __ldg(&p.val[k]);
-      e.j = col_of(c);
-      e.isInt = col_is_int(c) ? 1 : 0;
+      e.a = nextA;
+      e.j = col_of(nextC);
+      e.isInt = col_is_int(nextC) ? 1 : 0;
       stg[lane] = e;
+    }
+    const int kn = base + 32 + lane;
+    if (kn < ke) {
+      nextC = __ldg(&p.col[kn]);
+      nextA = __ldg(&p.val[kn]);
     }
     __syncwarp();
     const int cnt = min(32, ke - base);

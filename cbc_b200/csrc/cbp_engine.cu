@@ -606,12 +606,14 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   CK(cudaEventRecord(ctx->evA, ctx->stream));
   if ((rc = sv_reset_state(mat)))
     return rc;
+  const int raw = (flags & CBP_FLAG_RAW_ROUND) ? 1 : 0;
   sv_prepare_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(dl, du, mat->colType, n, mat->X[0], mat->X[1],
-    mat->dirty[0], mat->st, s, 1);
+    mat->dirty[0], mat->st, s, raw ? 0 : 1);
   ++ctx->stats.kernelLaunches;
   CK(cudaGetLastError());
 
   SvParams p;
+  p.raw = raw;
   p.val = mat->val;
   p.col = mat->col;
   p.tiles = mat->tiles;

@@ -58,6 +58,7 @@ struct SvParams {
   SvStatus *st;
   Scal s;
   int maxRounds;  // <=0: no limit
+  int raw;        // 1: do the row phase of ONE round and stop (no R9, no bookkeeping): row-sharded mode
   unsigned long long budgetNs;  // time limit measured from kernel start
 };
 
@@ -421,6 +422,14 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
       grid.sync();
     }
     sv_stamp(p, round, 1);
+    if (p.raw) {  // the caller combines the proposals of all row blocks and settles them itself
+      if (gtid == 0) {
+        p.st->rounds = 1;
+        p.st->stopReason = __ldcg(&p.st->infeasRow) != 0x7fffffff ? 4 : 2;
+        p.st->finalBuf = cur ^ 1;
+      }
+      return;
+    }
     // B: settle the changed columns (R9) and count them
     {
       int mine = 0;

@@ -41,7 +41,13 @@ enum {
 };
 
 enum {
-  CBP_FLAG_DEVICE_PTRS = 1 /* bound/result arrays are device pointers */
+  CBP_FLAG_DEVICE_PTRS = 1, /* bound/result arrays are device pointers */
+  /* cbp_propagate only: run the row phase of exactly ONE round over this matrix's rows and return
+   * the raw Jacobi proposals (max of accepted lower, min of accepted upper candidates per column),
+   * without R11, without settling crossings (R9) and without bookkeeping.  out->feasible == 0 only
+   * for a violated row (infeasibleRow).  For row-sharded multi-GPU runs: every rank does this on its
+   * row block, the proposals are combined with one max/min all-reduce, then settled once. */
+  CBP_FLAG_RAW_ROUND = 2
 };
 
 /* Stop reasons; numbering of CbcBoundPropagation::StopReason

@@ -309,20 +309,28 @@ static inline int settle_column(double *L, double *U, double oldUb, double tol, 
   return 0;
 }
 
-int orc_round(const orc_problem *p, const double *lb, const double *ub, double tol,
-  double *newLb, double *newUb, unsigned char *changed, int *nChanged,
-  int *infRow, int *infCol, double *minMargin)
+int orc_round_rows(const orc_problem *p, const double *lb, const double *ub, double tol,
+  double *newLb, double *newUb, unsigned char *changed, double *minMargin)
 {
   round_ctx c = { p, lb, ub, newLb, newUb, changed, tol, minMargin };
   if (newLb != lb)
     memcpy(newLb, lb, sizeof(double) * (size_t)p->n);
   if (newUb != ub)
     memcpy(newUb, ub, sizeof(double) * (size_t)p->n);
-  int badRow = -1, badCol = -1;
+  int badRow = -1;
   for (int i = 0; i < p->m; ++i) {
     if (process_row(&c, i, lb, ub) && badRow < 0)
       badRow = i;
   }
+  return badRow;
+}
+
+int orc_round(const orc_problem *p, const double *lb, const double *ub, double tol,
+  double *newLb, double *newUb, unsigned char *changed, int *nChanged,
+  int *infRow, int *infCol, double *minMargin)
+{
+  const int badRow = orc_round_rows(p, lb, ub, tol, newLb, newUb, changed, minMargin);
+  int badCol = -1;
   int cnt = 0;
   for (int j = 0; j < p->n; ++j) {
     if (!changed[j])

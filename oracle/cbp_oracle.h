@@ -84,6 +84,11 @@ int orc_round(const orc_problem *p, const double *lb, const double *ub, double t
   double *newLb, double *newUb, unsigned char *changed, int *nChanged,
   int *infRow, int *infCol, double *minMargin);
 
+/* The row phase of one round only (rules R3-R8): the unsettled Jacobi proposals.  Returns the
+ * smallest violated row or -1.  (What one rank computes in the row-sharded multi-GPU mode.) */
+int orc_round_rows(const orc_problem *p, const double *lb, const double *ub, double tol,
+  double *newLb, double *newUb, unsigned char *changed, double *minMargin);
+
 /* Phase 2: rounds to a fixpoint / maxRounds (<=0: no limit) / time limit.
  * lb/ub are updated in place with every completed feasible round.
  * roundChanged (nullable, roundCap entries) receives per-round counts. */

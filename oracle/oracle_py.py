@@ -136,6 +136,17 @@ def singletons(prob, lb, ub, tol=1e-7):
     return nt, nf.value, lb, ub
 
 
+def round_rows(prob, lb, ub, tol=1e-7):
+    """Row phase of one round: (newLb, newUb, first violated row or -1)."""
+    lb = np.ascontiguousarray(lb, np.float64)
+    ub = np.ascontiguousarray(ub, np.float64)
+    nlb, nub = np.empty_like(lb), np.empty_like(ub)
+    changed = np.zeros(prob.n, np.uint8)
+    lib().orc_round_rows.restype = C.c_int
+    bad = lib().orc_round_rows(C.byref(prob.s), _p(lb), _p(ub), C.c_double(tol), _p(nlb), _p(nub), _p(changed), None)
+    return nlb, nub, bad
+
+
 def propagate(prob, lb, ub, tol=1e-7, max_rounds=0, time_limit=1e100, gauss_seidel=False, round_cap=4096):
     lb = np.array(lb, np.float64)
     ub = np.array(ub, np.float64)
