@@ -38,7 +38,7 @@ SYMBOLS = [
     "cbp_create", "cbp_destroy", "cbp_set_stream", "cbp_last_error", "cbp_get_stats", "cbp_synchronize",
     "cbp_matrix_upload", "cbp_matrix_free", "cbp_singletons", "cbp_propagate", "cbp_propagate_batch",
     "cbp_propagate_batch_delta", "cbp_batch_load_delta", "cbp_batch_run",
-    "cbp_batch_fetch", "cbp_batch_fetch_dense", "cbp_row_activity", "cbp_sv_round_stamps",
+    "cbp_batch_fetch", "cbp_batch_fetch_dense", "cbp_row_activity", "cbp_sv_round_stamps", "cbp_singletons_noalloc",
 ]
 
 _lib = None
@@ -80,6 +80,8 @@ def load():
     lib.cbp_batch_fetch_dense.argtypes = [vp, vp, vp, i32]
     lib.cbp_row_activity.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32]
     lib.cbp_sv_round_stamps.argtypes = [vp, vp, i32]
+    lib.cbp_singletons_noalloc.argtypes = [i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, f64, vp, vp, f64,
+                                           C.POINTER(i32), C.POINTER(i32), vp]
     _lib = lib
     return lib
 
@@ -90,6 +92,21 @@ def _ptr(a):
     if isinstance(a, int):
         return C.c_void_p(a)
     return C.c_void_p(a.ctypes.data)
+
+
+NOALLOC_MAX_COLS = 262144
+
+
+def singletons_noalloc(m, n, row_start, col, val, sense, rhs, rng, col_type, inf, lb, ub, tol=1e-7, stream=0):
+    """cbp_singletons_noalloc: every array argument is a DEVICE pointer (int) on the current device; lb/ub are
+    updated in place.  Returns (rc, nTightened, nFixed); rc is the library's return code (0 = ok)."""
+    lib = load()
+    nt, nf = C.c_int(0), C.c_int(0)
+    rc = lib.cbp_singletons_noalloc(m, n, C.c_void_p(row_start), None, C.c_void_p(col), C.c_void_p(val),
+                                    C.c_void_p(sense), C.c_void_p(rhs), C.c_void_p(rng), C.c_void_p(col_type),
+                                    float(inf), C.c_void_p(lb), C.c_void_p(ub), float(tol), C.byref(nt), C.byref(nf),
+                                    C.c_void_p(stream))
+    return rc, nt.value, nf.value
 
 
 class Context:

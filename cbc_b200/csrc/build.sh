@@ -9,5 +9,5 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 "$NVCC" -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
   -fmad=false -Xcompiler -fPIC,-fvisibility=hidden,-O2 -shared \
   ${CBP_PTXAS_V:+-Xptxas -v} \
-  -o "$OUT/libcbp.so" "$HERE/cbp_engine.cu" -lcudart
+  -o "$OUT/libcbp.so" "$HERE/cbp_engine.cu" "$HERE/cbp_noalloc.cu" -lcudart
 echo "built $OUT/libcbp.so"

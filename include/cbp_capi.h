@@ -162,6 +162,31 @@ CBP_API int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, in
 /* Dense final bounds of the resident batch, B x n row-major per vector. */
 CBP_API int cbp_batch_fetch_dense(cbp_matrix *mat, double *lb, double *ub, int flags);
 
+/* Phase 1 for callers that cannot allocate device memory.  This entry point has no counterpart in
+ * the reference (which has no device at all); it exists for two kinds of caller: a process whose
+ * host application or LP code has already taken all free HBM into its own pool, where a late
+ * cudaMalloc from a worker thread fails; and node-level propagation on several Cbc worker threads,
+ * where cudaMalloc / cudaFree would stall the other threads' streams because both synchronise the
+ * device.  It does what cbp_singletons does (same rules, same results) but takes EVERY array from
+ * the caller as a device pointer on the current device — the row-major matrix exactly as
+ * getMatrixByRow() lays it out (rowLen may be NULL), row sense / rhs / range, colType, and lb / ub
+ * (n doubles each, updated in place; left untouched when *nTightened is -1) — and allocates
+ * nothing: its working memory is a fixed array inside the library image (about 4.1 MB, resident on
+ * every GPU that loads libcbp.so until the process exits).  Limits and rules:
+ *   - n must not exceed CBP_NOALLOC_MAX_COLS; larger problems get CBP_ERR_CAPACITY and a message
+ *     on stderr (use cbp_matrix_upload + cbp_singletons for those);
+ *   - the first call on each device looks up the device address of that array; make that first call
+ *     before starting any stream capture on that device;
+ *   - all calls on one device share the array (each call clears what it needs), so two calls whose
+ *     kernels could overlap on the GPU — different streams, different threads — race: serialise them;
+ *   - work is queued on cudaStream (a cudaStream_t, may be 0) and the call returns after it has
+ *     finished; nTightened / nFixed are host ints with the meaning they have in cbp_singletons. */
+#define CBP_NOALLOC_MAX_COLS 262144
+CBP_API int cbp_singletons_noalloc(int m, int n, const int64_t *rowStart, const int *rowLen,
+  const int *colIdx, const double *val, const char *rowSense, const double *rhs, const double *range,
+  const char *colType, double infinity, double *lb, double *ub, double primalTol, int *nTightened,
+  int *nFixed, void *cudaStream);
+
 /* Diagnostic: device timestamps (ns since the loop started, as seen by CTA 0) of the last
  * cbp_propagate: for each of the first rounds, after the row phase, after the long-row phase,
  * after the settle phase and after the stop decision; out gets 4 values per round.  Returns the
