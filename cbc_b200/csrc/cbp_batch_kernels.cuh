@@ -534,42 +534,74 @@ __global__ void bt_transpose_out_kernel(const BtParams p, int B, double *lb, dou
   }
 }
 
-// sparse answer, pass 1: how many columns each feasible vector changed
-__global__ void bt_count_updates_kernel(const BtParams p, int B, long long *count)
+// ---- sparse answer (updatedBounds() per vector) ------------------------------
+// `ever` is almost empty, so the scan is organised to skip it fast: a warp owns
+// (vector group, chunk of kUpdChunk columns); its lanes read the marks of 32
+// columns at a time, one word each, and only words that are not zero are looked
+// at bit by bit (lane = vector).  Pass 1 counts per (chunk, vector), a tiny
+// prefix kernel turns the counts into offsets, pass 2 writes (col, lb, ub) in
+// ascending column order.
+constexpr int kUpdChunk = 1024;
+
+template <bool kFill>
+__global__ void bt_updates_kernel(const BtParams p, int B, int *chunkCnt, const long long *__restrict__ start,
+  int *updCol, double *updLb, double *updUb)
+{
+  const int g = blockIdx.x, chunk = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  const int c0 = chunk * kUpdChunk, c1 = min(p.n, c0 + kUpdChunk);
+  if (c0 >= p.n)
+    return;
+  const int b = g * 32 + lane;
+  const bool live = b < B && p.vecStop[b] != 4;  // a vector proved infeasible lists nothing
+  const unsigned *e = p.ever + g;
+  const size_t slot = static_cast<size_t>(chunk) * p.Bp + b;
+  long long at = 0;
+  const Bnd *X = nullptr;
+  if (kFill && live) {
+    at = start[b] + chunkCnt[slot];
+    X = p.X[p.vecFinal[b]] + b;
+  }
+  int cnt = 0;
+  for (int j0 = c0; j0 < c1; j0 += 32) {
+    const int j = j0 + lane;
+    const unsigned word = j < c1 ? e[static_cast<size_t>(j) * p.G] : 0u;
+    unsigned any = __ballot_sync(0xffffffffu, word != 0u);
+    while (any) {
+      const int sl = __ffs(any) - 1;
+      any &= any - 1;
+      const unsigned w = __shfl_sync(0xffffffffu, word, sl);
+      if (live && ((w >> lane) & 1u)) {
+        if (kFill) {
+          const int col = j0 + sl;
+          const Bnd x = X[static_cast<size_t>(col) * p.Bp];
+          updCol[at] = col;
+          updLb[at] = x.lb;
+          updUb[at] = x.ub;
+          ++at;
+        }
+        ++cnt;
+      }
+    }
+  }
+  if (!kFill)
+    chunkCnt[slot] = cnt;
+}
+
+// per vector: exclusive prefix of its chunk counts (in place) and its total
+__global__ void bt_updates_prefix_kernel(int *chunkCnt, int nChunks, int Bp, int B, long long *count)
 {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B)
     return;
-  long long c = 0;
-  if (p.vecStop[b] != 4) {
-    const unsigned *e = p.ever + (b >> 5);
-    const unsigned bit = 1u << (b & 31);
-    for (int j = 0; j < p.n; ++j)
-      c += (e[static_cast<size_t>(j) * p.G] & bit) ? 1 : 0;
+  long long run = 0;
+  for (int c = 0; c < nChunks; ++c) {
+    const size_t slot = static_cast<size_t>(c) * Bp + b;
+    const int v = chunkCnt[slot];
+    chunkCnt[slot] = static_cast<int>(run);
+    run += v;
   }
-  count[b] = c;
-}
-
-// pass 2: columns in ascending order, as updatedBounds() pairs (col, (lb, ub))
-__global__ void bt_fill_updates_kernel(const BtParams p, int B, const long long *__restrict__ start,
-  int *updCol, double *updLb, double *updUb)
-{
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B || p.vecStop[b] == 4)
-    return;
-  const unsigned *e = p.ever + (b >> 5);
-  const unsigned bit = 1u << (b & 31);
-  const Bnd *X = p.X[p.vecFinal[b]] + b;
-  long long at = start[b];
-  for (int j = 0; j < p.n; ++j) {
-    if (e[static_cast<size_t>(j) * p.G] & bit) {
-      const Bnd x = X[static_cast<size_t>(j) * p.Bp];
-      updCol[at] = j;
-      updLb[at] = x.lb;
-      updUb[at] = x.ub;
-      ++at;
-    }
-  }
+  count[b] = run;
 }
 
 }  // namespace cbp

@@ -41,6 +41,7 @@ struct BatchState {
   unsigned *ever = nullptr, *active = nullptr;
   int *ints = nullptr;  // 7 arrays of Bp ints + anyActive
   long long *counts = nullptr;  // B+1
+  int *chunkCnt = nullptr;      // [ceil(n / kUpdChunk)][Bp] update counts / offsets
   // loaded input (device copies) so the batch can be re-expanded
   double *baseLb = nullptr, *baseUb = nullptr;
   long long *dStart = nullptr;
@@ -220,7 +221,7 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->longRowsBt, mat->sellVal, mat->sellCol, mat->sellOff, mat->longPart, mat->X[0],
     mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
-    mat->bt.ints, mat->bt.counts, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
+    mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd };
   for (void *p : ptrs)
     if (p)
@@ -762,7 +763,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
   const int Bp = (B + 31) / 32 * 32;
   const size_t cells = static_cast<size_t>(mat->n) * Bp;
   if (cells > bt.capCells || Bp > bt.capBp) {
-    void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts };
+    void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt };
     for (void *p : old)
       if (p)
         cudaFree(p);
@@ -770,6 +771,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.dirty[0] = bt.dirty[1] = bt.ever = bt.active = nullptr;
     bt.ints = nullptr;
     bt.counts = nullptr;
+    bt.chunkCnt = nullptr;
     bt.capCells = 0;
     bt.capBp = 0;
     const size_t words = cells / 32;
@@ -777,7 +779,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
       || dalloc(&bt.dirty[0], words) != cudaSuccess || dalloc(&bt.dirty[1], words) != cudaSuccess
       || dalloc(&bt.ever, words) != cudaSuccess || dalloc(&bt.active, Bp / 32) != cudaSuccess
       || dalloc(&bt.ints, static_cast<size_t>(Bp) * 7 + 8) != cudaSuccess
-      || dalloc(&bt.counts, static_cast<size_t>(Bp) + 1) != cudaSuccess) {
+      || dalloc(&bt.counts, static_cast<size_t>(Bp) + 1) != cudaSuccess
+      || dalloc(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp) != cudaSuccess) {
       ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
       return CBP_ERR_NOMEM;
     }
@@ -1086,8 +1089,12 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
   if (!updStart)
     return CBP_OK;
   const BtParams p = bt_params(mat, 0.0);
-  bt_count_updates_kernel<<<cdiv(bt.B, 64), 64, 0, ctx->stream>>>(p, bt.B, bt.counts);
-  ++ctx->stats.kernelLaunches;
+  const int nChunks = cdiv(mat->n, kUpdChunk);
+  const dim3 updGrid(bt.G, cdiv(nChunks, 4)), updBlock(128);
+  bt_updates_kernel<false><<<updGrid, updBlock, 0, ctx->stream>>>(p, bt.B, bt.chunkCnt, nullptr, nullptr, nullptr,
+    nullptr);
+  bt_updates_prefix_kernel<<<cdiv(bt.B, 128), 128, 0, ctx->stream>>>(bt.chunkCnt, nChunks, bt.Bp, bt.B, bt.counts);
+  ctx->stats.kernelLaunches += 2;
   std::vector<long long> cnt(bt.B + 1);
   CK(cudaMemcpyAsync(cnt.data(), bt.counts, sizeof(long long) * bt.B, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
@@ -1117,7 +1124,7 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
     CK(dalloc(&dLb, run));
     CK(dalloc(&dUb, run));
   }
-  bt_fill_updates_kernel<<<cdiv(bt.B, 64), 64, 0, ctx->stream>>>(p, bt.B, bt.counts, dCol, dLb, dUb);
+  bt_updates_kernel<true><<<updGrid, updBlock, 0, ctx->stream>>>(p, bt.B, bt.chunkCnt, bt.counts, dCol, dLb, dUb);
   ++ctx->stats.kernelLaunches;
   cudaError_t e = cudaGetLastError();
   if (!dev) {
