@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libcbp.so")
+LIB_PATH = os.environ.get("CBP_LIB", os.path.join(_HERE, "lib", "libcbp.so"))  # CBP_LIB: A/B builds while tuning
 
 FLAG_DEVICE_PTRS = 1
 FLAG_RAW_ROUND = 2
