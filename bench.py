@@ -340,7 +340,8 @@ def main():
     alg = algorithmic_bytes(inst, round_launches, vec_rounds, batch)
     achieved = alg / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "bt_rows_kernel" if batch else "sv_fixpoint_kernel",
+                "traffic": None,
+                "kernel": "bt_rows_long_kernel + bt_rows_kernel (one round)" if batch else "sv_fixpoint_kernel (per round)",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                 "kernel_ms_per_launch": kernel_ms / max(1, round_launches),
                 "algorithmic_bytes_per_launch": alg / max(1, round_launches)}

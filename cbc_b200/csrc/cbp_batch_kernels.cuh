@@ -202,6 +202,115 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
   bt_walk_tighten(p, src, strideB, kb, ke, lane, stage[warp], pl, sink);
 }
 
+// Same rows, but for matrices with so many columns that the bounds of a 32-vector group
+// (n x 512 B) no longer fit in L2: a warp then owns (32/W rows, W vectors) with W = 16, 8 or 4,
+// lanes [rowSlot][vector].  Work is (group, W-slice)-major, so everything running at one time
+// touches n x W x 16 bytes of bounds, which L2 holds across all the rows that use a column
+// (each cell comes from HBM once per round instead of once per row).  Every lane walks its own
+// row in CSR order; W lanes read W x 16 contiguous bytes.
+template <int W, bool kNoInf, bool kAllInt>
+__global__ void __launch_bounds__(kThreads, 4) bt_rows_narrow_kernel(const BtParams p, int cur)
+{
+  constexpr int kRows = 32 / W;      // rows per warp
+  constexpr int kSlices = 32 / W;    // W-slices per 32-vector group
+  const int rowBlocks = (p.nShortBt + kRows - 1) / kRows;
+  const long long widx = static_cast<long long>(blockIdx.x) * kWarps + (threadIdx.x >> 5);
+  if (widx >= static_cast<long long>(p.G) * kSlices * rowBlocks)
+    return;
+  const int lane = threadIdx.x & 31;
+  const int rb = static_cast<int>(widx % rowBlocks);
+  const int gs = static_cast<int>(widx / rowBlocks);
+  const int g = gs / kSlices, slice = gs % kSlices;
+  const int vl = slice * W + (lane % W);  // this lane's vector inside the 32-group
+  const unsigned act = __ldg(&p.active[g]);
+  if (((act >> (slice * W)) & ((W == 32) ? 0xffffffffu : ((1u << W) - 1u))) == 0u)
+    return;
+  const int ri = rb * kRows + lane / W;
+  const bool haveRow = ri < p.nShortBt;
+  const bool mine = haveRow && ((act >> vl) & 1u);
+  const int r = haveRow ? __ldg(&p.shortRowsBt[ri]) : 0;
+  const int b = g * 32 + vl;
+  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + b);
+  const unsigned strideB = static_cast<unsigned>(p.Bp) * static_cast<unsigned>(sizeof(Bnd));
+  const int kb = haveRow ? __ldg(&p.rowNz[r]) : 0, cnt = haveRow ? __ldg(&p.rowCnt[r]) : 0;
+
+  // Each row slot stages its next 8 entries in shared memory (its W lanes fetch them, the entries
+  // after those are already on their way), then every lane walks the 8 entries with 8 gathers in
+  // flight.  All slots of the warp step together up to the longest of their rows.
+  __shared__ Stg stage[kWarps][kRows * 8];
+  Stg *stg = stage[threadIdx.x >> 5] + (lane / W) * 8;
+  const int maxCnt = __reduce_max_sync(0xffffffffu, cnt);
+  const int e0 = lane % W, e1 = e0 + W;  // W = 4: two entries per lane; W >= 8: one (e1 unused)
+  double na0 = 0.0, na1 = 0.0;
+  int nc0 = 0, nc1 = 0;
+  if (e0 < 8 && e0 < cnt) {
+    nc0 = __ldg(&p.col[kb + e0]);
+    na0 = __ldg(&p.val[kb + e0]);
+  }
+  if (W < 8 && e1 < cnt) {
+    nc1 = __ldg(&p.col[kb + e1]);
+    na1 = __ldg(&p.val[kb + e1]);
+  }
+  RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+  for (int base = 0; base < maxCnt; base += 8) {
+    __syncwarp();
+    if (e0 < 8) {
+      Stg e;
+      e.a = na0;
+      e.j = col_of(nc0);
+      e.isInt = col_is_int(nc0) ? 1 : 0;
+      stg[e0] = e;
+    }
+    if (W < 8) {
+      Stg e;
+      e.a = na1;
+      e.j = col_of(nc1);
+      e.isInt = col_is_int(nc1) ? 1 : 0;
+      stg[e1] = e;
+    }
+    na0 = na1 = 0.0;
+    nc0 = nc1 = 0;
+    if (e0 < 8 && base + 8 + e0 < cnt) {
+      nc0 = __ldg(&p.col[kb + base + 8 + e0]);
+      na0 = __ldg(&p.val[kb + base + 8 + e0]);
+    }
+    if (W < 8 && base + 8 + e1 < cnt) {
+      nc1 = __ldg(&p.col[kb + base + 8 + e1]);
+      na1 = __ldg(&p.val[kb + base + 8 + e1]);
+    }
+    __syncwarp();
+    Bnd x[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)  // entries past the row's end are (0, column 0): a harmless gather
+      x[u] = ldcg_bnd(reinterpret_cast<const Bnd *>(
+        src + static_cast<unsigned long long>(static_cast<unsigned>(stg[u].j)) * strideB));
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const double a = stg[u].a;
+      if (a != 0.0)
+        bt_acc<kNoInf, 0>(ra, a, kAllInt ? true : stg[u].isInt != 0, x[u], p.s.inf);
+    }
+  }
+  RowPlan pl = plan_row(ra, haveRow ? __ldg(&p.rowLB[r]) : 0.0, haveRow ? __ldg(&p.rowUB[r]) : 0.0, p.s);
+  if (!mine) {
+    pl.infeasible = false;
+    pl.sideU = false;
+    pl.sideL = false;
+  }
+  if (pl.infeasible)
+    atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
+  if (pl.sideU || pl.sideL) {
+    BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, static_cast<size_t>(p.Bp), p.G, 1u << vl };
+    for (int k = 0; k < cnt; ++k) {
+      const int c = __ldg(&p.col[kb + k]);
+      const double a = __ldg(&p.val[kb + k]);
+      const int j = col_of(c);
+      const Bnd x = ldcg_bnd(reinterpret_cast<const Bnd *>(src + static_cast<unsigned long long>(static_cast<unsigned>(j)) * strideB));
+      tighten_nz(sink, pl, a, j, col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+    }
+  }
+}
+
 // Rows longer than kBtLongLen: a CTA owns (row, group); its 8 warps split the
 // row into 8 contiguous pieces, the partial activities are combined in warp
 // order through shared memory.  With a whole CTA per row the CTAs in flight

@@ -9,6 +9,7 @@
 #include <climits>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -988,12 +989,39 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       ++ctx->stats.kernelLaunches;
     }
     if (warps > 0) {
-      switch (variant) {
-      case 0: bt_rows_kernel<false, false><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
-      case 1: bt_rows_kernel<false, true><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
-      case 2: bt_rows_kernel<true, false><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
-      default: bt_rows_kernel<true, true><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+      // vectors per warp: the widest slice whose bounds (n x W x 16 B) stay well inside L2
+      const double lineBytes = 16.0 * mat->n;
+      static const double budget = getenv("CBP_L2_BUDGET_MB") ? atof(getenv("CBP_L2_BUDGET_MB")) * 1e6 : 48e6;
+      const int W = lineBytes * 32 <= budget ? 32 : (lineBytes * 16 <= budget ? 16 : (lineBytes * 8 <= budget ? 8 : 4));
+      const int rowsPerWarp = 32 / W;
+      const long long narrowWarps = static_cast<long long>(bt.G) * rowsPerWarp * cdiv(mat->nShortBt, rowsPerWarp);
+      if (narrowWarps / kWarps > INT_MAX) {
+        ctx->err = "cbp_batch_run: batch too large for one launch";
+        return CBP_ERR_ARG;
       }
+      const int narrowGrid = cdiv(narrowWarps, kWarps);
+#define CBP_NARROW(WW)                                                                                      \
+  switch (variant) {                                                                                        \
+  case 0: bt_rows_narrow_kernel<WW, false, false><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;            \
+  case 1: bt_rows_narrow_kernel<WW, false, true><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;             \
+  case 2: bt_rows_narrow_kernel<WW, true, false><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;             \
+  default: bt_rows_narrow_kernel<WW, true, true><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;             \
+  }
+      if (W == 32) {
+        switch (variant) {
+        case 0: bt_rows_kernel<false, false><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+        case 1: bt_rows_kernel<false, true><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+        case 2: bt_rows_kernel<true, false><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+        default: bt_rows_kernel<true, true><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+        }
+      } else if (W == 16) {
+        CBP_NARROW(16)
+      } else if (W == 8) {
+        CBP_NARROW(8)
+      } else {
+        CBP_NARROW(4)
+      }
+#undef CBP_NARROW
       ++ctx->stats.kernelLaunches;
     }
     CK(cudaEventRecord(ctx->evPool[1], st));

@@ -227,6 +227,29 @@ def test_batch_base_needs_rounding(oracle, gpu_ctx):
     _check_batch(oracle, gpu_ctx, inst, s, v, b, "fractional base")
 
 
+@pytest.mark.parametrize("n,m", [(100_000, 40_000), (300_000, 120_000), (700_000, 280_000)])
+def test_batch_wide_matrices_use_narrow_vector_slices(oracle, gpu_ctx, n, m):
+    """More columns than a 32-vector group's bounds fit in L2 for: the engine switches to 16-, 8- and 4-vector
+    slices per warp (bt_rows_narrow_kernel); results must not depend on that choice."""
+    inst = I.knapsack_assignment(m=m, n=n, seed=55)
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 37, max_depth=40, seed=56)
+    mat = capi.Matrix(gpu_ctx, inst)
+    res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)
+    ores, Lo, Uo = oracle.propagate_batch_delta(oracle.Problem(inst), inst.lb, inst.ub, s, v, b, threads=8)
+    for k in ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason"):
+        assert np.array_equal(res[k], ores[k]), k
+    L0, U0 = I.expand_deltas(inst.lb, inst.ub, s, v, b)
+    for k in range(37):
+        cols = uc[us[k]:us[k + 1]]
+        if not res["feasible"][k]:
+            continue
+        want = np.flatnonzero((Lo[k] != L0[k]) | (Uo[k] != U0[k]))
+        assert np.array_equal(cols, want)
+        assert np.array_equal(ul[us[k]:us[k + 1]], Lo[k][want]) and np.array_equal(uu[us[k]:us[k + 1]], Uo[k][want])
+    assert res["nChanged"].sum() > 0 and (~res["feasible"].astype(bool)).any()
+    mat.close()
+
+
 def test_fixpoint_is_idempotent_at_size(gpu_ctx):
     """Size-independent property on a larger instance: propagating a fixpoint again changes nothing
     and takes exactly one round; the planted point survives."""
