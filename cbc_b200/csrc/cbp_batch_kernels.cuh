@@ -1,13 +1,16 @@
 // cbp_batch_kernels.cuh — B bound vectors over one matrix.
 //
-// Layout in HBM: bounds are [column][vector] (Bnd = {lb, ub}, 16 B), the
-// vector count padded to a multiple of 32, so the 32 lanes of a warp read the
-// 32 vectors of one column as one contiguous 512-byte line.  A warp owns
-// (row, group of 32 vectors); the row's (a, j) pairs are warp-uniform, so the
-// matrix is fetched once per warp while every lane accumulates its own
-// vector's activities sequentially in CSR order — bit-for-bit the order of the
-// CPU restatement.  Two bound buffers give Jacobi rounds; accepted candidates
-// are atomic min/max on the other buffer plus a dirty bit per (column, vector).
+// Layout in HBM ("slice-major"): the vectors are cut into slices of W (32, 16, 8 or 4, chosen
+// when the batch is loaded); inside a slice the bounds are [column][vector]:
+//     cell(j, b) = ((b / W) * n + j) * W + b % W,      each cell a Bnd = {lb, ub} (16 B).
+// The W lanes that own a slice read the W vectors of one column as one contiguous W x 16-byte
+// piece (512 B for W = 32), consecutive columns are adjacent, and everything that runs at one
+// time touches one or two slices — a compact range for L2 and the TLB.  The marks (dirty /
+// ever) are one 32-bit word per (32-vector group, column), group-major.
+// A warp owns rows x vectors; the matrix entries are shared by its lanes while every lane
+// accumulates its own vector's activities sequentially in CSR order — bit for bit the order of
+// the CPU restatement.  Two bound buffers give Jacobi rounds; accepted candidates are atomic
+// min/max on the other buffer plus a mark per (column, vector).
 #pragma once
 #include "cbp_device.cuh"
 
@@ -25,9 +28,10 @@ struct BtParams {
   const int *shortRowsBt, *longRowsBt;  // kept-row indices by batch class
   int nShortBt, nLongBt;
   int mKept, n, Bp, G;  // Bp = padded vector count, G = Bp / 32
+  int W;                // vectors per slice
   Bnd *X[2];
-  unsigned *dirty[2];   // [n][G]
-  unsigned *ever;       // [n][G] union of the dirty marks of applied rounds
+  unsigned *dirty[2];   // [G][n]
+  unsigned *ever;       // [G][n] union of the marks of applied rounds
   unsigned *active;     // [G]
   int *vecInfRow, *vecInfCol;  // [Bp] min violating row / crossing column (INT_MAX none)
   int *vecChanged;             // [Bp] changed columns in the running round
@@ -36,21 +40,34 @@ struct BtParams {
   Scal s;
 };
 
+// first cell (column 0) of vector b; column j is W cells further per column
+__device__ __forceinline__ size_t bt_base(const BtParams &p, int b)
+{
+  return (static_cast<size_t>(b / p.W) * p.n) * p.W + (b % p.W);
+}
+__device__ __forceinline__ size_t bt_cell(const BtParams &p, int j, int b)
+{
+  return bt_base(p, b) + static_cast<size_t>(j) * p.W;
+}
+__device__ __forceinline__ size_t bt_word(const BtParams &p, int j, int g)
+{
+  return static_cast<size_t>(g) * p.n + j;
+}
+
 struct BtSink {
-  Bnd *dst;         // already offset to this lane's vector: dst[j * Bp]
-  unsigned *dirty;  // already offset to this warp's group: dirty[j * G]
-  size_t Bp;
-  int G;
+  Bnd *dst;         // already at this lane's vector, column 0
+  unsigned *dirty;  // already at this warp's group, column 0
+  int W;
   unsigned bit;
   __device__ __forceinline__ void ub(int j, double v)
   {
-    atomic_min_f64(&dst[static_cast<size_t>(j) * Bp].ub, v);
-    atomicOr(&dirty[static_cast<size_t>(j) * G], bit);
+    atomic_min_f64(&dst[static_cast<size_t>(j) * W].ub, v);
+    atomicOr(&dirty[j], bit);
   }
   __device__ __forceinline__ void lb(int j, double v)
   {
-    atomic_max_f64(&dst[static_cast<size_t>(j) * Bp].lb, v);
-    atomicOr(&dirty[static_cast<size_t>(j) * G], bit);
+    atomic_max_f64(&dst[static_cast<size_t>(j) * W].lb, v);
+    atomicOr(&dirty[j], bit);
   }
 };
 
@@ -182,8 +199,8 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
     return;
   const bool mine = (act >> lane) & 1u;
   const int b = g * 32 + lane;
-  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + b);
-  const unsigned strideB = static_cast<unsigned>(p.Bp) * static_cast<unsigned>(sizeof(Bnd));
+  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + bt_base(p, b));
+  const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
   const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
 
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
@@ -198,7 +215,7 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
     atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
   if (!__any_sync(0xffffffffu, pl.sideU || pl.sideL))
     return;
-  BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, static_cast<size_t>(p.Bp), p.G, 1u << lane };
+  BtSink sink = { p.X[cur ^ 1] + bt_base(p, b), p.dirty[cur] + bt_word(p, 0, g), p.W, 1u << lane };
   bt_walk_tighten(p, src, strideB, kb, ke, lane, stage[warp], pl, sink);
 }
 
@@ -230,8 +247,8 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_narrow_kernel(const BtPar
   const bool mine = haveRow && ((act >> vl) & 1u);
   const int r = haveRow ? __ldg(&p.shortRowsBt[ri]) : 0;
   const int b = g * 32 + vl;
-  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + b);
-  const unsigned strideB = static_cast<unsigned>(p.Bp) * static_cast<unsigned>(sizeof(Bnd));
+  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + bt_base(p, b));
+  const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
   const int kb = haveRow ? __ldg(&p.rowNz[r]) : 0, cnt = haveRow ? __ldg(&p.rowCnt[r]) : 0;
 
   // Each row slot stages its next 8 entries in shared memory (its W lanes fetch them, the entries
@@ -300,7 +317,7 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_narrow_kernel(const BtPar
   if (pl.infeasible)
     atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
   if (pl.sideU || pl.sideL) {
-    BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, static_cast<size_t>(p.Bp), p.G, 1u << vl };
+    BtSink sink = { p.X[cur ^ 1] + bt_base(p, b), p.dirty[cur] + bt_word(p, 0, g), p.W, 1u << vl };
     for (int k = 0; k < cnt; ++k) {
       const int c = __ldg(&p.col[kb + k]);
       const double a = __ldg(&p.val[kb + k]);
@@ -329,8 +346,8 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParam
     return;
   const bool mine = (act >> lane) & 1u;
   const int b = g * 32 + lane;
-  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + b);
-  const unsigned strideB = static_cast<unsigned>(p.Bp) * static_cast<unsigned>(sizeof(Bnd));
+  const char *__restrict__ src = reinterpret_cast<const char *>(p.X[cur] + bt_base(p, b));
+  const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
   const int kb = __ldg(&p.rowNz[r]), cnt = __ldg(&p.rowCnt[r]);
   const int ksplit = kb + __ldg(&p.rowPos[r]);              // first negative coefficient
   const int per = ((cnt + kWarps - 1) / kWarps + 31) & ~31;  // 32-aligned pieces
@@ -355,12 +372,12 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParam
     atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
   if (!__syncthreads_or(pl.sideU || pl.sideL))
     return;
-  BtSink sink = { p.X[cur ^ 1] + b, p.dirty[cur] + g, static_cast<size_t>(p.Bp), p.G, 1u << lane };
+  BtSink sink = { p.X[cur ^ 1] + bt_base(p, b), p.dirty[cur] + bt_word(p, 0, g), p.W, 1u << lane };
   bt_walk_tighten(p, src, strideB, wb, we, lane, stage[warp], pl, sink);
 }
 
 // After the rows phase: settle every (column, vector) marked in this round
-// (R9), count changed columns per vector.  One thread per dirty word.
+// (R9), count changed columns per vector.  One thread per mark word.
 __global__ void bt_settle_kernel(const BtParams p, int cur)
 {
   const size_t nW = static_cast<size_t>(p.n) * p.G;
@@ -370,20 +387,18 @@ __global__ void bt_settle_kernel(const BtParams p, int cur)
   unsigned bits = p.dirty[cur][w];
   if (!bits)
     return;
-  const int j = static_cast<int>(w / p.G), g = static_cast<int>(w % p.G);
-  const size_t base = static_cast<size_t>(j) * p.Bp + static_cast<size_t>(g) * 32;
-  const Bnd *src = p.X[cur] + base;
-  Bnd *dst = p.X[cur ^ 1] + base;
+  const int g = static_cast<int>(w / p.n), j = static_cast<int>(w % p.n);
   while (bits) {
     const int l = __ffs(bits) - 1;
     bits &= bits - 1;
-    Bnd x = dst[l];
-    const double L0 = x.lb, U0 = x.ub;
     const int b = g * 32 + l;
-    if (settle(x.lb, x.ub, src[l].ub, p.s))
+    const size_t at = bt_cell(p, j, b);
+    Bnd x = p.X[cur ^ 1][at];
+    const double L0 = x.lb, U0 = x.ub;
+    if (settle(x.lb, x.ub, p.X[cur][at].ub, p.s))
       atomicMin(&p.vecInfCol[b], j);
     else if (x.lb != L0 || x.ub != U0)
-      dst[l] = x;
+      p.X[cur ^ 1][at] = x;
     atomicAdd(&p.vecChanged[b], 1);
   }
 }
@@ -444,10 +459,7 @@ __global__ void bt_carry_kernel(const BtParams p, int cur)
   if (!bits0)
     return;
   p.dirty[cur][w] = 0u;
-  const int j = static_cast<int>(w / p.G), g = static_cast<int>(w % p.G);
-  const size_t base = static_cast<size_t>(j) * p.Bp + static_cast<size_t>(g) * 32;
-  Bnd *stale = p.X[cur] + base;
-  const Bnd *fresh = p.X[cur ^ 1] + base;
+  const int g = static_cast<int>(w / p.n), j = static_cast<int>(w % p.n);
   // a vector's round was applied iff it is still running or stopped with the
   // new buffer as its answer
   unsigned applied = 0u;
@@ -458,8 +470,10 @@ __global__ void bt_carry_kernel(const BtParams p, int cur)
     bits &= bits - 1;
     const int b = g * 32 + l;
     const bool running = (act >> l) & 1u;
-    if (running)
-      stale[l] = fresh[l];
+    if (running) {
+      const size_t at = bt_cell(p, j, b);
+      p.X[cur][at] = p.X[cur ^ 1][at];
+    }
     if (running || p.vecFinal[b] == (cur ^ 1))
       applied |= 1u << l;
   }
@@ -483,12 +497,12 @@ __global__ void bt_base_check_kernel(const double *__restrict__ baseLb, const do
 
 // every vector starts from the base bounds; both buffers are written
 __global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double *__restrict__ baseUb,
-  int n, size_t Bp, Bnd *X0, Bnd *X1)
+  int n, int W, size_t cells, Bnd *X0, Bnd *X1)
 {
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= static_cast<size_t>(n) * Bp)
+  if (i >= cells)
     return;
-  const int j = static_cast<int>(i / Bp);
+  const int j = static_cast<int>((i / W) % n);
   Bnd x;
   x.lb = __ldg(&baseLb[j]);
   x.ub = __ldg(&baseUb[j]);
@@ -505,11 +519,10 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B)
     return;
-  const size_t Bp = static_cast<size_t>(p.Bp);
   const long long k0 = start[b], k1 = start[b + 1];
   for (long long k = k0; k < k1; ++k) {
     const unsigned v = var[k];
-    const size_t at = static_cast<size_t>(v & 0x7fffffffu) * Bp + b;
+    const size_t at = bt_cell(p, static_cast<int>(v & 0x7fffffffu), b);
     Bnd x = p.X[0][at];
     if (v & 0x80000000u)
       x.ub = bnd[k];
@@ -522,24 +535,25 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
     return;
   for (long long k = k0; k < k1; ++k) {
     const int j = static_cast<int>(var[k] & 0x7fffffffu);
-    const size_t at = static_cast<size_t>(j) * Bp + b;
+    const size_t at = bt_cell(p, j, b);
     Bnd x = p.X[0][at];
     const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);
     if (r == 2)
       atomicMin(&p.vecInfCol[b], j);
     else if (r == 1) {
-      atomicOr(&p.dirty[0][static_cast<size_t>(j) * p.G + (b >> 5)], 1u << (b & 31));
+      atomicOr(&p.dirty[0][bt_word(p, j, b >> 5)], 1u << (b & 31));
       p.X[0][at] = x;
       p.X[1][at] = x;
     }
   }
 }
 
-// dense input, B x n row-major per vector -> [column][vector]; 32x32 tiles
+// dense input, B x n row-major per vector -> slice-major cells; 32x32 tiles
 __global__ void bt_transpose_in_kernel(const double *__restrict__ lb, const double *__restrict__ ub,
-  int B, int n, size_t Bp, Bnd *X0, double padLb, double padUb)
+  int B, const BtParams p, double padLb, double padUb)
 {
   __shared__ double tl[32][33], tu[32][33];
+  const int n = p.n;
   const int j0 = blockIdx.x * 32, b0 = blockIdx.y * 32;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
     const int b = b0 + i, j = j0 + threadIdx.x;
@@ -554,7 +568,7 @@ __global__ void bt_transpose_in_kernel(const double *__restrict__ lb, const doub
       Bnd x;
       x.lb = tl[threadIdx.x][i];
       x.ub = tu[threadIdx.x][i];
-      X0[static_cast<size_t>(j) * Bp + b] = x;
+      p.X[0][bt_cell(p, j, b)] = x;
     }
   }
 }
@@ -563,17 +577,18 @@ __global__ void bt_transpose_in_kernel(const double *__restrict__ lb, const doub
 __global__ void bt_prepass_kernel(const BtParams p, int B)
 {
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const size_t Bp = static_cast<size_t>(p.Bp);
-  if (i >= static_cast<size_t>(p.n) * Bp)
+  if (i >= static_cast<size_t>(p.n) * p.Bp)
     return;
-  const int j = static_cast<int>(i / Bp), b = static_cast<int>(i % Bp);
+  const int v = static_cast<int>(i % p.W);
+  const int j = static_cast<int>((i / p.W) % p.n);
+  const int b = static_cast<int>(i / (static_cast<size_t>(p.W) * p.n)) * p.W + v;
   Bnd x = p.X[0][i];
   if (b < B) {
     const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);
     if (r == 2)
       atomicMin(&p.vecInfCol[b], j);
     else if (r == 1) {
-      atomicOr(&p.dirty[0][static_cast<size_t>(j) * p.G + (b >> 5)], 1u << (b & 31));
+      atomicOr(&p.dirty[0][bt_word(p, j, b >> 5)], 1u << (b & 31));
       p.X[0][i] = x;
     }
   }
@@ -619,16 +634,15 @@ __global__ void bt_init_state_kernel(const BtParams p, int B)
 
 // ---- fetching -------------------------------------------------------------------
 
-// dense answer: [column][vector] of each vector's final buffer -> B x n row-major
+// dense answer: each vector's final buffer -> B x n row-major
 __global__ void bt_transpose_out_kernel(const BtParams p, int B, double *lb, double *ub)
 {
   __shared__ double tl[32][33], tu[32][33];
   const int j0 = blockIdx.x * 32, b0 = blockIdx.y * 32;
-  const size_t Bp = static_cast<size_t>(p.Bp);
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
     const int j = j0 + i, b = b0 + threadIdx.x;
     if (j < p.n && b < B) {
-      const Bnd x = p.X[p.vecFinal[b]][static_cast<size_t>(j) * Bp + b];
+      const Bnd x = p.X[p.vecFinal[b]][bt_cell(p, j, b)];
       tl[i][threadIdx.x] = x.lb;
       tu[i][threadIdx.x] = x.ub;
     }
@@ -663,18 +677,18 @@ __global__ void bt_updates_kernel(const BtParams p, int B, int *chunkCnt, const 
     return;
   const int b = g * 32 + lane;
   const bool live = b < B && p.vecStop[b] != 4;  // a vector proved infeasible lists nothing
-  const unsigned *e = p.ever + g;
+  const unsigned *e = p.ever + bt_word(p, 0, g);
   const size_t slot = static_cast<size_t>(chunk) * p.Bp + b;
   long long at = 0;
   const Bnd *X = nullptr;
   if (kFill && live) {
     at = start[b] + chunkCnt[slot];
-    X = p.X[p.vecFinal[b]] + b;
+    X = p.X[p.vecFinal[b]] + bt_base(p, b);
   }
   int cnt = 0;
   for (int j0 = c0; j0 < c1; j0 += 32) {
     const int j = j0 + lane;
-    const unsigned word = j < c1 ? e[static_cast<size_t>(j) * p.G] : 0u;
+    const unsigned word = j < c1 ? e[j] : 0u;
     unsigned any = __ballot_sync(0xffffffffu, word != 0u);
     while (any) {
       const int sl = __ffs(any) - 1;
@@ -683,7 +697,7 @@ __global__ void bt_updates_kernel(const BtParams p, int B, int *chunkCnt, const 
       if (live && ((w >> lane) & 1u)) {
         if (kFill) {
           const int col = j0 + sl;
-          const Bnd x = X[static_cast<size_t>(col) * p.Bp];
+          const Bnd x = X[static_cast<size_t>(col) * p.W];
           updCol[at] = col;
           updLb[at] = x.lb;
           updUb[at] = x.ub;

@@ -36,6 +36,7 @@ struct cbp_ctx {
 
 struct BatchState {
   int B = 0, Bp = 0, G = 0;
+  int W = 32;  // vectors per slice of the slice-major bounds layout
   size_t cells = 0;  // n * Bp
   Bnd *X[2] = { nullptr, nullptr };
   unsigned *dirty[2] = { nullptr, nullptr };
@@ -798,6 +799,12 @@ static int bt_reserve(cbp_matrix *mat, int B)
   bt.Bp = Bp;
   bt.G = Bp / 32;
   bt.cells = cells;
+  // slice width: the widest W whose slice (n x W x 16 bytes of bounds) stays well inside L2
+  {
+    static const double budget = getenv("CBP_L2_BUDGET_MB") ? atof(getenv("CBP_L2_BUDGET_MB")) * 1e6 : 48e6;
+    const double lineBytes = 16.0 * mat->n;
+    bt.W = lineBytes * 32 <= budget ? 32 : (lineBytes * 16 <= budget ? 16 : (lineBytes * 8 <= budget ? 8 : 4));
+  }
   return CBP_OK;
 }
 
@@ -822,6 +829,7 @@ static BtParams bt_params(cbp_matrix *mat, double tol)
   p.n = mat->n;
   p.Bp = bt.Bp;
   p.G = bt.G;
+  p.W = bt.W;
   p.X[0] = bt.X[0];
   p.X[1] = bt.X[1];
   p.dirty[0] = bt.dirty[0];
@@ -934,7 +942,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     bt_base_check_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->colType, mat->n, p.s,
       p.anyActive);
     CK(cudaMemcpyAsync(&need, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));
-    bt_expand_kernel<<<cellGrid, 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.Bp, bt.X[0], bt.X[1]);
+    bt_expand_kernel<<<cellGrid, 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.W, bt.cells, bt.X[0], bt.X[1]);
     ctx->stats.kernelLaunches += 2;
     CK(cudaStreamSynchronize(st));
     fullPrepass = need != 0;
@@ -989,10 +997,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       ++ctx->stats.kernelLaunches;
     }
     if (warps > 0) {
-      // vectors per warp: the widest slice whose bounds (n x W x 16 B) stay well inside L2
-      const double lineBytes = 16.0 * mat->n;
-      static const double budget = getenv("CBP_L2_BUDGET_MB") ? atof(getenv("CBP_L2_BUDGET_MB")) * 1e6 : 48e6;
-      const int W = lineBytes * 32 <= budget ? 32 : (lineBytes * 16 <= budget ? 16 : (lineBytes * 8 <= budget ? 8 : 4));
+      const int W = bt.W;  // vectors per warp = slice width of the layout
       const int rowsPerWarp = 32 / W;
       const long long narrowWarps = static_cast<long long>(bt.G) * rowsPerWarp * cdiv(mat->nShortBt, rowsPerWarp);
       if (narrowWarps / kWarps > INT_MAX) {
@@ -1244,7 +1249,7 @@ int cbp_propagate_batch(cbp_matrix *mat, int B, double *lb, double *ub, double p
     }
   }
   dim3 grid(cdiv(mat->n, 32), bt.Bp / 32), block(32, 8);
-  bt_transpose_in_kernel<<<grid, block, 0, ctx->stream>>>(dl, du, B, mat->n, bt.Bp, bt.X[0], 0.0, 0.0);
+  bt_transpose_in_kernel<<<grid, block, 0, ctx->stream>>>(dl, du, B, bt_params(mat, primalTol), 0.0, 0.0);
   ++ctx->stats.kernelLaunches;
   bt.loaded = true;
   bt.denseLoaded = true;
