@@ -801,7 +801,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
   bt.cells = cells;
   // slice width: the widest W whose slice (n x W x 16 bytes of bounds) stays well inside L2
   {
-    static const double budget = getenv("CBP_L2_BUDGET_MB") ? atof(getenv("CBP_L2_BUDGET_MB")) * 1e6 : 48e6;
+    static const double budget = getenv("CBP_L2_BUDGET_MB") ? atof(getenv("CBP_L2_BUDGET_MB")) * 1e6 : 1e15;  // measured so far: W = 32 wins (profiles/README.md)
     const double lineBytes = 16.0 * mat->n;
     bt.W = lineBytes * 32 <= budget ? 32 : (lineBytes * 16 <= budget ? 16 : (lineBytes * 8 <= budget ? 8 : 4));
   }

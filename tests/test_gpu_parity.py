@@ -228,26 +228,33 @@ def test_batch_base_needs_rounding(oracle, gpu_ctx):
 
 
 @pytest.mark.parametrize("n,m", [(100_000, 40_000), (300_000, 120_000), (700_000, 280_000)])
-def test_batch_wide_matrices_use_narrow_vector_slices(oracle, gpu_ctx, n, m):
-    """More columns than a 32-vector group's bounds fit in L2 for: the engine switches to 16-, 8- and 4-vector
-    slices per warp (bt_rows_narrow_kernel); results must not depend on that choice."""
-    inst = I.knapsack_assignment(m=m, n=n, seed=55)
-    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 37, max_depth=40, seed=56)
-    mat = capi.Matrix(gpu_ctx, inst)
-    res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)
-    ores, Lo, Uo = oracle.propagate_batch_delta(oracle.Problem(inst), inst.lb, inst.ub, s, v, b, threads=8)
-    for k in ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason"):
-        assert np.array_equal(res[k], ores[k]), k
-    L0, U0 = I.expand_deltas(inst.lb, inst.ub, s, v, b)
-    for k in range(37):
-        cols = uc[us[k]:us[k + 1]]
-        if not res["feasible"][k]:
-            continue
-        want = np.flatnonzero((Lo[k] != L0[k]) | (Uo[k] != U0[k]))
-        assert np.array_equal(cols, want)
-        assert np.array_equal(ul[us[k]:us[k + 1]], Lo[k][want]) and np.array_equal(uu[us[k]:us[k + 1]], Uo[k][want])
-    assert res["nChanged"].sum() > 0 and (~res["feasible"].astype(bool)).any()
-    mat.close()
+def test_batch_wide_matrices_use_narrow_vector_slices(oracle, gpu_ctx, n, m, monkeypatch):
+    """Slice widths 16, 8 and 4 of the slice-major layout (bt_rows_narrow_kernel), forced through the
+    CBP_L2_BUDGET_MB knob (the default keeps W = 32); results must not depend on the width."""
+    import subprocess
+    import sys
+    import os
+
+    # the knob is read once per process: run this case in a child process with the knob set
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from cbc_b200 import capi, instances as I; from oracle import oracle_py as O\n"
+        "inst = I.knapsack_assignment(m=%d, n=%d, seed=55)\n"
+        "s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 37, max_depth=40, seed=56)\n"
+        "ctx = capi.Context(); mat = capi.Matrix(ctx, inst)\n"
+        "res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)\n"
+        "Lg, Ug = mat.batch_fetch_dense()\n"
+        "ores, Lo, Uo = O.propagate_batch_delta(O.Problem(inst), inst.lb, inst.ub, s, v, b, threads=8)\n"
+        "for k in ('feasible','rounds','nChanged','infeasibleRow','infeasibleCol','stopReason'):\n"
+        "    assert np.array_equal(res[k], ores[k]), k\n"
+        "f = res['feasible'].astype(bool)\n"
+        "assert np.array_equal(Lg[f], Lo[f]) and np.array_equal(Ug[f], Uo[f])\n"
+        "assert res['nChanged'].sum() > 0 and (~f).any()\n"
+        "print('OK')\n") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                            os.path.dirname(os.path.abspath(__file__)), m, n)
+    env = dict(os.environ, CBP_L2_BUDGET_MB="48")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
 
 
 def test_fixpoint_is_idempotent_at_size(gpu_ctx):
