@@ -334,11 +334,16 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_narrow_kernel(const BtPar
 // cover only one or two vector groups, whose bounds (n x 512 B each) then stay
 // in L2 across all the rows that use them.  Such rows are stored with their
 // positive coefficients first (rowPos of them), so no per-nonzero sign test.
+#ifndef CBP_LONG_WARPS
+#define CBP_LONG_WARPS 8
+#endif
+constexpr int kLongWarps = CBP_LONG_WARPS;  // warps that share one long row
+
 template <bool kNoInf, bool kAllInt>
-__global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParams p, int cur)
+__global__ void __launch_bounds__(kLongWarps * 32, 2048 / (kLongWarps * 32) / 2) bt_rows_long_kernel(const BtParams p, int cur)
 {
-  __shared__ RowAct red[kWarps][32];
-  __shared__ Stg stage[kWarps][32];
+  __shared__ RowAct red[kLongWarps][32];
+  __shared__ Stg stage[kLongWarps][32];
   const int g = blockIdx.x / p.nLongBt, r = __ldg(&p.longRowsBt[blockIdx.x % p.nLongBt]);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned act = __ldg(&p.active[g]);
@@ -350,7 +355,7 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParam
   const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
   const int kb = __ldg(&p.rowNz[r]), cnt = __ldg(&p.rowCnt[r]);
   const int ksplit = kb + __ldg(&p.rowPos[r]);              // first negative coefficient
-  const int per = ((cnt + kWarps - 1) / kWarps + 31) & ~31;  // 32-aligned pieces
+  const int per = ((cnt + kLongWarps - 1) / kLongWarps + 31) & ~31;  // 32-aligned pieces
   const int wb = min(kb + warp * per, kb + cnt), we = min(wb + per, kb + cnt);
 
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
@@ -360,7 +365,7 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_long_kernel(const BtParam
   __syncthreads();
   RowAct tot = red[0][lane];
 #pragma unroll
-  for (int w = 1; w < kWarps; ++w)
+  for (int w = 1; w < kLongWarps; ++w)
     combine(tot, red[w][lane]);
   RowPlan pl = plan_row(tot, __ldg(&p.rowLB[r]), __ldg(&p.rowUB[r]), p.s);
   if (!mine) {

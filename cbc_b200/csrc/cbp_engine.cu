@@ -989,10 +989,10 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     if (longGrid > 0) {
       const int lg = static_cast<int>(longGrid);
       switch (variant) {
-      case 0: bt_rows_long_kernel<false, false><<<lg, kThreads, 0, st>>>(p, cur); break;
-      case 1: bt_rows_long_kernel<false, true><<<lg, kThreads, 0, st>>>(p, cur); break;
-      case 2: bt_rows_long_kernel<true, false><<<lg, kThreads, 0, st>>>(p, cur); break;
-      default: bt_rows_long_kernel<true, true><<<lg, kThreads, 0, st>>>(p, cur); break;
+      case 0: bt_rows_long_kernel<false, false><<<lg, kLongWarps * 32, 0, st>>>(p, cur); break;
+      case 1: bt_rows_long_kernel<false, true><<<lg, kLongWarps * 32, 0, st>>>(p, cur); break;
+      case 2: bt_rows_long_kernel<true, false><<<lg, kLongWarps * 32, 0, st>>>(p, cur); break;
+      default: bt_rows_long_kernel<true, true><<<lg, kLongWarps * 32, 0, st>>>(p, cur); break;
       }
       ++ctx->stats.kernelLaunches;
     }
