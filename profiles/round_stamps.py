@@ -1,5 +1,5 @@
 import sys, numpy as np
-sys.path.insert(0, '/root/repo')
+import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cbc_b200 import capi, instances as I
 import bench
 w = bench.make_workload(sys.argv[1] if len(sys.argv) > 1 else "c3")
