@@ -53,6 +53,12 @@ def make_workload(name, rank=0, scale=1.0):
         inst = I.mixed_bigm(m=sz, n=sz)
         return dict(inst=inst, kind="single", lb=inst.lb, ub=inst.ub, deltas=None, B=1,
                     desc=f"c3: mixed-integer {inst.m}x{inst.n}, {inst.nnz} nnz, single-vector fixpoint")
+    if name == "c3s":  # same shape as c3, but 90% of a row's columns lie near its diagonal position
+        sz = max(1000, int(1_000_000 * scale))
+        inst = I.mixed_bigm(m=sz, n=sz, locality=0.9, band=2048)
+        return dict(inst=inst, kind="single", lb=inst.lb, ub=inst.ub, deltas=None, B=1,
+                    desc=f"c3s: mixed-integer {inst.m}x{inst.n}, {inst.nnz} nnz, staircase structure (90% of a row's "
+                         f"columns within +-2048 of its diagonal position), single-vector fixpoint")
     if name == "c5":
         inst = I.power_law(n=max(1000, int(1_000_000 * scale)), nnz_target=max(10000, int(5_000_000 * scale)),
                            dense_len=max(100, int(100_000 * scale)))

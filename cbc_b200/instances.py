@@ -156,11 +156,14 @@ def _finish_cover(name, m, n, rowStart, col, val, fix_frac, g, seed):
 # C3: mixed-integer with big-M rows
 # --------------------------------------------------------------------------
 def mixed_bigm(m=1_000_000, n=1_000_000, avg_len=10.0, fix_frac=0.05, tight_frac=0.35,
-               seed=SEED0 + 3, name="c3_mixed"):
+               seed=SEED0 + 3, name="c3_mixed", locality=0.0, band=2048):
     """50% binary / 20% general integer in [0,U] / 30% continuous in [0,1e3]
     (2% of those with an infinite upper bound).  Rows: 40% knapsack 'L' with
     integer weights, 30% big-M rows x - M*y + extras <= rhs, 20% equalities,
-    10% ranged.  All data is integral or dyadic so row sums are exact."""
+    10% ranged.  All data is integral or dyadic so row sums are exact.
+    Columns of a row are uniform over all n by default (no locality at all: the worst case for
+    the bound gathers); with locality=p a fraction p of them falls within +-band of the row's
+    diagonal position, the staircase / block structure most real MILPs have."""
     g = _rng(seed)
     u = g.random(n)
     colType = np.where(u < 0.5, 1, np.where(u < 0.7, 2, 0)).astype(np.int8)
@@ -180,6 +183,11 @@ def mixed_bigm(m=1_000_000, n=1_000_000, avg_len=10.0, fix_frac=0.05, tight_frac
     ln = np.maximum(2, g.poisson(avg_len, size=m))
     rows = np.repeat(np.arange(m, dtype=np.int64), ln)
     cols = g.integers(0, n, size=rows.size)
+    if locality > 0.0:
+        near = g.random(rows.size) < locality
+        centre = (rows * n) // m
+        local = np.clip(centre + g.integers(-band, band + 1, size=rows.size), 0, n - 1)
+        cols = np.where(near, local, cols)
     rowStart, col, _, rows = _csr_from_pairs(m, n, rows, cols, np.zeros(rows.size))
     nnz = col.size
     rt = g.random(m)
