@@ -22,6 +22,10 @@ constexpr int kShortLen = 32;      // rows up to this length: one thread per row
 #endif
 constexpr int kSvChunk = CBP_SV_CHUNK;        // sliced-ELL steps whose loads are in flight together
 constexpr int kSvNoTileBlocks = CBP_SV_NT_BLOCKS;  // CTAs per SM of the short-rows-only variant
+#ifndef CBP_SV_P2ROWS
+#define CBP_SV_P2ROWS 2
+#endif
+constexpr int kSvPass2Rows = CBP_SV_P2ROWS;  // rows whose second-pass loads are in flight together
 constexpr int kSellWindow = 4096;  // short rows are sorted by length inside windows of this many rows
 constexpr int kAlign = 16;         // tile starts are multiples of 16 entries (128 B of val)
 constexpr int kStampRounds = 64;   // rounds whose phase timestamps are kept (diagnostic)
@@ -163,6 +167,22 @@ __device__ __forceinline__ void accumulate(RowAct &r, double a, bool isInt, doub
   const double w = fabs(a) * useful_range(a > 0.0 ? hi - lo : lo - hi, isInt);
   const double wf = (loInf || hiInf) ? 0.0 : w;
   r.maxRange = wf > r.maxRange ? wf : r.maxRange;
+}
+
+// Same result as accumulate(), organised for the common case: both bounds finite (then no
+// counters, no zeroing) — the rare infinite bound takes the general path.
+__device__ __forceinline__ void accumulate_fast(RowAct &r, double a, bool isInt, const Bnd &x, double INF)
+{
+  const bool pos = a > 0.0;
+  const double lo = pos ? x.lb : x.ub, hi = pos ? x.ub : x.lb;
+  if (fabs(x.lb) < INF && fabs(x.ub) < INF) {
+    r.minAct = fma(a, lo, r.minAct);
+    r.maxAct = fma(a, hi, r.maxAct);
+    const double w = fabs(a) * useful_range(x.ub - x.lb, isInt);
+    r.maxRange = w > r.maxRange ? w : r.maxRange;
+  } else {
+    accumulate(r, a, isInt, lo, hi, INF);
+  }
 }
 
 __device__ __forceinline__ void combine(RowAct &r, const RowAct &o)

@@ -715,6 +715,13 @@ int cbp_sv_round_stamps(cbp_matrix *mat, unsigned *out, int maxRounds)
   const int cnt = std::min(maxRounds, kStampRounds);
   CK(cudaMemcpy(out, reinterpret_cast<const char *>(mat->st) + offsetof(SvStatus, stamps), sizeof(unsigned) * 4 * cnt,
     cudaMemcpyDeviceToHost));
+  if (getenv("CBP_STAMPS_X"))  // tuning aid: CTA 0's own A1 / rows timestamps instead of columns 1 and 3
+    for (int r = 0; r < cnt; ++r) {
+      unsigned x[2];
+      CK(cudaMemcpy(x, reinterpret_cast<const char *>(mat->st) + offsetof(SvStatus, stampsX) + 8 * r, 8, cudaMemcpyDeviceToHost));
+      out[4 * r + 1] = x[0];
+      out[4 * r + 3] = x[1];
+    }
   return cnt;
 }
 

@@ -30,6 +30,7 @@ struct SvStatus {
   // diagnostic: globaltimer seen by CTA 0 after the row phase, the long-row phase, the settle
   // phase and the decision of each of the first kStampRounds rounds (ns since t0)
   unsigned stamps[kStampRounds][4];
+  unsigned stampsX[kStampRounds][2];  // CTA 0 only: after A1, after its own share of the rows (before the barrier)
   int roundChanged[kRoundCap];
 };
 
@@ -277,12 +278,9 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
       for (int u = 0; u < kSvChunk; ++u)  // padding points at column 0: a harmless, shared gather
         x[u] = ldcg_bnd(&src[col_of(cj[u])]);
 #pragma unroll
-      for (int u = 0; u < kSvChunk; ++u) {  // padding has a == 0: fma(0, x, s) == s, range 0, finite
-        const bool pad = a[u] == 0.0;
-        const double lo = pad ? 0.0 : (a[u] > 0.0 ? x[u].lb : x[u].ub);
-        const double hi = pad ? 0.0 : (a[u] > 0.0 ? x[u].ub : x[u].lb);
-        accumulate(ra, a[u], col_is_int(cj[u]), lo, hi, p.s.inf);
-      }
+      for (int u = 0; u < kSvChunk; ++u)  // padding has a == 0 and is skipped
+        if (a[u] != 0.0)
+          accumulate_fast(ra, a[u], col_is_int(cj[u]), x[u], p.s.inf);
     }
     RowPlan pl = plan_row(ra, rl, ru, p.s);
     if (!valid) {
@@ -299,13 +297,13 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
     unsigned todo = __ballot_sync(0xffffffffu, pl.sideU || pl.sideL);
     const int packed = min(pl.infMin, 2) | (min(pl.infMax, 2) << 2) | (pl.sideU ? 16 : 0) | (pl.sideL ? 32 : 0);
     while (todo) {
-      // up to four rows per trip, all their loads issued before the first use
-      int owner[4];
-      double a4[4];
-      int c4[4];
-      Bnd x4[4];
+      // up to kSvPass2Rows rows per trip, all their loads issued before the first use
+      int owner[kSvPass2Rows];
+      double a4[kSvPass2Rows];
+      int c4[kSvPass2Rows];
+      Bnd x4[kSvPass2Rows];
 #pragma unroll
-      for (int t = 0; t < 4; ++t) {
+      for (int t = 0; t < kSvPass2Rows; ++t) {
         owner[t] = todo ? __ffs(todo) - 1 : -1;
         todo &= todo - 1;
         a4[t] = 0.0;
@@ -317,10 +315,10 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
         }
       }
 #pragma unroll
-      for (int t = 0; t < 4; ++t)
+      for (int t = 0; t < kSvPass2Rows; ++t)
         x4[t] = ldcg_bnd(&src[col_of(c4[t])]);
 #pragma unroll
-      for (int t = 0; t < 4; ++t) {
+      for (int t = 0; t < kSvPass2Rows; ++t) {
         if (owner[t] < 0)
           break;  // uniform
         RowPlan q;
@@ -411,8 +409,18 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
           prev[j0 >> 5] = 0u;
       }
     }
+    if (blockIdx.x == 0 && tid == 0 && round < kStampRounds) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      p.st->stampsX[round][0] = static_cast<unsigned>(t - p.st->t0);
+    }
     // A2: stream the matrix: short rows from the sliced-ELL copy, the rest as TMA-staged tiles
     sv_short_rows(p, src, sink, &p.st->sliceCtr[cur]);
+    if (blockIdx.x == 0 && tid == 0 && round < kStampRounds) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      p.st->stampsX[round][1] = static_cast<unsigned>(t - p.st->t0);
+    }
     if (kTiles)
       sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
     grid.sync();
