@@ -201,6 +201,13 @@ class Matrix:
         out["roundChanged"] = [int(x) for x in rc_arr[: min(done, round_cap)] if x >= 0]
         return out, lb, ub
 
+    def propagate_ptrs(self, lb_ptr, ub_ptr, tol=1e-7, max_rounds=0, time_limit=1e100):
+        """lb/ub are HOST pointers (ints), e.g. into pinned memory; updated in place."""
+        r = Result()
+        self.ctx.check(self.ctx.lib.cbp_propagate(self.h, C.c_void_p(lb_ptr), C.c_void_p(ub_ptr), tol, max_rounds,
+                                                  time_limit, C.byref(r), None, 0, 0), "cbp_propagate")
+        return _res_dict(r)
+
     def propagate_device(self, lb_ptr, ub_ptr, tol=1e-7, max_rounds=0, time_limit=1e100, raw_round=False):
         """lb/ub are device pointers (ints) to n doubles each, updated in place.  raw_round: see
         CBP_FLAG_RAW_ROUND (one round's unsettled proposals, for row-sharded runs)."""
