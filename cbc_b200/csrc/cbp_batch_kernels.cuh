@@ -16,6 +16,13 @@
 
 namespace cbp {
 
+// one accepted candidate of round 0: column (bit 31 = upper bound), vector, value
+struct __align__(16) BtLogEntry {
+  unsigned var;
+  int b;
+  double v;
+};
+
 struct BtParams {
   const double *val;
   const int *col;
@@ -37,6 +44,12 @@ struct BtParams {
   int *vecChanged;             // [Bp] changed columns in the running round
   int *vecRounds, *vecTotal, *vecStop, *vecFinal;  // [Bp]
   int *anyActive;
+  // round 0 of a base+deltas batch: accepted candidates go to this list instead of the second
+  // bound buffer, which then is only built for the vector groups that need it
+  struct BtLogEntry *log;
+  unsigned *logCount;
+  unsigned logCap;
+  int *groupFlag;  // [G] this group has candidates or R11 changes
   Scal s;
 };
 
@@ -68,6 +81,58 @@ struct BtSink {
   {
     atomic_max_f64(&dst[static_cast<size_t>(j) * W].lb, v);
     atomicOr(&dirty[j], bit);
+  }
+};
+
+// round-0 variant: the candidate is appended to the list (entries past the capacity are counted but
+// dropped; the host then falls back to the two-buffer round)
+struct BtLogSink {
+  BtLogEntry *log;
+  unsigned *count;
+  unsigned cap;
+  int *flag;  // this warp's group flag
+  int b;
+  __device__ __forceinline__ void put(unsigned var, double v)
+  {
+    // one atomic per group of lanes that arrive here together (they usually do: same row, same
+    // candidate, 32 similar vectors)
+    const unsigned peers = __activemask();
+    const int leader = __ffs(peers) - 1;
+    const int laneId = threadIdx.x & 31;
+    unsigned base = 0;
+    if (laneId == leader)
+      base = atomicAdd(count, static_cast<unsigned>(__popc(peers)));
+    base = __shfl_sync(peers, base, leader);
+    const unsigned at = base + __popc(peers & ((1u << laneId) - 1u));
+    if (at < cap) {
+      BtLogEntry e;
+      e.var = var;
+      e.b = b;
+      e.v = v;
+      log[at] = e;
+    }
+    *flag = 1;
+  }
+  __device__ __forceinline__ void ub(int j, double v) { put(static_cast<unsigned>(j) | 0x80000000u, v); }
+  __device__ __forceinline__ void lb(int j, double v) { put(static_cast<unsigned>(j), v); }
+};
+
+template <bool kLog>
+struct BtSinkFor {
+  typedef BtSink type;
+  static __device__ __forceinline__ BtSink make(const BtParams &p, int cur, int g, int b, int bitIdx)
+  {
+    BtSink s = { p.X[cur ^ 1] + bt_base(p, b), p.dirty[cur] + bt_word(p, 0, g), p.W, 1u << bitIdx };
+    return s;
+  }
+};
+template <>
+struct BtSinkFor<true> {
+  typedef BtLogSink type;
+  static __device__ __forceinline__ BtLogSink make(const BtParams &p, int, int g, int b, int)
+  {
+    BtLogSink s = { p.log, p.logCount, p.logCap, p.groupFlag + g, b };
+    return s;
   }
 };
 
@@ -154,8 +219,9 @@ __device__ __forceinline__ void bt_walk_sum(const BtParams &p, const char *__res
 }
 
 // second walk, only for warps where some lane's row can tighten something
+template <class Sink>
 __device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const char *__restrict__ src,
-  unsigned strideB, int kb, int ke, int lane, Stg *stg, const RowPlan &pl, BtSink &sink)
+  unsigned strideB, int kb, int ke, int lane, Stg *stg, const RowPlan &pl, Sink &sink)
 {
   const bool want = pl.sideU || pl.sideL;
   for (int base = kb; base < ke; base += 32) {
@@ -185,7 +251,7 @@ __device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const char *_
 // One round, rows phase, rows up to kBtLongLen nonzeros: a warp owns (row,
 // group of 32 vectors) and sums in CSR order.  Work is group-major so that the
 // warps running at the same time share few vector groups.
-template <bool kNoInf, bool kAllInt>
+template <bool kNoInf, bool kAllInt, bool kLog>
 __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, int cur)
 {
   __shared__ Stg stage[kWarps][32];
@@ -215,7 +281,7 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
     atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
   if (!__any_sync(0xffffffffu, pl.sideU || pl.sideL))
     return;
-  BtSink sink = { p.X[cur ^ 1] + bt_base(p, b), p.dirty[cur] + bt_word(p, 0, g), p.W, 1u << lane };
+  typename BtSinkFor<kLog>::type sink = BtSinkFor<kLog>::make(p, cur, g, b, lane);
   bt_walk_tighten(p, src, strideB, kb, ke, lane, stage[warp], pl, sink);
 }
 
@@ -339,7 +405,7 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_narrow_kernel(const BtPar
 #endif
 constexpr int kLongWarps = CBP_LONG_WARPS;  // warps that share one long row
 
-template <bool kNoInf, bool kAllInt>
+template <bool kNoInf, bool kAllInt, bool kLog>
 __global__ void __launch_bounds__(kLongWarps * 32, 2048 / (kLongWarps * 32) / 2) bt_rows_long_kernel(const BtParams p, int cur)
 {
   __shared__ RowAct red[kLongWarps][32];
@@ -377,35 +443,48 @@ __global__ void __launch_bounds__(kLongWarps * 32, 2048 / (kLongWarps * 32) / 2)
     atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
   if (!__syncthreads_or(pl.sideU || pl.sideL))
     return;
-  BtSink sink = { p.X[cur ^ 1] + bt_base(p, b), p.dirty[cur] + bt_word(p, 0, g), p.W, 1u << lane };
+  typename BtSinkFor<kLog>::type sink = BtSinkFor<kLog>::make(p, cur, g, b, lane);
   bt_walk_tighten(p, src, strideB, wb, we, lane, stage[warp], pl, sink);
 }
 
-// After the rows phase: settle every (column, vector) marked in this round
-// (R9), count changed columns per vector.  One thread per mark word.
-__global__ void bt_settle_kernel(const BtParams p, int cur)
+// After the rows phase: settle every (column, vector) marked in this round (R9) and count the
+// changed columns per vector.  A warp takes 32 consecutive columns of one vector group: lane i
+// fetches column i's mark word, then the words that are not zero are handled one at a time with
+// lane = vector, so the 32 cells of a column are read and written as one 512-byte piece and every
+// lane keeps its own vector's count in a register (one atomic per lane at the end, instead of one
+// per changed bound).
+__global__ void __launch_bounds__(kThreads) bt_settle_kernel(const BtParams p, int cur)
 {
-  const size_t nW = static_cast<size_t>(p.n) * p.G;
-  const size_t w = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (w >= nW)
-    return;
-  unsigned bits = p.dirty[cur][w];
-  if (!bits)
-    return;
-  const int g = static_cast<int>(w / p.n), j = static_cast<int>(w % p.n);
-  while (bits) {
-    const int l = __ffs(bits) - 1;
-    bits &= bits - 1;
-    const int b = g * 32 + l;
-    const size_t at = bt_cell(p, j, b);
-    Bnd x = p.X[cur ^ 1][at];
-    const double L0 = x.lb, U0 = x.ub;
-    if (settle(x.lb, x.ub, p.X[cur][at].ub, p.s))
-      atomicMin(&p.vecInfCol[b], j);
-    else if (x.lb != L0 || x.ub != U0)
-      p.X[cur ^ 1][at] = x;
-    atomicAdd(&p.vecChanged[b], 1);
+  const int g = blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const int warpsPerGrid = gridDim.x * kWarps;
+  const int b = g * 32 + lane;
+  const size_t base = bt_base(p, b);
+  const unsigned *marks = p.dirty[cur] + bt_word(p, 0, g);
+  int mine = 0;
+  for (int j0 = (blockIdx.x * kWarps + (threadIdx.x >> 5)) * 32; j0 < p.n; j0 += warpsPerGrid * 32) {
+    const int j = j0 + lane;
+    const unsigned word = j < p.n ? marks[j] : 0u;
+    unsigned any = __ballot_sync(0xffffffffu, word != 0u);
+    while (any) {
+      const int sl = __ffs(any) - 1;
+      any &= any - 1;
+      const unsigned w = __shfl_sync(0xffffffffu, word, sl);
+      if ((w >> lane) & 1u) {
+        const int col = j0 + sl;
+        const size_t at = base + static_cast<size_t>(col) * p.W;
+        Bnd x = p.X[cur ^ 1][at];
+        const double L0 = x.lb, U0 = x.ub;
+        if (settle(x.lb, x.ub, p.X[cur][at].ub, p.s))
+          atomicMin(&p.vecInfCol[b], col);
+        else if (x.lb != L0 || x.ub != U0)
+          p.X[cur ^ 1][at] = x;
+        ++mine;
+      }
+    }
   }
+  if (mine)
+    atomicAdd(&p.vecChanged[b], mine);
 }
 
 // Per-vector bookkeeping of src/CbcBoundPropagation.cpp:129-189 after a round.
@@ -450,40 +529,43 @@ __global__ void bt_state_kernel(const BtParams p, int cur, int round, int limit,
   }
 }
 
-// Start of the next round: copy this round's settled values into the buffer
-// that becomes the atomics target (it was the source, so it is stale exactly
-// at the marked entries), only for vectors that go on; fold the marks of
-// applied rounds into `ever`; clear the marks.
-__global__ void bt_carry_kernel(const BtParams p, int cur)
+// Start of the next round: copy this round's settled values into the buffer that becomes the
+// atomics target (it was the source, so it is stale exactly at the marked entries), only for vectors
+// that go on; fold the marks of applied rounds into `ever`; clear the marks.  Same walk as the
+// settle kernel: lane i owns column i's word, lanes become vectors for the words that are not zero.
+__global__ void __launch_bounds__(kThreads) bt_carry_kernel(const BtParams p, int cur)
 {
-  const size_t nW = static_cast<size_t>(p.n) * p.G;
-  const size_t w = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (w >= nW)
-    return;
-  const unsigned bits0 = p.dirty[cur][w];
-  if (!bits0)
-    return;
-  p.dirty[cur][w] = 0u;
-  const int g = static_cast<int>(w / p.n), j = static_cast<int>(w % p.n);
-  // a vector's round was applied iff it is still running or stopped with the
-  // new buffer as its answer
-  unsigned applied = 0u;
-  unsigned bits = bits0;
+  const int g = blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const int warpsPerGrid = gridDim.x * kWarps;
+  const int b = g * 32 + lane;
+  const size_t base = bt_base(p, b);
+  unsigned *marks = p.dirty[cur] + bt_word(p, 0, g);
+  unsigned *ever = p.ever + bt_word(p, 0, g);
   const unsigned act = p.active[g];
-  while (bits) {
-    const int l = __ffs(bits) - 1;
-    bits &= bits - 1;
-    const int b = g * 32 + l;
-    const bool running = (act >> l) & 1u;
-    if (running) {
-      const size_t at = bt_cell(p, j, b);
-      p.X[cur][at] = p.X[cur ^ 1][at];
+  const bool running = (act >> lane) & 1u;
+  // a vector's round was applied iff it is still running or stopped with the new buffer as its answer
+  const bool appliedMe = running || p.vecFinal[b] == (cur ^ 1);
+  const unsigned appliedMask = __ballot_sync(0xffffffffu, appliedMe);
+  for (int j0 = (blockIdx.x * kWarps + (threadIdx.x >> 5)) * 32; j0 < p.n; j0 += warpsPerGrid * 32) {
+    const int j = j0 + lane;
+    const unsigned word = j < p.n ? marks[j] : 0u;
+    if (word) {
+      marks[j] = 0u;
+      if (word & appliedMask)
+        ever[j] |= word & appliedMask;
     }
-    if (running || p.vecFinal[b] == (cur ^ 1))
-      applied |= 1u << l;
+    unsigned any = __ballot_sync(0xffffffffu, (word & act) != 0u);
+    while (any) {
+      const int sl = __ffs(any) - 1;
+      any &= any - 1;
+      const unsigned w = __shfl_sync(0xffffffffu, word, sl);
+      if (running && ((w >> lane) & 1u)) {
+        const size_t at = base + static_cast<size_t>(j0 + sl) * p.W;
+        p.X[cur][at] = p.X[cur ^ 1][at];
+      }
+    }
   }
-  if (applied)
-    p.ever[w] |= applied;
 }
 
 // ---- loading ------------------------------------------------------------------
@@ -512,14 +594,45 @@ __global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double
   x.lb = __ldg(&baseLb[j]);
   x.ub = __ldg(&baseUb[j]);
   X0[i] = x;
-  X1[i] = x;
+  if (X1)  // null: the second buffer is built later, only for the groups that need it
+    X1[i] = x;
+}
+
+// second buffer := first buffer, for the vector groups whose flag is set (all if flags == nullptr)
+__global__ void bt_copy_groups_kernel(const BtParams p, const int *__restrict__ flags)
+{
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<size_t>(p.n) * p.Bp)
+    return;
+  if (flags) {
+    const int b = static_cast<int>(i / (static_cast<size_t>(p.W) * p.n)) * p.W + static_cast<int>(i % p.W);
+    if (!flags[b >> 5])
+      return;
+  }
+  p.X[1][i] = p.X[0][i];
+}
+
+// round 0's candidate list, applied to the (now valid) second buffer exactly as the direct sink would
+__global__ void bt_apply_log_kernel(const BtParams p, unsigned count)
+{
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const BtLogEntry e = p.log[i];
+  const int j = static_cast<int>(e.var & 0x7fffffffu);
+  Bnd *cell = &p.X[1][bt_cell(p, j, e.b)];
+  if (e.var & 0x80000000u)
+    atomic_min_f64(&cell->ub, e.v);
+  else
+    atomic_max_f64(&cell->lb, e.v);
+  atomicOr(&p.dirty[0][bt_word(p, j, e.b >> 5)], 1u << (e.b & 31));
 }
 
 // node bound diffs, applied in order inside a vector (one thread per vector).
 // With cellPrepass the touched cells also get R11 here (the fast path, taken
 // when no base column needs R11, so untouched cells are already final).
 __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsigned *__restrict__ var,
-  const double *__restrict__ bnd, int B, const BtParams p, int cellPrepass)
+  const double *__restrict__ bnd, int B, const BtParams p, int cellPrepass, int lazy)
 {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B)
@@ -534,7 +647,8 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
     else
       x.lb = bnd[k];
     p.X[0][at] = x;
-    p.X[1][at] = x;
+    if (!lazy)
+      p.X[1][at] = x;
   }
   if (!cellPrepass)
     return;
@@ -548,7 +662,10 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
     else if (r == 1) {
       atomicOr(&p.dirty[0][bt_word(p, j, b >> 5)], 1u << (b & 31));
       p.X[0][at] = x;
-      p.X[1][at] = x;
+      if (!lazy)
+        p.X[1][at] = x;
+      else
+        p.groupFlag[b >> 5] = 1;
     }
   }
 }

@@ -44,6 +44,9 @@ struct BatchState {
   int *ints = nullptr;  // 7 arrays of Bp ints + anyActive
   long long *counts = nullptr;  // B+1
   int *chunkCnt = nullptr;      // [ceil(n / kUpdChunk)][Bp] update counts / offsets
+  BtLogEntry *log = nullptr;    // round-0 candidate list (lazy second buffer)
+  unsigned logCap = 0;
+  int *groupFlag = nullptr;     // [G] + 1 word for the list's counter
   // loaded input (device copies) so the batch can be re-expanded
   double *baseLb = nullptr, *baseUb = nullptr;
   long long *dStart = nullptr;
@@ -101,7 +104,8 @@ struct cbp_matrix {
 
 static thread_local std::string g_createErr;
 
-static constexpr size_t kSvSmallSmem = 0;  // the short-rows-only variant needs no dynamic shared memory
+static constexpr size_t kSvSmallSmem = 0;
+static constexpr unsigned kBtLogCap = 4u << 20;  // round-0 candidate list: 4M entries (64 MB)  // the short-rows-only variant needs no dynamic shared memory
 
 template <class T>
 static cudaError_t dalloc(T **p, size_t count)
@@ -223,7 +227,7 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->longRowsBt, mat->sellVal, mat->sellCol, mat->sellOff, mat->longPart, mat->X[0],
     mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
-    mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
+    mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd };
   for (void *p : ptrs)
     if (p)
@@ -772,7 +776,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
   const int Bp = (B + 31) / 32 * 32;
   const size_t cells = static_cast<size_t>(mat->n) * Bp;
   if (cells > bt.capCells || Bp > bt.capBp) {
-    void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt };
+    void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt,
+      bt.log, bt.groupFlag };
     for (void *p : old)
       if (p)
         cudaFree(p);
@@ -781,6 +786,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.ints = nullptr;
     bt.counts = nullptr;
     bt.chunkCnt = nullptr;
+    bt.log = nullptr;
+    bt.groupFlag = nullptr;
     bt.capCells = 0;
     bt.capBp = 0;
     const size_t words = cells / 32;
@@ -789,12 +796,16 @@ static int bt_reserve(cbp_matrix *mat, int B)
       || dalloc(&bt.ever, words) != cudaSuccess || dalloc(&bt.active, Bp / 32) != cudaSuccess
       || dalloc(&bt.ints, static_cast<size_t>(Bp) * 7 + 8) != cudaSuccess
       || dalloc(&bt.counts, static_cast<size_t>(Bp) + 1) != cudaSuccess
-      || dalloc(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp) != cudaSuccess) {
+      || dalloc(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp) != cudaSuccess
+      || dalloc(&bt.groupFlag, static_cast<size_t>(Bp / 32) + 1) != cudaSuccess
+      || dalloc(&bt.log, kBtLogCap) != cudaSuccess) {
       ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
       return CBP_ERR_NOMEM;
     }
     bt.capCells = cells;
     bt.capBp = Bp;
+    // CBP_LOG_CAP: tests shrink the list to exercise the fall-back to the two-buffer first round
+    bt.logCap = getenv("CBP_LOG_CAP") ? std::min<unsigned>(kBtLogCap, static_cast<unsigned>(atol(getenv("CBP_LOG_CAP")))) : kBtLogCap;
   }
   if (!bt.baseLb) {
     if (dalloc(&bt.baseLb, mat->n) != cudaSuccess || dalloc(&bt.baseUb, mat->n) != cudaSuccess) {
@@ -852,6 +863,10 @@ static BtParams bt_params(cbp_matrix *mat, double tol)
   p.vecStop = q + 5 * bt.Bp;
   p.vecFinal = q + 6 * bt.Bp;
   p.anyActive = q + 7 * bt.Bp;
+  p.log = bt.log;
+  p.logCap = bt.logCap;
+  p.groupFlag = bt.groupFlag;
+  p.logCount = reinterpret_cast<unsigned *>(bt.groupFlag + bt.G);
   p.s = make_scal(mat, tol);
   return p;
 }
@@ -937,7 +952,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   bt_init_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, bt.B);
   ++ctx->stats.kernelLaunches;
   const int cellGrid = cdiv(static_cast<long long>(bt.cells), 256);
-  bool fullPrepass = true;
+  bool fullPrepass = true, lazy = false;
   if (!bt.denseLoaded) {
     // base + deltas: expand here, so a loaded batch can be run any number of times
     if (bt.consumed) {
@@ -949,12 +964,21 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     bt_base_check_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->colType, mat->n, p.s,
       p.anyActive);
     CK(cudaMemcpyAsync(&need, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));
-    bt_expand_kernel<<<cellGrid, 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.W, bt.cells, bt.X[0], bt.X[1]);
-    ctx->stats.kernelLaunches += 2;
+    CK(cudaMemsetAsync(bt.groupFlag, 0, sizeof(int) * (bt.G + 1), st));
     CK(cudaStreamSynchronize(st));
     fullPrepass = need != 0;
+    // Lazy second buffer: most vectors of a node batch reach their fixpoint in the first round without
+    // a single accepted candidate, so the other bound buffer is built after that round and only for the
+    // vector groups that have candidates (collected in a list) or R11 changes.
+    // (worth it for shallow changes per vector — strong-branching arms, probes; deep dives tighten so much
+    // in their first round that the direct two-buffer round is the cheaper one)
+    lazy = !fullPrepass && bt.W == 32 && !getenv("CBP_NO_LAZY_X1") && (bt.nDelta <= 2ll * bt.B || getenv("CBP_LAZY_X1"));
+    bt_expand_kernel<<<cellGrid, 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.W, bt.cells, bt.X[0],
+      lazy ? nullptr : bt.X[1]);
+    ctx->stats.kernelLaunches += 2;
     if (bt.nDelta > 0) {
-      bt_delta_kernel<<<cdiv(bt.B, 128), 128, 0, st>>>(bt.dStart, bt.dVar, bt.dBnd, bt.B, p, fullPrepass ? 0 : 1);
+      bt_delta_kernel<<<cdiv(bt.B, 128), 128, 0, st>>>(bt.dStart, bt.dVar, bt.dBnd, bt.B, p, fullPrepass ? 0 : 1,
+        lazy ? 1 : 0);
       ++ctx->stats.kernelLaunches;
     }
   } else {
@@ -978,7 +1002,8 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     ctx->err = "cbp_batch_run: batch too large for one launch";
     return CBP_ERR_ARG;
   }
-  const int wordGrid = cdiv(static_cast<long long>(words), 256);
+  // settle / carry: blockIdx.y = vector group, x strides over blocks of 32 columns
+  const dim3 markGrid(std::max(1, std::min(cdiv(mat->n, 32 * kWarps), 4096 / std::max(1, bt.G) + 1)), bt.G);
   double roundKernelMs = 0.0;
   int roundKernelLaunches = 0;
   int any = 1;
@@ -991,53 +1016,89 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     const int cur = round & 1;
     CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
     CK(cudaEventRecord(ctx->evPool[0], st));
-    // kernel variants: <no infinite bound in this batch, no continuous column in this matrix>
+    // kernel variants: <no infinite bound in this batch, no continuous column in this matrix, candidates to a list>
     const int variant = (bt.hasInf ? 0 : 2) | (mat->allInt ? 1 : 0);
-    if (longGrid > 0) {
-      const int lg = static_cast<int>(longGrid);
-      switch (variant) {
-      case 0: bt_rows_long_kernel<false, false><<<lg, kLongWarps * 32, 0, st>>>(p, cur); break;
-      case 1: bt_rows_long_kernel<false, true><<<lg, kLongWarps * 32, 0, st>>>(p, cur); break;
-      case 2: bt_rows_long_kernel<true, false><<<lg, kLongWarps * 32, 0, st>>>(p, cur); break;
-      default: bt_rows_long_kernel<true, true><<<lg, kLongWarps * 32, 0, st>>>(p, cur); break;
+    auto launch_rows = [&](bool toList) {
+      if (longGrid > 0) {
+        const int lg = static_cast<int>(longGrid);
+        const int nt = kLongWarps * 32;
+#define CBP_LONG(A, B_)                                                              \
+  if (toList)                                                                        \
+    bt_rows_long_kernel<A, B_, true><<<lg, nt, 0, st>>>(p, cur);                     \
+  else                                                                               \
+    bt_rows_long_kernel<A, B_, false><<<lg, nt, 0, st>>>(p, cur);
+        switch (variant) {
+        case 0: CBP_LONG(false, false) break;
+        case 1: CBP_LONG(false, true) break;
+        case 2: CBP_LONG(true, false) break;
+        default: CBP_LONG(true, true) break;
+        }
+#undef CBP_LONG
+        ++ctx->stats.kernelLaunches;
       }
-      ++ctx->stats.kernelLaunches;
-    }
-    if (warps > 0) {
-      const int W = bt.W;  // vectors per warp = slice width of the layout
-      const int rowsPerWarp = 32 / W;
-      const long long narrowWarps = static_cast<long long>(bt.G) * rowsPerWarp * cdiv(mat->nShortBt, rowsPerWarp);
-      if (narrowWarps / kWarps > INT_MAX) {
-        ctx->err = "cbp_batch_run: batch too large for one launch";
-        return CBP_ERR_ARG;
-      }
-      const int narrowGrid = cdiv(narrowWarps, kWarps);
+      if (warps > 0 && bt.W == 32) {
+#define CBP_SHORT(A, B_)                                                             \
+  if (toList)                                                                        \
+    bt_rows_kernel<A, B_, true><<<rowsGrid, kThreads, 0, st>>>(p, cur);              \
+  else                                                                               \
+    bt_rows_kernel<A, B_, false><<<rowsGrid, kThreads, 0, st>>>(p, cur);
+        switch (variant) {
+        case 0: CBP_SHORT(false, false) break;
+        case 1: CBP_SHORT(false, true) break;
+        case 2: CBP_SHORT(true, false) break;
+        default: CBP_SHORT(true, true) break;
+        }
+#undef CBP_SHORT
+        ++ctx->stats.kernelLaunches;
+      } else if (warps > 0) {
+        const int W = bt.W;  // vectors per warp = slice width of the layout
+        const int rowsPerWarp = 32 / W;
+        const long long narrowWarps = static_cast<long long>(bt.G) * rowsPerWarp * cdiv(mat->nShortBt, rowsPerWarp);
+        const int narrowGrid = cdiv(narrowWarps, kWarps);
 #define CBP_NARROW(WW)                                                                                      \
   switch (variant) {                                                                                        \
-  case 0: bt_rows_narrow_kernel<WW, false, false><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;            \
-  case 1: bt_rows_narrow_kernel<WW, false, true><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;             \
-  case 2: bt_rows_narrow_kernel<WW, true, false><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;             \
-  default: bt_rows_narrow_kernel<WW, true, true><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;             \
+  case 0: bt_rows_narrow_kernel<WW, false, false><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;          \
+  case 1: bt_rows_narrow_kernel<WW, false, true><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;           \
+  case 2: bt_rows_narrow_kernel<WW, true, false><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;           \
+  default: bt_rows_narrow_kernel<WW, true, true><<<narrowGrid, kThreads, 0, st>>>(p, cur); break;           \
   }
-      if (W == 32) {
-        switch (variant) {
-        case 0: bt_rows_kernel<false, false><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
-        case 1: bt_rows_kernel<false, true><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
-        case 2: bt_rows_kernel<true, false><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
-        default: bt_rows_kernel<true, true><<<rowsGrid, kThreads, 0, st>>>(p, cur); break;
+        if (W == 16) {
+          CBP_NARROW(16)
+        } else if (W == 8) {
+          CBP_NARROW(8)
+        } else {
+          CBP_NARROW(4)
         }
-      } else if (W == 16) {
-        CBP_NARROW(16)
-      } else if (W == 8) {
-        CBP_NARROW(8)
-      } else {
-        CBP_NARROW(4)
-      }
 #undef CBP_NARROW
-      ++ctx->stats.kernelLaunches;
-    }
+        ++ctx->stats.kernelLaunches;
+      }
+    };
+    const bool listRound = lazy && round == 0;
+    launch_rows(listRound);
     CK(cudaEventRecord(ctx->evPool[1], st));
-    bt_settle_kernel<<<wordGrid, 256, 0, st>>>(p, cur);
+    if (listRound) {
+      // which groups need the second buffer, and did the list hold every candidate?
+      std::vector<int> flags(bt.G + 1);
+      CK(cudaMemcpyAsync(flags.data(), bt.groupFlag, sizeof(int) * (bt.G + 1), cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      const unsigned count = static_cast<unsigned>(flags[bt.G]);
+      bool anyFlag = false;
+      for (int g = 0; g < bt.G; ++g)
+        anyFlag = anyFlag || flags[g] != 0;
+      if (count > bt.logCap) {  // too many for the list: build the whole buffer and redo the round directly
+        bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, nullptr);
+        ++ctx->stats.kernelLaunches;
+        launch_rows(false);
+      } else if (anyFlag) {
+        bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, bt.groupFlag);
+        ++ctx->stats.kernelLaunches;
+        if (count > 0) {
+          bt_apply_log_kernel<<<cdiv(count, 256), 256, 0, st>>>(p, count);
+          ++ctx->stats.kernelLaunches;
+        }
+      }
+    }
+    bt_settle_kernel<<<markGrid, kThreads, 0, st>>>(p, cur);
     int timeUp = 0;
     if (timeLimitSec < 1.0e9) {  // a real limit: look at the clock between rounds
       CK(cudaEventRecord(ctx->evB, st));
@@ -1047,7 +1108,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       timeUp = ms * 1.0e-3 >= timeLimitSec;
     }
     bt_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, cur, round, limit, timeUp);
-    bt_carry_kernel<<<wordGrid, 256, 0, st>>>(p, cur);
+    bt_carry_kernel<<<markGrid, kThreads, 0, st>>>(p, cur);
     ctx->stats.kernelLaunches += 3;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&any, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -257,6 +257,34 @@ def test_batch_wide_matrices_use_narrow_vector_slices(oracle, gpu_ctx, n, m, mon
     assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
 
 
+@pytest.mark.parametrize("env", [{"CBP_LOG_CAP": "7", "CBP_LAZY_X1": "1"}, {"CBP_LAZY_X1": "1"}, {"CBP_NO_LAZY_X1": "1"}],
+                         ids=["list_overflows", "lazy_buffer", "no_lazy_buffer"])
+def test_batch_first_round_variants(env):
+    """The first round of a base+deltas batch normally collects candidates in a list and builds the second
+    bound buffer afterwards; a list that is too small, or the feature switched off, must give the same answer."""
+    import os
+    import subprocess
+    import sys
+
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "from cbc_b200 import capi, instances as I; from oracle import oracle_py as O\n"
+        "inst = I.knapsack_assignment(m=3000, n=8000, seed=41)\n"
+        "s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 70, max_depth=48, seed=42)\n"
+        "ctx = capi.Context(); mat = capi.Matrix(ctx, inst)\n"
+        "res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)\n"
+        "Lg, Ug = mat.batch_fetch_dense()\n"
+        "ores, Lo, Uo = O.propagate_batch_delta(O.Problem(inst), inst.lb, inst.ub, s, v, b, threads=8)\n"
+        "for k in ('feasible','rounds','nChanged','infeasibleRow','infeasibleCol','stopReason'):\n"
+        "    assert np.array_equal(res[k], ores[k]), k\n"
+        "assert np.array_equal(Lg, Lo) and np.array_equal(Ug, Uo)\n"
+        "assert res['nChanged'].sum() > 100\n"
+        "print('OK')\n") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),)
+    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True,
+                         timeout=600)
+    assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
+
+
 def test_fixpoint_is_idempotent_at_size(gpu_ctx):
     """Size-independent property on a larger instance: propagating a fixpoint again changes nothing
     and takes exactly one round; the planted point survives."""
