@@ -42,7 +42,7 @@ def make_workload(name, rank=0, scale=1.0):
                     desc=f"c2: fast0507-shaped set cover {inst.m}x{inst.n}, {inst.nnz} nnz, 30% columns fixed at 0, "
                          f"{B} strong-branching bound vectors per GPU (base + one bound change each)")
     if name == "c4":
-        inst = I.knapsack_assignment()
+        inst = I.knapsack_assignment(root_fixpoint=True)  # the node's own bounds are already propagated
         B = max(64, int(2048 * scale))
         s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, B, max_depth=64, seed=I.SEED0 + 200 + rank)
         return dict(inst=inst, kind="batch", lb=inst.lb, ub=inst.ub, deltas=(s, v, b), B=B,

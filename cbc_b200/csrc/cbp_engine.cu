@@ -55,7 +55,7 @@ struct BatchState {
   long long nDelta = 0;
   bool loaded = false, denseLoaded = false, consumed = false;
   bool hasInf = true;  // some input bound may be infinite (false only when checked)
-  size_t capCells = 0, capDelta = 0;
+  size_t capCells = 0, capDelta = 0, capStart = 0;
   int capBp = 0;
 };
 
@@ -905,11 +905,17 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
     }
     bt.capDelta = static_cast<size_t>(nDelta);
   }
-  if (bt.dStart)
-    cudaFree(bt.dStart);
-  bt.dStart = nullptr;
-  if (dalloc(&bt.dStart, static_cast<size_t>(B) + 1) != cudaSuccess)
-    return CBP_ERR_NOMEM;
+  if (!bt.dStart || static_cast<size_t>(B) + 1 > bt.capStart) {
+    if (bt.dStart)
+      cudaFree(bt.dStart);
+    bt.dStart = nullptr;
+    bt.capStart = 0;
+    if (dalloc(&bt.dStart, static_cast<size_t>(B) + 1) != cudaSuccess) {
+      ctx->err = "batch workspace: delta offsets";
+      return CBP_ERR_NOMEM;
+    }
+    bt.capStart = static_cast<size_t>(B) + 1;
+  }
   CK(cudaMemcpyAsync(bt.baseLb, baseLb, sizeof(double) * mat->n, kind, ctx->stream));
   CK(cudaMemcpyAsync(bt.baseUb, baseUb, sizeof(double) * mat->n, kind, ctx->stream));
   CK(cudaMemcpyAsync(bt.dStart, deltaStart, sizeof(long long) * (B + 1), kind, ctx->stream));

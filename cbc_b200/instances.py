@@ -234,9 +234,11 @@ def mixed_bigm(m=1_000_000, n=1_000_000, avg_len=10.0, fix_frac=0.05, tight_frac
 # C4: knapsack + assignment
 # --------------------------------------------------------------------------
 def knapsack_assignment(m=200_000, n=500_000, seed=SEED0 + 4, name="c4_knapassign", knap_per_col=5,
-                        slack_max=6):
+                        slack_max=6, root_fixpoint=False):
     """Every binary column sits in 1 assignment row (sum x = 1) and
-    `knap_per_col` knapsack rows (integer weights 1..20)."""
+    `knap_per_col` knapsack rows (integer weights 1..20).  root_fixpoint=True gives every knapsack
+    at least the capacity of its heaviest item, so the root bounds are already a propagation
+    fixpoint (a node as the solver would hand it to a dive) and only the dive's own fixings propagate."""
     g = _rng(seed)
     mE = max(1, m // 4)
     mK = m - mE
@@ -263,6 +265,10 @@ def knapsack_assignment(m=200_000, n=500_000, seed=SEED0 + 4, name="c4_knapassig
     rl[:mE] = 1.0
     ru[:mE] = 1.0
     ru[mE:] = act[mE:] + g.integers(0, slack_max + 1, size=mK)
+    if root_fixpoint:
+        heaviest = np.zeros(m)
+        np.maximum.at(heaviest, rws, val)
+        ru[mE:] = np.maximum(ru[mE:], heaviest[mE:])
     sense, rhs, rge = _sense_from_bounds(rl, ru, COIN_INF)
     return Instance(name, m, n, rowStart, col, val, sense, rhs, rge, np.ones(n, np.int8),
                     np.zeros(n), np.ones(n), COIN_INF, xstar, {"seed": seed, "mE": mE})
