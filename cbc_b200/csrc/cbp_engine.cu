@@ -79,7 +79,7 @@ struct cbp_matrix {
   int nShortBt = 0, nLongBt = 0;
   int nTiles = 0, firstLongTile = 0, nLong = 0, nParts = 0, nSing = 0;
   double *sellVal = nullptr;
-  int *sellCol = nullptr, *sellOff = nullptr;
+  int *sellCol = nullptr, *sellOff = nullptr, *sliceOrder = nullptr;
   int nSlices = 0, mShort = 0;
   // device, single-vector workspace
   RowAct *longPart = nullptr;
@@ -224,7 +224,7 @@ void cbp_matrix_free(cbp_matrix *mat)
   cudaSetDevice(mat->ctx->device);
   void *ptrs[] = { mat->val, mat->col, mat->tiles, mat->rp, mat->rowLB, mat->rowUB, mat->rowOrig,
     mat->rowNz, mat->rowCnt, mat->rowPos, mat->longRows, mat->colType, mat->singRows, mat->shortRowsBt,
-    mat->longRowsBt, mat->sellVal, mat->sellCol, mat->sellOff, mat->longPart, mat->X[0],
+    mat->longRowsBt, mat->sellVal, mat->sellCol, mat->sellOff, mat->sliceOrder, mat->longPart, mat->X[0],
     mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
     mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
@@ -465,6 +465,13 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   up(&mat->sellVal, hSellVal);
   up(&mat->sellCol, hSellCol);
   up(&mat->sellOff, hSellOff);
+  std::vector<int> hOrder(hSellOff.size() - 1);
+  for (size_t i = 0; i < hOrder.size(); ++i)
+    hOrder[i] = static_cast<int>(i);
+  std::stable_sort(hOrder.begin(), hOrder.end(), [&](int a, int b) {
+    return hSellOff[a + 1] - hSellOff[a] > hSellOff[b + 1] - hSellOff[b];
+  });
+  up(&mat->sliceOrder, hOrder);
   mat->nSlices = static_cast<int>(hSellOff.size()) - 1;
   mat->mShort = static_cast<int>(cls[kShort].size());
   std::vector<int> hShortBt, hLongBt;
@@ -638,6 +645,7 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   p.sellVal = mat->sellVal;
   p.sellCol = mat->sellCol;
   p.sellOff = mat->sellOff;
+  p.sliceOrder = mat->sliceOrder;
   p.nSlices = mat->nSlices;
   p.mShort = mat->mShort;
   p.X[0] = mat->X[0];

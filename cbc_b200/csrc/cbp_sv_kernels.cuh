@@ -51,6 +51,7 @@ struct SvParams {
   const double *sellVal;
   const int *sellCol;
   const int *sellOff;  // nSlices + 1
+  const int *sliceOrder;  // slices by decreasing length: the order in which they are handed out
   int nSlices, mShort;
   // state
   Bnd *X[2];
@@ -250,7 +251,7 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
     next = atomicAdd(ctr, 1);
   next = __shfl_sync(0xffffffffu, next, 0);
   while (next < p.nSlices) {
-    const int s = next;
+    const int s = __ldg(&p.sliceOrder[next]);  // longest first, so the round's tail is made of the shortest
     if (lane == 0)
       next = atomicAdd(ctr, 1);
     const int off = __ldg(&p.sellOff[s]);
@@ -384,6 +385,7 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
   }
 
   const int limit = p.maxRounds > 0 ? p.maxRounds : 0x7fffffff;
+  bool sparse = false;  // last round changed few columns: scan the marks word-wise
   for (int round = 0;; ++round) {
     const int cur = round & 1;
     const Bnd *src = p.X[cur];
@@ -394,7 +396,23 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
     // round changed (it was that round's source, so it is stale there), and
     // clear that round's marks.  Atomics: rows of this round may hit the same
     // column at the same time.
-    if (round > 0) {
+    if (round > 0 && sparse) {
+      // few columns changed last round: one mark word per thread, its few bits one after the other
+      unsigned *prev = p.dirty[cur ^ 1];
+      for (int w = gtid; w < p.nWords; w += gsize) {
+        unsigned bits = __ldcg(&prev[w]);
+        if (!bits)
+          continue;
+        prev[w] = 0u;
+        while (bits) {
+          const int j = (w << 5) + __ffs(bits) - 1;
+          bits &= bits - 1;
+          const Bnd b = ldcg_bnd(&src[j]);
+          atomic_max_f64(&dst[j].lb, b.lb);
+          atomic_min_f64(&dst[j].ub, b.ub);
+        }
+      }
+    } else if (round > 0) {
       unsigned *prev = p.dirty[cur ^ 1];
       for (int j0 = gtid & ~31; j0 < p.n; j0 += gsize) {  // one column per thread, one word per warp
         const int j = j0 + (tid & 31);
@@ -442,6 +460,23 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
     {
       int mine = 0;
       const unsigned *dw = p.dirty[cur];
+      if (sparse) {  // (the previous round's count is the predictor; either path is correct for any count)
+        for (int w = gtid; w < p.nWords; w += gsize) {
+          unsigned bits = __ldcg(&dw[w]);
+          mine += __popc(bits);
+          while (bits) {
+            const int j = (w << 5) + __ffs(bits) - 1;
+            bits &= bits - 1;
+            Bnd b = ldcg_bnd(&dst[j]);
+            const double oldUb = __ldcg(&src[j].ub);
+            const double L0 = b.lb, U0 = b.ub;
+            if (settle(b.lb, b.ub, oldUb, p.s))
+              atomicMin(&p.st->infeasCol, j);
+            else if (b.lb != L0 || b.ub != U0)
+              dst[j] = b;
+          }
+        }
+      } else
       for (int j0 = gtid & ~31; j0 < p.n; j0 += gsize) {  // one column per thread, one word per warp
         const int j = j0 + (tid & 31);
         const unsigned bits = __ldcg(&dw[j0 >> 5]);
@@ -504,6 +539,7 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
         p.st->nChangedTotal += changed;
       }
     }
+    sparse = changed < (p.nWords >> 2);
     if (stop) {
       if (gtid == 0) {
         p.st->rounds = round + 1;
