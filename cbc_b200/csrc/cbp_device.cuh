@@ -28,6 +28,7 @@ constexpr int kSvNoTileBlocks = CBP_SV_NT_BLOCKS;  // CTAs per SM of the short-r
 constexpr int kSvPass2Rows = CBP_SV_P2ROWS;  // rows whose second-pass loads are in flight together
 constexpr int kSellWindow = 4096;  // short rows are sorted by length inside windows of this many rows
 constexpr int kAlign = 16;         // tile starts are multiples of 16 entries (128 B of val)
+constexpr int kMaxPeers = 8;       // GPUs of one NVSwitch box in a row-sharded run
 constexpr int kStampRounds = 64;   // rounds whose phase timestamps are kept (diagnostic)
 constexpr int kRoundCap = 1024;    // per-round counts kept on the device
 constexpr int kBtLongLen = 256;    // batch mode: longer rows get a whole CTA per (row, group)

@@ -90,6 +90,14 @@ struct cbp_matrix {
   double *dLb = nullptr, *dUb = nullptr;  // staging for host-pointer calls
   int *dRes = nullptr;                    // small int scratch
   double *dAct = nullptr;                 // row-activity staging (2m doubles + 2m ints)
+  // row-sharded runs over peer memory: one state block per rank, mapped into every rank
+  struct P2P {
+    unsigned char *block = nullptr;  // own block: X0 | X1 | dirty0 | dirty1 | status
+    size_t offX1 = 0, offD0 = 0, offD1 = 0, offSt = 0, bytes = 0;
+    int world = 0, rank = 0;
+    unsigned char *peer[kMaxPeers] = {};  // every rank's block as seen from here (peer[rank] == block)
+    bool prepared = false;
+  } p2p;
   BatchState bt;
 };
 
@@ -152,11 +160,13 @@ cbp_ctx *cbp_create(int device)
   ctx->ownsStream = true;
   cudaEventCreate(&ctx->evA);
   cudaEventCreate(&ctx->evB);
-  cudaFuncSetAttribute(sv_fixpoint_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaFuncSetAttribute(sv_fixpoint_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    static_cast<int>(sizeof(SvSmem)));
+  cudaFuncSetAttribute(sv_fixpoint_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
     static_cast<int>(sizeof(SvSmem)));
   int perSM = 0, perSM2 = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, sv_fixpoint_kernel<true>, kThreads, sizeof(SvSmem));
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM2, sv_fixpoint_kernel<false>, kThreads, kSvSmallSmem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, sv_fixpoint_kernel<true, true>, kThreads, sizeof(SvSmem));
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM2, sv_fixpoint_kernel<false, true>, kThreads, kSvSmallSmem);
   ctx->svBlocksPerSM = perSM;
   ctx->svBlocksPerSMNoTiles = perSM2;
   if (perSM < 1 || perSM2 < 1) {
@@ -232,6 +242,11 @@ void cbp_matrix_free(cbp_matrix *mat)
   for (void *p : ptrs)
     if (p)
       cudaFree(p);
+  for (int r = 0; r < mat->p2p.world; ++r)
+    if (r != mat->p2p.rank && mat->p2p.peer[r])
+      cudaIpcCloseMemHandle(mat->p2p.peer[r]);
+  if (mat->p2p.block)
+    cudaFree(mat->p2p.block);
   delete mat;
 }
 
@@ -532,7 +547,36 @@ static int sv_stage_out(cbp_matrix *mat, const Bnd *X, double *lb, double *ub, i
   return CBP_OK;
 }
 
-static int sv_reset_state(cbp_matrix *mat)
+// where one run keeps its state: the matrix's own buffers, or its block of a row-sharded group
+struct SvState {
+  Bnd *X[2];
+  unsigned *dirty[2];
+  SvStatus *st;
+};
+
+static SvState sv_own_state(cbp_matrix *mat)
+{
+  SvState v;
+  v.X[0] = mat->X[0];
+  v.X[1] = mat->X[1];
+  v.dirty[0] = mat->dirty[0];
+  v.dirty[1] = mat->dirty[1];
+  v.st = mat->st;
+  return v;
+}
+
+static SvState sv_block_state(const cbp_matrix *mat, unsigned char *base)
+{
+  SvState v;
+  v.X[0] = reinterpret_cast<Bnd *>(base);
+  v.X[1] = reinterpret_cast<Bnd *>(base + mat->p2p.offX1);
+  v.dirty[0] = reinterpret_cast<unsigned *>(base + mat->p2p.offD0);
+  v.dirty[1] = reinterpret_cast<unsigned *>(base + mat->p2p.offD1);
+  v.st = reinterpret_cast<SvStatus *>(base + mat->p2p.offSt);
+  return v;
+}
+
+static int sv_reset_state(cbp_matrix *mat, const SvState &v)
 {
   cbp_ctx *ctx = mat->ctx;
   SvStatus init;
@@ -540,11 +584,120 @@ static int sv_reset_state(cbp_matrix *mat)
   init.infeasRow = INT_MAX;
   init.infeasCol = INT_MAX;
   // only the head of the status block needs initial values
-  CK(cudaMemsetAsync(mat->st, 0, sizeof(SvStatus), ctx->stream));
-  CK(cudaMemcpyAsync(mat->st, &init, offsetof(SvStatus, roundChanged), cudaMemcpyHostToDevice,
+  CK(cudaMemsetAsync(v.st, 0, sizeof(SvStatus), ctx->stream));
+  CK(cudaMemcpyAsync(v.st, &init, offsetof(SvStatus, roundChanged), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemsetAsync(v.dirty[0], 0, sizeof(unsigned) * mat->nWords, ctx->stream));
+  CK(cudaMemsetAsync(v.dirty[1], 0, sizeof(unsigned) * mat->nWords, ctx->stream));
+  return CBP_OK;
+}
+
+static SvParams sv_params(cbp_matrix *mat, const SvState &v, const Scal &s, int maxRounds, double timeLimitSec,
+  int raw)
+{
+  SvParams p;
+  p.raw = raw;
+  p.val = mat->val;
+  p.col = mat->col;
+  p.tiles = mat->tiles;
+  p.rp = mat->rp;
+  p.rowLB = mat->rowLB;
+  p.rowUB = mat->rowUB;
+  p.rowOrig = mat->rowOrig;
+  p.longRows = mat->longRows;
+  p.colType = mat->colType;
+  p.longPart = mat->longPart;
+  p.nTiles = mat->nTiles;
+  p.firstLongTile = mat->firstLongTile;
+  p.nLong = mat->nLong;
+  p.n = mat->n;
+  p.sellVal = mat->sellVal;
+  p.sellCol = mat->sellCol;
+  p.sellOff = mat->sellOff;
+  p.sliceOrder = mat->sliceOrder;
+  p.nSlices = mat->nSlices;
+  p.mShort = mat->mShort;
+  p.X[0] = v.X[0];
+  p.X[1] = v.X[1];
+  p.dirty[0] = v.dirty[0];
+  p.dirty[1] = v.dirty[1];
+  p.nWords = mat->nWords;
+  p.st = v.st;
+  p.s = s;
+  p.maxRounds = maxRounds;
+  p.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
+  p.world = 0;
+  p.rank = 0;
+  p.rowOffset = 0;
+  return p;
+}
+
+// launch the persistent loop, wait, fill `out`, write the bounds back
+static int sv_launch_and_collect(cbp_matrix *mat, const SvParams &pIn, const SvState &v, bool p2p, double *lb,
+  double *ub, cbp_result *out, int *roundChanged, int roundCap, int flags)
+{
+  cbp_ctx *ctx = mat->ctx;
+  SvParams p = pIn;
+  const bool tiles = mat->nTiles > 0;
+  const int maxGrid = (tiles ? ctx->svBlocksPerSM : ctx->svBlocksPerSMNoTiles) * ctx->numSMs;
+  const int want = std::max(std::max(mat->nTiles, cdiv(mat->nSlices, kWarps)), cdiv(mat->nWords, kThreads));
+  const int grid = std::max(1, std::min(maxGrid, want));
+  void *args[] = { &p };
+  while (ctx->evPool.size() < 2) {
+    cudaEvent_t e;
+    CK(cudaEventCreate(&e));
+    ctx->evPool.push_back(e);
+  }
+  cudaEvent_t k0 = ctx->evPool[0], k1 = ctx->evPool[1];
+  CK(cudaEventRecord(k0, ctx->stream));
+  void *fn = tiles ? (p2p ? reinterpret_cast<void *>(sv_fixpoint_kernel<true, true>)
+                          : reinterpret_cast<void *>(sv_fixpoint_kernel<true, false>))
+                   : (p2p ? reinterpret_cast<void *>(sv_fixpoint_kernel<false, true>)
+                          : reinterpret_cast<void *>(sv_fixpoint_kernel<false, false>));
+  CK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), args, tiles ? sizeof(SvSmem) : kSvSmallSmem,
     ctx->stream));
-  CK(cudaMemsetAsync(mat->dirty[0], 0, sizeof(unsigned) * mat->nWords, ctx->stream));
-  CK(cudaMemsetAsync(mat->dirty[1], 0, sizeof(unsigned) * mat->nWords, ctx->stream));
+  CK(cudaEventRecord(k1, ctx->stream));
+  ++ctx->stats.kernelLaunches;
+
+  struct Head {
+    SvStatus s;
+  };
+  SvStatus head;
+  CK(cudaMemcpyAsync(&head, v.st, offsetof(SvStatus, roundChanged), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  if (p2p && head.p2pError) {
+    ctx->err = "row-sharded run: a rank did not reach the barrier in time";
+    return CBP_ERR_CUDA;
+  }
+  out->rounds = head.rounds;
+  out->stopReason = head.stopReason;
+  out->nChanged = head.nChangedTotal;
+  if (head.stopReason == CBP_STOP_INFEASIBLE) {
+    out->feasible = 0;
+    if (head.infeasRow != INT_MAX)
+      out->infeasibleRow = head.infeasRow;
+    else if (head.infeasCol != INT_MAX)
+      out->infeasibleCol = head.infeasCol;
+  }
+  int rc = sv_stage_out(mat, v.X[head.finalBuf & 1], lb, ub, flags);
+  if (rc)
+    return rc;
+  if (roundChanged && roundCap > 0) {
+    const int done = head.rounds - (head.stopReason == CBP_STOP_INFEASIBLE ? 1 : 0);
+    const int cnt = std::min(std::min(roundCap, done), kRoundCap);
+    if (cnt > 0)
+      CK(cudaMemcpyAsync(roundChanged, v.st->roundChanged, sizeof(int) * cnt, cudaMemcpyDeviceToHost,
+        ctx->stream));
+  }
+  CK(cudaEventRecord(ctx->evB, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  float ms = 0.f, kms = 0.f;
+  cudaEventElapsedTime(&ms, ctx->evA, ctx->evB);
+  cudaEventElapsedTime(&kms, k0, k1);
+  out->seconds = ms * 1.0e-3;
+  ctx->stats.lastRunMs = ms;
+  ctx->stats.lastRoundKernelMs = kms;
+  ctx->stats.lastRoundKernelLaunches = 1;
+  ctx->stats.lastRoundsTotal = head.rounds;
   return CBP_OK;
 }
 
@@ -561,7 +714,7 @@ int cbp_singletons(cbp_matrix *mat, double *lb, double *ub, double primalTol, in
   int rc = sv_stage_in(mat, lb, ub, flags, &dl, &du);
   if (rc)
     return rc;
-  if ((rc = sv_reset_state(mat)))
+  if ((rc = sv_reset_state(mat, sv_own_state(mat))))
     return rc;
   CK(cudaMemsetAsync(mat->dRes, 0, sizeof(int) * 4, ctx->stream));
   sv_prepare_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(dl, du, mat->colType, n, mat->X[0], mat->X[1],
@@ -618,104 +771,126 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
   if (rc)
     return rc;
   CK(cudaEventRecord(ctx->evA, ctx->stream));
-  if ((rc = sv_reset_state(mat)))
+  const SvState v = sv_own_state(mat);
+  if ((rc = sv_reset_state(mat, v)))
     return rc;
   const int raw = (flags & CBP_FLAG_RAW_ROUND) ? 1 : 0;
-  sv_prepare_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(dl, du, mat->colType, n, mat->X[0], mat->X[1],
-    mat->dirty[0], mat->st, s, raw ? 0 : 1);
+  sv_prepare_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(dl, du, mat->colType, n, v.X[0], v.X[1], v.dirty[0], v.st,
+    s, raw ? 0 : 1);
   ++ctx->stats.kernelLaunches;
   CK(cudaGetLastError());
+  const SvParams p = sv_params(mat, v, s, maxRounds, timeLimitSec, raw);
+  return sv_launch_and_collect(mat, p, v, false, lb, ub, out, roundChanged, roundCap, flags);
+}
 
-  SvParams p;
-  p.raw = raw;
-  p.val = mat->val;
-  p.col = mat->col;
-  p.tiles = mat->tiles;
-  p.rp = mat->rp;
-  p.rowLB = mat->rowLB;
-  p.rowUB = mat->rowUB;
-  p.rowOrig = mat->rowOrig;
-  p.longRows = mat->longRows;
-  p.colType = mat->colType;
-  p.longPart = mat->longPart;
-  p.nTiles = mat->nTiles;
-  p.firstLongTile = mat->firstLongTile;
-  p.nLong = mat->nLong;
-  p.n = n;
-  p.sellVal = mat->sellVal;
-  p.sellCol = mat->sellCol;
-  p.sellOff = mat->sellOff;
-  p.sliceOrder = mat->sliceOrder;
-  p.nSlices = mat->nSlices;
-  p.mShort = mat->mShort;
-  p.X[0] = mat->X[0];
-  p.X[1] = mat->X[1];
-  p.dirty[0] = mat->dirty[0];
-  p.dirty[1] = mat->dirty[1];
-  p.nWords = mat->nWords;
-  p.st = mat->st;
-  p.s = s;
-  p.maxRounds = maxRounds;
-  p.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
-  const bool tiles = mat->nTiles > 0;
-  const int maxGrid = (tiles ? ctx->svBlocksPerSM : ctx->svBlocksPerSMNoTiles) * ctx->numSMs;
-  const int want = std::max(std::max(mat->nTiles, cdiv(mat->nSlices, kWarps)), cdiv(mat->nWords, kThreads));
-  const int grid = std::max(1, std::min(maxGrid, want));
-  void *args[] = { &p };
-  cudaEvent_t k0, k1;
-  if (ctx->evPool.size() < 2) {
-    cudaEvent_t e;
-    while (ctx->evPool.size() < 2) {
-      CK(cudaEventCreate(&e));
-      ctx->evPool.push_back(e);
-    }
+// ----------------------------------------------------------------------------
+// single vector, rows sharded over the GPUs of one box (peer memory)
+// ----------------------------------------------------------------------------
+int cbp_p2p_export(cbp_matrix *mat, void *handleOut)
+{
+  if (!mat || !handleOut)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  cbp_matrix::P2P &q = mat->p2p;
+  if (!q.block) {
+    auto up256 = [](size_t x) { return (x + 255) & ~static_cast<size_t>(255); };
+    q.offX1 = up256(sizeof(Bnd) * mat->n);
+    q.offD0 = q.offX1 + up256(sizeof(Bnd) * mat->n);
+    q.offD1 = q.offD0 + up256(sizeof(unsigned) * mat->nWords);
+    q.offSt = q.offD1 + up256(sizeof(unsigned) * mat->nWords);
+    q.bytes = q.offSt + up256(sizeof(SvStatus));
+    CK(cudaMalloc(reinterpret_cast<void **>(&q.block), q.bytes));
   }
-  k0 = ctx->evPool[0];
-  k1 = ctx->evPool[1];
-  CK(cudaEventRecord(k0, ctx->stream));
-  if (tiles)
-    CK(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(sv_fixpoint_kernel<true>), dim3(grid),
-      dim3(kThreads), args, sizeof(SvSmem), ctx->stream));
-  else
-    CK(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(sv_fixpoint_kernel<false>), dim3(grid),
-      dim3(kThreads), args, kSvSmallSmem, ctx->stream));
-  CK(cudaEventRecord(k1, ctx->stream));
-  ++ctx->stats.kernelLaunches;
-
-  SvStatus head;
-  CK(cudaMemcpyAsync(&head, mat->st, offsetof(SvStatus, roundChanged), cudaMemcpyDeviceToHost,
-    ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
-  out->rounds = head.rounds;
-  out->stopReason = head.stopReason;
-  out->nChanged = head.nChangedTotal;
-  if (head.stopReason == CBP_STOP_INFEASIBLE) {
-    out->feasible = 0;
-    if (head.infeasRow != INT_MAX)
-      out->infeasibleRow = head.infeasRow;
-    else if (head.infeasCol != INT_MAX)
-      out->infeasibleCol = head.infeasCol;
-  }
-  if ((rc = sv_stage_out(mat, mat->X[head.finalBuf & 1], lb, ub, flags)))
-    return rc;
-  if (roundChanged && roundCap > 0) {
-    const int done = head.rounds - (head.stopReason == CBP_STOP_INFEASIBLE ? 1 : 0);
-    const int cnt = std::min(std::min(roundCap, done), kRoundCap);
-    if (cnt > 0)
-      CK(cudaMemcpyAsync(roundChanged, mat->st->roundChanged, sizeof(int) * cnt, cudaMemcpyDeviceToHost,
-        ctx->stream));
-  }
-  CK(cudaEventRecord(ctx->evB, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
-  float ms = 0.f, kms = 0.f;
-  cudaEventElapsedTime(&ms, ctx->evA, ctx->evB);
-  cudaEventElapsedTime(&kms, k0, k1);
-  out->seconds = ms * 1.0e-3;
-  ctx->stats.lastRunMs = ms;
-  ctx->stats.lastRoundKernelMs = kms;
-  ctx->stats.lastRoundKernelLaunches = 1;
-  ctx->stats.lastRoundsTotal = head.rounds;
+  static_assert(sizeof(cudaIpcMemHandle_t) == CBP_P2P_HANDLE_BYTES, "handle size");
+  cudaIpcMemHandle_t h;
+  CK(cudaIpcGetMemHandle(&h, q.block));
+  memcpy(handleOut, &h, sizeof(h));
   return CBP_OK;
+}
+
+int cbp_p2p_attach(cbp_matrix *mat, int rank, int world, const void *handles)
+{
+  if (!mat || !handles || world < 1 || world > kMaxPeers || rank < 0 || rank >= world || !mat->p2p.block)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  cbp_matrix::P2P &q = mat->p2p;
+  q.world = world;
+  q.rank = rank;
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) {
+      q.peer[r] = q.block;
+      continue;
+    }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const unsigned char *>(handles) + static_cast<size_t>(r) * sizeof(h), sizeof(h));
+    void *ptr = nullptr;
+    CK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    q.peer[r] = static_cast<unsigned char *>(ptr);
+  }
+  return CBP_OK;
+}
+
+int cbp_p2p_prepare(cbp_matrix *mat, const double *lb, const double *ub, double primalTol, int flags)
+{
+  if (!mat || !lb || !ub || mat->p2p.world < 1)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  cbp_matrix::P2P &q = mat->p2p;
+  const Scal s = make_scal(mat, primalTol);
+  const double *dl, *du;
+  int rc = sv_stage_in(mat, const_cast<double *>(lb), const_cast<double *>(ub), flags, &dl, &du);
+  if (rc)
+    return rc;
+  CK(cudaEventRecord(ctx->evA, ctx->stream));
+  const SvState v = sv_block_state(mat, q.block);
+  if ((rc = sv_reset_state(mat, v)))
+    return rc;
+  // the peer tables: every rank's block as this rank sees it
+  SvStatus tab;
+  memset(&tab, 0, sizeof(tab));
+  for (int r = 0; r < q.world; ++r) {
+    const SvState pv = sv_block_state(mat, q.peer[r]);
+    tab.peerX[0][r] = pv.X[0];
+    tab.peerX[1][r] = pv.X[1];
+    tab.peerDirty[0][r] = pv.dirty[0];
+    tab.peerDirty[1][r] = pv.dirty[1];
+    tab.peerSt[r] = pv.st;
+  }
+  const size_t tabOff = offsetof(SvStatus, peerX);
+  CK(cudaMemcpyAsync(reinterpret_cast<unsigned char *>(v.st) + tabOff, reinterpret_cast<unsigned char *>(&tab) + tabOff,
+    sizeof(SvStatus) - tabOff, cudaMemcpyHostToDevice, ctx->stream));
+  sv_prepare_kernel<<<cdiv(mat->n, 256), 256, 0, ctx->stream>>>(dl, du, mat->colType, mat->n, v.X[0], v.X[1],
+    v.dirty[0], v.st, s, 1);
+  ++ctx->stats.kernelLaunches;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(ctx->stream));
+  q.prepared = true;
+  return CBP_OK;
+}
+
+int cbp_p2p_run(cbp_matrix *mat, double *lb, double *ub, double primalTol, int maxRounds, double timeLimitSec,
+  int rowOffset, cbp_result *out, int *roundChanged, int roundCap, int flags)
+{
+  if (!mat || !lb || !ub || !out || !mat->p2p.prepared)
+    return CBP_ERR_ARG;
+  cbp_ctx *ctx = mat->ctx;
+  CK(cudaSetDevice(ctx->device));
+  cbp_matrix::P2P &q = mat->p2p;
+  q.prepared = false;
+  memset(out, 0, sizeof(*out));
+  out->feasible = 1;
+  out->infeasibleRow = -1;
+  out->infeasibleCol = -1;
+  const Scal s = make_scal(mat, primalTol);
+  const SvState v = sv_block_state(mat, q.block);
+  SvParams p = sv_params(mat, v, s, maxRounds, timeLimitSec, 0);
+  p.world = q.world;
+  p.rank = q.rank;
+  p.rowOffset = rowOffset;
+  return sv_launch_and_collect(mat, p, v, true, lb, ub, out, roundChanged, roundCap, flags);
 }
 
 int cbp_sv_round_stamps(cbp_matrix *mat, unsigned *out, int maxRounds)

@@ -27,6 +27,15 @@ struct SvStatus {
   int sliceCtr[2];  // next short-row slice to hand out in the running round (slot = round & 1)
   int pad;
   unsigned long long t0;  // globaltimer at kernel start
+  // row-sharded runs over peer memory: arrivals of all ranks at the cross-GPU barrier (monotone),
+  // and a flag that a rank gave up waiting
+  unsigned long long arrive;
+  int p2pError;
+  int pad2;
+  // peer mappings of every rank's state block (this rank included), filled by the host
+  Bnd *peerX[2][kMaxPeers];
+  unsigned *peerDirty[2][kMaxPeers];
+  struct SvStatus *peerSt[kMaxPeers];
   // diagnostic: globaltimer seen by CTA 0 after the row phase, the long-row phase, the settle
   // phase and the decision of each of the first kStampRounds rounds (ns since t0)
   unsigned stamps[kStampRounds][4];
@@ -60,6 +69,9 @@ struct SvParams {
   SvStatus *st;
   Scal s;
   int maxRounds;  // <=0: no limit
+  // row-sharded over `world` GPUs (0 or 1: not sharded): the same state block on every rank, reached
+  // through peer mappings; candidates and flags are written to ALL ranks' blocks
+  int world, rank, rowOffset;
   int raw;        // 1: do the row phase of ONE round and stop (no R9, no bookkeeping): row-sharded mode
   unsigned long long budgetNs;  // time limit measured from kernel start
 };
@@ -88,6 +100,39 @@ struct SvSink {
   {
     atomic_max_f64(&dst[j].lb, v);
     mark(j);
+  }
+};
+
+// Row-sharded variant: every accepted candidate goes to every rank's copy of the target buffer
+// (system-scope atomics over NVLink peer mappings; the local rank is one of the peers), so after
+// the round's barrier all ranks hold the same proposals — the exchange IS the tightening kernel.
+struct SvPeerSink {
+  const SvStatus *st;  // holds the peer tables
+  int buf;             // target buffer / mark buffer of this round: peerX[buf], peerDirty[buf ^ 1]
+  int world;
+  __device__ __forceinline__ void ub(int j, double v)
+  {
+    const long long bits = __double_as_longlong(v);
+    for (int q = 0; q < world; ++q) {
+      Bnd *cell = &st->peerX[buf][q][j];
+      if (v >= 0.0)
+        atomicMin_system(reinterpret_cast<long long *>(&cell->ub), bits);
+      else
+        atomicMax_system(reinterpret_cast<unsigned long long *>(&cell->ub), static_cast<unsigned long long>(bits));
+      atomicOr_system(&st->peerDirty[buf ^ 1][q][j >> 5], 1u << (j & 31));
+    }
+  }
+  __device__ __forceinline__ void lb(int j, double v)
+  {
+    const long long bits = __double_as_longlong(v);
+    for (int q = 0; q < world; ++q) {
+      Bnd *cell = &st->peerX[buf][q][j];
+      if (v >= 0.0)
+        atomicMax_system(reinterpret_cast<long long *>(&cell->lb), bits);
+      else
+        atomicMin_system(reinterpret_cast<unsigned long long *>(&cell->lb), static_cast<unsigned long long>(bits));
+      atomicOr_system(&st->peerDirty[buf ^ 1][q][j >> 5], 1u << (j & 31));
+    }
   }
 };
 
@@ -140,15 +185,21 @@ __device__ __forceinline__ RowAct ldcg_rowact(const RowAct *q)
 
 __device__ __forceinline__ void sv_flag_row(const SvParams &p, int row)
 {
-  atomicMin(&p.st->infeasRow, p.rowOrig[row]);
+  const int global = p.rowOrig[row] + p.rowOffset;
+  if (p.world > 1) {
+    for (int q = 0; q < p.world; ++q)
+      atomicMin_system(&p.st->peerSt[q]->infeasRow, global);
+  } else {
+    atomicMin(&p.st->infeasRow, global);
+  }
 }
 
 // One pass over tiles [tBegin, tEnd) for this CTA.  phaseL=false: round phase A
 // (short / medium rows completely, long-row chunks: partial sums only).
 // phaseL=true: long-row chunks again, now with the whole row's activity known.
-template <bool phaseL>
+template <bool phaseL, class Sink>
 __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_t (&parity)[2],
-  int tBegin, int tEnd, const Bnd *__restrict__ src, SvSink &sink)
+  int tBegin, int tEnd, const Bnd *__restrict__ src, Sink &sink)
 {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int t = tBegin + blockIdx.x;
@@ -242,7 +293,8 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
 // Slices are handed out through an atomic counter (a warp asks for its next
 // slice before it starts the current one), so a round ends when the work
 // ends, not when the unluckiest statically assigned warp does.
-__device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink,
+template <class Sink>
+__device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__restrict__ src, Sink &sink,
   int *ctr)
 {
   const int lane = threadIdx.x & 31;
@@ -349,9 +401,65 @@ __device__ __forceinline__ void sv_stamp(const SvParams &p, int round, int which
   }
 }
 
+// Barrier of a round phase.  Not sharded: the grid barrier.  Sharded: every thread first pushes its
+// peer writes out (system fence), the grid meets, CTA 0 announces this rank on every rank's block and
+// waits until all ranks have announced themselves `epoch` times, then the grid meets again.  A rank
+// that waits longer than ~4 s (a peer died) raises p2pError everywhere it can and everybody leaves.
+template <bool kP2P>
+__device__ __forceinline__ bool sv_barrier(cooperative_groups::grid_group &grid, const SvParams &p,
+  unsigned long long &epoch)
+{
+  if (!kP2P) {
+    grid.sync();
+    return true;
+  }
+  __threadfence_system();
+  grid.sync();
+  ++epoch;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    for (int q = 0; q < p.world; ++q)
+      atomicAdd_system(&p.st->peerSt[q]->arrive, 1ull);
+    const unsigned long long want = epoch * static_cast<unsigned long long>(p.world);
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+    volatile unsigned long long *mine = &p.st->arrive;
+    volatile int *err = &p.st->p2pError;
+    while (*mine < want && !*err) {
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      if (t - t0 > 4000000000ull) {
+        for (int q = 0; q < p.world; ++q)
+          atomicExch_system(&p.st->peerSt[q]->p2pError, 1);
+        break;
+      }
+    }
+    __threadfence_system();
+  }
+  grid.sync();
+  return __ldcg(&p.st->p2pError) == 0;
+}
+
 // kTiles=false is the variant for matrices whose rows are all short: no
 // shared-memory staging, fewer registers, more resident warps.
-template <bool kTiles>
+template <bool kP2P>
+struct SvSinkFor {
+  typedef SvSink type;
+  static __device__ __forceinline__ SvSink make(const SvParams &p, int cur)
+  {
+    SvSink s = { p.X[cur ^ 1], p.dirty[cur] };
+    return s;
+  }
+};
+template <>
+struct SvSinkFor<true> {
+  typedef SvPeerSink type;
+  static __device__ __forceinline__ SvPeerSink make(const SvParams &p, int cur)
+  {
+    SvPeerSink s = { p.st, cur ^ 1, p.world };
+    return s;
+  }
+};
+
+template <bool kTiles, bool kP2P>
 __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fixpoint_kernel(const SvParams p)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -385,12 +493,13 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
   }
 
   const int limit = p.maxRounds > 0 ? p.maxRounds : 0x7fffffff;
+  unsigned long long epoch = 0;  // cross-GPU barriers passed so far (sharded runs)
   bool sparse = false;  // last round changed few columns: scan the marks word-wise
   for (int round = 0;; ++round) {
     const int cur = round & 1;
     const Bnd *src = p.X[cur];
     Bnd *dst = p.X[cur ^ 1];
-    SvSink sink = { dst, p.dirty[cur] };
+    typename SvSinkFor<kP2P>::type sink = SvSinkFor<kP2P>::make(p, cur);
 
     // A1: bring the target buffer up to date at the columns the previous
     // round changed (it was that round's source, so it is stale there), and
@@ -441,11 +550,13 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
     }
     if (kTiles)
       sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
-    grid.sync();
+    if (!sv_barrier<kP2P>(grid, p, epoch))
+      break;
     sv_stamp(p, round, 0);
-    if (kTiles && p.nLong > 0) {
+    if (kTiles && p.nLong > 0) {  // (long-row partials are rank-local: a row lives on one rank)
       sv_stream<true>(p, sm, parity, p.firstLongTile, p.nTiles, src, sink);
-      grid.sync();
+      if (!sv_barrier<kP2P>(grid, p, epoch))
+        break;
     }
     sv_stamp(p, round, 1);
     if (p.raw) {  // the caller combines the proposals of all row blocks and settles them itself
@@ -508,12 +619,20 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
           p.st->sliceCtr[cur ^ 1] = 0;
           unsigned long long t;
           asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-          if (t - p.st->t0 >= p.budgetNs)
-            p.st->timeUp = 1;
+          if (t - p.st->t0 >= p.budgetNs) {
+            if (kP2P) {  // rank 0's clock decides for everybody
+              if (p.rank == 0)
+                for (int q = 0; q < p.world; ++q)
+                  atomicExch_system(&p.st->peerSt[q]->timeUp, 1);
+            } else {
+              p.st->timeUp = 1;
+            }
+          }
         }
       }
     }
-    grid.sync();
+    if (!sv_barrier<kP2P>(grid, p, epoch))
+      break;
     sv_stamp(p, round, 2);
     // every thread takes the same decision from the same global words
     const int badRow = __ldcg(&p.st->infeasRow), badCol = __ldcg(&p.st->infeasCol);

@@ -7,6 +7,9 @@ torch.distributed for the plumbing.
   vector is replicated, and each Jacobi round ends with ONE max-allreduce over [lb ; -ub ; flags]
   (`propagate_row_sharded`).  The per-rank round is whatever `local_round` does — the CUDA engine on
   a GPU, or any other implementation of one round in the CPU tests of this logic.
+  `PeerShardedMatrix` is the fused form of the same decomposition for the GPUs of one box: the
+  exchange happens inside the tightening kernel over NVLink peer memory (cbp_p2p_* in
+  include/cbp_capi.h), torch.distributed only carries the IPC handles and the host barrier.
 """
 import numpy as np
 
@@ -163,3 +166,48 @@ def cuda_local_round(mat, tol=1e-7):
         r = mat.propagate_device(nlb.data_ptr(), nub.data_ptr(), tol=tol, max_rounds=1, raw_round=True)
         return nlb, nub, (r["infeasibleRow"] if not r["feasible"] else -1)
     return fn
+
+
+class PeerShardedMatrix:
+    """One rank's block of rows of `inst`, wired to the other ranks' state blocks over peer memory.
+
+    Collective constructor (every rank of `group` calls it with the same instance).  `propagate` is
+    collective as well and returns the same result and bounds on every rank."""
+
+    def __init__(self, ctx, inst, group=None):
+        import torch.distributed as dist
+
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.r0, self.r1 = row_blocks(inst.rowStart, self.world)[self.rank]
+        self.n = inst.n
+        sub = sub_instance(inst, self.r0, self.r1)
+        from .capi import Matrix
+
+        self.mat = Matrix(ctx, sub)
+        handles = [None] * self.world
+        dist.all_gather_object(handles, self.mat.p2p_export(), group=group)
+        self.mat.p2p_attach(self.rank, self.world, handles)
+        dist.barrier(group=group)
+
+    def propagate(self, lb, ub, tol=1e-7, max_rounds=0, time_limit=1e100):
+        import torch.distributed as dist
+
+        lb = np.array(lb, np.float64)
+        ub = np.array(ub, np.float64)
+        self.mat.p2p_prepare(lb, ub, tol)
+        dist.barrier(group=self.group)  # nobody may write into a block that is still being reset
+        res = self.mat.p2p_run(lb, ub, self.r0, tol, max_rounds, time_limit)
+        return res, lb, ub
+
+    def propagate_device(self, lb_ptr, ub_ptr, tol=1e-7, max_rounds=0, time_limit=1e100):
+        """Same with the bounds already in this rank's HBM (n doubles each, updated in place)."""
+        import torch.distributed as dist
+
+        self.mat.p2p_prepare(lb_ptr, ub_ptr, tol, device_ptrs=True)
+        dist.barrier(group=self.group)
+        return self.mat.p2p_run(lb_ptr, ub_ptr, self.r0, tol, max_rounds, time_limit, device_ptrs=True)
+
+    def close(self):
+        self.mat.close()
