@@ -217,6 +217,8 @@ def main():
     ap.add_argument("--impl", default="cbc_b200")
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--rowshard", default="peer", choices=["peer", "nccl"],
+                    help="single-vector workloads at N>1: fused peer-memory kernel, or one NCCL all-reduce per round")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -274,9 +276,28 @@ def main():
             r = mat.propagate_device(dlb.data_ptr(), dub.data_ptr())
             st = ctx.stats()
             return r["rounds"], st["lastRoundKernelMs"], r["rounds"]
+    elif args.rowshard == "peer":
+        # single vector over a row-sharded matrix: this rank owns a block of rows (balanced by nonzeros);
+        # accepted candidates go straight into every rank's bound vector over NVLink from inside the
+        # persistent kernel, ranks meet at barriers in peer memory (cbp_p2p_propagate)
+        from cbc_b200 import multigpu as MG
+
+        mat.close()
+        sh = MG.PeerShardedMatrix(ctx, inst)
+        mat = sh.mat
+        dlb0 = torch.tensor(work["lb"], device="cuda")
+        dub0 = torch.tensor(work["ub"], device="cuda")
+        dlb, dub = dlb0.clone(), dub0.clone()
+
+        def step():
+            dlb.copy_(dlb0)
+            dub.copy_(dub0)
+            r = sh.propagate_device(dlb.data_ptr(), dub.data_ptr())
+            st = ctx.stats()
+            # every rank does all rounds; count the rounds once (rank 0) so the SUM over ranks is the job's
+            return (r["rounds"] if rank == 0 else 0), st["lastRoundKernelMs"], r["rounds"]
     else:
-        # single vector over a row-sharded matrix: this rank owns a block of rows (balanced by
-        # nonzeros); one max all-reduce over [lb ; -ub ; flag] per round (NCCL over NVLink)
+        # the unfused form: one raw round per launch, one NCCL max all-reduce over [lb ; -ub ; flag] per round
         from cbc_b200 import multigpu as MG
 
         r0, r1 = MG.row_blocks(inst.rowStart, world)[rank]
@@ -286,12 +307,10 @@ def main():
         dlb0 = torch.tensor(work["lb"], device="cuda")
         dub0 = torch.tensor(work["ub"], device="cuda")
         isint = torch.tensor(inst.colType != 0, device="cuda")
-        sharded_ms = [0.0]
 
         def step():
             r, _, _ = MG.propagate_row_sharded(local_round, dlb0.clone(), dub0.clone(), isint, row_offset=r0,
                                                inf=inst.inf)
-            # every rank does all rounds; count the rounds once (rank 0) so the SUM over ranks is the job's
             return (r["rounds"] if rank == 0 else 0), 0.0, r["rounds"]
     for _ in range(W):
         step()
@@ -327,6 +346,17 @@ def main():
             res, us, uc, ul, uu = mat.propagate_batch_delta(work["lb"], work["ub"], s, v, b)
             return int(res["rounds"].sum()), uc.size
         h2d = 16 * inst.n + 8 * (len(s)) + 12 * len(v)
+    elif world > 1 and args.rowshard == "peer":
+        lb_pin0 = torch.from_numpy(np.ascontiguousarray(work["lb"])).pin_memory()
+        ub_pin0 = torch.from_numpy(np.ascontiguousarray(work["ub"])).pin_memory()
+        lb_pin, ub_pin = lb_pin0.clone().pin_memory(), ub_pin0.clone().pin_memory()
+
+        def e2e_step():
+            lb_pin.copy_(lb_pin0)
+            ub_pin.copy_(ub_pin0)
+            r = mat.p2p_propagate(lb_pin.numpy(), ub_pin.numpy(), sh.r0)
+            return (r["rounds"] if rank == 0 else 0), 0
+        h2d = 16 * inst.n
     elif world > 1:
         def e2e_step():
             lb_h = torch.from_numpy(work["lb"]).pin_memory()
@@ -378,6 +408,8 @@ def main():
         peaks = json.load(open(pk_path))
     peak = float(peaks.get("hbm_gbs", 6650.0))
     alg = algorithmic_bytes(inst, round_launches, vec_rounds, batch)
+    if world > 1 and not batch:
+        peak *= world  # the whole matrix is streamed once per round by all ranks together
     achieved = alg / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None,
@@ -397,12 +429,13 @@ def main():
         "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak" if batch else "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": work["desc"] + (f", rows sharded over {world} GPUs, one max all-reduce of [lb;-ub] "
-                                              f"per round" if (world > 1 and not batch) else ""), "l2": "inputs larger than L2" if (alg / max(1, round_launches)) > 126e6
+        "config": {"workload": work["desc"] + (f", rows sharded over {world} GPUs" if (world > 1 and not batch) else ""), "l2": "inputs larger than L2" if (alg / max(1, round_launches)) > 126e6
                    else "working set fits L2; matrix re-read every round by design",
                    "vectors_per_gpu": work["B"],
                    "sharding": "node batch sharded across GPUs, no collective" if batch else
-                   ("rows sharded, NCCL max all-reduce per round" if world > 1 else "single GPU")},
+                   (("rows sharded, candidates exchanged inside the kernel over NVLink peer memory"
+                     if args.rowshard == "peer" else "rows sharded, NCCL max all-reduce per round")
+                    if world > 1 else "single GPU")},
         "roofline": roofline,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
         "gpu_launches": int(launches),

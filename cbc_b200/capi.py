@@ -39,7 +39,7 @@ SYMBOLS = [
     "cbp_matrix_upload", "cbp_matrix_free", "cbp_singletons", "cbp_propagate", "cbp_propagate_batch",
     "cbp_propagate_batch_delta", "cbp_batch_load_delta", "cbp_batch_run",
     "cbp_batch_fetch", "cbp_batch_fetch_dense", "cbp_row_activity", "cbp_sv_round_stamps", "cbp_singletons_noalloc",
-    "cbp_p2p_export", "cbp_p2p_attach", "cbp_p2p_prepare", "cbp_p2p_run",
+    "cbp_p2p_export", "cbp_p2p_attach", "cbp_p2p_propagate",
 ]
 P2P_HANDLE_BYTES = 64
 ROUND_CAP = 1024
@@ -83,10 +83,9 @@ def load():
     lib.cbp_batch_fetch_dense.argtypes = [vp, vp, vp, i32]
     lib.cbp_row_activity.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32]
     lib.cbp_sv_round_stamps.argtypes = [vp, vp, i32]
-    lib.cbp_p2p_export.argtypes = [vp, vp]
+    lib.cbp_p2p_export.argtypes = [vp, i32, vp]
     lib.cbp_p2p_attach.argtypes = [vp, i32, i32, vp]
-    lib.cbp_p2p_prepare.argtypes = [vp, vp, vp, f64, i32]
-    lib.cbp_p2p_run.argtypes = [vp, vp, vp, f64, i32, f64, i32, C.POINTER(Result), vp, i32, i32]
+    lib.cbp_p2p_propagate.argtypes = [vp, vp, vp, f64, i32, f64, i32, C.POINTER(Result), vp, i32, i32]
     lib.cbp_singletons_noalloc.argtypes = [i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, f64, vp, vp, f64,
                                            C.POINTER(i32), C.POINTER(i32), vp]
     _lib = lib
@@ -226,10 +225,10 @@ class Matrix:
         return _res_dict(r)
 
     # -- rows sharded over the GPUs of one box (peer memory) ----------------
-    def p2p_export(self):
-        """This rank's state block as a CUDA IPC handle (bytes)."""
+    def p2p_export(self, world):
+        """This rank's state block (for a group of `world` ranks) as a CUDA IPC handle (bytes)."""
         h = (C.c_ubyte * P2P_HANDLE_BYTES)()
-        self.ctx.check(self.ctx.lib.cbp_p2p_export(self.h, h), "cbp_p2p_export")
+        self.ctx.check(self.ctx.lib.cbp_p2p_export(self.h, world, h), "cbp_p2p_export")
         return bytes(h)
 
     def p2p_attach(self, rank, world, handles):
@@ -238,25 +237,18 @@ class Matrix:
         assert len(blob) == world * P2P_HANDLE_BYTES
         self.ctx.check(self.ctx.lib.cbp_p2p_attach(self.h, rank, world, blob), "cbp_p2p_attach")
 
-    def p2p_prepare(self, lb, ub, tol=1e-7, device_ptrs=False):
-        if device_ptrs:
-            a, b, flags = C.c_void_p(lb), C.c_void_p(ub), FLAG_DEVICE_PTRS
-        else:
-            self._p2p_lb = np.ascontiguousarray(lb, np.float64)
-            self._p2p_ub = np.ascontiguousarray(ub, np.float64)
-            a, b, flags = _ptr(self._p2p_lb), _ptr(self._p2p_ub), 0
-        self.ctx.check(self.ctx.lib.cbp_p2p_prepare(self.h, a, b, tol, flags), "cbp_p2p_prepare")
-
-    def p2p_run(self, lb, ub, row_offset, tol=1e-7, max_rounds=0, time_limit=1e100, device_ptrs=False):
-        """lb/ub: writable numpy arrays (or device pointers) that receive the final bounds."""
+    def p2p_propagate(self, lb, ub, row_offset, tol=1e-7, max_rounds=0, time_limit=1e100, device_ptrs=False):
+        """Collective over the attached group.  lb/ub: writable contiguous float64 numpy arrays (or device
+        pointers) holding the input bounds; they receive the final bounds."""
         r = Result()
         per_round = np.zeros(ROUND_CAP, np.int32)
         if device_ptrs:
             a, b, flags = C.c_void_p(lb), C.c_void_p(ub), FLAG_DEVICE_PTRS
         else:
             a, b, flags = _ptr(lb), _ptr(ub), 0
-        self.ctx.check(self.ctx.lib.cbp_p2p_run(self.h, a, b, tol, max_rounds, time_limit, row_offset, C.byref(r),
-                                                _ptr(per_round), ROUND_CAP, flags), "cbp_p2p_run")
+        self.ctx.check(self.ctx.lib.cbp_p2p_propagate(self.h, a, b, tol, max_rounds, time_limit, row_offset,
+                                                      C.byref(r), _ptr(per_round), ROUND_CAP, flags),
+                       "cbp_p2p_propagate")
         d = _res_dict(r)
         done = d["rounds"] - (0 if d["feasible"] else 1)
         d["roundChanged"] = per_round[:max(0, min(done, ROUND_CAP))].tolist()

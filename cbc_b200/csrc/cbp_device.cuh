@@ -21,7 +21,15 @@ constexpr int kShortLen = 32;      // rows up to this length: one thread per row
 #define CBP_SV_NT_BLOCKS 3
 #endif
 constexpr int kSvChunk = CBP_SV_CHUNK;        // sliced-ELL steps whose loads are in flight together
+#ifndef CBP_SV_CHUNK_SHARDED
+#define CBP_SV_CHUNK_SHARDED 8
+#endif
+constexpr int kSvChunkSharded = CBP_SV_CHUNK_SHARDED;  // the same for the row-sharded kernel (which has fewer registers to spare)
 constexpr int kSvNoTileBlocks = CBP_SV_NT_BLOCKS;  // CTAs per SM of the short-rows-only variant
+#ifndef CBP_SV_SHARDED_BLOCKS
+#define CBP_SV_SHARDED_BLOCKS 3
+#endif
+constexpr int kSvShardedBlocks = CBP_SV_SHARDED_BLOCKS;  // CTAs per SM of the row-sharded variants
 #ifndef CBP_SV_P2ROWS
 #define CBP_SV_P2ROWS 2
 #endif
@@ -88,21 +96,49 @@ __device__ __forceinline__ bool col_is_int(int packed) { return packed < 0; }
 // stored: R7 adds +0.0).  For v >= 0 signed-int order equals double order and
 // any negative double is a negative int; for v < 0 unsigned order is reversed
 // double order among negatives and every non-negative double is smaller.
+// Reductions written as PTX `red`: nothing comes back, the thread does not wait.  (Left to the
+// compiler, an atomicMax whose result is unused becomes RED in some kernels and a returning ATOM in
+// others; the latter holds the issuing warp's scoreboard until L2 answers.)
+__device__ __forceinline__ void red_max_s64(void *addr, long long v)
+{
+  asm volatile("red.relaxed.gpu.global.max.s64 [%0], %1;" ::"l"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_min_s64(void *addr, long long v)
+{
+  asm volatile("red.relaxed.gpu.global.min.s64 [%0], %1;" ::"l"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_max_u64(void *addr, unsigned long long v)
+{
+  asm volatile("red.relaxed.gpu.global.max.u64 [%0], %1;" ::"l"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_min_u64(void *addr, unsigned long long v)
+{
+  asm volatile("red.relaxed.gpu.global.min.u64 [%0], %1;" ::"l"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_min_s32(int *addr, int v)
+{
+  asm volatile("red.relaxed.gpu.global.min.s32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_or_b32(unsigned *addr, unsigned v)
+{
+  asm volatile("red.relaxed.gpu.global.or.b32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+
+// max / min on doubles through the ordering of their bit patterns: as signed integers for values >= 0,
+// reversed as unsigned integers for negative ones
 __device__ __forceinline__ void atomic_max_f64(double *addr, double v)
 {
   if (v >= 0.0)
-    atomicMax(reinterpret_cast<long long *>(addr), __double_as_longlong(v));
+    red_max_s64(addr, __double_as_longlong(v));
   else
-    atomicMin(reinterpret_cast<unsigned long long *>(addr),
-      static_cast<unsigned long long>(__double_as_longlong(v)));
+    red_min_u64(addr, static_cast<unsigned long long>(__double_as_longlong(v)));
 }
 __device__ __forceinline__ void atomic_min_f64(double *addr, double v)
 {
   if (v >= 0.0)
-    atomicMin(reinterpret_cast<long long *>(addr), __double_as_longlong(v));
+    red_min_s64(addr, __double_as_longlong(v));
   else
-    atomicMax(reinterpret_cast<unsigned long long *>(addr),
-      static_cast<unsigned long long>(__double_as_longlong(v)));
+    red_max_u64(addr, static_cast<unsigned long long>(__double_as_longlong(v)));
 }
 
 __device__ __forceinline__ Bnd ldcg_bnd(const Bnd *p)

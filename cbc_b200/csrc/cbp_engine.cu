@@ -26,8 +26,7 @@ struct cbp_ctx {
   cudaStream_t stream = nullptr;
   bool ownsStream = false;
   int numSMs = 0;
-  int svBlocksPerSM = 0;       // persistent kernel with tile staging
-  int svBlocksPerSMNoTiles = 0;  // ... for matrices with short rows only
+  int svBlocksPerSM[2][2] = {};  // resident CTAs per SM of the persistent kernel, [tile staging][row-sharded]
   std::string err;
   cbp_stats stats {};
   cudaEvent_t evA = nullptr, evB = nullptr;
@@ -92,11 +91,16 @@ struct cbp_matrix {
   double *dAct = nullptr;                 // row-activity staging (2m doubles + 2m ints)
   // row-sharded runs over peer memory: one state block per rank, mapped into every rank
   struct P2P {
-    unsigned char *block = nullptr;  // own block: X0 | X1 | dirty0 | dirty1 | status
-    size_t offX1 = 0, offD0 = 0, offD1 = 0, offSt = 0, bytes = 0;
+    // own block: X0 | X1 | dirty0 | dirty1 | proposals [2][world][n] | their marks [2][world][words] | status
+    unsigned char *block = nullptr;
+    size_t offX1 = 0, offD0 = 0, offD1 = 0, offP = 0, offM = 0, offSt = 0, bytes = 0;
+    size_t strideP = 0, strideD = 0;  // elements between two ranks' slots
     int world = 0, rank = 0;
     unsigned char *peer[kMaxPeers] = {};  // every rank's block as seen from here (peer[rank] == block)
-    bool prepared = false;
+    unsigned long long epoch = 0;  // cross-GPU barriers passed so far (the same number on every rank)
+    bool attached = false;
+    bool broken = false;  // a rank timed out: the group cannot be used again
+    bool lastRunHere = false;  // the latest single-vector run used this block (for cbp_sv_round_stamps)
   } p2p;
   BatchState bt;
 };
@@ -164,12 +168,16 @@ cbp_ctx *cbp_create(int device)
     static_cast<int>(sizeof(SvSmem)));
   cudaFuncSetAttribute(sv_fixpoint_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
     static_cast<int>(sizeof(SvSmem)));
-  int perSM = 0, perSM2 = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, sv_fixpoint_kernel<true, true>, kThreads, sizeof(SvSmem));
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM2, sv_fixpoint_kernel<false, true>, kThreads, kSvSmallSmem);
-  ctx->svBlocksPerSM = perSM;
-  ctx->svBlocksPerSMNoTiles = perSM2;
-  if (perSM < 1 || perSM2 < 1) {
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->svBlocksPerSM[1][0], sv_fixpoint_kernel<true, false>, kThreads,
+    sizeof(SvSmem));
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->svBlocksPerSM[1][1], sv_fixpoint_kernel<true, true>, kThreads,
+    sizeof(SvSmem));
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->svBlocksPerSM[0][0], sv_fixpoint_kernel<false, false>, kThreads,
+    kSvSmallSmem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->svBlocksPerSM[0][1], sv_fixpoint_kernel<false, true>, kThreads,
+    kSvSmallSmem);
+  if (ctx->svBlocksPerSM[0][0] < 1 || ctx->svBlocksPerSM[0][1] < 1 || ctx->svBlocksPerSM[1][0] < 1
+    || ctx->svBlocksPerSM[1][1] < 1) {
     fprintf(stderr, "cbp_create: persistent kernel does not fit on this device\n");
     cbp_destroy(ctx);
     return nullptr;
@@ -243,7 +251,7 @@ void cbp_matrix_free(cbp_matrix *mat)
     if (p)
       cudaFree(p);
   for (int r = 0; r < mat->p2p.world; ++r)
-    if (r != mat->p2p.rank && mat->p2p.peer[r])
+    if (mat->p2p.attached && r != mat->p2p.rank && mat->p2p.peer[r])
       cudaIpcCloseMemHandle(mat->p2p.peer[r]);
   if (mat->p2p.block)
     cudaFree(mat->p2p.block);
@@ -552,6 +560,8 @@ struct SvState {
   Bnd *X[2];
   unsigned *dirty[2];
   SvStatus *st;
+  Bnd *inP[2];  // row-sharded runs only: proposal slots [world] and their marks, per round parity
+  unsigned *inD[2];
 };
 
 static SvState sv_own_state(cbp_matrix *mat)
@@ -562,6 +572,8 @@ static SvState sv_own_state(cbp_matrix *mat)
   v.dirty[0] = mat->dirty[0];
   v.dirty[1] = mat->dirty[1];
   v.st = mat->st;
+  v.inP[0] = v.inP[1] = nullptr;
+  v.inD[0] = v.inD[1] = nullptr;
   return v;
 }
 
@@ -573,6 +585,11 @@ static SvState sv_block_state(const cbp_matrix *mat, unsigned char *base)
   v.dirty[0] = reinterpret_cast<unsigned *>(base + mat->p2p.offD0);
   v.dirty[1] = reinterpret_cast<unsigned *>(base + mat->p2p.offD1);
   v.st = reinterpret_cast<SvStatus *>(base + mat->p2p.offSt);
+  const cbp_matrix::P2P &q = mat->p2p;
+  v.inP[0] = reinterpret_cast<Bnd *>(base + q.offP);
+  v.inP[1] = v.inP[0] + q.strideP * q.world;
+  v.inD[0] = reinterpret_cast<unsigned *>(base + q.offM);
+  v.inD[1] = v.inD[0] + q.strideD * q.world;
   return v;
 }
 
@@ -583,8 +600,10 @@ static int sv_reset_state(cbp_matrix *mat, const SvState &v)
   memset(&init, 0, sizeof(init));
   init.infeasRow = INT_MAX;
   init.infeasCol = INT_MAX;
-  // only the head of the status block needs initial values
-  CK(cudaMemsetAsync(v.st, 0, sizeof(SvStatus), ctx->stream));
+  for (int r = 0; r < kMaxPeers; ++r)
+    init.inRowFlag[0][r] = init.inRowFlag[1][r] = INT_MAX;
+  // only the head of the status block needs initial values; the arrival counter at its end lives on
+  CK(cudaMemsetAsync(v.st, 0, offsetof(SvStatus, arrive), ctx->stream));
   CK(cudaMemcpyAsync(v.st, &init, offsetof(SvStatus, roundChanged), cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaMemsetAsync(v.dirty[0], 0, sizeof(unsigned) * mat->nWords, ctx->stream));
   CK(cudaMemsetAsync(v.dirty[1], 0, sizeof(unsigned) * mat->nWords, ctx->stream));
@@ -622,12 +641,24 @@ static SvParams sv_params(cbp_matrix *mat, const SvState &v, const Scal &s, int 
   p.dirty[1] = v.dirty[1];
   p.nWords = mat->nWords;
   p.st = v.st;
+  p.inP[0] = v.inP[0];
+  p.inP[1] = v.inP[1];
+  p.inD[0] = v.inD[0];
+  p.inD[1] = v.inD[1];
+  p.strideP = mat->p2p.strideP;
+  p.strideD = mat->p2p.strideD;
+  for (int k = 0; k < 2; ++k) {
+    p.myP[k] = v.inP[k] ? v.inP[k] + mat->p2p.rank * mat->p2p.strideP : nullptr;
+    p.myD[k] = v.inD[k] ? v.inD[k] + mat->p2p.rank * mat->p2p.strideD : nullptr;
+    p.myRowFlag[k] = &v.st->inRowFlag[k][mat->p2p.rank];
+  }
   p.s = s;
   p.maxRounds = maxRounds;
   p.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
   p.world = 0;
   p.rank = 0;
   p.rowOffset = 0;
+  p.epoch0 = 0;
   return p;
 }
 
@@ -638,7 +669,7 @@ static int sv_launch_and_collect(cbp_matrix *mat, const SvParams &pIn, const SvS
   cbp_ctx *ctx = mat->ctx;
   SvParams p = pIn;
   const bool tiles = mat->nTiles > 0;
-  const int maxGrid = (tiles ? ctx->svBlocksPerSM : ctx->svBlocksPerSMNoTiles) * ctx->numSMs;
+  const int maxGrid = ctx->svBlocksPerSM[tiles ? 1 : 0][p2p ? 1 : 0] * ctx->numSMs;
   const int want = std::max(std::max(mat->nTiles, cdiv(mat->nSlices, kWarps)), cdiv(mat->nWords, kThreads));
   const int grid = std::max(1, std::min(maxGrid, want));
   void *args[] = { &p };
@@ -649,6 +680,7 @@ static int sv_launch_and_collect(cbp_matrix *mat, const SvParams &pIn, const SvS
   }
   cudaEvent_t k0 = ctx->evPool[0], k1 = ctx->evPool[1];
   CK(cudaEventRecord(k0, ctx->stream));
+  mat->p2p.lastRunHere = p2p;
   void *fn = tiles ? (p2p ? reinterpret_cast<void *>(sv_fixpoint_kernel<true, true>)
                           : reinterpret_cast<void *>(sv_fixpoint_kernel<true, false>))
                    : (p2p ? reinterpret_cast<void *>(sv_fixpoint_kernel<false, true>)
@@ -664,9 +696,13 @@ static int sv_launch_and_collect(cbp_matrix *mat, const SvParams &pIn, const SvS
   SvStatus head;
   CK(cudaMemcpyAsync(&head, v.st, offsetof(SvStatus, roundChanged), cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
-  if (p2p && head.p2pError) {
-    ctx->err = "row-sharded run: a rank did not reach the barrier in time";
-    return CBP_ERR_CUDA;
+  if (p2p) {
+    if (head.p2pError) {
+      mat->p2p.broken = true;
+      ctx->err = "row-sharded run: a rank did not reach the barrier in time";
+      return CBP_ERR_CUDA;
+    }
+    mat->p2p.epoch = head.epochEnd;
   }
   out->rounds = head.rounds;
   out->stopReason = head.stopReason;
@@ -786,21 +822,31 @@ int cbp_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int
 // ----------------------------------------------------------------------------
 // single vector, rows sharded over the GPUs of one box (peer memory)
 // ----------------------------------------------------------------------------
-int cbp_p2p_export(cbp_matrix *mat, void *handleOut)
+int cbp_p2p_export(cbp_matrix *mat, int world, void *handleOut)
 {
-  if (!mat || !handleOut)
+  if (!mat || !handleOut || world < 1 || world > kMaxPeers)
     return CBP_ERR_ARG;
   cbp_ctx *ctx = mat->ctx;
   CK(cudaSetDevice(ctx->device));
   cbp_matrix::P2P &q = mat->p2p;
+  if (q.block && q.world != world) {
+    ctx->err = "cbp_p2p_export: this matrix already belongs to a group of another size";
+    return CBP_ERR_ARG;
+  }
   if (!q.block) {
     auto up256 = [](size_t x) { return (x + 255) & ~static_cast<size_t>(255); };
+    q.world = world;
+    q.strideP = up256(sizeof(Bnd) * mat->n) / sizeof(Bnd);
+    q.strideD = up256(sizeof(unsigned) * mat->nWords) / sizeof(unsigned);
     q.offX1 = up256(sizeof(Bnd) * mat->n);
     q.offD0 = q.offX1 + up256(sizeof(Bnd) * mat->n);
     q.offD1 = q.offD0 + up256(sizeof(unsigned) * mat->nWords);
-    q.offSt = q.offD1 + up256(sizeof(unsigned) * mat->nWords);
+    q.offP = q.offD1 + up256(sizeof(unsigned) * mat->nWords);
+    q.offM = q.offP + 2 * world * q.strideP * sizeof(Bnd);
+    q.offSt = q.offM + 2 * world * q.strideD * sizeof(unsigned);
     q.bytes = q.offSt + up256(sizeof(SvStatus));
     CK(cudaMalloc(reinterpret_cast<void **>(&q.block), q.bytes));
+    CK(cudaMemset(q.block, 0, q.bytes));
   }
   static_assert(sizeof(cudaIpcMemHandle_t) == CBP_P2P_HANDLE_BYTES, "handle size");
   cudaIpcMemHandle_t h;
@@ -811,13 +857,13 @@ int cbp_p2p_export(cbp_matrix *mat, void *handleOut)
 
 int cbp_p2p_attach(cbp_matrix *mat, int rank, int world, const void *handles)
 {
-  if (!mat || !handles || world < 1 || world > kMaxPeers || rank < 0 || rank >= world || !mat->p2p.block)
+  if (!mat || !handles || world != mat->p2p.world || rank < 0 || rank >= world || !mat->p2p.block)
     return CBP_ERR_ARG;
   cbp_ctx *ctx = mat->ctx;
   CK(cudaSetDevice(ctx->device));
   cbp_matrix::P2P &q = mat->p2p;
-  q.world = world;
   q.rank = rank;
+  q.attached = true;
   for (int r = 0; r < world; ++r) {
     if (r == rank) {
       q.peer[r] = q.block;
@@ -832,16 +878,25 @@ int cbp_p2p_attach(cbp_matrix *mat, int rank, int world, const void *handles)
   return CBP_OK;
 }
 
-int cbp_p2p_prepare(cbp_matrix *mat, const double *lb, const double *ub, double primalTol, int flags)
+int cbp_p2p_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int maxRounds, double timeLimitSec,
+  int rowOffset, cbp_result *out, int *roundChanged, int roundCap, int flags)
 {
-  if (!mat || !lb || !ub || mat->p2p.world < 1)
+  if (!mat || !lb || !ub || !out || !mat->p2p.attached)
     return CBP_ERR_ARG;
   cbp_ctx *ctx = mat->ctx;
-  CK(cudaSetDevice(ctx->device));
   cbp_matrix::P2P &q = mat->p2p;
+  if (q.broken) {
+    ctx->err = "row-sharded group unusable after a barrier timeout";
+    return CBP_ERR_ARG;
+  }
+  CK(cudaSetDevice(ctx->device));
+  memset(out, 0, sizeof(*out));
+  out->feasible = 1;
+  out->infeasibleRow = -1;
+  out->infeasibleCol = -1;
   const Scal s = make_scal(mat, primalTol);
   const double *dl, *du;
-  int rc = sv_stage_in(mat, const_cast<double *>(lb), const_cast<double *>(ub), flags, &dl, &du);
+  int rc = sv_stage_in(mat, lb, ub, flags, &dl, &du);
   if (rc)
     return rc;
   CK(cudaEventRecord(ctx->evA, ctx->stream));
@@ -853,43 +908,39 @@ int cbp_p2p_prepare(cbp_matrix *mat, const double *lb, const double *ub, double 
   memset(&tab, 0, sizeof(tab));
   for (int r = 0; r < q.world; ++r) {
     const SvState pv = sv_block_state(mat, q.peer[r]);
-    tab.peerX[0][r] = pv.X[0];
-    tab.peerX[1][r] = pv.X[1];
-    tab.peerDirty[0][r] = pv.dirty[0];
-    tab.peerDirty[1][r] = pv.dirty[1];
+    for (int k = 0; k < 2; ++k) {  // this rank's slot over there
+      tab.pushP[k][r] = pv.inP[k] + q.rank * q.strideP;
+      tab.pushD[k][r] = pv.inD[k] + q.rank * q.strideD;
+    }
     tab.peerSt[r] = pv.st;
   }
-  const size_t tabOff = offsetof(SvStatus, peerX);
+  tab.inP[0] = v.inP[0];
+  tab.inP[1] = v.inP[1];
+  tab.inD[0] = v.inD[0];
+  tab.inD[1] = v.inD[1];
+  tab.strideP = q.strideP;
+  tab.strideD = q.strideD;
+  tab.world = q.world;
+  tab.rank = q.rank;
+  tab.nWords = mat->nWords;
+  tab.scal = s;
+  const size_t tabOff = offsetof(SvStatus, pushP), tabEnd = offsetof(SvStatus, stamps);
   CK(cudaMemcpyAsync(reinterpret_cast<unsigned char *>(v.st) + tabOff, reinterpret_cast<unsigned char *>(&tab) + tabOff,
-    sizeof(SvStatus) - tabOff, cudaMemcpyHostToDevice, ctx->stream));
+    tabEnd - tabOff, cudaMemcpyHostToDevice, ctx->stream));
+  // no proposals in this rank's own slots, no marks in any slot; what R11 changes is marked as a
+  // (valueless) proposal of round 0 so that every rank counts it there
+  for (int k = 0; k < 2; ++k)
+    sv_no_proposals_kernel<<<cdiv(mat->n, 256), 256, 0, ctx->stream>>>(v.inP[k] + q.rank * q.strideP, mat->n);
+  CK(cudaMemsetAsync(v.inD[0], 0, q.offSt - q.offM, ctx->stream));
   sv_prepare_kernel<<<cdiv(mat->n, 256), 256, 0, ctx->stream>>>(dl, du, mat->colType, mat->n, v.X[0], v.X[1],
-    v.dirty[0], v.st, s, 1);
-  ++ctx->stats.kernelLaunches;
+    v.inD[0] + q.rank * q.strideD, v.st, s, 1);
+  ctx->stats.kernelLaunches += 3;
   CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(ctx->stream));
-  q.prepared = true;
-  return CBP_OK;
-}
-
-int cbp_p2p_run(cbp_matrix *mat, double *lb, double *ub, double primalTol, int maxRounds, double timeLimitSec,
-  int rowOffset, cbp_result *out, int *roundChanged, int roundCap, int flags)
-{
-  if (!mat || !lb || !ub || !out || !mat->p2p.prepared)
-    return CBP_ERR_ARG;
-  cbp_ctx *ctx = mat->ctx;
-  CK(cudaSetDevice(ctx->device));
-  cbp_matrix::P2P &q = mat->p2p;
-  q.prepared = false;
-  memset(out, 0, sizeof(*out));
-  out->feasible = 1;
-  out->infeasibleRow = -1;
-  out->infeasibleCol = -1;
-  const Scal s = make_scal(mat, primalTol);
-  const SvState v = sv_block_state(mat, q.block);
   SvParams p = sv_params(mat, v, s, maxRounds, timeLimitSec, 0);
   p.world = q.world;
   p.rank = q.rank;
   p.rowOffset = rowOffset;
+  p.epoch0 = q.epoch;
   return sv_launch_and_collect(mat, p, v, true, lb, ub, out, roundChanged, roundCap, flags);
 }
 
@@ -900,14 +951,17 @@ int cbp_sv_round_stamps(cbp_matrix *mat, unsigned *out, int maxRounds)
   cbp_ctx *ctx = mat->ctx;
   CK(cudaSetDevice(ctx->device));
   const int cnt = std::min(maxRounds, kStampRounds);
-  CK(cudaMemcpy(out, reinterpret_cast<const char *>(mat->st) + offsetof(SvStatus, stamps), sizeof(unsigned) * 4 * cnt,
+  const SvStatus *st = mat->p2p.lastRunHere ? sv_block_state(mat, mat->p2p.block).st : mat->st;
+  CK(cudaMemcpy(out, reinterpret_cast<const char *>(st) + offsetof(SvStatus, stamps), sizeof(unsigned) * 4 * cnt,
     cudaMemcpyDeviceToHost));
   if (getenv("CBP_STAMPS_X"))  // tuning aid: CTA 0's own A1 / rows timestamps instead of columns 1 and 3
     for (int r = 0; r < cnt; ++r) {
-      unsigned x[2];
-      CK(cudaMemcpy(x, reinterpret_cast<const char *>(mat->st) + offsetof(SvStatus, stampsX) + 8 * r, 8, cudaMemcpyDeviceToHost));
+      unsigned x[4];
+      CK(cudaMemcpy(x, reinterpret_cast<const char *>(st) + offsetof(SvStatus, stampsX) + 16 * r, 16, cudaMemcpyDeviceToHost));
       out[4 * r + 1] = x[0];
       out[4 * r + 3] = x[1];
+      if (getenv("CBP_STAMPS_TOP"))
+        out[4 * r + 0] = x[2];
     }
   return cnt;
 }

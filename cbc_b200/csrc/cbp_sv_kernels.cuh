@@ -9,6 +9,7 @@
 // loop has stopped.
 #pragma once
 #include <cooperative_groups.h>
+#include <math_constants.h>
 
 #include "cbp_device.cuh"
 
@@ -27,20 +28,37 @@ struct SvStatus {
   int sliceCtr[2];  // next short-row slice to hand out in the running round (slot = round & 1)
   int pad;
   unsigned long long t0;  // globaltimer at kernel start
-  // row-sharded runs over peer memory: arrivals of all ranks at the cross-GPU barrier (monotone),
-  // and a flag that a rank gave up waiting
-  unsigned long long arrive;
+  // row-sharded runs over peer memory: cross-GPU barriers passed when the kernel left (the next
+  // run starts counting there), and a flag that a rank gave up waiting
+  unsigned long long epochEnd;
   int p2pError;
-  int pad2;
-  // peer mappings of every rank's state block (this rank included), filled by the host
-  Bnd *peerX[2][kMaxPeers];
-  unsigned *peerDirty[2][kMaxPeers];
+  int abortRun;  // written by CTA 0 only: leave the kernel (a barrier timed out)
+  unsigned long long goEpoch;  // written by CTA 0 only: the last cross-GPU barrier all ranks have reached
+  unsigned long long ctaArrive;  // CTAs of this rank that have reached a cross-GPU barrier in this run
+  // per round parity: every rank's first violated row (whole-matrix index; slot = rank, pushed by its
+  // owner), and rank 0's "time is up"
+  int inRowFlag[2][kMaxPeers];
+  int inTime[2];
+  // where this rank's proposals go on every rank q: q's inbox slot for this rank (per round parity),
+  // and q's status block
+  Bnd *pushP[2][kMaxPeers];
+  unsigned *pushD[2][kMaxPeers];
   struct SvStatus *peerSt[kMaxPeers];
+  // constants of a row-sharded run, filled by the host: the exchange routines are separate functions
+  // and fetch them here instead of taking them as arguments
+  Bnd *inP[2];
+  unsigned *inD[2];
+  size_t strideP, strideD;
+  int world, rank, nWords, pad3;
+  Scal scal;
   // diagnostic: globaltimer seen by CTA 0 after the row phase, the long-row phase, the settle
   // phase and the decision of each of the first kStampRounds rounds (ns since t0)
   unsigned stamps[kStampRounds][4];
-  unsigned stampsX[kStampRounds][2];  // CTA 0 only: after A1, after its own share of the rows (before the barrier)
+  unsigned stampsX[kStampRounds][4];  // CTA 0 only: after A1, after its own share of the rows (before the barrier)
   int roundChanged[kRoundCap];
+  // row-sharded runs: arrivals of all ranks at the cross-GPU barrier.  Monotone over the life of the
+  // block and never reset: a peer that is ahead may already have announced itself for the next run.
+  unsigned long long arrive;
 };
 
 struct SvParams {
@@ -69,9 +87,22 @@ struct SvParams {
   SvStatus *st;
   Scal s;
   int maxRounds;  // <=0: no limit
-  // row-sharded over `world` GPUs (0 or 1: not sharded): the same state block on every rank, reached
-  // through peer mappings; candidates and flags are written to ALL ranks' blocks
+  // rows sharded over `world` GPUs.  inP[k] / inD[k] (k = round & 1) hold one slot per rank: n proposals
+  // (strideP apart) and their mark words (strideD apart).  Accepted candidates go into this rank's OWN
+  // slot; after the rows of a round every rank copies its marked proposals into its slot on every other
+  // rank over NVLink; after the round's barrier every rank settles its own full copy of the bounds from
+  // its (now local) slots.
+  Bnd *inP[2];
+  unsigned *inD[2];
+  size_t strideP, strideD;
+  // this rank's own slot and row flag per round parity, spelled out by the host: a plain parameter
+  // can be re-read where it is needed, an address computed in the kernel would sit in registers
+  // across the row loops
+  Bnd *myP[2];
+  unsigned *myD[2];
+  int *myRowFlag[2];
   int world, rank, rowOffset;
+  unsigned long long epoch0;  // cross-GPU barriers this group has passed in earlier runs
   int raw;        // 1: do the row phase of ONE round and stop (no R9, no bookkeeping): row-sharded mode
   unsigned long long budgetNs;  // time limit measured from kernel start
 };
@@ -86,11 +117,12 @@ struct SvSmem {
   RowAct stash[kThreads];  // a long row's chunk partials, fetched one per thread
 };
 
-// publishes accepted candidates into the round's target buffer
+// publishes accepted candidates into the round's target buffer (row-sharded: the proposal buffer)
 struct SvSink {
   Bnd *dst;
   unsigned *dirty;
-  __device__ __forceinline__ void mark(int j) { atomicOr(&dirty[j >> 5], 1u << (j & 31)); }
+  int *rowFlag;  // min over violated rows
+  __device__ __forceinline__ void mark(int j) { red_or_b32(&dirty[j >> 5], 1u << (j & 31)); }
   __device__ __forceinline__ void ub(int j, double v)
   {
     atomic_min_f64(&dst[j].ub, v);
@@ -101,39 +133,7 @@ struct SvSink {
     atomic_max_f64(&dst[j].lb, v);
     mark(j);
   }
-};
-
-// Row-sharded variant: every accepted candidate goes to every rank's copy of the target buffer
-// (system-scope atomics over NVLink peer mappings; the local rank is one of the peers), so after
-// the round's barrier all ranks hold the same proposals — the exchange IS the tightening kernel.
-struct SvPeerSink {
-  const SvStatus *st;  // holds the peer tables
-  int buf;             // target buffer / mark buffer of this round: peerX[buf], peerDirty[buf ^ 1]
-  int world;
-  __device__ __forceinline__ void ub(int j, double v)
-  {
-    const long long bits = __double_as_longlong(v);
-    for (int q = 0; q < world; ++q) {
-      Bnd *cell = &st->peerX[buf][q][j];
-      if (v >= 0.0)
-        atomicMin_system(reinterpret_cast<long long *>(&cell->ub), bits);
-      else
-        atomicMax_system(reinterpret_cast<unsigned long long *>(&cell->ub), static_cast<unsigned long long>(bits));
-      atomicOr_system(&st->peerDirty[buf ^ 1][q][j >> 5], 1u << (j & 31));
-    }
-  }
-  __device__ __forceinline__ void lb(int j, double v)
-  {
-    const long long bits = __double_as_longlong(v);
-    for (int q = 0; q < world; ++q) {
-      Bnd *cell = &st->peerX[buf][q][j];
-      if (v >= 0.0)
-        atomicMax_system(reinterpret_cast<long long *>(&cell->lb), bits);
-      else
-        atomicMin_system(reinterpret_cast<unsigned long long *>(&cell->lb), static_cast<unsigned long long>(bits));
-      atomicOr_system(&st->peerDirty[buf ^ 1][q][j >> 5], 1u << (j & 31));
-    }
-  }
+  __device__ __forceinline__ void flag_row(int row) { red_min_s32(rowFlag, row); }
 };
 
 __device__ __forceinline__ void sv_issue(const SvParams &p, SvSmem &sm, int t, int stage)
@@ -183,23 +183,12 @@ __device__ __forceinline__ RowAct ldcg_rowact(const RowAct *q)
   return r;
 }
 
-__device__ __forceinline__ void sv_flag_row(const SvParams &p, int row)
-{
-  const int global = p.rowOrig[row] + p.rowOffset;
-  if (p.world > 1) {
-    for (int q = 0; q < p.world; ++q)
-      atomicMin_system(&p.st->peerSt[q]->infeasRow, global);
-  } else {
-    atomicMin(&p.st->infeasRow, global);
-  }
-}
-
 // One pass over tiles [tBegin, tEnd) for this CTA.  phaseL=false: round phase A
 // (short / medium rows completely, long-row chunks: partial sums only).
 // phaseL=true: long-row chunks again, now with the whole row's activity known.
-template <bool phaseL, class Sink>
+template <bool phaseL>
 __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_t (&parity)[2],
-  int tBegin, int tEnd, const Bnd *__restrict__ src, Sink &sink)
+  int tBegin, int tEnd, const Bnd *__restrict__ src, SvSink &sink)
 {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int t = tBegin + blockIdx.x;
@@ -231,7 +220,7 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
         const int row = T.rowBegin + r;
         const RowPlan pl = plan_row(ra, p.rowLB[row], p.rowUB[row], p.s);
         if (pl.infeasible && lane == 0)
-          sv_flag_row(p, row);
+          sink.flag_row(p.rowOrig[row] + p.rowOffset);
         if (pl.sideU || pl.sideL) {
           for (int k = kb + lane; k < ke; k += 32) {
             const double2 lh = sm.lohi[k];
@@ -272,7 +261,7 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
         }
         const RowPlan pl = plan_row(tot, p.rowLB[lr.row], p.rowUB[lr.row], p.s);
         if (pl.infeasible && tid == 0 && T.chunkIdx == 0)
-          sv_flag_row(p, lr.row);
+          sink.flag_row(p.rowOrig[lr.row] + p.rowOffset);
         if (pl.sideU || pl.sideL) {
           for (int k = tid; k < T.nzCount; k += kThreads) {
             const double2 lh = sm.lohi[k];
@@ -293,8 +282,8 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
 // Slices are handed out through an atomic counter (a warp asks for its next
 // slice before it starts the current one), so a round ends when the work
 // ends, not when the unluckiest statically assigned warp does.
-template <class Sink>
-__device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__restrict__ src, Sink &sink,
+template <int kChunk>
+__device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink,
   int *ctr)
 {
   const int lane = threadIdx.x & 31;
@@ -314,12 +303,12 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
     const double *__restrict__ v = p.sellVal + off + lane;
     const int *__restrict__ c = p.sellCol + off + lane;
     RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-    for (int k = 0; k < len; k += kSvChunk) {
-      double a[kSvChunk];
-      int cj[kSvChunk];
-      Bnd x[kSvChunk];
+    for (int k = 0; k < len; k += kChunk) {
+      double a[kChunk];
+      int cj[kChunk];
+      Bnd x[kChunk];
 #pragma unroll
-      for (int u = 0; u < kSvChunk; ++u) {
+      for (int u = 0; u < kChunk; ++u) {
         a[u] = 0.0;
         cj[u] = 0;
         if (k + u < len) {  // uniform
@@ -327,13 +316,16 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
           a[u] = __ldg(&v[(k + u) << 5]);
         }
       }
+      unsigned isInt = 0u;  // the columns' integrality flags, so that the indices can die once the gathers are out
 #pragma unroll
-      for (int u = 0; u < kSvChunk; ++u)  // padding points at column 0: a harmless, shared gather
+      for (int u = 0; u < kChunk; ++u) {  // padding points at column 0: a harmless, shared gather
         x[u] = ldcg_bnd(&src[col_of(cj[u])]);
+        isInt |= col_is_int(cj[u]) ? 1u << u : 0u;
+      }
 #pragma unroll
-      for (int u = 0; u < kSvChunk; ++u)  // padding has a == 0 and is skipped
+      for (int u = 0; u < kChunk; ++u)  // padding has a == 0 and is skipped
         if (a[u] != 0.0)
-          accumulate_fast(ra, a[u], col_is_int(cj[u]), x[u], p.s.inf);
+          accumulate_fast(ra, a[u], (isInt >> u) & 1u, x[u], p.s.inf);
     }
     RowPlan pl = plan_row(ra, rl, ru, p.s);
     if (!valid) {
@@ -342,7 +334,7 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
       pl.sideL = false;
     }
     if (pl.infeasible)
-      sv_flag_row(p, row);
+      sink.flag_row(p.rowOrig[row] + p.rowOffset);
     // Second pass, one row at a time and nonzero-parallel: the lanes of the
     // warp take the (<= 32) nonzeros of each row that may tighten something;
     // that row's plan is broadcast by shuffle.  Rows that cannot tighten cost
@@ -401,70 +393,254 @@ __device__ __forceinline__ void sv_stamp(const SvParams &p, int round, int which
   }
 }
 
-// Barrier of a round phase.  Not sharded: the grid barrier.  Sharded: every thread first pushes its
-// peer writes out (system fence), the grid meets, CTA 0 announces this rank on every rank's block and
-// waits until all ranks have announced themselves `epoch` times, then the grid meets again.  A rank
-// that waits longer than ~4 s (a peer died) raises p2pError everywhere it can and everybody leaves.
-template <bool kP2P>
-__device__ __forceinline__ bool sv_barrier(cooperative_groups::grid_group &grid, const SvParams &p,
-  unsigned long long &epoch)
+// Cross-GPU barrier of a row-sharded run (no grid barrier inside: the CTAs count themselves in on a
+// local word).  The last CTA of this rank to get here announces the rank on every rank's arrival
+// counter; CTA 0 waits until all ranks have announced themselves `epoch` times and publishes its verdict
+// on a local word, which the other CTAs wait for.  Only CTA 0 decides, so all CTAs of a rank leave the
+// same way.  A rank that waits longer than its patience (a peer died) raises p2pError on every rank it
+// can reach, and everybody leaves the kernel.  Threads that wrote to peer memory have fenced at system
+// scope before they come here.
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *q)
 {
-  if (!kP2P) {
-    grid.sync();
-    return true;
-  }
-  __threadfence_system();
-  grid.sync();
-  ++epoch;
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    for (int q = 0; q < p.world; ++q)
-      atomicAdd_system(&p.st->peerSt[q]->arrive, 1ull);
-    const unsigned long long want = epoch * static_cast<unsigned long long>(p.world);
-    unsigned long long t0, t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
-    volatile unsigned long long *mine = &p.st->arrive;
-    volatile int *err = &p.st->p2pError;
-    while (*mine < want && !*err) {
-      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-      if (t - t0 > 4000000000ull) {
-        for (int q = 0; q < p.world; ++q)
-          atomicExch_system(&p.st->peerSt[q]->p2pError, 1);
-        break;
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(q) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long *q)
+{
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(q) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned long long *q, unsigned long long v)
+{
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(q), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_sys_add(unsigned long long *q, unsigned long long v)
+{
+  asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(q), "l"(v) : "memory");
+}
+
+// epoch: number of this barrier in the life of the group; nth: its number within this run (from 1).
+// Not inlined (its registers must not weigh on the row loops), arguments by value.
+__device__ __noinline__ bool sv_peer_barrier(SvStatus *st, unsigned long long epoch, unsigned long long nth,
+  int world, unsigned long long patienceNs)
+{
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned long long before = atomicAdd(&st->ctaArrive, 1ull);
+    if (before + 1 == nth * gridDim.x) {  // the last CTA of this rank: everything this rank wrote is out
+      __threadfence();
+      for (int q = 0; q < world; ++q)
+        red_release_sys_add(&st->peerSt[q]->arrive, 1ull);
+    }
+    if (blockIdx.x == 0) {
+      const unsigned long long want = epoch * static_cast<unsigned long long>(world);
+      unsigned long long t0, t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+      volatile int *err = &st->p2pError;
+      bool ok = true;
+      while (ld_acquire_sys(&st->arrive) < want) {
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        if (*err || t - t0 > patienceNs) {
+          for (int q = 0; q < world; ++q)
+            atomicExch_system(&st->peerSt[q]->p2pError, 1);
+          ok = false;
+          break;
+        }
+      }
+      if (ok)
+        st_release_gpu(&st->goEpoch, epoch);
+      else
+        *reinterpret_cast<volatile int *>(&st->abortRun) = 1;
+    } else {
+      volatile int *ab = &st->abortRun;
+      while (ld_acquire_gpu(&st->goEpoch) < epoch && !*ab) {
       }
     }
-    __threadfence_system();
   }
-  grid.sync();
-  return __ldcg(&p.st->p2pError) == 0;
+  __syncthreads();
+  return *reinterpret_cast<volatile int *>(&st->abortRun) == 0;
+}
+
+// Row-sharded, after the rows of a round: copy this rank's marked proposals (and the mark words, the
+// row flag, rank 0's clock verdict) into this rank's slot on every other rank.  Plain stores over
+// NVLink, nothing waits for an answer; the system fence at the end makes them visible before this
+// thread reaches the barrier that announces them.  One thread per word of 32 columns.
+// (Not inlined, constants fetched from the status block: its registers must not weigh on the row loops
+// of the kernel.)
+struct SvPeerArgs {
+  Bnd *inP;       // this round's slots
+  unsigned *inD;
+  Bnd *oldP;      // this rank's own slot of the previous round
+  unsigned *oldD;
+  size_t strideP, strideD;
+  int world, rank, nWords, k;
+};
+
+__device__ __forceinline__ SvPeerArgs sv_peer_args(const SvStatus *st, int k)
+{
+  SvPeerArgs a;
+  a.strideP = st->strideP;
+  a.strideD = st->strideD;
+  a.world = __ldg(&st->world);
+  a.rank = __ldg(&st->rank);
+  a.nWords = __ldg(&st->nWords);
+  a.k = k;
+  a.inP = st->inP[k];  // (plain loads: written by the host before the launch, never by the kernel)
+  a.inD = st->inD[k];
+  a.oldP = st->inP[k ^ 1] + a.rank * a.strideP;
+  a.oldD = st->inD[k ^ 1] + a.rank * a.strideD;
+  return a;
+}
+
+__device__ __noinline__ void sv_peer_push(SvStatus *st, int k, int gtid, int gsize)
+{
+  const SvPeerArgs p = sv_peer_args(st, k);
+  const Bnd *myP = p.inP + p.rank * p.strideP;
+  const unsigned *myD = p.inD + p.rank * p.strideD;
+  bool wrote = false;
+  for (int w = gtid; w < p.nWords; w += gsize) {
+    unsigned bits = __ldcg(&myD[w]);
+    if (!bits)
+      continue;
+    wrote = true;
+#pragma unroll
+    for (int q = 0; q < kMaxPeers; ++q)
+      if (q < p.world && q != p.rank)
+        st->pushD[k][q][w] = bits;
+    while (bits) {  // four columns per trip: their loads are issued together
+      int j4[4];
+      Bnd b4[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        j4[u] = bits ? (w << 5) + __ffs(bits) - 1 : -1;
+        bits &= bits - 1;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (j4[u] >= 0)
+          b4[u] = ldcg_bnd(&myP[j4[u]]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (j4[u] < 0)
+          break;
+#pragma unroll
+        for (int q = 0; q < kMaxPeers; ++q)
+          if (q < p.world && q != p.rank)
+            st->pushP[k][q][j4[u]] = b4[u];
+      }
+    }
+  }
+  if (gtid == 0) {
+    const int rf = __ldcg(&st->inRowFlag[k][p.rank]);
+    const int tf = p.rank == 0 ? __ldcg(&st->inTime[k]) : 0;
+    for (int q = 0; q < p.world; ++q)
+      if (q != p.rank) {
+        if (rf != 0x7fffffff)
+          st->peerSt[q]->inRowFlag[k][p.rank] = rf;
+        if (tf)
+          st->peerSt[q]->inTime[k] = 1;
+      }
+    wrote = true;
+  }
+  if (wrote)
+    __threadfence_system();
+}
+
+// Row-sharded settle: every rank combines all ranks' proposals of this round for the marked columns,
+// applies R9 to its own full copy of the bounds and counts the changed columns — the same work on the
+// same data on every rank, so all ranks take the same decision without a second exchange.  One thread
+// per word of 32 columns.  Also withdraws this rank's own proposals of the PREVIOUS round and clears the
+// other ranks' marks of this one (nobody writes those slots again before the round after next, and
+// nobody can get there without this rank reaching the next barrier first).
+__device__ __noinline__ int sv_peer_settle(SvStatus *st, int k, const Bnd *__restrict__ src, Bnd *dst,
+  unsigned *dirtyOut, int gtid, int gsize)
+{
+  const SvPeerArgs p = sv_peer_args(st, k);
+  Scal sc;
+  sc.inf = __ldg(&st->scal.inf);
+  sc.tol = __ldg(&st->scal.tol);
+  sc.feasTol = __ldg(&st->scal.feasTol);
+  int mine = 0;
+  Bnd *oldP = p.oldP;
+  unsigned *oldD = p.oldD;
+  for (int w = gtid; w < p.nWords; w += gsize) {
+    unsigned bq[kMaxPeers];
+    unsigned any = 0u;
+#pragma unroll
+    for (int q = 0; q < kMaxPeers; ++q) {
+      bq[q] = q < p.world ? __ldcg(&p.inD[q * p.strideD + w]) : 0u;
+      any |= bq[q];
+    }
+    const unsigned old = __ldcg(&oldD[w]);
+    if (old) {
+      oldD[w] = 0u;
+      unsigned bits = old;
+      while (bits) {
+        const int j = (w << 5) + __ffs(bits) - 1;
+        bits &= bits - 1;
+        Bnd none;
+        none.lb = -CUDART_INF;
+        none.ub = CUDART_INF;
+        oldP[j] = none;
+      }
+    }
+    if (!any)
+      continue;
+#pragma unroll
+    for (int q = 0; q < kMaxPeers; ++q)
+      if (q < p.world && q != p.rank && bq[q])
+        p.inD[q * p.strideD + w] = 0u;
+    dirtyOut[w] = any;
+    mine += __popc(any);
+    unsigned bits = any;
+    while (bits) {
+      const int t = __ffs(bits) - 1;
+      const int j = (w << 5) + t;
+      bits &= bits - 1;
+      Bnd b = ldcg_bnd(&src[j]);
+      const double oldUb = b.ub;
+      Bnd c[kMaxPeers];
+#pragma unroll
+      for (int q = 0; q < kMaxPeers; ++q)  // all slots' loads are issued before the first use
+        if (q < p.world && ((bq[q] >> t) & 1u))
+          c[q] = ldcg_bnd(&p.inP[q * p.strideP + j]);
+#pragma unroll
+      for (int q = 0; q < kMaxPeers; ++q)
+        if (q < p.world && ((bq[q] >> t) & 1u)) {
+          b.lb = fmax(b.lb, c[q].lb);
+          b.ub = fmin(b.ub, c[q].ub);
+        }
+      if (settle(b.lb, b.ub, oldUb, sc))
+        red_min_s32(&st->infeasCol, j);
+      else
+        dst[j] = b;
+    }
+  }
+  // the flags of the round: every rank's first violated row, rank 0's clock
+  if (gtid == 0) {
+    int rf = 0x7fffffff;
+    for (int q = 0; q < p.world; ++q)
+      rf = min(rf, __ldcg(&st->inRowFlag[k][q]));
+    if (rf != 0x7fffffff)
+      st->infeasRow = rf;
+    if (__ldcg(&st->inTime[k]))
+      st->timeUp = 1;
+  }
+  return mine;
 }
 
 // kTiles=false is the variant for matrices whose rows are all short: no
 // shared-memory staging, fewer registers, more resident warps.
-template <bool kP2P>
-struct SvSinkFor {
-  typedef SvSink type;
-  static __device__ __forceinline__ SvSink make(const SvParams &p, int cur)
-  {
-    SvSink s = { p.X[cur ^ 1], p.dirty[cur] };
-    return s;
-  }
-};
-template <>
-struct SvSinkFor<true> {
-  typedef SvPeerSink type;
-  static __device__ __forceinline__ SvPeerSink make(const SvParams &p, int cur)
-  {
-    SvPeerSink s = { p.st, cur ^ 1, p.world };
-    return s;
-  }
-};
-
 template <bool kTiles, bool kP2P>
-__global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fixpoint_kernel(const SvParams p)
+__global__ void __launch_bounds__(kThreads, kP2P ? kSvShardedBlocks : (kTiles ? 3 : kSvNoTileBlocks)) sv_fixpoint_kernel(const SvParams p)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SvSmem &sm = *reinterpret_cast<SvSmem *>(smem_raw);  // kTiles=false: launched without it, never touched
   __shared__ int s_cnt[kWarps];
+  __shared__ int s_dec[4];
   cg::grid_group grid = cg::this_grid();
   const int tid = threadIdx.x;
   const int gtid = blockIdx.x * kThreads + tid, gsize = gridDim.x * kThreads;
@@ -488,18 +664,38 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
       p.st->rounds = 1;
       p.st->stopReason = 4;
       p.st->finalBuf = 0;
+      p.st->epochEnd = p.epoch0;  // (sharded: every rank takes this exit, nobody waits for anybody)
     }
     return;
   }
 
   const int limit = p.maxRounds > 0 ? p.maxRounds : 0x7fffffff;
-  unsigned long long epoch = 0;  // cross-GPU barriers passed so far (sharded runs)
+  // sharded runs pass one cross-GPU barrier at the start and one per round: barrier number
+  // p.epoch0 + 1 at the start, p.epoch0 + 2 + round in a round
+  // sharded: nobody reads a peer's block before that peer has reset it for this run (its kernel
+  // follows its prepare kernels in stream order, so its arrival here says so).  Ranks reach this point
+  // at host speed, hence the long patience.
+  if (kP2P && !sv_peer_barrier(p.st, p.epoch0 + 1, 1ull, p.world, 30000000000ull)) {
+    if (gtid == 0)
+      p.st->epochEnd = p.epoch0 + 1;
+    return;
+  }
   bool sparse = false;  // last round changed few columns: scan the marks word-wise
-  for (int round = 0;; ++round) {
+  int round = 0;
+  for (;; ++round) {
     const int cur = round & 1;
     const Bnd *src = p.X[cur];
     Bnd *dst = p.X[cur ^ 1];
-    typename SvSinkFor<kP2P>::type sink = SvSinkFor<kP2P>::make(p, cur);
+#ifdef CBP_FINE_STAMPS
+    if (blockIdx.x == 0 && tid == 0 && round < kStampRounds) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      p.st->stampsX[round][2] = static_cast<unsigned>(t - p.st->t0);
+    }
+#endif
+    // not sharded: candidates go straight into the target buffer; sharded: into this round's proposals
+    SvSink sink = { kP2P ? p.myP[cur] : dst, kP2P ? p.myD[cur] : p.dirty[cur],
+      kP2P ? p.myRowFlag[cur] : &p.st->infeasRow };
 
     // A1: bring the target buffer up to date at the columns the previous
     // round changed (it was that round's source, so it is stale there), and
@@ -542,7 +738,7 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
       p.st->stampsX[round][0] = static_cast<unsigned>(t - p.st->t0);
     }
     // A2: stream the matrix: short rows from the sliced-ELL copy, the rest as TMA-staged tiles
-    sv_short_rows(p, src, sink, &p.st->sliceCtr[cur]);
+    sv_short_rows<kP2P ? kSvChunkSharded : kSvChunk>(p, src, sink, &p.st->sliceCtr[cur]);
     if (blockIdx.x == 0 && tid == 0 && round < kStampRounds) {
       unsigned long long t;
       asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -550,15 +746,32 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
     }
     if (kTiles)
       sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
-    if (!sv_barrier<kP2P>(grid, p, epoch))
-      break;
-    sv_stamp(p, round, 0);
-    if (kTiles && p.nLong > 0) {  // (long-row partials are rank-local: a row lives on one rank)
-      sv_stream<true>(p, sm, parity, p.firstLongTile, p.nTiles, src, sink);
-      if (!sv_barrier<kP2P>(grid, p, epoch))
+    if (kP2P) {
+      if (kTiles && p.nLong > 0) {  // (long-row partials are rank-local: a row lives on one rank)
+        grid.sync();
+        sv_stream<true>(p, sm, parity, p.firstLongTile, p.nTiles, src, sink);
+      }
+      if (p.rank == 0 && gtid == 0) {  // rank 0's clock decides for everybody
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        if (t - p.st->t0 >= p.budgetNs)
+          p.st->inTime[cur] = 1;
+      }
+      grid.sync();  // all proposals of this rank are in its own slot
+      sv_peer_push(p.st, cur, gtid, gsize);
+      if (!sv_peer_barrier(p.st, p.epoch0 + 2 + round, 2ull + round, p.world, 4000000000ull))
         break;
+      sv_stamp(p, round, 0);
+      sv_stamp(p, round, 1);
+    } else {
+      grid.sync();
+      sv_stamp(p, round, 0);
+      if (kTiles && p.nLong > 0) {
+        sv_stream<true>(p, sm, parity, p.firstLongTile, p.nTiles, src, sink);
+        grid.sync();
+      }
+      sv_stamp(p, round, 1);
     }
-    sv_stamp(p, round, 1);
     if (p.raw) {  // the caller combines the proposals of all row blocks and settles them itself
       if (gtid == 0) {
         p.st->rounds = 1;
@@ -571,7 +784,9 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
     {
       int mine = 0;
       const unsigned *dw = p.dirty[cur];
-      if (sparse) {  // (the previous round's count is the predictor; either path is correct for any count)
+      if (kP2P) {
+        mine = sv_peer_settle(p.st, cur, src, dst, p.dirty[cur], gtid, gsize);
+      } else if (sparse) {  // (the previous round's count is the predictor; either path is correct for any count)
         for (int w = gtid; w < p.nWords; w += gsize) {
           unsigned bits = __ldcg(&dw[w]);
           mine += __popc(bits);
@@ -619,24 +834,25 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
           p.st->sliceCtr[cur ^ 1] = 0;
           unsigned long long t;
           asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-          if (t - p.st->t0 >= p.budgetNs) {
-            if (kP2P) {  // rank 0's clock decides for everybody
-              if (p.rank == 0)
-                for (int q = 0; q < p.world; ++q)
-                  atomicExch_system(&p.st->peerSt[q]->timeUp, 1);
-            } else {
-              p.st->timeUp = 1;
-            }
-          }
+          if (!kP2P && t - p.st->t0 >= p.budgetNs)
+            p.st->timeUp = 1;
         }
       }
     }
-    if (!sv_barrier<kP2P>(grid, p, epoch))
-      break;
+    grid.sync();  // (sharded too: every rank settled the same data, nothing more to exchange)
     sv_stamp(p, round, 2);
-    // every thread takes the same decision from the same global words
-    const int badRow = __ldcg(&p.st->infeasRow), badCol = __ldcg(&p.st->infeasCol);
-    const int changed = __ldcg(&p.st->chg[cur]);
+    // every thread takes the same decision from the same global words (fetched once per CTA: the
+    // whole grid asking one L2 line for them costs microseconds)
+    if (tid == 0) {
+      s_dec[0] = __ldcg(&p.st->infeasRow);
+      s_dec[1] = __ldcg(&p.st->infeasCol);
+      s_dec[2] = __ldcg(&p.st->chg[cur]);
+      s_dec[3] = __ldcg(&p.st->timeUp);
+    }
+    __syncthreads();
+    const int badRow = s_dec[0], badCol = s_dec[1];
+    const int changed = s_dec[2];
+    const int timeUp = s_dec[3];
     int stop = 0;
     int fin = cur;
     if (badRow != 0x7fffffff || badCol != 0x7fffffff)
@@ -646,7 +862,7 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
     else if (round + 1 >= limit) {
       stop = 2;  // HitMaxRounds: the last round is applied
       fin = cur ^ 1;
-    } else if (__ldcg(&p.st->timeUp)) {
+    } else if (timeUp) {
       stop = 3;  // HitTimeLimit, checked before the next round would start
       fin = cur ^ 1;
     }
@@ -668,9 +884,23 @@ __global__ void __launch_bounds__(kThreads, kTiles ? 3 : kSvNoTileBlocks) sv_fix
       break;
     }
   }
+  if (kP2P && gtid == 0)
+    p.st->epochEnd = p.epoch0 + 2 + round;
 }
 
 // ---- small helper kernels ---------------------------------------------------
+
+// row-sharded runs: empty proposal buffers (no proposal = (-inf, +inf))
+__global__ void sv_no_proposals_kernel(Bnd *P, size_t count)
+{
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < count) {
+    Bnd none;
+    none.lb = -CUDART_INF;
+    none.ub = CUDART_INF;
+    P[i] = none;
+  }
+}
 
 // interleave lb/ub into both state buffers, apply R11, mark what it changed
 __global__ void sv_prepare_kernel(const double *__restrict__ lb, const double *__restrict__ ub,

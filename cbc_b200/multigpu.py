@@ -9,7 +9,7 @@ torch.distributed for the plumbing.
   a GPU, or any other implementation of one round in the CPU tests of this logic.
   `PeerShardedMatrix` is the fused form of the same decomposition for the GPUs of one box: the
   exchange happens inside the tightening kernel over NVLink peer memory (cbp_p2p_* in
-  include/cbp_capi.h), torch.distributed only carries the IPC handles and the host barrier.
+  include/cbp_capi.h), torch.distributed only carries the IPC handles at set-up.
 """
 import numpy as np
 
@@ -187,27 +187,19 @@ class PeerShardedMatrix:
 
         self.mat = Matrix(ctx, sub)
         handles = [None] * self.world
-        dist.all_gather_object(handles, self.mat.p2p_export(), group=group)
+        dist.all_gather_object(handles, self.mat.p2p_export(self.world), group=group)
         self.mat.p2p_attach(self.rank, self.world, handles)
         dist.barrier(group=group)
 
     def propagate(self, lb, ub, tol=1e-7, max_rounds=0, time_limit=1e100):
-        import torch.distributed as dist
-
         lb = np.array(lb, np.float64)
         ub = np.array(ub, np.float64)
-        self.mat.p2p_prepare(lb, ub, tol)
-        dist.barrier(group=self.group)  # nobody may write into a block that is still being reset
-        res = self.mat.p2p_run(lb, ub, self.r0, tol, max_rounds, time_limit)
+        res = self.mat.p2p_propagate(lb, ub, self.r0, tol, max_rounds, time_limit)
         return res, lb, ub
 
     def propagate_device(self, lb_ptr, ub_ptr, tol=1e-7, max_rounds=0, time_limit=1e100):
         """Same with the bounds already in this rank's HBM (n doubles each, updated in place)."""
-        import torch.distributed as dist
-
-        self.mat.p2p_prepare(lb_ptr, ub_ptr, tol, device_ptrs=True)
-        dist.barrier(group=self.group)
-        return self.mat.p2p_run(lb_ptr, ub_ptr, self.r0, tol, max_rounds, time_limit, device_ptrs=True)
+        return self.mat.p2p_propagate(lb_ptr, ub_ptr, self.r0, tol, max_rounds, time_limit, device_ptrs=True)
 
     def close(self):
         self.mat.close()

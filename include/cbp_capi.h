@@ -165,22 +165,25 @@ CBP_API int cbp_batch_fetch_dense(cbp_matrix *mat, double *lb, double *ub, int f
 /* Single bound vector over a matrix whose ROWS are sharded over the GPUs of one box (one process per
  * GPU; every rank uploads its own block of rows with cbp_matrix_upload and holds the whole bound
  * vector).  The round loop of src/CbcBoundPropagation.cpp:107-195 then runs as one persistent kernel
- * per rank; an accepted candidate is written with NVLink atomics into every rank's copy of the bounds
- * (peer mappings of one state block per rank), and the ranks meet at a barrier in peer memory twice a
- * round — the exchange is part of the tightening kernel, there is no separate collective.
- *   cbp_p2p_export : allocate this rank's state block, return its CUDA IPC handle (64 bytes);
- *   cbp_p2p_attach : map all ranks' blocks (handles = world x 64 bytes, in rank order);
- *   cbp_p2p_prepare: load lb / ub (the same on every rank), reset the block, apply R11;
- *                    the CALLER must put a host barrier across the ranks between prepare and run;
- *   cbp_p2p_run    : run the loop; rowOffset = index of this rank's first row in the whole matrix
- *                    (infeasibleRow is reported in whole-matrix numbering); every rank gets the same
- *                    result and the same bounds.  Ranks must call run within a few seconds of each
- *                    other: a rank that waits ~4 s at a barrier gives up and every rank returns an error. */
+ * per rank.  Inside a round a rank collects the candidates its rows accept, copies the columns it
+ * changed into its slot of every other rank's state block (NVLink peer mappings, plain stores), meets
+ * the other ranks at a barrier kept in peer memory, and settles its own full copy of the bounds from
+ * what all ranks sent — the exchange is part of the kernel, there is no separate collective and no
+ * host round trip per round.
+ *   cbp_p2p_export   : allocate this rank's state block for a group of `world` ranks (<= 8), return its
+ *                      CUDA IPC handle (64 bytes);
+ *   cbp_p2p_attach   : map all ranks' blocks (handles = world x 64 bytes, in rank order);
+ *   cbp_p2p_propagate: collective over the group: every rank calls it with the same lb / ub, tolerance
+ *                      and limits; rowOffset = index of this rank's first row in the whole matrix
+ *                      (infeasibleRow is reported in whole-matrix numbering).  Every rank gets the same
+ *                      result and the same bounds.  The kernels find each other on their own: no host
+ *                      barrier is needed around the call.  A rank that waits ~30 s for the others to start,
+ *                      or ~4 s at a barrier inside the loop, gives up; then every rank returns an error and
+ *                      the group is unusable. */
 #define CBP_P2P_HANDLE_BYTES 64
-CBP_API int cbp_p2p_export(cbp_matrix *mat, void *handleOut);
+CBP_API int cbp_p2p_export(cbp_matrix *mat, int world, void *handleOut);
 CBP_API int cbp_p2p_attach(cbp_matrix *mat, int rank, int world, const void *handles);
-CBP_API int cbp_p2p_prepare(cbp_matrix *mat, const double *lb, const double *ub, double primalTol, int flags);
-CBP_API int cbp_p2p_run(cbp_matrix *mat, double *lb, double *ub, double primalTol, int maxRounds,
+CBP_API int cbp_p2p_propagate(cbp_matrix *mat, double *lb, double *ub, double primalTol, int maxRounds,
   double timeLimitSec, int rowOffset, cbp_result *out, int *roundChanged, int roundCap, int flags);
 
 /* Phase 1 for callers that cannot allocate device memory.  This entry point has no counterpart in

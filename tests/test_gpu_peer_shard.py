@@ -24,12 +24,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def test_world_of_one_equals_oracle(oracle, gpu_ctx, maker):
     inst = maker()
     mat = capi.Matrix(gpu_ctx, inst)
-    mat.p2p_attach(0, 1, [mat.p2p_export()])
+    mat.p2p_attach(0, 1, [mat.p2p_export(1)])
     ro, lo, uo = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
     for _ in range(2):
         lb, ub = np.array(inst.lb, np.float64), np.array(inst.ub, np.float64)
-        mat.p2p_prepare(lb, ub)
-        r = mat.p2p_run(lb, ub, 0)
+        r = mat.p2p_propagate(lb, ub, 0)
         for k in ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason", "roundChanged"):
             assert r[k] == ro[k], (k, r[k], ro[k])
         assert_same_bounds(inst.colType, lb, ub, lo, uo, "world of one")
@@ -39,12 +38,12 @@ def test_world_of_one_equals_oracle(oracle, gpu_ctx, maker):
     mat.close()
 
 
-def test_run_without_prepare_is_refused(gpu_ctx):
+def test_unattached_matrix_is_refused(gpu_ctx):
     inst = I.micro("knapsack")
     mat = capi.Matrix(gpu_ctx, inst)
     lb, ub = np.array(inst.lb, np.float64), np.array(inst.ub, np.float64)
     with pytest.raises(capi.CbpError):
-        mat.p2p_run(lb, ub, 0)
+        mat.p2p_propagate(lb, ub, 0)
     mat.close()
 
 
