@@ -50,6 +50,10 @@ struct BtParams {
   unsigned *logCount;
   unsigned logCap;
   int *groupFlag;  // [G] this group has candidates or R11 changes
+  // first round of a base+diffs batch run "from the base": a vector's bounds are the shared base bounds
+  // except at the few columns its diffs touch; those cells alone have been written to X[0]
+  const Bnd *baseX;       // [n]
+  const unsigned *dmask;  // [G][n] which vectors of the group differ from the base at column j
   Scal s;
 };
 
@@ -143,6 +147,17 @@ struct __align__(16) Stg {
   int isInt;
 };
 
+// The same for the first round of a base+diffs batch (32 bytes): coefficient, the column's BASE bounds,
+// the group's diff mask for the column, and an upper bound (rounded up, single precision) of
+// |a| * (ub - lb) of the base bounds.  The column index (integrality in bit 31) sits in a separate array,
+// it is only needed by lanes whose own vector differs from the base there.
+struct __align__(16) StgB {
+  double a;
+  double lb, ub;
+  unsigned mask;
+  float w;
+};
+
 // R3 for one (nonzero, vector).  kNoInf: no bound of this batch is infinite
 // (checked when the batch is loaded; tightening never creates infinities), so
 // the counters stay zero and the tests disappear.  kAllInt (walk): the matrix
@@ -218,10 +233,114 @@ __device__ __forceinline__ void bt_walk_sum(const BtParams &p, const char *__res
   }
 }
 
+// First round of a base+diffs batch: the same walk, but a vector's bounds for column j are the shared
+// base bounds unless the vector's diffs touch j (mask bit), and only then its own cell is read.  The
+// lanes fetch base bounds and mask of "their" nonzero together with (a, j) into shared memory, one block
+// ahead ((a, j) two blocks ahead: the base bounds need j), so the walk itself reads shared memory only:
+// every (nonzero, vector) pair is still summed in CSR order, but the 16 bytes per pair no longer come
+// through L2.
+// kNoInf: the row-level shortcut of plan_row only needs SOME upper bound of max |a| * useful_range (a
+// larger one lets more rows into the second walk, whose per-nonzero tests are exact, so results cannot
+// change); here it is kept in single precision, rounded up, and for the base bounds it is computed once
+// per nonzero by the staging lane.
+template <bool kNoInf, int kSign, bool kAllInt>
+__device__ __forceinline__ void bt_walk_sum_base(const BtParams &p, const char *__restrict__ src,
+  unsigned strideB, const unsigned *__restrict__ dm, int kb, int ke, int lane, StgB *stg, int *stgJ, RowAct &ra)
+{
+  double a1 = 0.0, a2 = 0.0;
+  int c1 = 0, c2 = 0;
+  if (kb + lane < ke) {
+    c1 = __ldg(&p.col[kb + lane]);
+    a1 = __ldg(&p.val[kb + lane]);
+  }
+  if (kb + 32 + lane < ke) {
+    c2 = __ldg(&p.col[kb + 32 + lane]);
+    a2 = __ldg(&p.val[kb + 32 + lane]);
+  }
+  double2 x1 = __ldg(reinterpret_cast<const double2 *>(&p.baseX[col_of(c1)]));
+  unsigned m1 = __ldg(&dm[col_of(c1)]);
+  float mr = 0.f;  // kNoInf: running upper bound of the row's largest |a| * range
+  for (int base = kb; base < ke; base += 32) {
+    // does any vector of this group differ from the base at one of these 32 columns?  (hardly ever: then
+    // the walk below needs no per-lane test at all)
+    const bool diffs = __any_sync(0xffffffffu, m1 != 0u);
+    __syncwarp();
+    {
+      StgB e;
+      e.a = a1;
+      e.lb = x1.x;
+      e.ub = x1.y;
+      e.mask = m1;
+      e.w = __fmul_ru(__double2float_ru(fabs(a1)), __double2float_ru(__dsub_ru(x1.y, x1.x)));
+      stg[lane] = e;
+      stgJ[lane] = c1;
+    }
+    a1 = a2;
+    c1 = c2;
+    x1 = __ldg(reinterpret_cast<const double2 *>(&p.baseX[col_of(c1)]));  // (past the end: column 0, harmless)
+    m1 = __ldg(&dm[col_of(c1)]);
+    a2 = 0.0;
+    c2 = 0;
+    const int kn = base + 64 + lane;
+    if (kn < ke) {
+      c2 = __ldg(&p.col[kn]);
+      a2 = __ldg(&p.val[kn]);
+    }
+    __syncwarp();
+    const int cnt = min(32, ke - base);
+    if (kNoInf && !diffs) {
+      if (cnt == 32) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {  // an entry = two 16-byte shared-memory broadcasts: {a, lb}, {ub, mask | w}
+          const double2 h0 = reinterpret_cast<const double2 *>(&stg[i])[0];
+          const double2 h1 = reinterpret_cast<const double2 *>(&stg[i])[1];
+          const float w = __int_as_float(__double2hiint(h1.y));
+          const bool pos = kSign > 0 ? true : (kSign < 0 ? false : h0.x > 0.0);
+          ra.minAct = fma(h0.x, pos ? h0.y : h1.x, ra.minAct);
+          ra.maxAct = fma(h0.x, pos ? h1.x : h0.y, ra.maxAct);
+          mr = fmaxf(mr, w);
+        }
+      } else {
+        for (int i = 0; i < cnt; ++i) {
+          const StgB e = stg[i];
+          const bool pos = kSign > 0 ? true : (kSign < 0 ? false : e.a > 0.0);
+          ra.minAct = fma(e.a, pos ? e.lb : e.ub, ra.minAct);
+          ra.maxAct = fma(e.a, pos ? e.ub : e.lb, ra.maxAct);
+          mr = fmaxf(mr, e.w);
+        }
+      }
+      continue;
+    }
+    for (int i = 0; i < cnt; ++i) {
+      const StgB e = stg[i];
+      Bnd x;
+      x.lb = e.lb;
+      x.ub = e.ub;
+      float w = e.w;
+      if ((e.mask >> lane) & 1u) {
+        x = ldcg_bnd(reinterpret_cast<const Bnd *>(
+          src + static_cast<unsigned long long>(static_cast<unsigned>(col_of(stgJ[i]))) * strideB));
+        w = __fmul_ru(__double2float_ru(fabs(e.a)), __double2float_ru(__dsub_ru(x.ub, x.lb)));
+      }
+      if (kNoInf) {
+        const bool pos = kSign > 0 ? true : (kSign < 0 ? false : e.a > 0.0);
+        ra.minAct = fma(e.a, pos ? x.lb : x.ub, ra.minAct);
+        ra.maxAct = fma(e.a, pos ? x.ub : x.lb, ra.maxAct);
+        mr = fmaxf(mr, w);
+      } else {
+        bt_acc<false, kSign>(ra, e.a, kAllInt ? true : col_is_int(stgJ[i]), x, p.s.inf);
+      }
+    }
+  }
+  if (kNoInf)
+    ra.maxRange = fmax(ra.maxRange, static_cast<double>(mr));
+}
+
 // second walk, only for warps where some lane's row can tighten something
-template <class Sink>
+template <bool kBase, class Sink>
 __device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const char *__restrict__ src,
-  unsigned strideB, int kb, int ke, int lane, Stg *stg, const RowPlan &pl, Sink &sink)
+  unsigned strideB, const unsigned *__restrict__ dm, int kb, int ke, int lane, Stg *stg, const RowPlan &pl,
+  Sink &sink)
 {
   const bool want = pl.sideU || pl.sideL;
   for (int base = kb; base < ke; base += 32) {
@@ -240,8 +359,15 @@ __device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const char *_
     if (want) {
       for (int i = 0; i < cnt; ++i) {
         const Stg e = stg[i];
-        const Bnd x = ldcg_bnd(reinterpret_cast<const Bnd *>(
-          src + static_cast<unsigned long long>(static_cast<unsigned>(e.j)) * strideB));
+        Bnd x;
+        if (kBase && !((__ldg(&dm[e.j]) >> lane) & 1u)) {
+          const double2 v = __ldg(reinterpret_cast<const double2 *>(&p.baseX[e.j]));
+          x.lb = v.x;
+          x.ub = v.y;
+        } else {
+          x = ldcg_bnd(reinterpret_cast<const Bnd *>(
+            src + static_cast<unsigned long long>(static_cast<unsigned>(e.j)) * strideB));
+        }
         tighten_nz(sink, pl, e.a, e.j, e.isInt != 0, e.a > 0.0 ? x.lb : x.ub, e.a > 0.0 ? x.ub : x.lb, p.s);
       }
     }
@@ -251,10 +377,13 @@ __device__ __forceinline__ void bt_walk_tighten(const BtParams &p, const char *_
 // One round, rows phase, rows up to kBtLongLen nonzeros: a warp owns (row,
 // group of 32 vectors) and sums in CSR order.  Work is group-major so that the
 // warps running at the same time share few vector groups.
-template <bool kNoInf, bool kAllInt, bool kLog>
+template <bool kNoInf, bool kAllInt, bool kLog, bool kBase = false>
 __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, int cur)
 {
-  __shared__ Stg stage[kWarps][32];
+  __shared__ __align__(16) unsigned char stageRaw[kWarps * 32 * (kBase ? sizeof(StgB) : sizeof(Stg))];
+  __shared__ int stageJ[kBase ? kWarps : 1][32];
+  Stg (*stage)[32] = reinterpret_cast<Stg (*)[32]>(stageRaw);
+  StgB (*stageB)[32] = reinterpret_cast<StgB (*)[32]>(stageRaw);
   const long long W = static_cast<long long>(blockIdx.x) * kWarps + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (W >= static_cast<long long>(p.G) * p.nShortBt)
@@ -269,8 +398,12 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
   const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
   const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
 
+  const unsigned *__restrict__ dm = kBase ? p.dmask + bt_word(p, 0, g) : nullptr;
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-  bt_walk_sum<kNoInf, 0, kAllInt>(p, src, strideB, kb, ke, lane, stage[warp], ra);
+  if (kBase)
+    bt_walk_sum_base<kNoInf, 0, kAllInt>(p, src, strideB, dm, kb, ke, lane, stageB[warp], stageJ[kBase ? warp : 0], ra);
+  else
+    bt_walk_sum<kNoInf, 0, kAllInt>(p, src, strideB, kb, ke, lane, stage[warp], ra);
   RowPlan pl = plan_row(ra, __ldg(&p.rowLB[r]), __ldg(&p.rowUB[r]), p.s);
   if (!mine) {
     pl.infeasible = false;
@@ -282,7 +415,8 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_kernel(const BtParams p, 
   if (!__any_sync(0xffffffffu, pl.sideU || pl.sideL))
     return;
   typename BtSinkFor<kLog>::type sink = BtSinkFor<kLog>::make(p, cur, g, b, lane);
-  bt_walk_tighten(p, src, strideB, kb, ke, lane, stage[warp], pl, sink);
+  bt_walk_tighten<kBase>(p, src, strideB, dm, kb, ke, lane, kBase ? reinterpret_cast<Stg *>(stageB[warp]) : stage[warp],
+    pl, sink);
 }
 
 // Same rows, but for matrices with so many columns that the bounds of a 32-vector group
@@ -405,11 +539,14 @@ __global__ void __launch_bounds__(kThreads, 4) bt_rows_narrow_kernel(const BtPar
 #endif
 constexpr int kLongWarps = CBP_LONG_WARPS;  // warps that share one long row
 
-template <bool kNoInf, bool kAllInt, bool kLog>
+template <bool kNoInf, bool kAllInt, bool kLog, bool kBase = false>
 __global__ void __launch_bounds__(kLongWarps * 32, 2048 / (kLongWarps * 32) / 2) bt_rows_long_kernel(const BtParams p, int cur)
 {
   __shared__ RowAct red[kLongWarps][32];
-  __shared__ Stg stage[kLongWarps][32];
+  __shared__ __align__(16) unsigned char stageRaw[kLongWarps * 32 * (kBase ? sizeof(StgB) : sizeof(Stg))];
+  __shared__ int stageJ[kBase ? kLongWarps : 1][32];
+  Stg (*stage)[32] = reinterpret_cast<Stg (*)[32]>(stageRaw);
+  StgB (*stageB)[32] = reinterpret_cast<StgB (*)[32]>(stageRaw);
   const int g = blockIdx.x / p.nLongBt, r = __ldg(&p.longRowsBt[blockIdx.x % p.nLongBt]);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned act = __ldg(&p.active[g]);
@@ -424,9 +561,16 @@ __global__ void __launch_bounds__(kLongWarps * 32, 2048 / (kLongWarps * 32) / 2)
   const int per = ((cnt + kLongWarps - 1) / kLongWarps + 31) & ~31;  // 32-aligned pieces
   const int wb = min(kb + warp * per, kb + cnt), we = min(wb + per, kb + cnt);
 
+  const unsigned *__restrict__ dm = kBase ? p.dmask + bt_word(p, 0, g) : nullptr;
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-  bt_walk_sum<kNoInf, 1, kAllInt>(p, src, strideB, wb, min(we, max(wb, ksplit)), lane, stage[warp], ra);
-  bt_walk_sum<kNoInf, -1, kAllInt>(p, src, strideB, max(wb, min(we, ksplit)), we, lane, stage[warp], ra);
+  if (kBase) {
+    int *sj = stageJ[kBase ? warp : 0];
+    bt_walk_sum_base<kNoInf, 1, kAllInt>(p, src, strideB, dm, wb, min(we, max(wb, ksplit)), lane, stageB[warp], sj, ra);
+    bt_walk_sum_base<kNoInf, -1, kAllInt>(p, src, strideB, dm, max(wb, min(we, ksplit)), we, lane, stageB[warp], sj, ra);
+  } else {
+    bt_walk_sum<kNoInf, 1, kAllInt>(p, src, strideB, wb, min(we, max(wb, ksplit)), lane, stage[warp], ra);
+    bt_walk_sum<kNoInf, -1, kAllInt>(p, src, strideB, max(wb, min(we, ksplit)), we, lane, stage[warp], ra);
+  }
   red[warp][lane] = ra;
   __syncthreads();
   RowAct tot = red[0][lane];
@@ -444,7 +588,183 @@ __global__ void __launch_bounds__(kLongWarps * 32, 2048 / (kLongWarps * 32) / 2)
   if (!__syncthreads_or(pl.sideU || pl.sideL))
     return;
   typename BtSinkFor<kLog>::type sink = BtSinkFor<kLog>::make(p, cur, g, b, lane);
-  bt_walk_tighten(p, src, strideB, wb, we, lane, stage[warp], pl, sink);
+  bt_walk_tighten<kBase>(p, src, strideB, dm, wb, we, lane, kBase ? reinterpret_cast<Stg *>(stageB[warp]) : stage[warp],
+    pl, sink);
+}
+
+// First round from the base, long rows, no infinite bound in the batch: the walk above with V vector
+// groups per warp.  What limits that walk is not arithmetic but the shared-memory broadcast: an entry is
+// two 16-byte reads that are handed to all 32 lanes (512 bytes of register writes each, 128 bytes per
+// clock and SM), two DFMAs behind them.  With V groups per warp every lane carries V vectors' sums and the
+// same two reads feed 2V DFMAs.
+template <int kSign, int V>
+__device__ __forceinline__ void bt_walk_sum_base_multi(const BtParams &p, const char *const (&src)[V],
+  unsigned strideB, const unsigned *const (&dm)[V], int kb, int ke, int lane, StgB *stg, int *stgJ,
+  unsigned (*stgM)[32], double (&mn)[V], double (&mx)[V], float (&mr)[V], float &mrBase)
+{
+  double a1 = 0.0, a2 = 0.0;
+  int c1 = 0, c2 = 0;
+  if (kb + lane < ke) {
+    c1 = __ldg(&p.col[kb + lane]);
+    a1 = __ldg(&p.val[kb + lane]);
+  }
+  if (kb + 32 + lane < ke) {
+    c2 = __ldg(&p.col[kb + 32 + lane]);
+    a2 = __ldg(&p.val[kb + 32 + lane]);
+  }
+  double2 x1 = __ldg(reinterpret_cast<const double2 *>(&p.baseX[col_of(c1)]));
+  unsigned m1[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v)
+    m1[v] = dm[v] ? __ldg(&dm[v][col_of(c1)]) : 0u;
+  for (int base = kb; base < ke; base += 32) {
+    unsigned anyM = 0u;
+#pragma unroll
+    for (int v = 0; v < V; ++v)
+      anyM |= m1[v];
+    const bool diffs = __any_sync(0xffffffffu, anyM != 0u);
+    __syncwarp();
+    {
+      StgB e;
+      e.a = a1;
+      e.lb = x1.x;
+      e.ub = x1.y;
+      e.mask = anyM;
+      e.w = __fmul_ru(__double2float_ru(fabs(a1)), __double2float_ru(__dsub_ru(x1.y, x1.x)));
+      stg[lane] = e;
+      if (diffs) {
+        stgJ[lane] = c1;
+#pragma unroll
+        for (int v = 0; v < V; ++v)
+          stgM[v][lane] = m1[v];
+      }
+    }
+    a1 = a2;
+    c1 = c2;
+    x1 = __ldg(reinterpret_cast<const double2 *>(&p.baseX[col_of(c1)]));
+#pragma unroll
+    for (int v = 0; v < V; ++v)
+      m1[v] = dm[v] ? __ldg(&dm[v][col_of(c1)]) : 0u;
+    a2 = 0.0;
+    c2 = 0;
+    const int kn = base + 64 + lane;
+    if (kn < ke) {
+      c2 = __ldg(&p.col[kn]);
+      a2 = __ldg(&p.val[kn]);
+    }
+    __syncwarp();
+    const int cnt = min(32, ke - base);
+    if (!diffs) {
+#pragma unroll 8
+      for (int i = 0; i < cnt; ++i) {
+        const double2 h0 = reinterpret_cast<const double2 *>(&stg[i])[0];  // {a, lb}
+        const double2 h1 = reinterpret_cast<const double2 *>(&stg[i])[1];  // {ub, mask | w}
+        const bool pos = kSign > 0 ? true : (kSign < 0 ? false : h0.x > 0.0);
+        const double lo = pos ? h0.y : h1.x, hi = pos ? h1.x : h0.y;
+#pragma unroll
+        for (int v = 0; v < V; ++v) {
+          mn[v] = fma(h0.x, lo, mn[v]);
+          mx[v] = fma(h0.x, hi, mx[v]);
+        }
+        mrBase = fmaxf(mrBase, __int_as_float(__double2hiint(h1.y)));
+      }
+      continue;
+    }
+    for (int i = 0; i < cnt; ++i) {
+      const StgB e = stg[i];
+      const bool pos = kSign > 0 ? true : (kSign < 0 ? false : e.a > 0.0);
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        Bnd x;
+        x.lb = e.lb;
+        x.ub = e.ub;
+        float w = e.w;
+        if ((stgM[v][i] >> lane) & 1u) {
+          x = ldcg_bnd(reinterpret_cast<const Bnd *>(
+            src[v] + static_cast<unsigned long long>(static_cast<unsigned>(col_of(stgJ[i]))) * strideB));
+          w = __fmul_ru(__double2float_ru(fabs(e.a)), __double2float_ru(__dsub_ru(x.ub, x.lb)));
+        }
+        mn[v] = fma(e.a, pos ? x.lb : x.ub, mn[v]);
+        mx[v] = fma(e.a, pos ? x.ub : x.lb, mx[v]);
+        mr[v] = fmaxf(mr[v], w);
+      }
+    }
+  }
+}
+
+template <int V>
+__global__ void __launch_bounds__(kLongWarps * 32, 2) bt_rows_long_base_kernel(const BtParams p)
+{
+  __shared__ RowAct red[V][kLongWarps][32];
+  __shared__ StgB stageB[kLongWarps][32];
+  __shared__ int stageJ[kLongWarps][32];
+  __shared__ unsigned stageM[kLongWarps][V][32];
+  const int q = blockIdx.x / p.nLongBt, r = __ldg(&p.longRowsBt[blockIdx.x % p.nLongBt]);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned act[V];
+  unsigned anyAct = 0u;
+  const char *src[V];
+  const unsigned *dm[V];
+  const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    const int g = q * V + v;
+    act[v] = g < p.G ? __ldg(&p.active[g]) : 0u;
+    anyAct |= act[v];
+    const int b = min(g, p.G - 1) * 32 + lane;
+    src[v] = reinterpret_cast<const char *>(p.X[0] + bt_base(p, b));
+    dm[v] = g < p.G ? p.dmask + bt_word(p, 0, g) : nullptr;
+  }
+  if (anyAct == 0u)
+    return;
+  const int kb = __ldg(&p.rowNz[r]), cnt = __ldg(&p.rowCnt[r]);
+  const int ksplit = kb + __ldg(&p.rowPos[r]);
+  const int per = ((cnt + kLongWarps - 1) / kLongWarps + 31) & ~31;
+  const int wb = min(kb + warp * per, kb + cnt), we = min(wb + per, kb + cnt);
+
+  double mn[V], mx[V];
+  float mr[V], mrBase = 0.f;
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    mn[v] = 0.0;
+    mx[v] = 0.0;
+    mr[v] = 0.f;
+  }
+  bt_walk_sum_base_multi<1, V>(p, src, strideB, dm, wb, min(we, max(wb, ksplit)), lane, stageB[warp], stageJ[warp],
+    stageM[warp], mn, mx, mr, mrBase);
+  bt_walk_sum_base_multi<-1, V>(p, src, strideB, dm, max(wb, min(we, ksplit)), we, lane, stageB[warp], stageJ[warp],
+    stageM[warp], mn, mx, mr, mrBase);
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    RowAct ra = { mn[v], mx[v], static_cast<double>(fmaxf(mr[v], mrBase)), 0, 0 };
+    red[v][warp][lane] = ra;
+  }
+  __syncthreads();
+  const double rl = __ldg(&p.rowLB[r]), ru = __ldg(&p.rowUB[r]);
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    const int g = q * V + v;
+    if (g >= p.G)
+      break;
+    RowAct tot = red[v][0][lane];
+#pragma unroll
+    for (int w = 1; w < kLongWarps; ++w)
+      combine(tot, red[v][w][lane]);
+    RowPlan pl = plan_row(tot, rl, ru, p.s);
+    if (!((act[v] >> lane) & 1u)) {
+      pl.infeasible = false;
+      pl.sideU = false;
+      pl.sideL = false;
+    }
+    const int b = g * 32 + lane;
+    if (pl.infeasible && warp == 0)
+      atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
+    // (every warp holds the same plans, so they all take the same branch; the walk itself only needs the warp)
+    if (__any_sync(0xffffffffu, pl.sideU || pl.sideL)) {
+      BtLogSink sink = BtSinkFor<true>::make(p, 0, g, b, lane);
+      bt_walk_tighten<true>(p, src[v], strideB, dm[v], wb, we, lane, reinterpret_cast<Stg *>(stageB[warp]), pl, sink);
+    }
+  }
 }
 
 // After the rows phase: settle every (column, vector) marked in this round (R9) and count the
@@ -598,6 +918,41 @@ __global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double
     X1[i] = x;
 }
 
+// interleaved copy of the base bounds for the first round "from the base"
+__global__ void bt_base_pack_kernel(const double *__restrict__ baseLb, const double *__restrict__ baseUb, int n,
+  Bnd *baseX)
+{
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) {
+    Bnd x;
+    x.lb = baseLb[j];
+    x.ub = baseUb[j];
+    baseX[j] = x;
+  }
+}
+
+// after a first round "from the base": build both bound buffers (base bounds, the vector's own cells
+// where its diffs touched a column) for the vector groups whose flag equals `want` (all if flags == nullptr)
+__global__ void bt_expand_groups_kernel(const BtParams p, const int *__restrict__ flags, int want)
+{
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<size_t>(p.n) * p.Bp)
+    return;
+  const int b = static_cast<int>(i / (static_cast<size_t>(p.W) * p.n)) * p.W + static_cast<int>(i % p.W);
+  const int g = b >> 5;
+  if (flags && (flags[g] != 0) != (want != 0))
+    return;
+  const int j = static_cast<int>((i / p.W) % p.n);
+  Bnd x;
+  if ((p.dmask[bt_word(p, j, g)] >> (b & 31)) & 1u) {
+    x = p.X[0][i];
+  } else {
+    x = p.baseX[j];
+    p.X[0][i] = x;
+  }
+  p.X[1][i] = x;
+}
+
 // second buffer := first buffer, for the vector groups whose flag is set (all if flags == nullptr)
 __global__ void bt_copy_groups_kernel(const BtParams p, const int *__restrict__ flags)
 {
@@ -638,10 +993,21 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
   if (b >= B)
     return;
   const long long k0 = start[b], k1 = start[b + 1];
-  for (long long k = k0; k < k1; ++k) {
+  unsigned *dmaskW = const_cast<unsigned *>(p.dmask);  // lazy == 2: nothing has been expanded, cells are the base
+  for (long long k = k0; k < k1; ++k) {                // bounds until this vector's diffs touch them
     const unsigned v = var[k];
-    const size_t at = bt_cell(p, static_cast<int>(v & 0x7fffffffu), b);
-    Bnd x = p.X[0][at];
+    const int jv = static_cast<int>(v & 0x7fffffffu);
+    const size_t at = bt_cell(p, jv, b);
+    Bnd x;
+    if (lazy == 2) {
+      unsigned *w = &dmaskW[bt_word(p, jv, b >> 5)];
+      const bool had = (*reinterpret_cast<volatile unsigned *>(w) >> (b & 31)) & 1u;  // (own bit: set by this thread only)
+      x = had ? p.X[0][at] : p.baseX[jv];
+      if (!had)
+        atomicOr(w, 1u << (b & 31));
+    } else {
+      x = p.X[0][at];
+    }
     if (v & 0x80000000u)
       x.ub = bnd[k];
     else

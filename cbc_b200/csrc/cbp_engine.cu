@@ -46,6 +46,10 @@ struct BatchState {
   BtLogEntry *log = nullptr;    // round-0 candidate list (lazy second buffer)
   unsigned logCap = 0;
   int *groupFlag = nullptr;     // [G] + 1 word for the list's counter
+  Bnd *baseX = nullptr;         // first round from the base: interleaved base bounds
+  unsigned *dmask = nullptr;    // ... and [G][n] which vectors differ from them at a column
+  bool baseMode = false;        // the last run started from the base
+  std::vector<int> groupBuilt;  // ... and built the bound buffers of these groups only
   // loaded input (device copies) so the batch can be re-expanded
   double *baseLb = nullptr, *baseUb = nullptr;
   long long *dStart = nullptr;
@@ -1014,7 +1018,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
   const size_t cells = static_cast<size_t>(mat->n) * Bp;
   if (cells > bt.capCells || Bp > bt.capBp) {
     void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt,
-      bt.log, bt.groupFlag };
+      bt.log, bt.groupFlag, bt.dmask };
+    bt.dmask = nullptr;
     for (void *p : old)
       if (p)
         cudaFree(p);
@@ -1031,6 +1036,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
     if (dalloc(&bt.X[0], cells) != cudaSuccess || dalloc(&bt.X[1], cells) != cudaSuccess
       || dalloc(&bt.dirty[0], words) != cudaSuccess || dalloc(&bt.dirty[1], words) != cudaSuccess
       || dalloc(&bt.ever, words) != cudaSuccess || dalloc(&bt.active, Bp / 32) != cudaSuccess
+      || dalloc(&bt.dmask, words) != cudaSuccess
       || dalloc(&bt.ints, static_cast<size_t>(Bp) * 7 + 8) != cudaSuccess
       || dalloc(&bt.counts, static_cast<size_t>(Bp) + 1) != cudaSuccess
       || dalloc(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp) != cudaSuccess
@@ -1045,7 +1051,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.logCap = getenv("CBP_LOG_CAP") ? std::min<unsigned>(kBtLogCap, static_cast<unsigned>(atol(getenv("CBP_LOG_CAP")))) : kBtLogCap;
   }
   if (!bt.baseLb) {
-    if (dalloc(&bt.baseLb, mat->n) != cudaSuccess || dalloc(&bt.baseUb, mat->n) != cudaSuccess) {
+    if (dalloc(&bt.baseLb, mat->n) != cudaSuccess || dalloc(&bt.baseUb, mat->n) != cudaSuccess
+      || dalloc(&bt.baseX, mat->n) != cudaSuccess) {
       ctx->err = "batch workspace: base bounds";
       return CBP_ERR_NOMEM;
     }
@@ -1103,6 +1110,8 @@ static BtParams bt_params(cbp_matrix *mat, double tol)
   p.log = bt.log;
   p.logCap = bt.logCap;
   p.groupFlag = bt.groupFlag;
+  p.baseX = bt.baseX;
+  p.dmask = bt.dmask;
   p.logCount = reinterpret_cast<unsigned *>(bt.groupFlag + bt.G);
   p.s = make_scal(mat, tol);
   return p;
@@ -1195,7 +1204,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   bt_init_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, bt.B);
   ++ctx->stats.kernelLaunches;
   const int cellGrid = cdiv(static_cast<long long>(bt.cells), 256);
-  bool fullPrepass = true, lazy = false;
+  bool fullPrepass = true, lazy = false, fromBase = false;
   if (!bt.denseLoaded) {
     // base + deltas: expand here, so a loaded batch can be run any number of times
     if (bt.consumed) {
@@ -1216,12 +1225,22 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     // (worth it for shallow changes per vector — strong-branching arms, probes; deep dives tighten so much
     // in their first round that the direct two-buffer round is the cheaper one)
     lazy = !fullPrepass && bt.W == 32 && !getenv("CBP_NO_LAZY_X1") && (bt.nDelta <= 2ll * bt.B || getenv("CBP_LAZY_X1"));
-    bt_expand_kernel<<<cellGrid, 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.W, bt.cells, bt.X[0],
-      lazy ? nullptr : bt.X[1]);
-    ctx->stats.kernelLaunches += 2;
+    // ... and when that is so, neither buffer is built before the first round: it runs "from the base"
+    // (shared base bounds + the cells the diffs touch), and the buffers are built afterwards for the
+    // groups that go on
+    fromBase = lazy && !getenv("CBP_NO_BASE_ROUND");
+    ++ctx->stats.kernelLaunches;
+    if (fromBase) {
+      bt_base_pack_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.baseX);
+      CK(cudaMemsetAsync(bt.dmask, 0, sizeof(unsigned) * words, st));
+    } else {
+      bt_expand_kernel<<<cellGrid, 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.W, bt.cells, bt.X[0],
+        lazy ? nullptr : bt.X[1]);
+    }
+    ++ctx->stats.kernelLaunches;
     if (bt.nDelta > 0) {
       bt_delta_kernel<<<cdiv(bt.B, 128), 128, 0, st>>>(bt.dStart, bt.dVar, bt.dBnd, bt.B, p, fullPrepass ? 0 : 1,
-        lazy ? 1 : 0);
+        fromBase ? 2 : (lazy ? 1 : 0));
       ++ctx->stats.kernelLaunches;
     }
   } else {
@@ -1235,6 +1254,8 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     bt_prepass_kernel<<<cellGrid, 256, 0, st>>>(p, bt.B);
     ++ctx->stats.kernelLaunches;
   }
+  bt.baseMode = fromBase;
+  bt.groupBuilt.assign(bt.G, fromBase ? 0 : 1);
   bt_prepass_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p);
   ++ctx->stats.kernelLaunches;
   CK(cudaGetLastError());
@@ -1261,12 +1282,21 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     CK(cudaEventRecord(ctx->evPool[0], st));
     // kernel variants: <no infinite bound in this batch, no continuous column in this matrix, candidates to a list>
     const int variant = (bt.hasInf ? 0 : 2) | (mat->allInt ? 1 : 0);
-    auto launch_rows = [&](bool toList) {
-      if (longGrid > 0) {
+    auto launch_rows = [&](bool toList, bool base) {
+      const int mode = base ? 2 : (toList ? 1 : 0);  // base implies the list
+      if (longGrid > 0 && mode == 2 && !bt.hasInf && !getenv("CBP_NO_MULTI_GROUP")) {
+        // no infinite bound anywhere: four vector groups per warp share every staged matrix entry
+        constexpr int V = 4;
+        const long long lg = static_cast<long long>(cdiv(bt.G, V)) * mat->nLongBt;
+        bt_rows_long_base_kernel<V><<<static_cast<int>(lg), kLongWarps * 32, 0, st>>>(p);
+        ++ctx->stats.kernelLaunches;
+      } else if (longGrid > 0) {
         const int lg = static_cast<int>(longGrid);
         const int nt = kLongWarps * 32;
 #define CBP_LONG(A, B_)                                                              \
-  if (toList)                                                                        \
+  if (mode == 2)                                                                     \
+    bt_rows_long_kernel<A, B_, true, true><<<lg, nt, 0, st>>>(p, cur);               \
+  else if (mode == 1)                                                                \
     bt_rows_long_kernel<A, B_, true><<<lg, nt, 0, st>>>(p, cur);                     \
   else                                                                               \
     bt_rows_long_kernel<A, B_, false><<<lg, nt, 0, st>>>(p, cur);
@@ -1281,7 +1311,9 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       }
       if (warps > 0 && bt.W == 32) {
 #define CBP_SHORT(A, B_)                                                             \
-  if (toList)                                                                        \
+  if (mode == 2)                                                                     \
+    bt_rows_kernel<A, B_, true, true><<<rowsGrid, kThreads, 0, st>>>(p, cur);        \
+  else if (mode == 1)                                                                \
     bt_rows_kernel<A, B_, true><<<rowsGrid, kThreads, 0, st>>>(p, cur);              \
   else                                                                               \
     bt_rows_kernel<A, B_, false><<<rowsGrid, kThreads, 0, st>>>(p, cur);
@@ -1317,10 +1349,10 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       }
     };
     const bool listRound = lazy && round == 0;
-    launch_rows(listRound);
+    launch_rows(listRound, listRound && fromBase);
     CK(cudaEventRecord(ctx->evPool[1], st));
     if (listRound) {
-      // which groups need the second buffer, and did the list hold every candidate?
+      // which groups need the bound buffers, and did the list hold every candidate?
       std::vector<int> flags(bt.G + 1);
       CK(cudaMemcpyAsync(flags.data(), bt.groupFlag, sizeof(int) * (bt.G + 1), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
@@ -1328,12 +1360,23 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       bool anyFlag = false;
       for (int g = 0; g < bt.G; ++g)
         anyFlag = anyFlag || flags[g] != 0;
-      if (count > bt.logCap) {  // too many for the list: build the whole buffer and redo the round directly
-        bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, nullptr);
+      if (count > bt.logCap) {  // too many for the list: build the whole buffers and redo the round directly
+        if (fromBase) {
+          bt_expand_groups_kernel<<<cellGrid, 256, 0, st>>>(p, nullptr, 1);
+          bt.groupBuilt.assign(bt.G, 1);
+        } else {
+          bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, nullptr);
+        }
         ++ctx->stats.kernelLaunches;
-        launch_rows(false);
+        launch_rows(false, false);
       } else if (anyFlag) {
-        bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, bt.groupFlag);
+        if (fromBase) {
+          bt_expand_groups_kernel<<<cellGrid, 256, 0, st>>>(p, bt.groupFlag, 1);
+          for (int g = 0; g < bt.G; ++g)
+            bt.groupBuilt[g] = flags[g] != 0;
+        } else {
+          bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, bt.groupFlag);
+        }
         ++ctx->stats.kernelLaunches;
         if (count > 0) {
           bt_apply_log_kernel<<<cdiv(count, 256), 256, 0, st>>>(p, count);
@@ -1507,6 +1550,20 @@ int cbp_batch_fetch_dense(cbp_matrix *mat, double *lb, double *ub, int flags)
       cudaFree(dl);
       ctx->err = "cbp_batch_fetch_dense: staging";
       return CBP_ERR_NOMEM;
+    }
+  }
+  if (bt.baseMode) {
+    // a run that started from the base built the bound buffers only for the vector groups that went past
+    // their first round; the others still are "base + diffs": build them now
+    bool missing = false;
+    for (int g = 0; g < bt.G; ++g)
+      missing = missing || !bt.groupBuilt[g];
+    if (missing) {
+      CK(cudaMemcpyAsync(bt.groupFlag, bt.groupBuilt.data(), sizeof(int) * bt.G, cudaMemcpyHostToDevice, ctx->stream));
+      bt_expand_groups_kernel<<<cdiv(static_cast<long long>(bt.cells), 256), 256, 0, ctx->stream>>>(p, bt.groupFlag, 0);
+      ++ctx->stats.kernelLaunches;
+      CK(cudaStreamSynchronize(ctx->stream));  // (groupBuilt is host memory that changes next)
+      bt.groupBuilt.assign(bt.G, 1);
     }
   }
   dim3 grid(cdiv(mat->n, 32), cdiv(bt.B, 32)), block(32, 8);

@@ -257,8 +257,42 @@ def test_batch_wide_matrices_use_narrow_vector_slices(oracle, gpu_ctx, n, m, mon
     assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
 
 
-@pytest.mark.parametrize("env", [{"CBP_LOG_CAP": "7", "CBP_LAZY_X1": "1"}, {"CBP_LAZY_X1": "1"}, {"CBP_NO_LAZY_X1": "1"}],
-                         ids=["list_overflows", "lazy_buffer", "no_lazy_buffer"])
+def test_batch_first_round_from_the_base(oracle, gpu_ctx):
+    """A batch with few diffs per vector runs its first round from the shared base bounds and builds the
+    per-vector buffers only for groups that go on: vectors that repeat a column in their diffs, vectors
+    with no diff at all, a last group that is not full, groups where nothing happens next to groups
+    where a lot does, and the dense read-back of groups that were never built."""
+    inst = I.fast0507_shaped(m=101, n=9000, fix_frac=0.996, seed=22)
+    r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    inst.lb, inst.ub = lb0, ub0
+    s0, v0, b0 = I.strong_branch_deltas(inst, lb0, ub0, 40, seed=44)
+    free = np.flatnonzero(ub0 > lb0)
+    start, var, bnd = [0], [], []
+    for k in range(100):
+        if k < 40:  # strong-branching arms (groups 0 and 1: things happen)
+            var += list(v0[s0[k]:s0[k + 1]])
+            bnd += list(b0[s0[k]:s0[k + 1]])
+        elif k % 3 == 0:  # nothing
+            pass
+        elif k % 3 == 1:  # the same column twice: ub to 0, then lb to 0 (a no-op after the first)
+            j = int(free[(7 * k) % free.size])
+            var += [j | I.UPPER_FLAG, j]
+            bnd += [0.0, 0.0]
+        else:  # ub lowered twice, the second value counts; then raised back: ends where it started
+            j = int(free[(11 * k) % free.size])
+            var += [j | I.UPPER_FLAG, j | I.UPPER_FLAG]
+            bnd += [0.0, float(ub0[j])]
+        start.append(len(var))
+    s = np.array(start, np.int64)
+    v = np.array(var, np.uint32)
+    b = np.array(bnd, np.float64)
+    res = _check_batch(oracle, gpu_ctx, inst, s, v, b, "from the base")
+    assert res["nChanged"][:40].sum() > 0
+
+
+@pytest.mark.parametrize("env", [{"CBP_LOG_CAP": "7", "CBP_LAZY_X1": "1"}, {"CBP_LAZY_X1": "1"},
+                                 {"CBP_LAZY_X1": "1", "CBP_NO_BASE_ROUND": "1"}, {"CBP_NO_LAZY_X1": "1"}],
+                         ids=["list_overflows", "from_base", "lazy_buffer", "no_lazy_buffer"])
 def test_batch_first_round_variants(env):
     """The first round of a base+deltas batch normally collects candidates in a list and builds the second
     bound buffer afterwards; a list that is too small, or the feature switched off, must give the same answer."""
