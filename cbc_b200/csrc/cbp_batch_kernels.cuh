@@ -692,9 +692,22 @@ __device__ __forceinline__ void bt_walk_sum_base_multi(const BtParams &p, const 
   }
 }
 
+#ifndef CBP_BASE_V
+#define CBP_BASE_V 4
+#endif
+#ifndef CBP_BASE_WARPS
+#define CBP_BASE_WARPS 2
+#endif
+#ifndef CBP_BASE_MINB
+#define CBP_BASE_MINB 8
+#endif
+constexpr int kBaseGroups = CBP_BASE_V;     // vector groups per warp
+constexpr int kBaseWarps = CBP_BASE_WARPS;  // warps that share one long row
+
 template <int V>
-__global__ void __launch_bounds__(kLongWarps * 32, 2) bt_rows_long_base_kernel(const BtParams p)
+__global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_base_kernel(const BtParams p)
 {
+  constexpr int kLongWarps = kBaseWarps;  // (shadows the generic kernels' constant on purpose)
   __shared__ RowAct red[V][kLongWarps][32];
   __shared__ StgB stageB[kLongWarps][32];
   __shared__ int stageJ[kLongWarps][32];

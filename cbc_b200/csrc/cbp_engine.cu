@@ -1286,9 +1286,9 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       const int mode = base ? 2 : (toList ? 1 : 0);  // base implies the list
       if (longGrid > 0 && mode == 2 && !bt.hasInf && !getenv("CBP_NO_MULTI_GROUP")) {
         // no infinite bound anywhere: four vector groups per warp share every staged matrix entry
-        constexpr int V = 4;
+        constexpr int V = kBaseGroups;
         const long long lg = static_cast<long long>(cdiv(bt.G, V)) * mat->nLongBt;
-        bt_rows_long_base_kernel<V><<<static_cast<int>(lg), kLongWarps * 32, 0, st>>>(p);
+        bt_rows_long_base_kernel<V><<<static_cast<int>(lg), kBaseWarps * 32, 0, st>>>(p);
         ++ctx->stats.kernelLaunches;
       } else if (longGrid > 0) {
         const int lg = static_cast<int>(longGrid);
