@@ -49,6 +49,9 @@ struct BatchState {
   Bnd *baseX = nullptr;         // first round from the base: interleaved base bounds
   unsigned *dmask = nullptr;    // ... and [G][n] which vectors differ from them at a column
   bool baseMode = false;        // the last run started from the base
+  bool quiet = false;           // ... and no vector got a single candidate: no marks were ever set
+  double checkedTol = -1.0;     // R11 check of the base bounds: tolerance it was made for, result
+  bool baseNeedsPrepass = true;
   std::vector<int> groupBuilt;  // ... and built the bound buffers of these groups only
   // loaded input (device copies) so the batch can be re-expanded
   double *baseLb = nullptr, *baseUb = nullptr;
@@ -1162,6 +1165,7 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
     }
     bt.capStart = static_cast<size_t>(B) + 1;
   }
+  bt.checkedTol = -1.0;
   CK(cudaMemcpyAsync(bt.baseLb, baseLb, sizeof(double) * mat->n, kind, ctx->stream));
   CK(cudaMemcpyAsync(bt.baseUb, baseUb, sizeof(double) * mat->n, kind, ctx->stream));
   CK(cudaMemcpyAsync(bt.dStart, deltaStart, sizeof(long long) * (B + 1), kind, ctx->stream));
@@ -1199,26 +1203,40 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   cudaStream_t st = ctx->stream;
   CK(cudaEventRecord(ctx->evA, st));
   CK(cudaMemsetAsync(bt.dirty[0], 0, sizeof(unsigned) * words, st));
-  CK(cudaMemsetAsync(bt.dirty[1], 0, sizeof(unsigned) * words, st));
-  CK(cudaMemsetAsync(bt.ever, 0, sizeof(unsigned) * words, st));
+  bool restZeroed = false;  // dirty[1] and ever: not needed by a batch that ends quietly after its first round
+  auto zero_rest = [&]() -> int {
+    if (!restZeroed) {
+      CK(cudaMemsetAsync(bt.dirty[1], 0, sizeof(unsigned) * words, st));
+      CK(cudaMemsetAsync(bt.ever, 0, sizeof(unsigned) * words, st));
+      restZeroed = true;
+    }
+    return CBP_OK;
+  };
+  bt.quiet = false;
   bt_init_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, bt.B);
   ++ctx->stats.kernelLaunches;
   const int cellGrid = cdiv(static_cast<long long>(bt.cells), 256);
   bool fullPrepass = true, lazy = false, fromBase = false;
+  int rc0 = 0;
   if (!bt.denseLoaded) {
     // base + deltas: expand here, so a loaded batch can be run any number of times
     if (bt.consumed) {
       ctx->err = "cbp_batch_run: this batch was loaded dense and has already been run";
       return CBP_ERR_ARG;
     }
-    int need = 0;
-    CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
-    bt_base_check_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->colType, mat->n, p.s,
-      p.anyActive);
-    CK(cudaMemcpyAsync(&need, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (bt.checkedTol != primalTol) {  // (the loaded base bounds do not change between runs)
+      int need = 0;
+      CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
+      bt_base_check_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->colType, mat->n, p.s,
+        p.anyActive);
+      ++ctx->stats.kernelLaunches;
+      CK(cudaMemcpyAsync(&need, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      bt.baseNeedsPrepass = need != 0;
+      bt.checkedTol = primalTol;
+    }
     CK(cudaMemsetAsync(bt.groupFlag, 0, sizeof(int) * (bt.G + 1), st));
-    CK(cudaStreamSynchronize(st));
-    fullPrepass = need != 0;
+    fullPrepass = bt.baseNeedsPrepass;
     // Lazy second buffer: most vectors of a node batch reach their fixpoint in the first round without
     // a single accepted candidate, so the other bound buffer is built after that round and only for the
     // vector groups that have candidates (collected in a list) or R11 changes.
@@ -1229,7 +1247,8 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     // (shared base bounds + the cells the diffs touch), and the buffers are built afterwards for the
     // groups that go on
     fromBase = lazy && !getenv("CBP_NO_BASE_ROUND");
-    ++ctx->stats.kernelLaunches;
+    if (!fromBase && (rc0 = zero_rest()))
+      return rc0;
     if (fromBase) {
       bt_base_pack_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.baseX);
       CK(cudaMemsetAsync(bt.dmask, 0, sizeof(unsigned) * words, st));
@@ -1249,6 +1268,8 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       return CBP_ERR_ARG;
     }
     bt.consumed = true;
+    if ((rc0 = zero_rest()))
+      return rc0;
   }
   if (fullPrepass) {
     bt_prepass_kernel<<<cellGrid, 256, 0, st>>>(p, bt.B);
@@ -1360,6 +1381,21 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       bool anyFlag = false;
       for (int g = 0; g < bt.G; ++g)
         anyFlag = anyFlag || flags[g] != 0;
+      if (fromBase && !anyFlag && count == 0) {
+        // nobody has a candidate and R11 touched nothing: no mark was set, every vector stops here
+        // (fixpoint, or infeasible row); nothing to settle, nothing to carry, no update to report
+        bt_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, cur, round, limit, 0);
+        ++ctx->stats.kernelLaunches;
+        bt.quiet = true;
+        float ms = 0.f;
+        CK(cudaEventSynchronize(ctx->evPool[1]));
+        cudaEventElapsedTime(&ms, ctx->evPool[0], ctx->evPool[1]);
+        roundKernelMs += ms;
+        ++roundKernelLaunches;
+        break;
+      }
+      if ((rc0 = zero_rest()))
+        return rc0;
       if (count > bt.logCap) {  // too many for the list: build the whole buffers and redo the round directly
         if (fromBase) {
           bt_expand_groups_kernel<<<cellGrid, 256, 0, st>>>(p, nullptr, 1);
@@ -1475,6 +1511,13 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
     return rc;
   if (!updStart)
     return CBP_OK;
+  if (bt.quiet) {  // the run set no mark at all: no vector has an update
+    if (dev)
+      CK(cudaMemsetAsync(updStart, 0, sizeof(long long) * (bt.B + 1), ctx->stream));
+    else
+      memset(updStart, 0, sizeof(long long) * (bt.B + 1));
+    return CBP_OK;
+  }
   const BtParams p = bt_params(mat, 0.0);
   const int nChunks = cdiv(mat->n, kUpdChunk);
   const dim3 updGrid(bt.G, cdiv(nChunks, 4)), updBlock(128);
