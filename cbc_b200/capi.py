@@ -30,7 +30,8 @@ class Result(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("kernelLaunches", C.c_int64), ("lastRunMs", C.c_double), ("lastRoundKernelMs", C.c_double),
-                ("lastRoundKernelLaunches", C.c_int), ("lastRoundsTotal", C.c_int64)]
+                ("lastRoundKernelLaunches", C.c_int), ("lastRoundsTotal", C.c_int64),
+                ("lastFromBase", C.c_int), ("lastGroupsBuilt", C.c_int)]
 
 
 # every symbol include/cbp_capi.h declares (tests check that the library exports them all)
@@ -133,7 +134,8 @@ class Context:
         self.lib.cbp_get_stats(self.h, C.byref(s))
         return {"kernelLaunches": s.kernelLaunches, "lastRunMs": s.lastRunMs,
                 "lastRoundKernelMs": s.lastRoundKernelMs, "lastRoundKernelLaunches": s.lastRoundKernelLaunches,
-                "lastRoundsTotal": s.lastRoundsTotal}
+                "lastRoundsTotal": s.lastRoundsTotal, "lastFromBase": s.lastFromBase,
+                "lastGroupsBuilt": s.lastGroupsBuilt}
 
     def synchronize(self):
         self.check(self.lib.cbp_synchronize(self.h), "cbp_synchronize")

@@ -1454,6 +1454,11 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   for (int b = 0; b < bt.B; ++b)
     tot += rounds[b];
   ctx->stats.lastRoundsTotal = tot;
+  ctx->stats.lastFromBase = fromBase ? 1 : 0;
+  int built = 0;
+  for (int g = 0; g < bt.G; ++g)
+    built += bt.groupBuilt[g] ? 1 : 0;
+  ctx->stats.lastGroupsBuilt = built;
   return CBP_OK;
 }
 

@@ -82,6 +82,8 @@ typedef struct cbp_stats {
   double lastRoundKernelMs; /* time spent in the round kernel(s) of the last run */
   int lastRoundKernelLaunches;
   int64_t lastRoundsTotal; /* rounds summed over the vectors of the last run */
+  int lastFromBase;        /* batch: the first round ran from the shared base bounds (no per-vector buffers) */
+  int lastGroupsBuilt;     /* batch: vector groups (of 32) whose bound buffers were built afterwards */
 } cbp_stats;
 
 /* -- context ----------------------------------------------------------- */
