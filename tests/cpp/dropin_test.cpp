@@ -1,6 +1,6 @@
 // dropin_test.cpp — drives the C++ drop-ins the way Cbc's callers do, on top
 // of the COIN test double.  Usage:
-//   cbp_dropin_test <instance.bin> <out.bin> <level 1|2|3> <maxRounds> <logLevel> <timeLimit> [dive]
+//   cbp_dropin_test <instance.bin> <out.bin> <level 1|2|3> <maxRounds> <logLevel> <timeLimit> [dive | strong <cands.bin>]
 // Prints one "RESULT {json}" line; writes the solver's final column bounds to
 // out.bin (n doubles lb, n doubles ub).  With "dive" it instead performs the
 // single-round CoinBoundPropagation step of CbcHeuristicDive
@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "CbcBoundPropagation.hpp"
+#include "CbcStrongPropagation.hpp"
 #include "CoinBoundPropagation.hpp"
 #include "OsiSolverInterface.hpp"
 #include "cbp_capi.h"
@@ -154,6 +155,48 @@ int main(int argc, char **argv)
   const int level = atoi(argv[3]), maxRounds = atoi(argv[4]), logLevel = atoi(argv[5]);
   const double timeLimit = atof(argv[6]);
   const bool dive = argc > 7 && !strcmp(argv[7], "dive");
+  const bool strong = argc > 8 && !strcmp(argv[7], "strong");
+  if (strong) {
+    // what CbcNode::chooseDynamicBranch would do before its LP hot starts (src/CbcNode.cpp:3508-3626):
+    // cands.bin = int32 count, int32 columns[count], double values[count]
+    FILE *c = fopen(argv[8], "rb");
+    int cnt = 0;
+    if (!c || fread(&cnt, 4, 1, c) != 1 || cnt <= 0) {
+      fprintf(stderr, "cannot read %s\n", argv[8]);
+      return 2;
+    }
+    std::vector<int> cols(cnt);
+    std::vector<double> vals(cnt);
+    if (fread(cols.data(), 4, cnt, c) != static_cast<size_t>(cnt) || fread(vals.data(), 8, cnt, c) != static_cast<size_t>(cnt))
+      return 2;
+    fclose(c);
+    CbcStrongPropagation sp;
+    const bool ran = sp.run(&solver, cnt, cols.data(), vals.data(), maxRounds);
+    printf("RESULT {\"strong\": 1, \"ran\": %d, \"nInfeasibleArms\": %d, \"nodeInfeasible\": %d}\n", ran ? 1 : 0,
+      sp.numberInfeasibleArms(), sp.nodeInfeasible() ? 1 : 0);
+    // per arm: infeasible, row, col, rounds, number of implied bounds, and the implied bounds themselves
+    FILE *o = fopen(argv[2], "wb");
+    for (int k = 0; ran && k < cnt; ++k)
+      for (int w = 0; w < 2; ++w) {
+        const CbcStrongPropagation::Way way = static_cast<CbcStrongPropagation::Way>(w);
+        const CbcStrongPropagation::BoundList bl = sp.impliedBounds(k, way);
+        bool up = false;
+        double fb = 0.0;
+        const bool forced = sp.forcedBound(k, up, fb);
+        double head[8] = { sp.infeasible(k, way) ? 1.0 : 0.0, static_cast<double>(sp.infeasibleRow(k, way)),
+          static_cast<double>(sp.infeasibleCol(k, way)), static_cast<double>(sp.rounds(k, way)),
+          static_cast<double>(bl.size()), forced ? 1.0 : 0.0, up ? 1.0 : 0.0, fb };
+        fwrite(head, 8, 8, o);
+        for (const auto &e : bl) {
+          double rec[3] = { static_cast<double>(e.first), e.second.first, e.second.second };
+          fwrite(rec, 8, 3, o);
+        }
+      }
+    if (o)
+      fclose(o);
+    cbpReleaseThreadCache();
+    return 0;
+  }
   if (dive) {
     // the block of CbcHeuristicDive::solution, verbatim in shape
     const CoinPackedMatrix *matByRow = solver.getMatrixByRow();

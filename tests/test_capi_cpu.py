@@ -59,4 +59,6 @@ def test_dropin_library_links():
     # CbcBoundPropagation::run(OsiSolverInterface*, CoinMessageHandler*, int, Level, int, bool, double, double)
     assert "_ZN19CbcBoundPropagation3runEP18OsiSolverInterfaceP18CoinMessageHandleriNS_5LevelEibdd" in syms
     assert "_ZN20CoinBoundPropagationC1EiPKcPKdS3_PK16CoinPackedMatrixS1_S3_S3_dd" in syms
+    # CbcStrongPropagation::run(OsiSolverInterface*, int, int const*, double const*, int, double)
+    assert "_ZN20CbcStrongPropagation3runEP18OsiSolverInterfaceiPKiPKdid" in syms
     assert os.path.exists(os.path.join(ROOT, "cbc_b200", "lib", "cbp_dropin_test"))

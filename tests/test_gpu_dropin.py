@@ -111,3 +111,57 @@ def test_dive_step(oracle, tmp_path):
             assert np.array_equal(lb, lo) and np.array_equal(ub, uo)
         else:
             assert res["infeasibleRow"] == r["infeasibleRow"] and res["reasonToStop"] == 1
+
+
+def test_strong_branching_arms_match_oracle(oracle, tmp_path):
+    """CbcStrongPropagation: the 2 x numberToDo arms of a strong-branching step as one batch,
+    against the oracle run arm by arm: verdicts, rounds, implied bounds, forced fixings."""
+    inst = I.fast0507_shaped(m=101, n=9000, fix_frac=0.996, seed=22)
+    r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    inst.lb, inst.ub = lb0, ub0  # node bounds = propagated root
+    s, v, b = I.strong_branch_deltas(inst, lb0, ub0, 60, seed=71)
+    cols = (v[0::2] & 0x7FFFFFFF).astype(np.int32)
+    vals = b[0::2] + 0.5  # LP value between the two arms
+    ip, op, cp = str(tmp_path / "inst.bin"), str(tmp_path / "out.bin"), str(tmp_path / "cands.bin")
+    write_instance(inst, ip)
+    with open(cp, "wb") as f:
+        f.write(struct.pack("<i", len(cols)))
+        f.write(cols.tobytes())
+        f.write(np.ascontiguousarray(vals, np.float64).tobytes())
+    out = subprocess.run([DRIVER, ip, op, "3", "0", "0", "1e100", "strong", cp], capture_output=True, text=True,
+                         timeout=300)
+    assert out.returncode == 0, out.stderr
+    res = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("RESULT ")][0][7:])
+    assert res["ran"] == 1
+    ores, Lo, Uo = oracle.propagate_batch_delta(oracle.Problem(inst), lb0, ub0, s, v, b, threads=4)
+    L0, U0 = I.expand_deltas(lb0, ub0, s, v, b)
+    raw = np.fromfile(op)
+    at = 0
+    n_inf = 0
+    for k in range(len(cols)):
+        for w in range(2):
+            a = 2 * k + w
+            head = raw[at:at + 8]
+            at += 8
+            cnt = int(head[4])
+            rec = raw[at:at + 3 * cnt].reshape(cnt, 3)
+            at += 3 * cnt
+            assert int(head[0]) == (0 if ores["feasible"][a] else 1), (k, w)
+            assert int(head[3]) == ores["rounds"][a]
+            if not ores["feasible"][a]:
+                n_inf += 1
+                assert int(head[1]) == ores["infeasibleRow"][a] and int(head[2]) == ores["infeasibleCol"][a]
+                assert cnt == 0
+                continue
+            want = np.flatnonzero((Lo[a] != L0[a]) | (Uo[a] != U0[a]))
+            assert np.array_equal(rec[:, 0].astype(np.int64), want), (k, w)
+            assert np.array_equal(rec[:, 1], Lo[a][want]) and np.array_equal(rec[:, 2], Uo[a][want])
+            d_inf, u_inf = not ores["feasible"][2 * k], not ores["feasible"][2 * k + 1]
+            assert int(head[5]) == (1 if d_inf != u_inf else 0)
+            if d_inf != u_inf:
+                assert int(head[6]) == (0 if d_inf else 1)
+                assert head[7] == (np.ceil(vals[k]) if d_inf else np.floor(vals[k]))
+    assert at == raw.size
+    assert res["nInfeasibleArms"] == n_inf
+    both = any((not ores["feasible"][2 * k]) and (not ores["feasible"][2 * k + 1]) for k in range(len(cols)))
+    assert res["nodeInfeasible"] == (1 if both else 0)
