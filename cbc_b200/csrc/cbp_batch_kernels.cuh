@@ -705,7 +705,7 @@ constexpr int kBaseGroups = CBP_BASE_V;     // vector groups per warp
 constexpr int kBaseWarps = CBP_BASE_WARPS;  // warps that share one long row
 
 template <int V>
-__global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_base_kernel(const BtParams p)
+__global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_base_kernel(const BtParams p, int cur)
 {
   constexpr int kLongWarps = kBaseWarps;  // (shadows the generic kernels' constant on purpose)
   __shared__ RowAct red[V][kLongWarps][32];
@@ -725,7 +725,7 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
     act[v] = g < p.G ? __ldg(&p.active[g]) : 0u;
     anyAct |= act[v];
     const int b = min(g, p.G - 1) * 32 + lane;
-    src[v] = reinterpret_cast<const char *>(p.X[0] + bt_base(p, b));
+    src[v] = reinterpret_cast<const char *>(p.X[cur] + bt_base(p, b));
     dm[v] = g < p.G ? p.dmask + bt_word(p, 0, g) : nullptr;
   }
   if (anyAct == 0u)
@@ -774,7 +774,7 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
       atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
     // (every warp holds the same plans, so they all take the same branch; the walk itself only needs the warp)
     if (__any_sync(0xffffffffu, pl.sideU || pl.sideL)) {
-      BtLogSink sink = BtSinkFor<true>::make(p, 0, g, b, lane);
+      BtLogSink sink = BtSinkFor<true>::make(p, cur, g, b, lane);
       bt_walk_tighten<true>(p, src[v], strideB, dm[v], wb, we, lane, reinterpret_cast<Stg *>(stageB[warp]), pl, sink);
     }
   }
@@ -944,26 +944,42 @@ __global__ void bt_base_pack_kernel(const double *__restrict__ baseLb, const dou
   }
 }
 
-// after a first round "from the base": build both bound buffers (base bounds, the vector's own cells
-// where its diffs touched a column) for the vector groups whose flag equals `want` (all if flags == nullptr)
-__global__ void bt_expand_groups_kernel(const BtParams p, const int *__restrict__ flags, int want)
+// Leave the overlay form: every cell no diff or candidate has touched yet gets the base bounds in both
+// buffers (touched cells are valid in both already), so the classic two-buffer kernels can take over.
+__global__ void bt_overlay_expand_kernel(const BtParams p)
 {
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= static_cast<size_t>(p.n) * p.Bp)
     return;
   const int b = static_cast<int>(i / (static_cast<size_t>(p.W) * p.n)) * p.W + static_cast<int>(i % p.W);
-  const int g = b >> 5;
-  if (flags && (flags[g] != 0) != (want != 0))
-    return;
   const int j = static_cast<int>((i / p.W) % p.n);
-  Bnd x;
-  if ((p.dmask[bt_word(p, j, g)] >> (b & 31)) & 1u) {
-    x = p.X[0][i];
-  } else {
-    x = p.baseX[j];
-    p.X[0][i] = x;
-  }
+  if ((p.dmask[bt_word(p, j, b >> 5)] >> (b & 31)) & 1u)
+    return;
+  const Bnd x = p.baseX[j];
+  p.X[0][i] = x;
   p.X[1][i] = x;
+}
+
+// Overlay rounds, before the candidate list is applied: a cell that a candidate is about to tighten for
+// the first time becomes a real cell — base bounds in both buffers, mask bit set.  (A launch of its own:
+// the atomics of bt_apply_log_kernel must find every cell initialised.)
+__global__ void bt_overlay_touch_kernel(const BtParams p, unsigned count)
+{
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const BtLogEntry e = p.log[i];
+  const int j = static_cast<int>(e.var & 0x7fffffffu);
+  unsigned *w = const_cast<unsigned *>(&p.dmask[bt_word(p, j, e.b >> 5)]);
+  const unsigned bit = 1u << (e.b & 31);
+  if (__ldcg(w) & bit)
+    return;
+  if (atomicOr(w, bit) & bit)
+    return;  // somebody else got there first and writes the cell
+  const Bnd x = p.baseX[j];
+  const size_t at = bt_cell(p, j, e.b);
+  p.X[0][at] = x;
+  p.X[1][at] = x;
 }
 
 // second buffer := first buffer, for the vector groups whose flag is set (all if flags == nullptr)
@@ -981,19 +997,19 @@ __global__ void bt_copy_groups_kernel(const BtParams p, const int *__restrict__ 
 }
 
 // round 0's candidate list, applied to the (now valid) second buffer exactly as the direct sink would
-__global__ void bt_apply_log_kernel(const BtParams p, unsigned count)
+__global__ void bt_apply_log_kernel(const BtParams p, unsigned count, int cur)
 {
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count)
     return;
   const BtLogEntry e = p.log[i];
   const int j = static_cast<int>(e.var & 0x7fffffffu);
-  Bnd *cell = &p.X[1][bt_cell(p, j, e.b)];
+  Bnd *cell = &p.X[cur ^ 1][bt_cell(p, j, e.b)];
   if (e.var & 0x80000000u)
     atomic_min_f64(&cell->ub, e.v);
   else
     atomic_max_f64(&cell->lb, e.v);
-  atomicOr(&p.dirty[0][bt_word(p, j, e.b >> 5)], 1u << (e.b & 31));
+  atomicOr(&p.dirty[cur][bt_word(p, j, e.b >> 5)], 1u << (e.b & 31));
 }
 
 // node bound diffs, applied in order inside a vector (one thread per vector).
@@ -1026,7 +1042,7 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
     else
       x.lb = bnd[k];
     p.X[0][at] = x;
-    if (!lazy)
+    if (lazy != 1)  // (overlay form: a touched cell is valid in both buffers)
       p.X[1][at] = x;
   }
   if (!cellPrepass)
@@ -1041,9 +1057,9 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
     else if (r == 1) {
       atomicOr(&p.dirty[0][bt_word(p, j, b >> 5)], 1u << (b & 31));
       p.X[0][at] = x;
-      if (!lazy)
+      if (lazy != 1)
         p.X[1][at] = x;
-      else
+      if (lazy)
         p.groupFlag[b >> 5] = 1;
     }
   }

@@ -124,7 +124,7 @@ struct cbp_matrix {
 static thread_local std::string g_createErr;
 
 static constexpr size_t kSvSmallSmem = 0;
-static constexpr unsigned kBtLogCap = 4u << 20;  // round-0 candidate list: 4M entries (64 MB)  // the short-rows-only variant needs no dynamic shared memory
+static constexpr unsigned kBtLogCap = 16u << 20;  // candidate list of a list round: 16M entries (256 MB)  // the short-rows-only variant needs no dynamic shared memory
 
 template <class T>
 static cudaError_t dalloc(T **p, size_t count)
@@ -1292,6 +1292,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   double roundKernelMs = 0.0;
   int roundKernelLaunches = 0;
   int any = 1;
+  bool overlay = fromBase;  // the bound buffers hold only the cells diffs or candidates have touched
   while (ctx->evPool.size() < 2) {
     cudaEvent_t e;
     CK(cudaEventCreate(&e));
@@ -1300,6 +1301,8 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   for (int round = 0; any && !(timeLimitSec <= 0.0); ++round) {
     const int cur = round & 1;
     CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
+    if (overlay && round > 0)  // a new list (the first round's flags were seeded by the diffs' R11)
+      CK(cudaMemsetAsync(bt.groupFlag, 0, sizeof(int) * (bt.G + 1), st));
     CK(cudaEventRecord(ctx->evPool[0], st));
     // kernel variants: <no infinite bound in this batch, no continuous column in this matrix, candidates to a list>
     const int variant = (bt.hasInf ? 0 : 2) | (mat->allInt ? 1 : 0);
@@ -1309,7 +1312,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
         // no infinite bound anywhere: four vector groups per warp share every staged matrix entry
         constexpr int V = kBaseGroups;
         const long long lg = static_cast<long long>(cdiv(bt.G, V)) * mat->nLongBt;
-        bt_rows_long_base_kernel<V><<<static_cast<int>(lg), kBaseWarps * 32, 0, st>>>(p);
+        bt_rows_long_base_kernel<V><<<static_cast<int>(lg), kBaseWarps * 32, 0, st>>>(p, cur);
         ++ctx->stats.kernelLaunches;
       } else if (longGrid > 0) {
         const int lg = static_cast<int>(longGrid);
@@ -1369,11 +1372,11 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
         ++ctx->stats.kernelLaunches;
       }
     };
-    const bool listRound = lazy && round == 0;
-    launch_rows(listRound, listRound && fromBase);
+    const bool listRound = overlay || (lazy && round == 0);
+    launch_rows(listRound, overlay);
     CK(cudaEventRecord(ctx->evPool[1], st));
     if (listRound) {
-      // which groups need the bound buffers, and did the list hold every candidate?
+      // did anybody get a candidate, and did the list hold them all?  (first round: also, which groups did R11 touch)
       std::vector<int> flags(bt.G + 1);
       CK(cudaMemcpyAsync(flags.data(), bt.groupFlag, sizeof(int) * (bt.G + 1), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
@@ -1381,7 +1384,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       bool anyFlag = false;
       for (int g = 0; g < bt.G; ++g)
         anyFlag = anyFlag || flags[g] != 0;
-      if (fromBase && !anyFlag && count == 0) {
+      if (overlay && round == 0 && !anyFlag && count == 0) {
         // nobody has a candidate and R11 touched nothing: no mark was set, every vector stops here
         // (fixpoint, or infeasible row); nothing to settle, nothing to carry, no update to report
         bt_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, cur, round, limit, 0);
@@ -1397,25 +1400,28 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       if ((rc0 = zero_rest()))
         return rc0;
       if (count > bt.logCap) {  // too many for the list: build the whole buffers and redo the round directly
-        if (fromBase) {
-          bt_expand_groups_kernel<<<cellGrid, 256, 0, st>>>(p, nullptr, 1);
+        if (overlay) {
+          bt_overlay_expand_kernel<<<cellGrid, 256, 0, st>>>(p);
+          overlay = false;  // the classic two-buffer rounds from here on
           bt.groupBuilt.assign(bt.G, 1);
         } else {
           bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, nullptr);
         }
         ++ctx->stats.kernelLaunches;
         launch_rows(false, false);
-      } else if (anyFlag) {
-        if (fromBase) {
-          bt_expand_groups_kernel<<<cellGrid, 256, 0, st>>>(p, bt.groupFlag, 1);
-          for (int g = 0; g < bt.G; ++g)
-            bt.groupBuilt[g] = flags[g] != 0;
-        } else {
-          bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, bt.groupFlag);
+      } else if (overlay) {
+        // the bounds stay in overlay form: cells the candidates touch for the first time are created, then the
+        // list is applied exactly as the direct sink would have done
+        if (count > 0) {
+          bt_overlay_touch_kernel<<<cdiv(count, 256), 256, 0, st>>>(p, count);
+          bt_apply_log_kernel<<<cdiv(count, 256), 256, 0, st>>>(p, count, cur);
+          ctx->stats.kernelLaunches += 2;
         }
+      } else if (anyFlag) {
+        bt_copy_groups_kernel<<<cellGrid, 256, 0, st>>>(p, bt.groupFlag);
         ++ctx->stats.kernelLaunches;
         if (count > 0) {
-          bt_apply_log_kernel<<<cdiv(count, 256), 256, 0, st>>>(p, count);
+          bt_apply_log_kernel<<<cdiv(count, 256), 256, 0, st>>>(p, count, cur);
           ++ctx->stats.kernelLaunches;
         }
       }
@@ -1600,19 +1606,11 @@ int cbp_batch_fetch_dense(cbp_matrix *mat, double *lb, double *ub, int flags)
       return CBP_ERR_NOMEM;
     }
   }
-  if (bt.baseMode) {
-    // a run that started from the base built the bound buffers only for the vector groups that went past
-    // their first round; the others still are "base + diffs": build them now
-    bool missing = false;
-    for (int g = 0; g < bt.G; ++g)
-      missing = missing || !bt.groupBuilt[g];
-    if (missing) {
-      CK(cudaMemcpyAsync(bt.groupFlag, bt.groupBuilt.data(), sizeof(int) * bt.G, cudaMemcpyHostToDevice, ctx->stream));
-      bt_expand_groups_kernel<<<cdiv(static_cast<long long>(bt.cells), 256), 256, 0, ctx->stream>>>(p, bt.groupFlag, 0);
-      ++ctx->stats.kernelLaunches;
-      CK(cudaStreamSynchronize(ctx->stream));  // (groupBuilt is host memory that changes next)
-      bt.groupBuilt.assign(bt.G, 1);
-    }
+  if (bt.baseMode && !bt.groupBuilt.empty() && !bt.groupBuilt[0]) {
+    // the run stayed in overlay form (base bounds + touched cells): build the full buffers now
+    bt_overlay_expand_kernel<<<cdiv(static_cast<long long>(bt.cells), 256), 256, 0, ctx->stream>>>(p);
+    ++ctx->stats.kernelLaunches;
+    bt.groupBuilt.assign(bt.G, 1);
   }
   dim3 grid(cdiv(mat->n, 32), cdiv(bt.B, 32)), block(32, 8);
   bt_transpose_out_kernel<<<grid, block, 0, ctx->stream>>>(p, bt.B, dl, du);
