@@ -153,7 +153,7 @@ struct __align__(16) Stg {
 // it is only needed by lanes whose own vector differs from the base there.
 struct __align__(16) StgB {
   double a;
-  double lb, ub;
+  double lo, hi;  // the base bounds that enter minAct / maxAct: (lb, ub) for a > 0, (ub, lb) for a < 0
   unsigned mask;
   float w;
 };
@@ -268,8 +268,8 @@ __device__ __forceinline__ void bt_walk_sum_base(const BtParams &p, const char *
     {
       StgB e;
       e.a = a1;
-      e.lb = x1.x;
-      e.ub = x1.y;
+      e.lo = a1 > 0.0 ? x1.x : x1.y;
+      e.hi = a1 > 0.0 ? x1.y : x1.x;
       e.mask = m1;
       e.w = __fmul_ru(__double2float_ru(fabs(a1)), __double2float_ru(__dsub_ru(x1.y, x1.x)));
       stg[lane] = e;
@@ -291,21 +291,19 @@ __device__ __forceinline__ void bt_walk_sum_base(const BtParams &p, const char *
     if (kNoInf && !diffs) {
       if (cnt == 32) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {  // an entry = two 16-byte shared-memory broadcasts: {a, lb}, {ub, mask | w}
+        for (int i = 0; i < 32; ++i) {  // an entry = two 16-byte shared-memory broadcasts: {a, lo}, {hi, mask | w}
           const double2 h0 = reinterpret_cast<const double2 *>(&stg[i])[0];
           const double2 h1 = reinterpret_cast<const double2 *>(&stg[i])[1];
           const float w = __int_as_float(__double2hiint(h1.y));
-          const bool pos = kSign > 0 ? true : (kSign < 0 ? false : h0.x > 0.0);
-          ra.minAct = fma(h0.x, pos ? h0.y : h1.x, ra.minAct);
-          ra.maxAct = fma(h0.x, pos ? h1.x : h0.y, ra.maxAct);
+          ra.minAct = fma(h0.x, h0.y, ra.minAct);
+          ra.maxAct = fma(h0.x, h1.x, ra.maxAct);
           mr = fmaxf(mr, w);
         }
       } else {
         for (int i = 0; i < cnt; ++i) {
           const StgB e = stg[i];
-          const bool pos = kSign > 0 ? true : (kSign < 0 ? false : e.a > 0.0);
-          ra.minAct = fma(e.a, pos ? e.lb : e.ub, ra.minAct);
-          ra.maxAct = fma(e.a, pos ? e.ub : e.lb, ra.maxAct);
+          ra.minAct = fma(e.a, e.lo, ra.minAct);
+          ra.maxAct = fma(e.a, e.hi, ra.maxAct);
           mr = fmaxf(mr, e.w);
         }
       }
@@ -313,9 +311,10 @@ __device__ __forceinline__ void bt_walk_sum_base(const BtParams &p, const char *
     }
     for (int i = 0; i < cnt; ++i) {
       const StgB e = stg[i];
+      const bool pos = e.a > 0.0;
       Bnd x;
-      x.lb = e.lb;
-      x.ub = e.ub;
+      x.lb = pos ? e.lo : e.hi;
+      x.ub = pos ? e.hi : e.lo;
       float w = e.w;
       if ((e.mask >> lane) & 1u) {
         x = ldcg_bnd(reinterpret_cast<const Bnd *>(
@@ -323,7 +322,6 @@ __device__ __forceinline__ void bt_walk_sum_base(const BtParams &p, const char *
         w = __fmul_ru(__double2float_ru(fabs(e.a)), __double2float_ru(__dsub_ru(x.ub, x.lb)));
       }
       if (kNoInf) {
-        const bool pos = kSign > 0 ? true : (kSign < 0 ? false : e.a > 0.0);
         ra.minAct = fma(e.a, pos ? x.lb : x.ub, ra.minAct);
         ra.maxAct = fma(e.a, pos ? x.ub : x.lb, ra.maxAct);
         mr = fmaxf(mr, w);
@@ -627,8 +625,8 @@ __device__ __forceinline__ void bt_walk_sum_base_multi(const BtParams &p, const 
     {
       StgB e;
       e.a = a1;
-      e.lb = x1.x;
-      e.ub = x1.y;
+      e.lo = a1 > 0.0 ? x1.x : x1.y;
+      e.hi = a1 > 0.0 ? x1.y : x1.x;
       e.mask = anyM;
       e.w = __fmul_ru(__double2float_ru(fabs(a1)), __double2float_ru(__dsub_ru(x1.y, x1.x)));
       stg[lane] = e;
@@ -657,14 +655,12 @@ __device__ __forceinline__ void bt_walk_sum_base_multi(const BtParams &p, const 
     if (!diffs) {
 #pragma unroll 8
       for (int i = 0; i < cnt; ++i) {
-        const double2 h0 = reinterpret_cast<const double2 *>(&stg[i])[0];  // {a, lb}
-        const double2 h1 = reinterpret_cast<const double2 *>(&stg[i])[1];  // {ub, mask | w}
-        const bool pos = kSign > 0 ? true : (kSign < 0 ? false : h0.x > 0.0);
-        const double lo = pos ? h0.y : h1.x, hi = pos ? h1.x : h0.y;
+        const double2 h0 = reinterpret_cast<const double2 *>(&stg[i])[0];  // {a, lo}
+        const double2 h1 = reinterpret_cast<const double2 *>(&stg[i])[1];  // {hi, mask | w}
 #pragma unroll
         for (int v = 0; v < V; ++v) {
-          mn[v] = fma(h0.x, lo, mn[v]);
-          mx[v] = fma(h0.x, hi, mx[v]);
+          mn[v] = fma(h0.x, h0.y, mn[v]);
+          mx[v] = fma(h0.x, h1.x, mx[v]);
         }
         mrBase = fmaxf(mrBase, __int_as_float(__double2hiint(h1.y)));
       }
@@ -672,20 +668,20 @@ __device__ __forceinline__ void bt_walk_sum_base_multi(const BtParams &p, const 
     }
     for (int i = 0; i < cnt; ++i) {
       const StgB e = stg[i];
-      const bool pos = kSign > 0 ? true : (kSign < 0 ? false : e.a > 0.0);
+      const bool pos = e.a > 0.0;
 #pragma unroll
       for (int v = 0; v < V; ++v) {
-        Bnd x;
-        x.lb = e.lb;
-        x.ub = e.ub;
+        double lo = e.lo, hi = e.hi;
         float w = e.w;
         if ((stgM[v][i] >> lane) & 1u) {
-          x = ldcg_bnd(reinterpret_cast<const Bnd *>(
+          const Bnd x = ldcg_bnd(reinterpret_cast<const Bnd *>(
             src[v] + static_cast<unsigned long long>(static_cast<unsigned>(col_of(stgJ[i]))) * strideB));
+          lo = pos ? x.lb : x.ub;
+          hi = pos ? x.ub : x.lb;
           w = __fmul_ru(__double2float_ru(fabs(e.a)), __double2float_ru(__dsub_ru(x.ub, x.lb)));
         }
-        mn[v] = fma(e.a, pos ? x.lb : x.ub, mn[v]);
-        mx[v] = fma(e.a, pos ? x.ub : x.lb, mx[v]);
+        mn[v] = fma(e.a, lo, mn[v]);
+        mx[v] = fma(e.a, hi, mx[v]);
         mr[v] = fmaxf(mr[v], w);
       }
     }
@@ -776,6 +772,70 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
     if (__any_sync(0xffffffffu, pl.sideU || pl.sideL)) {
       BtLogSink sink = BtSinkFor<true>::make(p, cur, g, b, lane);
       bt_walk_tighten<true>(p, src[v], strideB, dm[v], wb, we, lane, reinterpret_cast<Stg *>(stageB[warp]), pl, sink);
+    }
+  }
+}
+
+// The same for rows up to kBtLongLen nonzeros: a warp owns (row, V vector groups), no shared partial sums.
+// Work is ordered group-quad-major so the warps in flight share their masks and touched cells.
+template <int V>
+__global__ void __launch_bounds__(kThreads, 2) bt_rows_short_base_kernel(const BtParams p, int cur)
+{
+  __shared__ StgB stageB[kWarps][32];
+  __shared__ int stageJ[kWarps][32];
+  __shared__ unsigned stageM[kWarps][V][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long item = static_cast<long long>(blockIdx.x) * kWarps + warp;
+  const int nQuad = (p.G + V - 1) / V;
+  if (item >= static_cast<long long>(nQuad) * p.nShortBt)
+    return;
+  const int q = static_cast<int>(item / p.nShortBt), r = __ldg(&p.shortRowsBt[item % p.nShortBt]);
+  unsigned act[V];
+  unsigned anyAct = 0u;
+  const char *src[V];
+  const unsigned *dm[V];
+  const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    const int g = q * V + v;
+    act[v] = g < p.G ? __ldg(&p.active[g]) : 0u;
+    anyAct |= act[v];
+    const int b = min(g, p.G - 1) * 32 + lane;
+    src[v] = reinterpret_cast<const char *>(p.X[cur] + bt_base(p, b));
+    dm[v] = g < p.G ? p.dmask + bt_word(p, 0, g) : nullptr;
+  }
+  if (anyAct == 0u)
+    return;
+  const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
+  double mn[V], mx[V];
+  float mr[V], mrBase = 0.f;
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    mn[v] = 0.0;
+    mx[v] = 0.0;
+    mr[v] = 0.f;
+  }
+  bt_walk_sum_base_multi<0, V>(p, src, strideB, dm, kb, ke, lane, stageB[warp], stageJ[warp], stageM[warp], mn, mx, mr,
+    mrBase);
+  const double rl = __ldg(&p.rowLB[r]), ru = __ldg(&p.rowUB[r]);
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    const int g = q * V + v;
+    if (g >= p.G)
+      break;
+    const RowAct tot = { mn[v], mx[v], static_cast<double>(fmaxf(mr[v], mrBase)), 0, 0 };
+    RowPlan pl = plan_row(tot, rl, ru, p.s);
+    if (!((act[v] >> lane) & 1u)) {
+      pl.infeasible = false;
+      pl.sideU = false;
+      pl.sideL = false;
+    }
+    const int b = g * 32 + lane;
+    if (pl.infeasible)
+      atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
+    if (__any_sync(0xffffffffu, pl.sideU || pl.sideL)) {
+      BtLogSink sink = BtSinkFor<true>::make(p, cur, g, b, lane);
+      bt_walk_tighten<true>(p, src[v], strideB, dm[v], kb, ke, lane, reinterpret_cast<Stg *>(stageB[warp]), pl, sink);
     }
   }
 }

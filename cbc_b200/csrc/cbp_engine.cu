@@ -1242,7 +1242,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     // vector groups that have candidates (collected in a list) or R11 changes.
     // (worth it for shallow changes per vector — strong-branching arms, probes; deep dives tighten so much
     // in their first round that the direct two-buffer round is the cheaper one)
-    lazy = !fullPrepass && bt.W == 32 && !getenv("CBP_NO_LAZY_X1") && (bt.nDelta <= 2ll * bt.B || getenv("CBP_LAZY_X1"));
+    lazy = !fullPrepass && bt.W == 32 && !getenv("CBP_NO_LAZY_X1") && (bt.nDelta <= 256ll * bt.B || getenv("CBP_LAZY_X1"));
     // ... and when that is so, neither buffer is built before the first round: it runs "from the base"
     // (shared base bounds + the cells the diffs touch), and the buffers are built afterwards for the
     // groups that go on
@@ -1333,7 +1333,12 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
 #undef CBP_LONG
         ++ctx->stats.kernelLaunches;
       }
-      if (warps > 0 && bt.W == 32) {
+      if (warps > 0 && mode == 2 && !bt.hasInf && !getenv("CBP_NO_MULTI_GROUP")) {
+        constexpr int V = kBaseGroups;
+        const long long items = static_cast<long long>(cdiv(bt.G, V)) * mat->nShortBt;
+        bt_rows_short_base_kernel<V><<<cdiv(items, kWarps), kThreads, 0, st>>>(p, cur);
+        ++ctx->stats.kernelLaunches;
+      } else if (warps > 0 && bt.W == 32) {
 #define CBP_SHORT(A, B_)                                                             \
   if (mode == 2)                                                                     \
     bt_rows_kernel<A, B_, true, true><<<rowsGrid, kThreads, 0, st>>>(p, cur);        \
@@ -1399,7 +1404,10 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       }
       if ((rc0 = zero_rest()))
         return rc0;
-      if (count > bt.logCap) {  // too many for the list: build the whole buffers and redo the round directly
+      // CBP_OVERLAY_ROUNDS: tests leave the overlay form after that many rounds to exercise the change-over
+      static const int overlayRounds = getenv("CBP_OVERLAY_ROUNDS") ? atoi(getenv("CBP_OVERLAY_ROUNDS")) : INT_MAX;
+      if (count > bt.logCap || (overlay && round >= overlayRounds)) {
+        // too many for the list: build the whole buffers and redo the round directly
         if (overlay) {
           bt_overlay_expand_kernel<<<cellGrid, 256, 0, st>>>(p);
           overlay = false;  // the classic two-buffer rounds from here on

@@ -290,12 +290,14 @@ def test_batch_first_round_from_the_base(oracle, gpu_ctx):
     assert res["nChanged"][:40].sum() > 0
 
 
-@pytest.mark.parametrize("env", [{"CBP_LOG_CAP": "7", "CBP_LAZY_X1": "1"}, {"CBP_LAZY_X1": "1"},
-                                 {"CBP_LAZY_X1": "1", "CBP_NO_BASE_ROUND": "1"}, {"CBP_NO_LAZY_X1": "1"}],
-                         ids=["list_overflows", "from_base", "lazy_buffer", "no_lazy_buffer"])
+@pytest.mark.parametrize("env", [{"CBP_LOG_CAP": "7"}, {}, {"CBP_OVERLAY_ROUNDS": "1"}, {"CBP_OVERLAY_ROUNDS": "2"},
+                                 {"CBP_NO_MULTI_GROUP": "1"}, {"CBP_NO_BASE_ROUND": "1"}, {"CBP_NO_LAZY_X1": "1"}],
+                         ids=["list_overflows", "overlay", "overlay_left_after_1", "overlay_left_after_2",
+                              "overlay_one_group_per_warp", "lazy_buffer", "no_lazy_buffer"])
 def test_batch_first_round_variants(env):
-    """The first round of a base+deltas batch normally collects candidates in a list and builds the second
-    bound buffer afterwards; a list that is too small, or the feature switched off, must give the same answer."""
+    """A base+deltas batch normally stays in overlay form (base bounds + touched cells, candidates through a list)
+    for all its rounds; a list that is too small, leaving the overlay form after one or two rounds, the older
+    lazy-second-buffer path and the plain two-buffer path must all give the same answer."""
     import os
     import subprocess
     import sys
