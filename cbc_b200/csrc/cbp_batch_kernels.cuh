@@ -881,8 +881,13 @@ __global__ void __launch_bounds__(kThreads) bt_settle_kernel(const BtParams p, i
 }
 
 // Per-vector bookkeeping of src/CbcBoundPropagation.cpp:129-189 after a round.
-__global__ void bt_state_kernel(const BtParams p, int cur, int round, int limit, int timeUp)
+// guard (may be null): two words — if either is non-zero the kernel does nothing (the host launches it ahead of
+// knowing whether the first round was quiet; the words are the candidate count and the diffs' R11 flag).
+__global__ void bt_state_kernel(const BtParams p, int cur, int round, int limit, int timeUp,
+  const int *__restrict__ guard = nullptr)
 {
+  if (guard && (guard[0] | guard[1]))
+    return;
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
   bool on = false;
@@ -1119,10 +1124,25 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
       p.X[0][at] = x;
       if (lazy != 1)
         p.X[1][at] = x;
-      if (lazy)
+      if (lazy) {
         p.groupFlag[b >> 5] = 1;
+        p.groupFlag[p.G + 1] = 1;  // "R11 changed some diff cell"
+      }
     }
   }
+}
+
+// after a quiet run from the base: take the diffs' bits out of the mask again, so that the next run of
+// this (or another) batch finds it empty without clearing all of it
+__global__ void bt_delta_unmask_kernel(const long long *__restrict__ start, const unsigned *__restrict__ var, int B,
+  const BtParams p)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B)
+    return;
+  unsigned *dmaskW = const_cast<unsigned *>(p.dmask);
+  for (long long k = start[b]; k < start[b + 1]; ++k)
+    atomicAnd(&dmaskW[bt_word(p, static_cast<int>(var[k] & 0x7fffffffu), b >> 5)], ~(1u << (b & 31)));
 }
 
 // dense input, B x n row-major per vector -> slice-major cells; 32x32 tiles

@@ -50,6 +50,7 @@ struct BatchState {
   unsigned *dmask = nullptr;    // ... and [G][n] which vectors differ from them at a column
   bool baseMode = false;        // the last run started from the base
   bool quiet = false;           // ... and no vector got a single candidate: no marks were ever set
+  bool dirty0Clean = false, dmaskClean = false;  // known to be all zero (left so by a quiet run)
   double checkedTol = -1.0;     // R11 check of the base bounds: tolerance it was made for, result
   bool baseNeedsPrepass = true;
   std::vector<int> groupBuilt;  // ... and built the bound buffers of these groups only
@@ -1043,13 +1044,14 @@ static int bt_reserve(cbp_matrix *mat, int B)
       || dalloc(&bt.ints, static_cast<size_t>(Bp) * 7 + 8) != cudaSuccess
       || dalloc(&bt.counts, static_cast<size_t>(Bp) + 1) != cudaSuccess
       || dalloc(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp) != cudaSuccess
-      || dalloc(&bt.groupFlag, static_cast<size_t>(Bp / 32) + 1) != cudaSuccess
+      || dalloc(&bt.groupFlag, static_cast<size_t>(Bp / 32) + 2) != cudaSuccess
       || dalloc(&bt.log, kBtLogCap) != cudaSuccess) {
       ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
       return CBP_ERR_NOMEM;
     }
     bt.capCells = cells;
     bt.capBp = Bp;
+    bt.dirty0Clean = bt.dmaskClean = false;
     // CBP_LOG_CAP: tests shrink the list to exercise the fall-back to the two-buffer first round
     bt.logCap = getenv("CBP_LOG_CAP") ? std::min<unsigned>(kBtLogCap, static_cast<unsigned>(atol(getenv("CBP_LOG_CAP")))) : kBtLogCap;
   }
@@ -1180,12 +1182,14 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
   // Are all input bounds finite?  Then the rows kernels drop their infinity tests.
   bt.hasInf = true;
   if (!(flags & CBP_FLAG_DEVICE_PTRS)) {
-    bool any = false;
-    for (int j = 0; j < mat->n && !any; ++j)
-      any = !(std::fabs(baseLb[j]) < mat->inf) || !(std::fabs(baseUb[j]) < mat->inf);
-    for (long long k = 0; k < nDelta && !any; ++k)
-      any = !(std::fabs(deltaBound[k]) < mat->inf);
-    bt.hasInf = any;
+    // (counting, not stopping at the first hit: the loops vectorise)
+    const double inf = mat->inf;
+    long long bad = 0;
+    for (int j = 0; j < mat->n; ++j)
+      bad += (!(std::fabs(baseLb[j]) < inf)) + (!(std::fabs(baseUb[j]) < inf));
+    for (long long k = 0; k < nDelta; ++k)
+      bad += !(std::fabs(deltaBound[k]) < inf);
+    bt.hasInf = bad != 0;
   }
   return CBP_OK;
 }
@@ -1202,7 +1206,9 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   const size_t words = bt.cells / 32;
   cudaStream_t st = ctx->stream;
   CK(cudaEventRecord(ctx->evA, st));
-  CK(cudaMemsetAsync(bt.dirty[0], 0, sizeof(unsigned) * words, st));
+  if (!bt.dirty0Clean)
+    CK(cudaMemsetAsync(bt.dirty[0], 0, sizeof(unsigned) * words, st));
+  bt.dirty0Clean = false;
   bool restZeroed = false;  // dirty[1] and ever: not needed by a batch that ends quietly after its first round
   auto zero_rest = [&]() -> int {
     if (!restZeroed) {
@@ -1235,7 +1241,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       bt.baseNeedsPrepass = need != 0;
       bt.checkedTol = primalTol;
     }
-    CK(cudaMemsetAsync(bt.groupFlag, 0, sizeof(int) * (bt.G + 1), st));
+    CK(cudaMemsetAsync(bt.groupFlag, 0, sizeof(int) * (bt.G + 2), st));
     fullPrepass = bt.baseNeedsPrepass;
     // Lazy second buffer: most vectors of a node batch reach their fixpoint in the first round without
     // a single accepted candidate, so the other bound buffer is built after that round and only for the
@@ -1251,7 +1257,9 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       return rc0;
     if (fromBase) {
       bt_base_pack_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.baseX);
-      CK(cudaMemsetAsync(bt.dmask, 0, sizeof(unsigned) * words, st));
+      if (!bt.dmaskClean)
+        CK(cudaMemsetAsync(bt.dmask, 0, sizeof(unsigned) * words, st));
+      bt.dmaskClean = false;
     } else {
       bt_expand_kernel<<<cellGrid, 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.W, bt.cells, bt.X[0],
         lazy ? nullptr : bt.X[1]);
@@ -1302,7 +1310,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     const int cur = round & 1;
     CK(cudaMemsetAsync(p.anyActive, 0, sizeof(int), st));
     if (overlay && round > 0)  // a new list (the first round's flags were seeded by the diffs' R11)
-      CK(cudaMemsetAsync(bt.groupFlag, 0, sizeof(int) * (bt.G + 1), st));
+      CK(cudaMemsetAsync(bt.groupFlag, 0, sizeof(int) * (bt.G + 2), st));
     CK(cudaEventRecord(ctx->evPool[0], st));
     // kernel variants: <no infinite bound in this batch, no continuous column in this matrix, candidates to a list>
     const int variant = (bt.hasInf ? 0 : 2) | (mat->allInt ? 1 : 0);
@@ -1380,6 +1388,10 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     const bool listRound = overlay || (lazy && round == 0);
     launch_rows(listRound, overlay);
     CK(cudaEventRecord(ctx->evPool[1], st));
+    if (overlay && round == 0) {  // in case the round turns out quiet (the kernel checks for itself): saves a round trip
+      bt_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, cur, round, limit, 0, bt.groupFlag + bt.G);
+      ++ctx->stats.kernelLaunches;
+    }
     if (listRound) {
       // did anybody get a candidate, and did the list hold them all?  (first round: also, which groups did R11 touch)
       std::vector<int> flags(bt.G + 1);
@@ -1392,8 +1404,13 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       if (overlay && round == 0 && !anyFlag && count == 0) {
         // nobody has a candidate and R11 touched nothing: no mark was set, every vector stops here
         // (fixpoint, or infeasible row); nothing to settle, nothing to carry, no update to report
-        bt_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, cur, round, limit, 0);
-        ++ctx->stats.kernelLaunches;
+        // (the guarded state kernel above has done the bookkeeping)
+        if (bt.nDelta > 0) {
+          bt_delta_unmask_kernel<<<cdiv(bt.B, 128), 128, 0, st>>>(bt.dStart, bt.dVar, bt.B, p);
+          ++ctx->stats.kernelLaunches;
+        }
+        bt.dmaskClean = true;
+        bt.dirty0Clean = true;
         bt.quiet = true;
         float ms = 0.f;
         CK(cudaEventSynchronize(ctx->evPool[1]));
@@ -1461,12 +1478,15 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   ctx->stats.lastRunMs = ms;
   ctx->stats.lastRoundKernelMs = roundKernelMs;
   ctx->stats.lastRoundKernelLaunches = roundKernelLaunches;
-  // rounds summed over vectors (for throughput accounting)
-  std::vector<int> rounds(bt.Bp);
-  CK(cudaMemcpy(rounds.data(), p.vecRounds, sizeof(int) * bt.Bp, cudaMemcpyDeviceToHost));
-  long long tot = 0;
-  for (int b = 0; b < bt.B; ++b)
-    tot += rounds[b];
+  // rounds summed over vectors (for throughput accounting); a quiet run: one round each
+  long long tot = bt.B;
+  if (!bt.quiet) {
+    std::vector<int> rounds(bt.Bp);
+    CK(cudaMemcpy(rounds.data(), p.vecRounds, sizeof(int) * bt.Bp, cudaMemcpyDeviceToHost));
+    tot = 0;
+    for (int b = 0; b < bt.B; ++b)
+      tot += rounds[b];
+  }
   ctx->stats.lastRoundsTotal = tot;
   ctx->stats.lastFromBase = fromBase ? 1 : 0;
   int built = 0;
