@@ -344,8 +344,14 @@ def main():
     # ---- end to end through the C ABI with HOST buffers (copies inside the timed region)
     e2e_steps = max(2, min(args.steps, 5))
     if batch:
+        # the step's inputs live in pinned host memory (numpy views of pinned torch tensors)
+        def pinned(a, dt):
+            return torch.from_numpy(np.ascontiguousarray(a, dt)).pin_memory().numpy()
+        lb_h, ub_h = pinned(work["lb"], np.float64), pinned(work["ub"], np.float64)
+        s_h, v_h, b_h = pinned(s, np.int64), pinned(v, np.uint32), pinned(b, np.float64)
+
         def e2e_step():
-            res, us, uc, ul, uu = mat.propagate_batch_delta(work["lb"], work["ub"], s, v, b)
+            res, us, uc, ul, uu = mat.propagate_batch_delta(lb_h, ub_h, s_h, v_h, b_h)
             return int(res["rounds"].sum()), uc.size
         h2d = 16 * inst.n + 8 * (len(s)) + 12 * len(v)
     elif world > 1 and args.rowshard == "peer":
