@@ -62,6 +62,11 @@ __device__ __forceinline__ size_t bt_base(const BtParams &p, int b)
 {
   return (static_cast<size_t>(b / p.W) * p.n) * p.W + (b % p.W);
 }
+// the same for the kernels that only exist for W = 32 (no runtime division)
+__device__ __forceinline__ size_t bt_base32(const BtParams &p, int b)
+{
+  return (static_cast<size_t>(b >> 5) * p.n) * 32 + (b & 31);
+}
 __device__ __forceinline__ size_t bt_cell(const BtParams &p, int j, int b)
 {
   return bt_base(p, b) + static_cast<size_t>(j) * p.W;
@@ -714,15 +719,15 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
   unsigned anyAct = 0u;
   const char *src[V];
   const unsigned *dm[V];
-  const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
+  constexpr unsigned strideB = 32u * static_cast<unsigned>(sizeof(Bnd));  // (these kernels exist for W = 32 only)
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     const int g = q * V + v;
     act[v] = g < p.G ? __ldg(&p.active[g]) : 0u;
     anyAct |= act[v];
-    const int b = min(g, p.G - 1) * 32 + lane;
-    src[v] = reinterpret_cast<const char *>(p.X[cur] + bt_base(p, b));
-    dm[v] = g < p.G ? p.dmask + bt_word(p, 0, g) : nullptr;
+    const int gc = min(g, p.G - 1);
+    src[v] = reinterpret_cast<const char *>(p.X[cur] + (static_cast<size_t>(gc) * p.n) * 32 + lane);
+    dm[v] = g < p.G ? p.dmask + static_cast<size_t>(g) * p.n : nullptr;
   }
   if (anyAct == 0u)
     return;
@@ -776,33 +781,36 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
   }
 }
 
+#ifndef CBP_SHORT_MINB
+#define CBP_SHORT_MINB 3
+#endif
 // The same for rows up to kBtLongLen nonzeros: a warp owns (row, V vector groups), no shared partial sums.
 // Work is ordered group-quad-major so the warps in flight share their masks and touched cells.
 template <int V>
-__global__ void __launch_bounds__(kThreads, 2) bt_rows_short_base_kernel(const BtParams p, int cur)
+__global__ void __launch_bounds__(kThreads, CBP_SHORT_MINB) bt_rows_short_base_kernel(const BtParams p, int cur)
 {
   __shared__ StgB stageB[kWarps][32];
   __shared__ int stageJ[kWarps][32];
   __shared__ unsigned stageM[kWarps][V][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const long long item = static_cast<long long>(blockIdx.x) * kWarps + warp;
-  const int nQuad = (p.G + V - 1) / V;
-  if (item >= static_cast<long long>(nQuad) * p.nShortBt)
+  // grid: x strides over the rows, y = group quad (quad-major: the warps in flight share masks and cells)
+  const int ri = blockIdx.x * kWarps + warp;
+  if (ri >= p.nShortBt)
     return;
-  const int q = static_cast<int>(item / p.nShortBt), r = __ldg(&p.shortRowsBt[item % p.nShortBt]);
+  const int q = blockIdx.y, r = __ldg(&p.shortRowsBt[ri]);
   unsigned act[V];
   unsigned anyAct = 0u;
   const char *src[V];
   const unsigned *dm[V];
-  const unsigned strideB = static_cast<unsigned>(p.W) * static_cast<unsigned>(sizeof(Bnd));
+  constexpr unsigned strideB = 32u * static_cast<unsigned>(sizeof(Bnd));  // (these kernels exist for W = 32 only)
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     const int g = q * V + v;
     act[v] = g < p.G ? __ldg(&p.active[g]) : 0u;
     anyAct |= act[v];
-    const int b = min(g, p.G - 1) * 32 + lane;
-    src[v] = reinterpret_cast<const char *>(p.X[cur] + bt_base(p, b));
-    dm[v] = g < p.G ? p.dmask + bt_word(p, 0, g) : nullptr;
+    const int gc = min(g, p.G - 1);
+    src[v] = reinterpret_cast<const char *>(p.X[cur] + (static_cast<size_t>(gc) * p.n) * 32 + lane);
+    dm[v] = g < p.G ? p.dmask + static_cast<size_t>(g) * p.n : nullptr;
   }
   if (anyAct == 0u)
     return;
@@ -823,6 +831,8 @@ __global__ void __launch_bounds__(kThreads, 2) bt_rows_short_base_kernel(const B
     const int g = q * V + v;
     if (g >= p.G)
       break;
+    if (act[v] == 0u)
+      continue;
     const RowAct tot = { mn[v], mx[v], static_cast<double>(fmaxf(mr[v], mrBase)), 0, 0 };
     RowPlan pl = plan_row(tot, rl, ru, p.s);
     if (!((act[v] >> lane) & 1u)) {

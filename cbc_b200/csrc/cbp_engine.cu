@@ -1343,8 +1343,8 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       }
       if (warps > 0 && mode == 2 && !bt.hasInf && !getenv("CBP_NO_MULTI_GROUP")) {
         constexpr int V = kBaseGroups;
-        const long long items = static_cast<long long>(cdiv(bt.G, V)) * mat->nShortBt;
-        bt_rows_short_base_kernel<V><<<cdiv(items, kWarps), kThreads, 0, st>>>(p, cur);
+        const dim3 sg(cdiv(mat->nShortBt, kWarps), cdiv(bt.G, V));
+        bt_rows_short_base_kernel<V><<<sg, kThreads, 0, st>>>(p, cur);
         ++ctx->stats.kernelLaunches;
       } else if (warps > 0 && bt.W == 32) {
 #define CBP_SHORT(A, B_)                                                             \
