@@ -255,10 +255,15 @@ __device__ __forceinline__ void sv_stream(const SvParams &p, SvSmem &sm, uint32_
           if (tid < nc)
             sm.stash[tid] = ldcg_rowact(&p.longPart[lr.firstPart + c0 + tid]);
           __syncthreads();
-          for (int c = 0; c < nc; ++c)
-            combine(tot, sm.stash[c]);
+          if (warp == 0)  // one warp walks them (all 256 threads would only queue up at the shared-memory port)
+            for (int c = 0; c < nc; ++c)
+              combine(tot, sm.stash[c]);
           __syncthreads();
         }
+        if (tid == 0)
+          sm.red[0] = tot;
+        __syncthreads();
+        tot = sm.red[0];
         const RowPlan pl = plan_row(tot, p.rowLB[lr.row], p.rowUB[lr.row], p.s);
         if (pl.infeasible && tid == 0 && T.chunkIdx == 0)
           sink.flag_row(p.rowOrig[lr.row] + p.rowOffset);

@@ -42,8 +42,10 @@ for name, fn in (("plain", lambda: mat.propagate_device(lb.data_ptr(), ub.data_p
     ms, rounds = run(fn)
     st = mat.round_stamps(64).astype(np.int64)
     print(f"{name}: kernel {ms:.3f} ms, {rounds} rounds")
-    for i in [1, 10, 20, 21]:
+    for i in [0, 1, 2, 3, 10, 20, 21]:
+        if i >= rounds:
+            break
         rowsDone, a1, settleDone, own = st[i]
-        start = st[i - 1][2]
+        start = st[i - 1][2] if i > 0 else 0
         print(f"  round {i}: A1 done +{(a1-start)/1e3:6.1f}  CTA0 rows done +{(own-start)/1e3:6.1f}  rows barrier passed "
               f"+{(rowsDone-start)/1e3:6.1f}  settle+barrier +{(settleDone-rowsDone)/1e3:5.1f}")
