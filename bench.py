@@ -429,12 +429,12 @@ def main():
         # The first round of a base+diffs batch reads the shared base bounds (L1/L2) plus the cells the diffs
         # touch instead of 32 n B bytes of per-vector bounds, so the §8d byte count is not a lower bound for
         # it and `frac` can exceed 1.  What limits the kernel instead is the shared-memory broadcast of the
-        # staged entries: 32 B per (nonzero, 4 vector groups) handed to 32 lanes at 128 B per clock and SM.
+        # staged entries: 24 B per (nonzero, 4 vector groups) handed to 32 lanes at 128 B per clock and SM.
         roofline["kernel"] = "bt_rows_long_base_kernel + bt_rows_kernel<base> (first round, from the base bounds)"
         props = torch.cuda.get_device_properties(local)
         smem_peak = props.multi_processor_count * 128.0 * (clk.summary().get("sm_mhz") or 1965) * 1e6 / 1e9
         pairs = inst.nnz * ((work["B"] + 127) // 128) * round_launches
-        smem_bytes = pairs * 32.0 * 32.0
+        smem_bytes = pairs * 24.0 * 32.0
         roofline["note"] = ("first round runs from the shared base bounds: per-vector bounds are not read, the "
                             "SURVEY 8d byte model does not bound this kernel; limiter is shared-memory broadcast")
         roofline["smem_broadcast"] = {"achieved": smem_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0,

@@ -602,9 +602,13 @@ __global__ void __launch_bounds__(kLongWarps * 32, 2048 / (kLongWarps * 32) / 2)
 // same two reads feed 2V DFMAs.
 template <int kSign, int V>
 __device__ __forceinline__ void bt_walk_sum_base_multi(const BtParams &p, const char *const (&src)[V],
-  unsigned strideB, const unsigned *const (&dm)[V], int kb, int ke, int lane, StgB *stg, int *stgJ,
+  unsigned strideB, const unsigned *const (&dm)[V], int kb, int ke, int lane, double2 *stgA, double *stgH, int *stgJ,
   unsigned (*stgM)[32], double (&mn)[V], double (&mx)[V], float (&mr)[V], float &mrBase)
 {
+  // A staged entry is 24 bytes here: {a, lo} in stgA, {hi} in stgH (the bytes that are broadcast to the lanes are
+  // what the walk costs).  The base bounds' |a| * (ub - lb) bound does not travel at all: the staging lanes take
+  // its maximum over the block with one warp reduction (adding the base value of a column that a lane has a cell
+  // of its own for only makes that lane's upper bound larger, which is allowed).
   double a1 = 0.0, a2 = 0.0;
   int c1 = 0, c2 = 0;
   if (kb + lane < ke) {
@@ -626,21 +630,17 @@ __device__ __forceinline__ void bt_walk_sum_base_multi(const BtParams &p, const 
     for (int v = 0; v < V; ++v)
       anyM |= m1[v];
     const bool diffs = __any_sync(0xffffffffu, anyM != 0u);
+    const float w1 = __fmul_ru(__double2float_ru(fabs(a1)), __double2float_ru(__dsub_ru(x1.y, x1.x)));
+    // (non-negative floats order like their bit patterns)
+    mrBase = fmaxf(mrBase, __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(w1))));
     __syncwarp();
-    {
-      StgB e;
-      e.a = a1;
-      e.lo = a1 > 0.0 ? x1.x : x1.y;
-      e.hi = a1 > 0.0 ? x1.y : x1.x;
-      e.mask = anyM;
-      e.w = __fmul_ru(__double2float_ru(fabs(a1)), __double2float_ru(__dsub_ru(x1.y, x1.x)));
-      stg[lane] = e;
-      if (diffs) {
-        stgJ[lane] = c1;
+    stgA[lane] = make_double2(a1, a1 > 0.0 ? x1.x : x1.y);
+    stgH[lane] = a1 > 0.0 ? x1.y : x1.x;
+    if (diffs) {
+      stgJ[lane] = c1;
 #pragma unroll
-        for (int v = 0; v < V; ++v)
-          stgM[v][lane] = m1[v];
-      }
+      for (int v = 0; v < V; ++v)
+        stgM[v][lane] = m1[v];
     }
     a1 = a2;
     c1 = c2;
@@ -660,34 +660,33 @@ __device__ __forceinline__ void bt_walk_sum_base_multi(const BtParams &p, const 
     if (!diffs) {
 #pragma unroll 8
       for (int i = 0; i < cnt; ++i) {
-        const double2 h0 = reinterpret_cast<const double2 *>(&stg[i])[0];  // {a, lo}
-        const double2 h1 = reinterpret_cast<const double2 *>(&stg[i])[1];  // {hi, mask | w}
+        const double2 h0 = stgA[i];  // {a, lo}
+        const double hi = stgH[i];
 #pragma unroll
         for (int v = 0; v < V; ++v) {
           mn[v] = fma(h0.x, h0.y, mn[v]);
-          mx[v] = fma(h0.x, h1.x, mx[v]);
+          mx[v] = fma(h0.x, hi, mx[v]);
         }
-        mrBase = fmaxf(mrBase, __int_as_float(__double2hiint(h1.y)));
       }
       continue;
     }
     for (int i = 0; i < cnt; ++i) {
-      const StgB e = stg[i];
-      const bool pos = e.a > 0.0;
+      const double2 h0 = stgA[i];
+      const double a = h0.x;
+      const double hiB = stgH[i];
+      const bool pos = a > 0.0;
 #pragma unroll
       for (int v = 0; v < V; ++v) {
-        double lo = e.lo, hi = e.hi;
-        float w = e.w;
+        double lo = h0.y, hi = hiB;
         if ((stgM[v][i] >> lane) & 1u) {
           const Bnd x = ldcg_bnd(reinterpret_cast<const Bnd *>(
             src[v] + static_cast<unsigned long long>(static_cast<unsigned>(col_of(stgJ[i]))) * strideB));
           lo = pos ? x.lb : x.ub;
           hi = pos ? x.ub : x.lb;
-          w = __fmul_ru(__double2float_ru(fabs(e.a)), __double2float_ru(__dsub_ru(x.ub, x.lb)));
+          mr[v] = fmaxf(mr[v], __fmul_ru(__double2float_ru(fabs(a)), __double2float_ru(__dsub_ru(x.ub, x.lb))));
         }
-        mn[v] = fma(e.a, lo, mn[v]);
-        mx[v] = fma(e.a, hi, mx[v]);
-        mr[v] = fmaxf(mr[v], w);
+        mn[v] = fma(a, lo, mn[v]);
+        mx[v] = fma(a, hi, mx[v]);
       }
     }
   }
@@ -710,7 +709,8 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
 {
   constexpr int kLongWarps = kBaseWarps;  // (shadows the generic kernels' constant on purpose)
   __shared__ RowAct red[V][kLongWarps][32];
-  __shared__ StgB stageB[kLongWarps][32];
+  __shared__ double2 stageA[kLongWarps][32];
+  __shared__ double stageH[kLongWarps][32];
   __shared__ int stageJ[kLongWarps][32];
   __shared__ unsigned stageM[kLongWarps][V][32];
   const int q = blockIdx.x / p.nLongBt, r = __ldg(&p.longRowsBt[blockIdx.x % p.nLongBt]);
@@ -744,10 +744,10 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
     mx[v] = 0.0;
     mr[v] = 0.f;
   }
-  bt_walk_sum_base_multi<1, V>(p, src, strideB, dm, wb, min(we, max(wb, ksplit)), lane, stageB[warp], stageJ[warp],
-    stageM[warp], mn, mx, mr, mrBase);
-  bt_walk_sum_base_multi<-1, V>(p, src, strideB, dm, max(wb, min(we, ksplit)), we, lane, stageB[warp], stageJ[warp],
-    stageM[warp], mn, mx, mr, mrBase);
+  bt_walk_sum_base_multi<1, V>(p, src, strideB, dm, wb, min(we, max(wb, ksplit)), lane, stageA[warp], stageH[warp],
+    stageJ[warp], stageM[warp], mn, mx, mr, mrBase);
+  bt_walk_sum_base_multi<-1, V>(p, src, strideB, dm, max(wb, min(we, ksplit)), we, lane, stageA[warp], stageH[warp],
+    stageJ[warp], stageM[warp], mn, mx, mr, mrBase);
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     RowAct ra = { mn[v], mx[v], static_cast<double>(fmaxf(mr[v], mrBase)), 0, 0 };
@@ -776,7 +776,7 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
     // (every warp holds the same plans, so they all take the same branch; the walk itself only needs the warp)
     if (__any_sync(0xffffffffu, pl.sideU || pl.sideL)) {
       BtLogSink sink = BtSinkFor<true>::make(p, cur, g, b, lane);
-      bt_walk_tighten<true>(p, src[v], strideB, dm[v], wb, we, lane, reinterpret_cast<Stg *>(stageB[warp]), pl, sink);
+      bt_walk_tighten<true>(p, src[v], strideB, dm[v], wb, we, lane, reinterpret_cast<Stg *>(stageA[warp]), pl, sink);
     }
   }
 }
@@ -789,7 +789,8 @@ __global__ void __launch_bounds__(kBaseWarps * 32, CBP_BASE_MINB) bt_rows_long_b
 template <int V>
 __global__ void __launch_bounds__(kThreads, CBP_SHORT_MINB) bt_rows_short_base_kernel(const BtParams p, int cur)
 {
-  __shared__ StgB stageB[kWarps][32];
+  __shared__ double2 stageA[kWarps][32];
+  __shared__ double stageH[kWarps][32];
   __shared__ int stageJ[kWarps][32];
   __shared__ unsigned stageM[kWarps][V][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -823,8 +824,8 @@ __global__ void __launch_bounds__(kThreads, CBP_SHORT_MINB) bt_rows_short_base_k
     mx[v] = 0.0;
     mr[v] = 0.f;
   }
-  bt_walk_sum_base_multi<0, V>(p, src, strideB, dm, kb, ke, lane, stageB[warp], stageJ[warp], stageM[warp], mn, mx, mr,
-    mrBase);
+  bt_walk_sum_base_multi<0, V>(p, src, strideB, dm, kb, ke, lane, stageA[warp], stageH[warp], stageJ[warp],
+    stageM[warp], mn, mx, mr, mrBase);
   const double rl = __ldg(&p.rowLB[r]), ru = __ldg(&p.rowUB[r]);
 #pragma unroll
   for (int v = 0; v < V; ++v) {
@@ -845,7 +846,7 @@ __global__ void __launch_bounds__(kThreads, CBP_SHORT_MINB) bt_rows_short_base_k
       atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[r]));
     if (__any_sync(0xffffffffu, pl.sideU || pl.sideL)) {
       BtLogSink sink = BtSinkFor<true>::make(p, cur, g, b, lane);
-      bt_walk_tighten<true>(p, src[v], strideB, dm[v], kb, ke, lane, reinterpret_cast<Stg *>(stageB[warp]), pl, sink);
+      bt_walk_tighten<true>(p, src[v], strideB, dm[v], kb, ke, lane, reinterpret_cast<Stg *>(stageA[warp]), pl, sink);
     }
   }
 }
