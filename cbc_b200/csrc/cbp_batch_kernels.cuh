@@ -11,6 +11,14 @@
 // accumulates its own vector's activities sequentially in CSR order — bit for bit the order of
 // the CPU restatement.  Two bound buffers give Jacobi rounds; accepted candidates are atomic
 // min/max on the other buffer plus a mark per (column, vector).
+//
+// Two forms of the bounds.  Classic: both buffers hold every cell (dense batches, bases that need R11).
+// Overlay (base + diffs batches): baseX[n] holds the shared base bounds, dmask[G][n] says which
+// vectors of a group have a cell of their own at a column, and only those cells of the two buffers are
+// valid; a round reads "base unless masked", collects its candidates in a list, creates the cells the
+// list touches for the first time, applies the list, and settles / carries on the marks as in the
+// classic form.  The overlay kernels carry several vector groups per warp: what they read per
+// nonzero comes from one shared-memory entry staged by one lane.
 #pragma once
 #include "cbp_device.cuh"
 
@@ -50,8 +58,8 @@ struct BtParams {
   unsigned *logCount;
   unsigned logCap;
   int *groupFlag;  // [G] this group has candidates or R11 changes
-  // first round of a base+diffs batch run "from the base": a vector's bounds are the shared base bounds
-  // except at the few columns its diffs touch; those cells alone have been written to X[0]
+  // overlay form of a base+diffs batch: a vector's bounds are the shared base bounds except at the columns
+  // its diffs or accepted candidates have touched; those cells alone are valid in X[0] / X[1]
   const Bnd *baseX;       // [n]
   const unsigned *dmask;  // [G][n] which vectors of the group differ from the base at column j
   Scal s;
@@ -595,7 +603,7 @@ __global__ void __launch_bounds__(kLongWarps * 32, 2048 / (kLongWarps * 32) / 2)
     pl, sink);
 }
 
-// First round from the base, long rows, no infinite bound in the batch: the walk above with V vector
+// Overlay rounds, long rows, no infinite bound in the batch: the walk above with V vector
 // groups per warp.  What limits that walk is not arithmetic but the shared-memory broadcast: an entry is
 // two 16-byte reads that are handed to all 32 lanes (512 bytes of register writes each, 128 bytes per
 // clock and SM), two DFMAs behind them.  With V groups per warp every lane carries V vectors' sums and the
@@ -1007,7 +1015,7 @@ __global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double
     X1[i] = x;
 }
 
-// interleaved copy of the base bounds for the first round "from the base"
+// interleaved copy of the base bounds for the overlay form
 __global__ void bt_base_pack_kernel(const double *__restrict__ baseLb, const double *__restrict__ baseUb, int n,
   Bnd *baseX)
 {
@@ -1072,7 +1080,7 @@ __global__ void bt_copy_groups_kernel(const BtParams p, const int *__restrict__ 
   p.X[1][i] = p.X[0][i];
 }
 
-// round 0's candidate list, applied to the (now valid) second buffer exactly as the direct sink would
+// a list round's candidates, applied to the target buffer exactly as the direct sink would
 __global__ void bt_apply_log_kernel(const BtParams p, unsigned count, int cur)
 {
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
