@@ -430,13 +430,15 @@ def main():
         # touch instead of 32 n B bytes of per-vector bounds, so the §8d byte count is not a lower bound for
         # it and `frac` can exceed 1.  What limits the kernel instead is the shared-memory broadcast of the
         # staged entries: 24 B per (nonzero, 4 vector groups) handed to 32 lanes at 128 B per clock and SM.
-        roofline["kernel"] = "bt_rows_long_base_kernel + bt_rows_kernel<base> (first round, from the base bounds)"
+        roofline["kernel"] = "bt_rows_long_base_kernel + bt_rows_short_base_kernel (a round in overlay form)"
         props = torch.cuda.get_device_properties(local)
         smem_peak = props.multi_processor_count * 128.0 * (clk.summary().get("sm_mhz") or 1965) * 1e6 / 1e9
         pairs = inst.nnz * ((work["B"] + 127) // 128) * round_launches
         smem_bytes = pairs * 24.0 * 32.0
-        roofline["note"] = ("first round runs from the shared base bounds: per-vector bounds are not read, the "
-                            "SURVEY 8d byte model does not bound this kernel; limiter is shared-memory broadcast")
+        roofline["note"] = ("overlay form: the round reads the shared base bounds plus the cells diffs / candidates have "
+                            "touched, per-vector bounds are never materialised, so the SURVEY 8d byte model does not bound "
+                            "this kernel (traffic = measured DRAM bytes per launch); limiters are the shared-memory "
+                            "broadcast of the staged entries and the FP64 pipe")
         roofline["smem_broadcast"] = {"achieved": smem_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0,
                                       "peak": smem_peak, "unit": "GB/s",
                                       "frac": (smem_bytes / (kernel_ms * 1e-3) / 1e9) / smem_peak if kernel_ms > 0 else 0.0}
