@@ -156,7 +156,7 @@ def cpu_run(work, threads, target_seconds, max_vectors=None):
         r, _, _ = O.propagate(prob, work["lb"], work["ub"])
         dt = time.perf_counter() - t0
         return dict(units=inst.nnz * r["rounds"], seconds=dt, sample=f"whole instance, {r['rounds']} rounds",
-                    threads=1)
+                    threads=1, results=r)
     s, v, b = work["deltas"]
     B = len(s) - 1
     # calibrate on a few vectors, then size the sample for ~target_seconds
@@ -173,7 +173,7 @@ def cpu_run(work, threads, target_seconds, max_vectors=None):
                                         threads=threads, want_bounds=False)
     dt = time.perf_counter() - t0
     return dict(units=inst.nnz * int(res["rounds"].sum()), seconds=dt,
-                sample=f"first {k} of {B} vectors of the same batch", threads=threads)
+                sample=f"first {k} of {B} vectors of the same batch", threads=threads, results=res)
 
 
 def run_reference(args, rank, world):
@@ -343,6 +343,7 @@ def main():
 
     # ---- end to end through the C ABI with HOST buffers (copies inside the timed region)
     e2e_steps = max(2, min(args.steps, 5))
+    last_result = [None]  # what the last end-to-end call returned (compared with the CPU leg below)
     if batch:
         # the step's inputs live in pinned host memory (numpy views of pinned torch tensors)
         def pinned(a, dt):
@@ -352,6 +353,7 @@ def main():
 
         def e2e_step():
             res, us, uc, ul, uu = mat.propagate_batch_delta(lb_h, ub_h, s_h, v_h, b_h)
+            last_result[0] = res
             return int(res["rounds"].sum()), uc.size
         h2d = 16 * inst.n + 8 * (len(s)) + 12 * len(v)
     elif world > 1 and args.rowshard == "peer":
@@ -384,6 +386,7 @@ def main():
             lb_pin.copy_(lb_pin0)
             ub_pin.copy_(ub_pin0)
             r = mat.propagate_ptrs(lb_pin.data_ptr(), ub_pin.data_ptr())
+            last_result[0] = r
             return r["rounds"], 0
         h2d = 16 * inst.n
     e2e_step()
@@ -473,6 +476,17 @@ def main():
         c = cpu_run(work, 1, 12.0)
         line["cpu_baseline"] = {"value": c["units"] / c["seconds"], "unit": UNIT, "cores": 1, "kind": "port",
                                 "sample": c["sample"]}
+        # the CPU leg's verdicts on its sample against what the CUDA path returned for the same vectors
+        keys = ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason")
+        g, o = last_result[0], c.get("results")
+        if g is not None and o is not None:
+            if batch:
+                k = len(o)
+                bad = sum(int(np.count_nonzero(np.asarray(g[key][:k]) != np.asarray(o[key]))) for key in keys)
+                line["cpu_baseline"]["agrees_with_gpu"] = {"vectors": k, "mismatches": bad}
+            else:
+                bad = sum(int(g[key] != o[key]) for key in ("feasible", "rounds", "nChanged", "stopReason"))
+                line["cpu_baseline"]["agrees_with_gpu"] = {"vectors": 1, "mismatches": bad}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
