@@ -254,7 +254,7 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
     mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
-    mat->bt.dBnd };
+    mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX };
   for (void *p : ptrs)
     if (p)
       cudaFree(p);
