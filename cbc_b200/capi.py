@@ -310,9 +310,9 @@ class Matrix:
         start = np.zeros(B + 1, np.int64)
         cap = int(upd_cap) if upd_cap is not None else max(1024, 4 * B)
         while True:
-            col = np.zeros(cap, np.int32)
-            lb = np.zeros(cap)
-            ub = np.zeros(cap)
+            col = np.empty(cap, np.int32)  # (only the first start[B] entries are written and returned)
+            lb = np.empty(cap)
+            ub = np.empty(cap)
             rc = self.ctx.lib.cbp_batch_fetch(self.h, _ptr(res), cap, _ptr(start), _ptr(col), _ptr(lb), _ptr(ub), 0)
             if rc == ERR_CAPACITY and upd_cap is None:
                 cap = int(start[B])
