@@ -185,7 +185,13 @@ def run_reference(args, rank, world):
     from oracle import oracle_py as O
 
     work = make_workload(args.workload, 0, args.scale)
-    threads = O.max_threads() if work["kind"] == "batch" else 1
+    # all the cores this process may run on — not omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1
+    # to the ranks it starts, which would silently make this arm single-threaded at N > 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    threads = max(cores, O.max_threads()) if work["kind"] == "batch" else 1
     per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         cpu_run(work, threads, per_step / 4)
