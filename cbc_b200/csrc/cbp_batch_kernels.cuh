@@ -1008,8 +1008,8 @@ __global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double
     return;
   const int j = static_cast<int>((i / W) % n);
   Bnd x;
-  x.lb = __ldg(&baseLb[j]);
-  x.ub = __ldg(&baseUb[j]);
+  x.lb = __ldg(&baseLb[j]) + 0.0;  // (no -0.0 in the bound arrays)
+  x.ub = __ldg(&baseUb[j]) + 0.0;
   X0[i] = x;
   if (X1)  // null: the second buffer is built later, only for the groups that need it
     X1[i] = x;
@@ -1022,8 +1022,8 @@ __global__ void bt_base_pack_kernel(const double *__restrict__ baseLb, const dou
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j < n) {
     Bnd x;
-    x.lb = baseLb[j];
-    x.ub = baseUb[j];
+    x.lb = baseLb[j] + 0.0;  // (no -0.0 in the bound arrays)
+    x.ub = baseUb[j] + 0.0;
     baseX[j] = x;
   }
 }
@@ -1096,6 +1096,14 @@ __global__ void bt_apply_log_kernel(const BtParams p, unsigned count, int cur)
   atomicOr(&p.dirty[cur][bt_word(p, j, e.b >> 5)], 1u << (e.b & 31));
 }
 
+// device-pointer batches: is every diff's column inside the matrix?  (host-pointer batches are checked on the host)
+__global__ void bt_delta_check_kernel(const unsigned *__restrict__ var, long long count, int n, int *bad)
+{
+  const long long k = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (k < count && diff_col(var[k]) >= n)
+    *bad = 1;
+}
+
 // node bound diffs, applied in order inside a vector (one thread per vector).
 // With cellPrepass the touched cells also get R11 here (the fast path, taken
 // when no base column needs R11, so untouched cells are already final).
@@ -1109,7 +1117,9 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
   unsigned *dmaskW = const_cast<unsigned *>(p.dmask);  // lazy == 2: nothing has been expanded, cells are the base
   for (long long k = k0; k < k1; ++k) {                // bounds until this vector's diffs touch them
     const unsigned v = var[k];
-    const int jv = static_cast<int>(v & 0x7fffffffu);
+    const int jv = diff_col(v);
+    if (jv >= p.n)  // (rejected when the batch was loaded; never index past the arrays)
+      continue;
     const size_t at = bt_cell(p, jv, b);
     Bnd x;
     if (lazy == 2) {
@@ -1121,10 +1131,11 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
     } else {
       x = p.X[0][at];
     }
-    if (v & 0x80000000u)
-      x.ub = bnd[k];
+    // (-0.0 never enters the bound arrays: the integer-ordered atomics rely on it)
+    if (v & kDiffUpper)
+      x.ub = bnd[k] + 0.0;
     else
-      x.lb = bnd[k];
+      x.lb = bnd[k] + 0.0;
     p.X[0][at] = x;
     if (lazy != 1)  // (overlay form: a touched cell is valid in both buffers)
       p.X[1][at] = x;
@@ -1132,7 +1143,9 @@ __global__ void bt_delta_kernel(const long long *__restrict__ start, const unsig
   if (!cellPrepass)
     return;
   for (long long k = k0; k < k1; ++k) {
-    const int j = static_cast<int>(var[k] & 0x7fffffffu);
+    const int j = diff_col(var[k]);
+    if (j >= p.n)
+      continue;
     const size_t at = bt_cell(p, j, b);
     Bnd x = p.X[0][at];
     const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);
@@ -1160,8 +1173,11 @@ __global__ void bt_delta_unmask_kernel(const long long *__restrict__ start, cons
   if (b >= B)
     return;
   unsigned *dmaskW = const_cast<unsigned *>(p.dmask);
-  for (long long k = start[b]; k < start[b + 1]; ++k)
-    atomicAnd(&dmaskW[bt_word(p, static_cast<int>(var[k] & 0x7fffffffu), b >> 5)], ~(1u << (b & 31)));
+  for (long long k = start[b]; k < start[b + 1]; ++k) {
+    const int j = diff_col(var[k]);
+    if (j < p.n)
+      atomicAnd(&dmaskW[bt_word(p, j, b >> 5)], ~(1u << (b & 31)));
+  }
 }
 
 // dense input, B x n row-major per vector -> slice-major cells; 32x32 tiles
@@ -1174,8 +1190,8 @@ __global__ void bt_transpose_in_kernel(const double *__restrict__ lb, const doub
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
     const int b = b0 + i, j = j0 + threadIdx.x;
     const bool ok = b < B && j < n;
-    tl[i][threadIdx.x] = ok ? lb[static_cast<size_t>(b) * n + j] : padLb;
-    tu[i][threadIdx.x] = ok ? ub[static_cast<size_t>(b) * n + j] : padUb;
+    tl[i][threadIdx.x] = (ok ? lb[static_cast<size_t>(b) * n + j] : padLb) + 0.0;  // (no -0.0 in the bound arrays)
+    tu[i][threadIdx.x] = (ok ? ub[static_cast<size_t>(b) * n + j] : padUb) + 0.0;
   }
   __syncthreads();
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {

@@ -92,6 +92,13 @@ constexpr int kColMask = 0x7fffffff;
 __device__ __forceinline__ int col_of(int packed) { return packed & kColMask; }
 __device__ __forceinline__ bool col_is_int(int packed) { return packed < 0; }
 
+// Node bound diffs arrive in CbcPartialNodeInfo's encoding (/root/reference/src/CbcPartialNodeInfo.cpp:139,196,
+// 208,220): bit 31 = upper bound, bit 30 = "can go odd way" (a flag applyBounds() sets, not part of the column),
+// bits 0-29 = column.
+constexpr unsigned kDiffUpper = 0x80000000u;
+constexpr unsigned kDiffColMask = 0x3fffffffu;
+__host__ __device__ __forceinline__ int diff_col(unsigned v) { return static_cast<int>(v & kDiffColMask); }
+
 // atomic max / min on doubles through the integer atomics (no -0.0 is ever
 // stored: R7 adds +0.0).  For v >= 0 signed-int order equals double order and
 // any negative double is a negative int; for v < 0 unsigned order is reversed
@@ -385,11 +392,13 @@ __device__ __forceinline__ void warp_reduce(RowAct &r)
     o.minAct = shfl_xor_f64(r.minAct, m);
     o.maxAct = shfl_xor_f64(r.maxAct, m);
     o.maxRange = shfl_xor_f64(r.maxRange, m);
-    const int packed = __shfl_xor_sync(0xffffffffu, (r.infMax << 16) | r.infMin, m);
-    o.infMin = packed & 0xffff;
-    o.infMax = packed >> 16;
+    o.infMin = 0;
+    o.infMax = 0;
     combine(r, o);
   }
+  // the counters as whole ints (a lane may hold thousands: rows of any length come through here)
+  r.infMin = __reduce_add_sync(0xffffffffu, r.infMin);
+  r.infMax = __reduce_add_sync(0xffffffffu, r.infMax);
 }
 
 // ---- TMA (bulk async copy) + mbarrier wrappers ------------------------------

@@ -1143,6 +1143,25 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
   }
   if (nDelta < 0 || (nDelta > 0 && (!deltaVar || !deltaBound)))
     return CBP_ERR_ARG;
+  // every diff must name a column of this matrix (bits 30 and 31 are flags, CbcPartialNodeInfo.cpp:139,208)
+  if (!(flags & CBP_FLAG_DEVICE_PTRS)) {
+    for (long long k = 0; k < nDelta; ++k)
+      if (diff_col(deltaVar[k]) >= mat->n) {
+        ctx->err = "cbp_batch_load_delta: a bound diff names a column outside the matrix";
+        return CBP_ERR_ARG;
+      }
+  } else if (nDelta > 0) {
+    int bad = 0;
+    CK(cudaMemsetAsync(mat->dRes, 0, sizeof(int), ctx->stream));
+    bt_delta_check_kernel<<<cdiv(nDelta, 256), 256, 0, ctx->stream>>>(deltaVar, nDelta, mat->n, mat->dRes);
+    ++ctx->stats.kernelLaunches;
+    CK(cudaMemcpyAsync(&bad, mat->dRes, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (bad) {
+      ctx->err = "cbp_batch_load_delta: a bound diff names a column outside the matrix";
+      return CBP_ERR_ARG;
+    }
+  }
   if (static_cast<size_t>(nDelta) > bt.capDelta || !bt.dStart) {
     void *old[] = { bt.dVar, bt.dBnd };
     for (void *p : old)

@@ -72,6 +72,7 @@ void *na_scratch_for_current_device()
 struct NaSink {
   double *lbOut, *ubOut;
   unsigned *dirty;
+  int *res;
   __device__ __forceinline__ void mark(int j) { atomicOr(&dirty[j >> 5], 1u << (j & 31)); }
   __device__ __forceinline__ void ub(int j, double v)
   {
@@ -87,7 +88,7 @@ struct NaSink {
 
 // The shared array still holds whatever the previous call left in it: copy
 // this call's round-start bounds in, and zero the marks and counters.
-__global__ void na_prepare_kernel(const double *__restrict__ lb, const double *__restrict__ ub, int n,
+__global__ void na_prepare_kernel(double *lb, double *ub, int n,
   Bnd *src, unsigned *dirty, int nWords, int *res)
 {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -96,6 +97,12 @@ __global__ void na_prepare_kernel(const double *__restrict__ lb, const double *_
     b.lb = lb[j];
     b.ub = ub[j];
     src[j] = b;
+    // the atomics below order doubles by their bit patterns and take -0.0 for the smallest negative
+    // number: the caller's arrays are the atomics' target here, so a -0.0 in them becomes +0.0
+    if (b.lb == 0.0)
+      lb[j] = 0.0;
+    if (b.ub == 0.0)
+      ub[j] = 0.0;
   }
   if (j < nWords)
     dirty[j] = 0u;
@@ -106,7 +113,7 @@ __global__ void na_prepare_kernel(const double *__restrict__ lb, const double *_
 // Variant of sv_singleton_kernel that reads the caller's row-major matrix as
 // it is (no re-tiled copy exists here): one thread per row; a row takes part
 // iff exactly one of its coefficients is nonzero.
-__global__ void na_singleton_rows_kernel(int m, const long long *__restrict__ rowStart,
+__global__ void na_singleton_rows_kernel(int m, int n, const long long *__restrict__ rowStart,
   const int *__restrict__ rowLen, const int *__restrict__ colIdx, const double *__restrict__ val,
   const char *__restrict__ rowSense, const double *__restrict__ rhs, const double *__restrict__ range,
   const char *__restrict__ colType, const Bnd *__restrict__ src, NaSink sink, Scal s)
@@ -135,6 +142,10 @@ __global__ void na_singleton_rows_kernel(int m, const long long *__restrict__ ro
     return;
   const double a = val[at];
   const int j = colIdx[at];
+  if (j < 0 || j >= n) {  // a column index outside the problem: report it, touch nothing
+    atomicAdd(&sink.res[3], 1);
+    return;
+  }
   const Bnd b = src[j];
   const bool isInt = colType && colType[j] != 0;
   if (ru < s.inf) {
@@ -151,7 +162,7 @@ __global__ void na_singleton_rows_kernel(int m, const long long *__restrict__ ro
   }
 }
 
-// R9 on the marked columns; res[0] changed, res[1] fixed, res[2] crossing
+// R9 on the marked columns; res[0] changed, res[1] fixed, res[2] crossing (res[3]: column indices out of range)
 __global__ void na_settle_kernel(const Bnd *__restrict__ src, double *lb, double *ub,
   const unsigned *__restrict__ dirty, int n, int *res, Scal s)
 {
@@ -211,8 +222,8 @@ extern "C" int cbp_singletons_noalloc(int m, int n, const int64_t *rowStart, con
   const int T = 256;
   na_prepare_kernel<<<(n + T - 1) / T, T, 0, st>>>(lb, ub, n, src, dirty, nWords, res);
   if (m > 0) {
-    NaSink sink = { lb, ub, dirty };
-    na_singleton_rows_kernel<<<(m + T - 1) / T, T, 0, st>>>(m, reinterpret_cast<const long long *>(rowStart),
+    NaSink sink = { lb, ub, dirty, res };
+    na_singleton_rows_kernel<<<(m + T - 1) / T, T, 0, st>>>(m, n, reinterpret_cast<const long long *>(rowStart),
       rowLen, colIdx, val, rowSense, rhs, range, colType, src, sink, s);
     na_settle_kernel<<<(n + T - 1) / T, T, 0, st>>>(src, lb, ub, dirty, n, res, s);
   }
@@ -222,7 +233,7 @@ extern "C" int cbp_singletons_noalloc(int m, int n, const int64_t *rowStart, con
     e = cudaMemcpyAsync(h, res, sizeof(h), cudaMemcpyDeviceToHost, st);
   if (e == cudaSuccess)
     e = cudaStreamSynchronize(st);
-  if (e == cudaSuccess && h[2] > 0) {
+  if (e == cudaSuccess && (h[2] > 0 || h[3] > 0)) {
     na_restore_kernel<<<(n + T - 1) / T, T, 0, st>>>(src, lb, ub, n);
     e = cudaGetLastError();
     if (e == cudaSuccess)
@@ -231,6 +242,10 @@ extern "C" int cbp_singletons_noalloc(int m, int n, const int64_t *rowStart, con
   if (e != cudaSuccess) {
     fprintf(stderr, "cbp_singletons_noalloc: %s\n", cudaGetErrorString(e));
     return CBP_ERR_CUDA;
+  }
+  if (h[3] > 0) {
+    fprintf(stderr, "cbp_singletons_noalloc: %d singleton rows name a column outside [0, %d)\n", h[3], n);
+    return CBP_ERR_ARG;
   }
   if (h[2] > 0) {
     *nTightened = -1;

@@ -915,7 +915,7 @@ __global__ void sv_prepare_kernel(const double *__restrict__ lb, const double *_
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n)
     return;
-  double l = lb[j], u = ub[j];
+  double l = lb[j] + 0.0, u = ub[j] + 0.0;  // (no -0.0 in the bound arrays: the integer-ordered atomics rely on it)
   const int r = doPrepass ? prepass_col(l, u, colType[j] != 0, s) : 0;
   if (r == 2)
     atomicMin(&st->infeasCol, j);

@@ -345,6 +345,8 @@ def power_law(n=1_000_000, nnz_target=5_000_000, n_dense=8, dense_len=100_000, a
 # /root/reference/src/CbcNode.cpp:265-273 (column | 0x80000000 = upper bound)
 # --------------------------------------------------------------------------
 UPPER_FLAG = np.uint32(0x80000000)
+ODD_WAY_FLAG = np.uint32(0x40000000)  # set by CbcPartialNodeInfo::applyBounds (src/CbcPartialNodeInfo.cpp:208,220); not part of the column
+COL_MASK = np.uint32(0x3FFFFFFF)      # the column is `variable & 0x3fffffff` (src/CbcPartialNodeInfo.cpp:139,196)
 
 
 def strong_branch_deltas(inst, lb, ub, n_candidates, seed=SEED0 + 11):
@@ -413,7 +415,7 @@ def expand_deltas(lb, ub, start, var, bnd):
     L = np.repeat(lb[None, :], B, axis=0)
     U = np.repeat(ub[None, :], B, axis=0)
     b = np.repeat(np.arange(B), np.diff(start))
-    j = (var & np.uint32(0x7FFFFFFF)).astype(np.int64)
+    j = (var & COL_MASK).astype(np.int64)
     isU = (var & UPPER_FLAG) != 0
     # later deltas of the same vector win: apply in order
     for k in np.flatnonzero(isU):
@@ -580,4 +582,14 @@ def micro(name):
                         np.array([ord("L"), ord("E")], np.uint8), np.array([3.0, 0.0]), np.zeros(2),
                         np.array([2, 0], np.int8), np.full(2, -inf), np.full(2, inf), inf,
                         np.array([1.0, 1.0]))
+    if name == "infeasible_preprocess":  # test/CInterfaceTest.c:261-326 (8 binaries a..h, 14 rows, infeasible only by search)
+        rows = [(1, 2, 5, 6), (0, 3, 4, 7), (0, 1), (2, 3), (4, 5), (6, 7), (0, 2), (1, 3), (2, 4), (3, 5), (4, 6),
+                (5, 7), (0, 6), (1, 7)]
+        start = np.zeros(15, np.int64)
+        np.cumsum([len(r) for r in rows], out=start[1:])
+        col = np.array([j for r in rows for j in r], np.int32)
+        sense = np.frombuffer(b"LLEEEELLLLLLLL", np.uint8).copy()
+        rhs = np.array([3.0, 3, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1])
+        return Instance("infeasible_preprocess", 14, 8, start, col, np.ones(col.size), sense, rhs, np.zeros(14),
+                        np.ones(8, np.int8), np.zeros(8), np.ones(8), inf)
     raise KeyError(name)

@@ -660,8 +660,14 @@ int orc_propagate_batch_delta(const orc_problem *p, const double *baseLb, const 
       memcpy(l, baseLb, sizeof(double) * n);
       memcpy(u, baseUb, sizeof(double) * n);
       for (int64_t k = deltaStart[b]; k < deltaStart[b + 1]; ++k) {
+        /* CbcPartialNodeInfo's encoding (src/CbcPartialNodeInfo.cpp:139,196,208): bit 31 = upper
+         * bound, bit 30 = "can go odd way" flag, bits 0-29 = column */
         const unsigned int v = deltaVar[k];
-        const unsigned int j = v & 0x7fffffffu;
+        const unsigned int j = v & 0x3fffffffu;
+        if (j >= (unsigned int)p->n) {
+          rc = -2;
+          continue;
+        }
         if (v & 0x80000000u)
           u[j] = deltaBound[k];
         else

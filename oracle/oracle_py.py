@@ -195,6 +195,8 @@ def propagate_batch_delta(prob, base_lb, base_ub, delta_start, delta_var, delta_
         _p(delta_bound), C.c_double(tol), C.c_int(max_rounds), C.c_double(time_limit), _p(res),
         _p(lbo), _p(ubo), C.c_int(threads),
     )
+    if rc == -2:
+        raise ValueError("a bound diff names a column outside the matrix")
     assert rc == 0
     return res, lbo, ubo
 

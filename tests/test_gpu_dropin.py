@@ -120,7 +120,7 @@ def test_strong_branching_arms_match_oracle(oracle, tmp_path):
     r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
     inst.lb, inst.ub = lb0, ub0  # node bounds = propagated root
     s, v, b = I.strong_branch_deltas(inst, lb0, ub0, 60, seed=71)
-    cols = (v[0::2] & 0x7FFFFFFF).astype(np.int32)
+    cols = (v[0::2] & 0x3FFFFFFF).astype(np.int32)
     vals = b[0::2] + 0.5  # LP value between the two arms
     ip, op, cp = str(tmp_path / "inst.bin"), str(tmp_path / "out.bin"), str(tmp_path / "cands.bin")
     write_instance(inst, ip)

@@ -23,7 +23,7 @@ def test_c2_full_batch_4096_vectors(oracle, gpu_ctx):
     pick = np.concatenate([np.arange(8), np.flatnonzero(res["nChanged"] > 0)[:8], np.flatnonzero(res["feasible"] == 0)[:4]])
     for k in pick:
         lb, ub = lb0.copy(), ub0.copy()
-        j = int(v[k] & 0x7FFFFFFF)
+        j = int(v[k] & 0x3FFFFFFF)
         if v[k] & 0x80000000:
             ub[j] = b[k]
         else:

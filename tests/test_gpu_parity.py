@@ -333,3 +333,81 @@ def test_fixpoint_is_idempotent_at_size(gpu_ctx):
     assert r2["rounds"] == 1 and r2["nChanged"] == 0
     assert np.array_equal(l1, l2) and np.array_equal(u1, u2)
     mat.close()
+
+
+def test_diff_encoding_flags_and_range(oracle, gpu_ctx):
+    """Bound diffs come in CbcPartialNodeInfo's encoding: bit 31 = upper bound, bit 30 = the 'can go odd way' flag
+    applyBounds() sets (/root/reference/src/CbcPartialNodeInfo.cpp:139,196,208,220) — not part of the column.  A diff
+    that names a column outside the matrix is refused, on the host path and on the device-pointer path alike."""
+    import torch
+
+    inst = I.knapsack_assignment(m=600, n=1500, seed=41)
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 40, max_depth=12, seed=42)
+    flagged = v.copy()
+    flagged[::3] |= I.ODD_WAY_FLAG
+    mat = capi.Matrix(gpu_ctx, inst)
+    r0 = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)
+    r1 = mat.propagate_batch_delta(inst.lb, inst.ub, s, flagged, b)
+    for a, c in zip(r0, r1):
+        assert np.array_equal(a, c) if a.dtype.names is None else all(
+            np.array_equal(a[k], c[k]) for k in ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol"))
+    ores, _, _ = oracle.propagate_batch_delta(oracle.Problem(inst), inst.lb, inst.ub, s, flagged, b, want_bounds=False)
+    for k in ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason"):
+        assert np.array_equal(r1[0][k], ores[k]), k
+    bad = v.copy()
+    bad[5] = np.uint32(inst.n + 7) | I.UPPER_FLAG
+    with pytest.raises(capi.CbpError):
+        mat.batch_load_delta(inst.lb, inst.ub, s, bad, b)
+    with pytest.raises(ValueError):
+        oracle.propagate_batch_delta(oracle.Problem(inst), inst.lb, inst.ub, s, bad, b, want_bounds=False)
+    # the same through device pointers
+    dl, du = torch.tensor(inst.lb, device="cuda"), torch.tensor(inst.ub, device="cuda")
+    ds = torch.tensor(s, device="cuda")
+    dv = torch.tensor(bad.astype(np.int64), device="cuda").to(torch.int32) if False else torch.tensor(
+        bad.view(np.int32), device="cuda")
+    db = torch.tensor(b, device="cuda")
+    rc = gpu_ctx.lib.cbp_batch_load_delta(mat.h, capi._ptr(dl.data_ptr()), capi._ptr(du.data_ptr()), len(s) - 1,
+                                          capi._ptr(ds.data_ptr()), capi._ptr(dv.data_ptr()), capi._ptr(db.data_ptr()),
+                                          capi.FLAG_DEVICE_PTRS)
+    assert rc == -1
+    mat.close()
+
+
+def test_negative_zero_bounds(oracle, gpu_ctx):
+    """-0.0 in the caller's bounds (the bit pattern the integer-ordered atomics would take for the most negative
+    number): a continuous column with ub = -0.0 and lb < 0 whose lower bound is tightened over two rounds."""
+    # x0 in [-8, -0.0] continuous, x1 in [0, 4] integer, x2 in [0, 10] continuous
+    # row 0: x0 + x1 >= -2 ; row 1: 2 x1 <= 3 ; row 2: x2 - x0 <= 2
+    inst = I.Instance("negzero", 3, 3, np.array([0, 2, 3, 5], np.int64), np.array([0, 1, 1, 2, 0], np.int32),
+                      np.array([1.0, 1.0, 2.0, 1.0, -1.0]), np.frombuffer(b"GLL", np.uint8).copy(),
+                      np.array([-2.0, 3.0, 2.0]), np.zeros(3), np.array([0, 2, 0], np.int8),
+                      np.array([-8.0, 0.0, 0.0]), np.array([-0.0, 4.0, 10.0]))
+    (rg, lg, ug), (ro, lo, uo) = _both(oracle, gpu_ctx, inst)
+    assert_same_result(rg, ro, "negzero")
+    assert rg["roundChanged"] == ro["roundChanged"] and rg["nChanged"] >= 3
+    assert_same_bounds(inst.colType, lg, ug, lo, uo, "negzero")
+    assert ug[2] == 2.0 and ug[1] == 1.0
+    # and as a batch (classic form and diffs)
+    mat = capi.Matrix(gpu_ctx, inst)
+    res, L, U = mat.propagate_batch(np.tile(inst.lb, (2, 1)), np.tile(inst.ub, (2, 1)))
+    assert np.array_equal(L[1], lo) and np.array_equal(U[1], uo)
+    res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, np.array([0.0, 4.0, 10.0]), np.array([0, 1], np.int64),
+                                                    np.array([0], np.uint32) | I.UPPER_FLAG, np.array([-0.0]))
+    assert int(res["rounds"][0]) == ro["rounds"] and int(res["nChanged"][0]) == ro["nChanged"]
+    mat.close()
+
+
+def test_row_activity_counters_long_free_row(oracle, gpu_ctx):
+    """One row of 80,000 columns that are free on both sides: both infinite-bound counters must come back as
+    80,000 (a 16-bit packing of the two counters in the warp reduction would wrap)."""
+    n = 80_000
+    inst = I.Instance("longfree", 1, n, np.array([0, n], np.int64), np.arange(n, dtype=np.int32), np.ones(n),
+                      np.frombuffer(b"L", np.uint8).copy(), np.array([5.0]), np.zeros(1), np.zeros(n, np.int8),
+                      np.full(n, -I.COIN_INF), np.full(n, I.COIN_INF))
+    mat = capi.Matrix(gpu_ctx, inst)
+    mn, mx, im, ix = mat.row_activity(inst.lb, inst.ub)
+    assert (int(im[0]), int(ix[0])) == (n, n) and mn[0] == 0.0 and mx[0] == 0.0
+    r, lb, ub = mat.propagate(inst.lb, inst.ub)
+    ro, lo, uo = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    assert_same_result(r, ro, "longfree")
+    mat.close()

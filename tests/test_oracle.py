@@ -115,3 +115,23 @@ def test_mps_round_trip(tmp_path, oracle):
     ra, la, ua = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
     rb, lb_, ub_ = oracle.propagate(oracle.Problem(back), back.lb, back.ub)
     assert ra["rounds"] == rb["rounds"] and np.array_equal(la, lb_) and np.array_equal(ua, ub_)
+
+
+def test_diff_encoding_flags_and_range(oracle):
+    # CbcPartialNodeInfo's encoding (src/CbcPartialNodeInfo.cpp:139,196,208): bit 31 = upper bound, bit 30 = the
+    # 'can go odd way' flag, bits 0-29 = column; a column outside the matrix is an error, not a wild write
+    inst = I.knapsack_assignment(m=400, n=1000, seed=11)
+    p = oracle.Problem(inst)
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 12, max_depth=10, seed=12)
+    flagged = v.copy()
+    flagged[::2] |= I.ODD_WAY_FLAG
+    r1, l1, u1 = oracle.propagate_batch_delta(p, inst.lb, inst.ub, s, v, b)
+    r2, l2, u2 = oracle.propagate_batch_delta(p, inst.lb, inst.ub, s, flagged, b)
+    assert np.array_equal(l1, l2) and np.array_equal(u1, u2) and np.array_equal(r1["rounds"], r2["rounds"])
+    L, U = I.expand_deltas(inst.lb, inst.ub, s, flagged, b)
+    L0, U0 = I.expand_deltas(inst.lb, inst.ub, s, v, b)
+    assert np.array_equal(L, L0) and np.array_equal(U, U0)
+    bad = v.copy()
+    bad[3] = np.uint32(inst.n) | I.UPPER_FLAG
+    with pytest.raises(ValueError):
+        oracle.propagate_batch_delta(p, inst.lb, inst.ub, s, bad, b)

@@ -52,13 +52,17 @@ def _instances():
     return a, b
 
 
-def test_noalloc_matches_allocating_entry_point_twice_in_a_row(gpu_ctx):
+def test_noalloc_matches_allocating_entry_point_twice_in_a_row(gpu_ctx, oracle):
     torch.cuda.set_device(0)
     for inst in _instances():  # two calls in a row, second one on a different problem
         mat = capi.Matrix(gpu_ctx, inst)
         nt_ref, nf_ref, lb_ref, ub_ref = mat.singletons(inst.lb, inst.ub)
         mat.close()
         assert nt_ref > 50 and nf_ref > 5
+        # ... and both are what the CPU oracle gives
+        nt_o, nf_o, lb_o, ub_o = oracle.singletons(oracle.Problem(inst), inst.lb, inst.ub)
+        assert (nt_ref, nf_ref) == (nt_o, nf_o)
+        assert_same_bounds(inst.colType, lb_ref, ub_ref, lb_o, ub_o, "singletons vs oracle")
         d = _device_copy(inst, inst.lb, inst.ub)
         rc, nt, nf = _call(inst, d)
         assert rc == 0
@@ -93,3 +97,12 @@ def test_noalloc_infeasible_leaves_bounds_and_oversize_is_refused(gpu_ctx):
                                        d["lb"].data_ptr(), d["ub"].data_ptr())
     assert rc == capi.ERR_CAPACITY
     assert np.array_equal(d["lb"].cpu().numpy(), inst.lb)
+    # a singleton row that names a column outside the problem: bad argument, bounds left as they came in
+    bad_col = d["col"].clone()
+    bad_col[-2] = inst.n + 3
+    rc, _, _ = capi.singletons_noalloc(inst.m, inst.n, d["rowStart"].data_ptr(), bad_col.data_ptr(),
+                                       d["val"].data_ptr(), d["sense"].data_ptr(), d["rhs"].data_ptr(),
+                                       d["range"].data_ptr(), d["colType"].data_ptr(), inst.inf, d["lb"].data_ptr(),
+                                       d["ub"].data_ptr())
+    assert rc == -1
+    assert np.array_equal(d["lb"].cpu().numpy(), inst.lb) and np.array_equal(d["ub"].cpu().numpy(), inst.ub)
