@@ -31,7 +31,8 @@ class Result(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("kernelLaunches", C.c_int64), ("lastRunMs", C.c_double), ("lastRoundKernelMs", C.c_double),
                 ("lastRoundKernelLaunches", C.c_int), ("lastRoundsTotal", C.c_int64),
-                ("lastFromBase", C.c_int), ("lastGroupsBuilt", C.c_int)]
+                ("lastFromBase", C.c_int), ("lastGroupsBuilt", C.c_int), ("lastMode", C.c_int),
+                ("lastHostSyncs", C.c_int), ("lastPairsWalked", C.c_int64), ("lastItems", C.c_int64)]
 
 
 # every symbol include/cbp_capi.h declares (tests check that the library exports them all)
@@ -135,7 +136,9 @@ class Context:
         return {"kernelLaunches": s.kernelLaunches, "lastRunMs": s.lastRunMs,
                 "lastRoundKernelMs": s.lastRoundKernelMs, "lastRoundKernelLaunches": s.lastRoundKernelLaunches,
                 "lastRoundsTotal": s.lastRoundsTotal, "lastFromBase": s.lastFromBase,
-                "lastGroupsBuilt": s.lastGroupsBuilt}
+                "lastGroupsBuilt": s.lastGroupsBuilt, "lastMode": s.lastMode, "lastHostSyncs": s.lastHostSyncs,
+                "lastPairsWalked": s.lastPairsWalked, "lastItems": s.lastItems,
+                "lastModeName": ("classic", "overlay-full-walk", "worklist")[s.lastMode] if 0 <= s.lastMode < 3 else "?"}
 
     def synchronize(self):
         self.check(self.lib.cbp_synchronize(self.h), "cbp_synchronize")

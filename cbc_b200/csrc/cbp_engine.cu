@@ -17,6 +17,7 @@
 #include "../../include/cbp_capi.h"
 #include "cbp_batch_kernels.cuh"
 #include "cbp_sv_kernels.cuh"
+#include "cbp_wl_kernels.cuh"
 
 using namespace cbp;
 
@@ -27,6 +28,7 @@ struct cbp_ctx {
   bool ownsStream = false;
   int numSMs = 0;
   int svBlocksPerSM[2][2] = {};  // resident CTAs per SM of the persistent kernel, [tile staging][row-sharded]
+  int wlBlocksPerSM = 0;         // ... of the worklist batch kernel
   std::string err;
   cbp_stats stats {};
   cudaEvent_t evA = nullptr, evB = nullptr;
@@ -64,6 +66,14 @@ struct BatchState {
   bool hasInf = true;  // some input bound may be infinite (false only when checked)
   size_t capCells = 0, capDelta = 0, capStart = 0;
   int capBp = 0;
+  // worklist form (cbp_wl_kernels.cuh)
+  WlItem *wlItemsS[2] = { nullptr, nullptr }, *wlItemsL[2] = { nullptr, nullptr };
+  WlCell *wlK = nullptr, *wlCells = nullptr;
+  WlCtl *wlCtl = nullptr;
+  int *wlInts = nullptr;  // vecChanged by round parity [2][Bp], active by round parity [2][G]
+  unsigned wlItemCap = 0, wlCellCap = 0;
+  unsigned wlPrevCells = 0;  // cells the last worklist run left in the masks
+  bool wlMarksKnown = false; // dmask / ever / dirty are all zero except for those cells
 };
 
 struct cbp_matrix {
@@ -88,6 +98,11 @@ struct cbp_matrix {
   double *sellVal = nullptr;
   int *sellCol = nullptr, *sellOff = nullptr, *sliceOrder = nullptr;
   int nSlices = 0, mShort = 0;
+  // column-major copy: rows (kept order) of every column, coefficient beside it
+  int *cscStart = nullptr, *cscRow = nullptr;
+  double *cscVal = nullptr;
+  int firstLongRow = 0;     // kept rows from here on are longer than a tile
+  int eventMaxChanged = 0;  // single vector: rounds after a round that changed at most this many columns are event-driven
   // device, single-vector workspace
   RowAct *longPart = nullptr;
   Bnd *X[2] = { nullptr, nullptr };
@@ -184,6 +199,7 @@ cbp_ctx *cbp_create(int device)
     kSvSmallSmem);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->svBlocksPerSM[0][1], sv_fixpoint_kernel<false, true>, kThreads,
     kSvSmallSmem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->wlBlocksPerSM, bt_worklist_kernel, kThreads, 0);
   if (ctx->svBlocksPerSM[0][0] < 1 || ctx->svBlocksPerSM[0][1] < 1 || ctx->svBlocksPerSM[1][0] < 1
     || ctx->svBlocksPerSM[1][1] < 1) {
     fprintf(stderr, "cbp_create: persistent kernel does not fit on this device\n");
@@ -250,11 +266,13 @@ void cbp_matrix_free(cbp_matrix *mat)
   cudaSetDevice(mat->ctx->device);
   void *ptrs[] = { mat->val, mat->col, mat->tiles, mat->rp, mat->rowLB, mat->rowUB, mat->rowOrig,
     mat->rowNz, mat->rowCnt, mat->rowPos, mat->longRows, mat->colType, mat->singRows, mat->shortRowsBt,
-    mat->longRowsBt, mat->sellVal, mat->sellCol, mat->sellOff, mat->sliceOrder, mat->longPart, mat->X[0],
+    mat->longRowsBt, mat->sellVal, mat->sellCol, mat->sellOff, mat->sliceOrder, mat->cscStart, mat->cscRow, mat->cscVal,
+    mat->longPart, mat->X[0],
     mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
     mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
-    mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX };
+    mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
+    mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts };
   for (void *p : ptrs)
     if (p)
       cudaFree(p);
@@ -505,6 +523,33 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   up(&mat->sliceOrder, hOrder);
   mat->nSlices = static_cast<int>(hSellOff.size()) - 1;
   mat->mShort = static_cast<int>(cls[kShort].size());
+  mat->firstLongRow = static_cast<int>(cls[kShort].size() + cls[kMedium].size());
+  {  // column-major copy of the kept rows (the CSC of north_star's "CSR and CSC copies in HBM")
+    std::vector<int> hCscStart(static_cast<size_t>(n) + 1, 0);
+    for (size_t r = 0; r < mKept; ++r)
+      for (int k = hNz[r]; k < hNz[r] + hCnt[r]; ++k)
+        ++hCscStart[static_cast<size_t>(hCol[k] & kColMask) + 1];
+    for (int j = 0; j < n; ++j)
+      hCscStart[j + 1] += hCscStart[j];
+    std::vector<int> hCscRow(static_cast<size_t>(hCscStart[n]) + 1), fill(hCscStart.begin(), hCscStart.end() - 1);
+    std::vector<double> hCscVal(static_cast<size_t>(hCscStart[n]) + 1);
+    for (size_t r = 0; r < mKept; ++r)
+      for (int k = hNz[r]; k < hNz[r] + hCnt[r]; ++k) {
+        const int at = fill[hCol[k] & kColMask]++;
+        hCscRow[at] = static_cast<int>(r);
+        hCscVal[at] = hVal[k];
+      }
+    up(&mat->cscStart, hCscStart);
+    up(&mat->cscRow, hCscRow);
+    up(&mat->cscVal, hCscVal);
+    // Event-driven rounds pay off while (changed columns) x (rows per column) x (nonzeros per row) stays a small
+    // part of the matrix: changed <= n m / (64 nnz) (measured on the 1M x 1M mixed instance: below ~1,500 changed
+    // columns the event-driven round beats the full scan).  CBP_EVENT_DIV replaces the 64 (0: never event-driven).
+    static const double evDiv = getenv("CBP_EVENT_DIV") ? atof(getenv("CBP_EVENT_DIV")) : 64.0;
+    mat->eventMaxChanged = (evDiv > 0.0 && nnzKept > 0)
+      ? static_cast<int>(std::min<double>(static_cast<double>(n) * static_cast<double>(mKept) / (evDiv * static_cast<double>(nnzKept)), 1.0e9))
+      : 0;
+  }
   std::vector<int> hShortBt, hLongBt;
   for (int r = 0; r < static_cast<int>(mKept); ++r)
     (hCnt[r] > kBtLongLen ? hLongBt : hShortBt).push_back(r);
@@ -643,6 +688,12 @@ static SvParams sv_params(cbp_matrix *mat, const SvState &v, const Scal &s, int 
   p.sliceOrder = mat->sliceOrder;
   p.nSlices = mat->nSlices;
   p.mShort = mat->mShort;
+  p.cscStart = mat->cscStart;
+  p.cscRow = mat->cscRow;
+  p.rowNz = mat->rowNz;
+  p.rowCnt = mat->rowCnt;
+  p.firstLongRow = mat->firstLongRow;
+  p.eventMaxChanged = mat->eventMaxChanged;
   p.X[0] = v.X[0];
   p.X[1] = v.X[1];
   p.dirty[0] = v.dirty[0];
@@ -1022,8 +1073,15 @@ static int bt_reserve(cbp_matrix *mat, int B)
   const size_t cells = static_cast<size_t>(mat->n) * Bp;
   if (cells > bt.capCells || Bp > bt.capBp) {
     void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt,
-      bt.log, bt.groupFlag, bt.dmask };
+      bt.log, bt.groupFlag, bt.dmask, bt.wlItemsS[0], bt.wlItemsS[1], bt.wlItemsL[0], bt.wlItemsL[1], bt.wlK, bt.wlCells,
+      bt.wlCtl, bt.wlInts };
     bt.dmask = nullptr;
+    bt.wlItemsS[0] = bt.wlItemsS[1] = bt.wlItemsL[0] = bt.wlItemsL[1] = nullptr;
+    bt.wlK = bt.wlCells = nullptr;
+    bt.wlCtl = nullptr;
+    bt.wlInts = nullptr;
+    bt.wlMarksKnown = false;
+    bt.wlPrevCells = 0;
     for (void *p : old)
       if (p)
         cudaFree(p);
@@ -1037,6 +1095,19 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.capCells = 0;
     bt.capBp = 0;
     const size_t words = cells / 32;
+    // list sizes follow the batch: candidates / changed cells / row items per round
+    const unsigned logCap = static_cast<unsigned>(std::min<size_t>(kBtLogCap, std::max<size_t>(1u << 20, static_cast<size_t>(Bp) * 2048)));
+    bt.wlItemCap = static_cast<unsigned>(std::min<size_t>(1u << 25, std::max<size_t>(1u << 20, static_cast<size_t>(Bp) * 4096)));
+    bt.wlCellCap = static_cast<unsigned>(std::min<size_t>(1u << 25, std::max<size_t>(1u << 20, static_cast<size_t>(Bp) * 1024)));
+    if (getenv("CBP_WL_ITEM_CAP"))  // tests shrink the item lists to exercise the hand-over to the full-walk path
+      bt.wlItemCap = static_cast<unsigned>(std::max<long>(1, atol(getenv("CBP_WL_ITEM_CAP"))));
+    if (dalloc(&bt.wlItemsS[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsS[1], bt.wlItemCap) != cudaSuccess
+      || dalloc(&bt.wlItemsL[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsL[1], bt.wlItemCap) != cudaSuccess
+      || dalloc(&bt.wlK, bt.wlCellCap) != cudaSuccess || dalloc(&bt.wlCells, bt.wlCellCap) != cudaSuccess
+      || dalloc(&bt.wlCtl, 1) != cudaSuccess || dalloc(&bt.wlInts, static_cast<size_t>(Bp) * 2 + static_cast<size_t>(Bp / 32) * 2 + 8) != cudaSuccess) {
+      ctx->err = std::string("batch workspace (worklists): ") + cudaGetErrorString(cudaGetLastError());
+      return CBP_ERR_NOMEM;
+    }
     if (dalloc(&bt.X[0], cells) != cudaSuccess || dalloc(&bt.X[1], cells) != cudaSuccess
       || dalloc(&bt.dirty[0], words) != cudaSuccess || dalloc(&bt.dirty[1], words) != cudaSuccess
       || dalloc(&bt.ever, words) != cudaSuccess || dalloc(&bt.active, Bp / 32) != cudaSuccess
@@ -1045,7 +1116,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
       || dalloc(&bt.counts, static_cast<size_t>(Bp) + 1) != cudaSuccess
       || dalloc(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp) != cudaSuccess
       || dalloc(&bt.groupFlag, static_cast<size_t>(Bp / 32) + 2) != cudaSuccess
-      || dalloc(&bt.log, kBtLogCap) != cudaSuccess) {
+      || dalloc(&bt.log, logCap) != cudaSuccess) {
       ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
       return CBP_ERR_NOMEM;
     }
@@ -1053,7 +1124,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.capBp = Bp;
     bt.dirty0Clean = bt.dmaskClean = false;
     // CBP_LOG_CAP: tests shrink the list to exercise the fall-back to the two-buffer first round
-    bt.logCap = getenv("CBP_LOG_CAP") ? std::min<unsigned>(kBtLogCap, static_cast<unsigned>(atol(getenv("CBP_LOG_CAP")))) : kBtLogCap;
+    bt.logCap = getenv("CBP_LOG_CAP") ? std::min<unsigned>(logCap, static_cast<unsigned>(atol(getenv("CBP_LOG_CAP")))) : logCap;
   }
   if (!bt.baseLb) {
     if (dalloc(&bt.baseLb, mat->n) != cudaSuccess || dalloc(&bt.baseUb, mat->n) != cudaSuccess
@@ -1213,6 +1284,97 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
   return CBP_OK;
 }
 
+// A base + diffs batch in worklist form (cbp_wl_kernels.cuh): a few set-up launches, ONE cooperative launch for all
+// rounds, one read-back of the control block.  *status: kWlOk, or why the caller must run the full-walk path instead.
+static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeLimitSec, int *status)
+{
+  cbp_ctx *ctx = mat->ctx;
+  BatchState &bt = mat->bt;
+  cudaStream_t st = ctx->stream;
+  const size_t words = bt.cells / 32;
+  if (!bt.wlMarksKnown) {  // first use, or the full-walk path ran in between: start from empty masks
+    CK(cudaMemsetAsync(bt.dirty[0], 0, sizeof(unsigned) * words, st));
+    CK(cudaMemsetAsync(bt.dirty[1], 0, sizeof(unsigned) * words, st));
+    CK(cudaMemsetAsync(bt.ever, 0, sizeof(unsigned) * words, st));
+    CK(cudaMemsetAsync(bt.dmask, 0, sizeof(unsigned) * words, st));
+    bt.wlPrevCells = 0;
+  }
+  bt.wlMarksKnown = false;  // (until this run has ended in good order)
+  bt.dmaskClean = bt.dirty0Clean = false;
+  WlParams w;
+  w.bt = p;
+  w.cscStart = mat->cscStart;
+  w.cscRow = mat->cscRow;
+  w.dStart = bt.dStart;
+  w.dVar = bt.dVar;
+  w.dBnd = bt.dBnd;
+  w.B = bt.B;
+  for (int k = 0; k < 2; ++k) {
+    w.itemsS[k] = bt.wlItemsS[k];
+    w.itemsL[k] = bt.wlItemsL[k];
+    w.vecChanged2[k] = bt.wlInts + static_cast<size_t>(k) * bt.Bp;
+    w.active2[k] = reinterpret_cast<unsigned *>(bt.wlInts + 2 * static_cast<size_t>(bt.Bp) + static_cast<size_t>(k) * bt.G);
+  }
+  w.K = bt.wlK;
+  w.cells = bt.wlCells;
+  w.itemCap = bt.wlItemCap;
+  w.kCap = bt.wlCellCap;
+  w.cellCap = bt.wlCellCap;
+  w.prevCells = bt.wlPrevCells;
+  w.ctl = bt.wlCtl;
+  w.limit = limit;
+  w.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
+  CK(cudaMemsetAsync(bt.wlCtl, 0, sizeof(WlCtl), st));
+  CK(cudaMemsetAsync(bt.wlInts, 0, sizeof(int) * (static_cast<size_t>(bt.Bp) * 2 + static_cast<size_t>(bt.G) * 2), st));
+  bt_init_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, bt.B);
+  CK(cudaMemcpyAsync(w.active2[0], p.active, sizeof(unsigned) * bt.G, cudaMemcpyDeviceToDevice, st));
+  bt_base_pack_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.baseX);
+  ctx->stats.kernelLaunches += 2;
+  const int grid = std::max(1, ctx->wlBlocksPerSM * ctx->numSMs);
+  void *args[] = { &w };
+  CK(cudaEventRecord(ctx->evPool[0], st));
+  CK(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(bt_worklist_kernel), dim3(grid), dim3(kThreads), args, 0, st));
+  CK(cudaEventRecord(ctx->evPool[1], st));
+  ++ctx->stats.kernelLaunches;
+  WlCtl h;
+  CK(cudaMemcpyAsync(&h, bt.wlCtl, sizeof(h), cudaMemcpyDeviceToHost, st));
+  CK(cudaEventRecord(ctx->evB, st));
+  CK(cudaStreamSynchronize(st));  // the one host synchronisation of the run
+  *status = h.status;
+  float kms = 0.f, ms = 0.f;
+  cudaEventElapsedTime(&kms, ctx->evPool[0], ctx->evPool[1]);
+  cudaEventElapsedTime(&ms, ctx->evA, ctx->evB);
+  if (h.status == kWlBaseNotFixpoint) {
+    bt.wlMarksKnown = true;  // (the kernel left before touching anything but the previous run's cells)
+    bt.wlPrevCells = 0;
+    return CBP_OK;
+  }
+  if (h.status != kWlOk)
+    return CBP_OK;
+  bt.wlMarksKnown = true;
+  bt.wlPrevCells = std::min(h.nCells, bt.wlCellCap);
+  bt.baseMode = true;
+  bt.quiet = false;
+  bt.groupBuilt.assign(bt.G, 0);
+  ctx->stats.lastRunMs = ms;
+  ctx->stats.lastRoundKernelMs = kms;
+  ctx->stats.lastRoundKernelLaunches = std::max(1, h.rounds);
+  ctx->stats.lastFromBase = 1;
+  ctx->stats.lastGroupsBuilt = 0;
+  ctx->stats.lastMode = 2;
+  ctx->stats.lastPairsWalked = static_cast<int64_t>(h.pairs);
+  ctx->stats.lastHostSyncs = 1;
+  ctx->stats.lastItems = static_cast<int64_t>(h.itemsTotal);
+  // rounds summed over the vectors (throughput accounting)
+  std::vector<int> rounds(bt.Bp);
+  CK(cudaMemcpy(rounds.data(), p.vecRounds, sizeof(int) * bt.Bp, cudaMemcpyDeviceToHost));
+  long long tot = 0;
+  for (int b = 0; b < bt.B; ++b)
+    tot += rounds[b];
+  ctx->stats.lastRoundsTotal = tot;
+  return CBP_OK;
+}
+
 int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeLimitSec)
 {
   if (!mat || !mat->bt.loaded)
@@ -1224,7 +1386,28 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   const int limit = maxRounds > 0 ? maxRounds : INT_MAX;
   const size_t words = bt.cells / 32;
   cudaStream_t st = ctx->stream;
+  while (ctx->evPool.size() < 2) {
+    cudaEvent_t e;
+    CK(cudaEventCreate(&e));
+    ctx->evPool.push_back(e);
+  }
   CK(cudaEventRecord(ctx->evA, st));
+  int hostSyncs = 0;
+  // Base + diffs batches first try the worklist form: one persistent kernel for all rounds, only the (row, vector)
+  // pairs that a changed column touches.  It hands back when the node bounds are not a propagation fixpoint (then
+  // every row can act for every vector) or when a list overflows.  CBP_NO_WORKLIST=1: tests and A/B runs.
+  static const bool noWorklist = getenv("CBP_NO_WORKLIST") != nullptr;
+  if (!bt.denseLoaded && !bt.consumed && bt.W == 32 && !noWorklist && !(timeLimitSec <= 0.0)) {
+    int wlStatus = kWlOk;
+    const int rcw = bt_wl_run(mat, p, limit, timeLimitSec, &wlStatus);
+    if (rcw)
+      return rcw;
+    ++hostSyncs;
+    if (wlStatus == kWlOk)
+      return CBP_OK;
+    CK(cudaEventRecord(ctx->evA, st));
+  }
+  bt.wlMarksKnown = false;  // the full-walk path below leaves marks the worklist form knows nothing about
   if (!bt.dirty0Clean)
     CK(cudaMemsetAsync(bt.dirty[0], 0, sizeof(unsigned) * words, st));
   bt.dirty0Clean = false;
@@ -1257,6 +1440,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       ++ctx->stats.kernelLaunches;
       CK(cudaMemcpyAsync(&need, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
+      ++hostSyncs;
       bt.baseNeedsPrepass = need != 0;
       bt.checkedTol = primalTol;
     }
@@ -1416,6 +1600,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       std::vector<int> flags(bt.G + 1);
       CK(cudaMemcpyAsync(flags.data(), bt.groupFlag, sizeof(int) * (bt.G + 1), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
+      ++hostSyncs;
       const unsigned count = static_cast<unsigned>(flags[bt.G]);
       bool anyFlag = false;
       for (int g = 0; g < bt.G; ++g)
@@ -1485,6 +1670,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&any, p.anyActive, sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    ++hostSyncs;
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ctx->evPool[0], ctx->evPool[1]);
     roundKernelMs += ms;
@@ -1507,6 +1693,10 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       tot += rounds[b];
   }
   ctx->stats.lastRoundsTotal = tot;
+  ctx->stats.lastMode = fromBase ? 1 : 0;
+  ctx->stats.lastPairsWalked = 0;
+  ctx->stats.lastItems = 0;
+  ctx->stats.lastHostSyncs = hostSyncs + 1;
   ctx->stats.lastFromBase = fromBase ? 1 : 0;
   int built = 0;
   for (int g = 0; g < bt.G; ++g)

@@ -39,6 +39,8 @@ struct SvStatus {
   // owner), and rank 0's "time is up"
   int inRowFlag[2][kMaxPeers];
   int inTime[2];
+  // every rank's event-round limit (pushed by its owner after the start barrier): all ranks use the smallest
+  int evMax[kMaxPeers];
   // where this rank's proposals go on every rank q: q's inbox slot for this rank (per round parity),
   // and q's status block
   Bnd *pushP[2][kMaxPeers];
@@ -80,6 +82,13 @@ struct SvParams {
   const int *sellOff;  // nSlices + 1
   const int *sliceOrder;  // slices by decreasing length: the order in which they are handed out
   int nSlices, mShort;
+  // column-major copy of the kept rows (which rows hold column j: cscRow[cscStart[j] .. cscStart[j+1]), kept-order
+  // row indices) and the rows' packed CSR extents: event-driven rounds walk from the changed columns to their rows
+  const int *cscStart;
+  const int *cscRow;
+  const int *rowNz, *rowCnt;
+  int firstLongRow;      // kept rows from here on are longer than a tile (always scanned in full)
+  int eventMaxChanged;   // a round that changed at most this many columns is followed by an event-driven round (0: never)
   // state
   Bnd *X[2];
   unsigned *dirty[2];
@@ -389,6 +398,140 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
   }
 }
 
+// One short row (<= kShortLen nonzeros) by one thread from the packed CSR copy: the same sums in the same order as
+// the sliced-ELL pass (entries in CSR order, accumulate_fast), so a row gives the same plan whichever pass visits it.
+__device__ __forceinline__ void sv_event_short_row(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink, int row)
+{
+  const int kb = __ldg(&p.rowNz[row]), cnt = __ldg(&p.rowCnt[row]);
+  RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+  for (int k = 0; k < cnt; k += 8) {
+    double a[8];
+    int cj[8];
+    Bnd x[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      a[u] = 0.0;
+      cj[u] = 0;
+      if (k + u < cnt) {
+        cj[u] = __ldg(&p.col[kb + k + u]);
+        a[u] = __ldg(&p.val[kb + k + u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      x[u] = ldcg_bnd(&src[col_of(cj[u])]);
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (a[u] != 0.0)
+        accumulate_fast(ra, a[u], col_is_int(cj[u]), x[u], p.s.inf);
+  }
+  const RowPlan pl = plan_row(ra, __ldg(&p.rowLB[row]), __ldg(&p.rowUB[row]), p.s);
+  if (pl.infeasible)
+    sink.flag_row(p.rowOrig[row] + p.rowOffset);
+  if (pl.sideU || pl.sideL)
+    for (int k = 0; k < cnt; k += 8) {  // (all loads of a chunk are issued before the first use)
+      double a[8];
+      int cj[8];
+      Bnd x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        a[u] = 0.0;
+        cj[u] = 0;
+        if (k + u < cnt) {
+          cj[u] = __ldg(&p.col[kb + k + u]);
+          a[u] = __ldg(&p.val[kb + k + u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        x[u] = ldcg_bnd(&src[col_of(cj[u])]);
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (a[u] != 0.0)
+          tighten_nz(sink, pl, a[u], col_of(cj[u]), col_is_int(cj[u]), a[u] > 0.0 ? x[u].lb : x[u].ub,
+            a[u] > 0.0 ? x[u].ub : x[u].lb, p.s);
+    }
+}
+
+// One medium row (kShortLen < nonzeros <= kTileNnz) by one warp: lanes stride over the row, butterfly — the
+// order of the tile pass.
+__device__ __forceinline__ void sv_event_medium_row(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink, int row,
+  int lane)
+{
+  const int kb = __ldg(&p.rowNz[row]), ke = kb + __ldg(&p.rowCnt[row]);
+  RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+  for (int k = kb + lane; k < ke; k += 32) {
+    const int c = __ldg(&p.col[k]);
+    const double a = __ldg(&p.val[k]);
+    const Bnd x = ldcg_bnd(&src[col_of(c)]);
+    accumulate(ra, a, col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s.inf);
+  }
+  warp_reduce(ra);
+  const RowPlan pl = plan_row(ra, __ldg(&p.rowLB[row]), __ldg(&p.rowUB[row]), p.s);
+  if (pl.infeasible && lane == 0)
+    sink.flag_row(p.rowOrig[row] + p.rowOffset);
+  if (pl.sideU || pl.sideL)
+    for (int k = kb + lane; k < ke; k += 32) {
+      const int c = __ldg(&p.col[k]);
+      const double a = __ldg(&p.val[k]);
+      const Bnd x = ldcg_bnd(&src[col_of(c)]);
+      tighten_nz(sink, pl, a, col_of(c), col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+    }
+}
+
+// Event-driven row phase: the previous round changed few columns, and a row none of whose columns moved would
+// only repeat what it did last round (same bounds, same candidates, all of them already rejected or applied), so only
+// the rows that hold a changed column are evaluated.  A warp takes one word of the previous round's marks; for each
+// marked column it brings the target buffer up to date (step A1) and walks the column's rows in the column-major
+// copy: short rows one per lane, medium rows one after the other by the whole warp.  A row that holds two changed
+// columns is evaluated twice; its candidates are max/min reductions, so that is harmless.  Rows longer than a tile
+// are not handled here: the caller scans them in full.
+__device__ __forceinline__ void sv_event_rows(const SvParams &p, const Bnd *__restrict__ src, Bnd *dst, unsigned *prev,
+  SvSink &sink)
+{
+  const int lane = threadIdx.x & 31;
+  const int gwarp = (blockIdx.x * kThreads + threadIdx.x) >> 5, nwarps = (gridDim.x * kThreads) >> 5;
+  for (int w0 = gwarp << 5; w0 < p.nWords; w0 += nwarps << 5) {  // 32 mark words per warp and trip, one per lane
+    const int wl = w0 + lane;
+    const unsigned mine = wl < p.nWords ? __ldcg(&prev[wl]) : 0u;
+    if (mine) {
+      prev[wl] = 0u;
+      unsigned bits = mine;  // A1 for this lane's marked columns
+      while (bits) {
+        const int j = (wl << 5) + __ffs(bits) - 1;
+        bits &= bits - 1;
+        const Bnd b = ldcg_bnd(&src[j]);
+        atomic_max_f64(&dst[j].lb, b.lb);
+        atomic_min_f64(&dst[j].ub, b.ub);
+      }
+    }
+    unsigned live = __ballot_sync(0xffffffffu, mine != 0u);
+    while (live) {
+      const int sl = __ffs(live) - 1;
+      live &= live - 1;
+      unsigned bits = __shfl_sync(0xffffffffu, mine, sl);
+      const int w = w0 + sl;
+      while (bits) {
+        const int j = (w << 5) + __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int cs = __ldg(&p.cscStart[j]), ce = __ldg(&p.cscStart[j + 1]);
+        for (int q0 = cs; q0 < ce; q0 += 32) {
+          const int q = q0 + lane;
+          const int row = q < ce ? __ldg(&p.cscRow[q]) : -1;
+          if (row >= 0 && row < p.mShort)
+            sv_event_short_row(p, src, sink, row);
+          unsigned med = __ballot_sync(0xffffffffu, row >= p.mShort && row < p.firstLongRow);
+          while (med) {
+            const int l = __ffs(med) - 1;
+            med &= med - 1;
+            sv_event_medium_row(p, src, sink, __shfl_sync(0xffffffffu, row, l), lane);
+          }
+        }
+      }
+    }
+  }
+}
+
 __device__ __forceinline__ void sv_stamp(const SvParams &p, int round, int which)
 {
   if (blockIdx.x == 0 && threadIdx.x == 0 && round < kStampRounds) {
@@ -645,7 +788,7 @@ __global__ void __launch_bounds__(kThreads, kP2P ? kSvShardedBlocks : (kTiles ? 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SvSmem &sm = *reinterpret_cast<SvSmem *>(smem_raw);  // kTiles=false: launched without it, never touched
   __shared__ int s_cnt[kWarps];
-  __shared__ int s_dec[4];
+  __shared__ int s_dec[5];
   cg::grid_group grid = cg::this_grid();
   const int tid = threadIdx.x;
   const int gtid = blockIdx.x * kThreads + tid, gsize = gridDim.x * kThreads;
@@ -685,7 +828,13 @@ __global__ void __launch_bounds__(kThreads, kP2P ? kSvShardedBlocks : (kTiles ? 
       p.st->epochEnd = p.epoch0 + 1;
     return;
   }
+  if (kP2P && gtid == 0) {  // (after the start barrier: every rank has reset its block for this run)
+    for (int q = 0; q < p.world; ++q)
+      p.st->peerSt[q]->evMax[p.rank] = p.eventMaxChanged;
+    __threadfence_system();
+  }
   bool sparse = false;  // last round changed few columns: scan the marks word-wise
+  bool event = false;   // ... so few that this round only visits the rows that hold one of them
   int round = 0;
   for (;; ++round) {
     const int cur = round & 1;
@@ -706,7 +855,9 @@ __global__ void __launch_bounds__(kThreads, kP2P ? kSvShardedBlocks : (kTiles ? 
     // round changed (it was that round's source, so it is stale there), and
     // clear that round's marks.  Atomics: rows of this round may hit the same
     // column at the same time.
-    if (round > 0 && sparse) {
+    if (event) {
+      // (A1 happens inside the event-driven row phase below, column by column)
+    } else if (round > 0 && sparse) {
       // few columns changed last round: one mark word per thread, its few bits one after the other
       unsigned *prev = p.dirty[cur ^ 1];
       for (int w = gtid; w < p.nWords; w += gsize) {
@@ -743,14 +894,17 @@ __global__ void __launch_bounds__(kThreads, kP2P ? kSvShardedBlocks : (kTiles ? 
       p.st->stampsX[round][0] = static_cast<unsigned>(t - p.st->t0);
     }
     // A2: stream the matrix: short rows from the sliced-ELL copy, the rest as TMA-staged tiles
-    sv_short_rows<kP2P ? kSvChunkSharded : kSvChunk>(p, src, sink, &p.st->sliceCtr[cur]);
+    if (event)
+      sv_event_rows(p, src, dst, p.dirty[cur ^ 1], sink);
+    else
+      sv_short_rows<kP2P ? kSvChunkSharded : kSvChunk>(p, src, sink, &p.st->sliceCtr[cur]);
     if (blockIdx.x == 0 && tid == 0 && round < kStampRounds) {
       unsigned long long t;
       asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
       p.st->stampsX[round][1] = static_cast<unsigned>(t - p.st->t0);
     }
-    if (kTiles)
-      sv_stream<false>(p, sm, parity, 0, p.nTiles, src, sink);
+    if (kTiles)  // (event rounds: the medium rows were visited from their columns; rows longer than a tile are scanned in full)
+      sv_stream<false>(p, sm, parity, event ? p.firstLongTile : 0, p.nTiles, src, sink);
     if (kP2P) {
       if (kTiles && p.nLong > 0) {  // (long-row partials are rank-local: a row lives on one rank)
         grid.sync();
@@ -853,6 +1007,11 @@ __global__ void __launch_bounds__(kThreads, kP2P ? kSvShardedBlocks : (kTiles ? 
       s_dec[1] = __ldcg(&p.st->infeasCol);
       s_dec[2] = __ldcg(&p.st->chg[cur]);
       s_dec[3] = __ldcg(&p.st->timeUp);
+      int ev = p.eventMaxChanged;
+      if (kP2P)  // (pushed before this round's cross-GPU barrier, the same values on every rank)
+        for (int q = 0; q < p.world; ++q)
+          ev = min(ev, __ldcg(&p.st->evMax[q]));
+      s_dec[4] = ev;
     }
     __syncthreads();
     const int badRow = s_dec[0], badCol = s_dec[1];
@@ -880,6 +1039,7 @@ __global__ void __launch_bounds__(kThreads, kP2P ? kSvShardedBlocks : (kTiles ? 
       }
     }
     sparse = changed < (p.nWords >> 2);
+    event = changed <= s_dec[4];
     if (stop) {
       if (gtid == 0) {
         p.st->rounds = round + 1;

@@ -84,6 +84,11 @@ typedef struct cbp_stats {
   int64_t lastRoundsTotal; /* rounds summed over the vectors of the last run */
   int lastFromBase;        /* batch: the first round ran from the shared base bounds (no per-vector buffers) */
   int lastGroupsBuilt;     /* batch: vector groups (of 32) whose bound buffers were built afterwards */
+  int lastMode;            /* batch: 0 classic two-buffer rounds, 1 overlay rounds that walk every (row, vector) pair,
+                              2 worklist form (one persistent kernel, only the pairs a changed column touches) */
+  int lastHostSyncs;       /* batch: host synchronisations between the start and the end of the run */
+  int64_t lastPairsWalked; /* batch, worklist form: (nonzero, vector) pairs walked by all rounds */
+  int64_t lastItems;       /* batch, worklist form: (row, vector) items evaluated by all rounds */
 } cbp_stats;
 
 /* -- context ----------------------------------------------------------- */

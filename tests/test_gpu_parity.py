@@ -290,8 +290,12 @@ def test_batch_first_round_from_the_base(oracle, gpu_ctx):
     assert res["nChanged"][:40].sum() > 0
 
 
-@pytest.mark.parametrize("env", [{"CBP_LOG_CAP": "7"}, {}, {"CBP_OVERLAY_ROUNDS": "1"}, {"CBP_OVERLAY_ROUNDS": "2"},
-                                 {"CBP_NO_MULTI_GROUP": "1"}, {"CBP_NO_BASE_ROUND": "1"}, {"CBP_NO_LAZY_X1": "1"}],
+@pytest.mark.parametrize("env", [{"CBP_LOG_CAP": "7", "CBP_NO_WORKLIST": "1"}, {"CBP_NO_WORKLIST": "1"},
+                                 {"CBP_OVERLAY_ROUNDS": "1", "CBP_NO_WORKLIST": "1"},
+                                 {"CBP_OVERLAY_ROUNDS": "2", "CBP_NO_WORKLIST": "1"},
+                                 {"CBP_NO_MULTI_GROUP": "1", "CBP_NO_WORKLIST": "1"},
+                                 {"CBP_NO_BASE_ROUND": "1", "CBP_NO_WORKLIST": "1"},
+                                 {"CBP_NO_LAZY_X1": "1", "CBP_NO_WORKLIST": "1"}],
                          ids=["list_overflows", "overlay", "overlay_left_after_1", "overlay_left_after_2",
                               "overlay_one_group_per_warp", "lazy_buffer", "no_lazy_buffer"])
 def test_batch_first_round_variants(env):

@@ -1,0 +1,169 @@
+"""GPU: node batches in worklist form (cbc_b200/csrc/cbp_wl_kernels.cuh) — the persistent kernel that evaluates only
+the (row, vector) pairs a changed column touches — against the CPU oracle run vector by vector, and against the
+full-walk kernels it hands over to.  The worklist form is taken when the node bounds are a propagation fixpoint."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from cbc_b200 import capi
+from cbc_b200 import instances as I
+from helpers import assert_same_bounds
+
+pytestmark = pytest.mark.gpu
+KEYS = ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason")
+
+
+def _node(oracle, inst):
+    """node bounds = the propagated root (what Cbc hands to strong branching / a dive)"""
+    r, lb, ub = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    assert r["feasible"]
+    inst.lb, inst.ub = lb, ub
+    return inst
+
+
+def _check(oracle, ctx, inst, s, v, b, what, want_mode=2, **kw):
+    mat = capi.Matrix(ctx, inst)
+    ores, Lo, Uo = oracle.propagate_batch_delta(oracle.Problem(inst), inst.lb, inst.ub, s, v, b, threads=8, **kw)
+    L0, U0 = I.expand_deltas(inst.lb, inst.ub, s, v, b)
+    for rep in range(2):  # twice: the second run starts from what the first left in the masks
+        res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b, **kw)
+        st = ctx.stats()
+        assert st["lastMode"] == want_mode, (what, st)
+        if want_mode == 2:
+            assert st["lastHostSyncs"] == 1
+        for k in KEYS:
+            bad = np.flatnonzero(res[k] != ores[k])
+            assert bad.size == 0, f"{what}: {k} differs for vectors {bad[:8]}: {res[k][bad[:8]]} vs {ores[k][bad[:8]]}"
+        Lg, Ug = mat.batch_fetch_dense()
+        for k in range(len(s) - 1):
+            assert_same_bounds(inst.colType, Lg[k], Ug[k], Lo[k], Uo[k], f"{what} vector {k}")
+            cols = uc[us[k]:us[k + 1]]
+            if not res["feasible"][k]:
+                assert cols.size == 0
+                continue
+            want = np.flatnonzero((Lg[k] != L0[k]) | (Ug[k] != U0[k]))
+            assert np.array_equal(cols, want), f"{what} vector {k}: update list"
+            assert np.array_equal(ul[us[k]:us[k + 1]], Lg[k][want]) and np.array_equal(uu[us[k]:us[k + 1]], Ug[k][want])
+    mat.close()
+    return res, st
+
+
+def test_worklist_dives_short_rows(oracle, gpu_ctx):
+    inst = I.knapsack_assignment(m=3000, n=8000, seed=41, root_fixpoint=True)
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 70, max_depth=48, seed=42)
+    res, st = _check(oracle, gpu_ctx, inst, s, v, b, "dives")
+    assert res["rounds"].max() >= 2 and res["nChanged"].sum() > 100
+    assert 0 < st["lastPairsWalked"] < inst.nnz * int(res["rounds"].sum()) // 10
+
+
+def test_worklist_dives_that_fail(oracle, gpu_ctx):
+    # dives that mostly leave the planted point: violated rows and crossing columns among the vectors
+    inst = I.knapsack_assignment(m=3000, n=8000, seed=41, root_fixpoint=True)
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 70, max_depth=48, seed=42, follow_xstar=0.3)
+    res, _ = _check(oracle, gpu_ctx, inst, s, v, b, "failing dives")
+    f = res["feasible"].astype(bool)
+    assert f.any() and (~f).any()
+
+
+def test_worklist_strong_branching_long_rows(oracle, gpu_ctx):
+    inst = _node(oracle, I.fast0507_shaped(m=101, n=9000, fix_frac=0.996, seed=22))
+    s, v, b = I.strong_branch_deltas(inst, inst.lb, inst.ub, 48, seed=43)
+    res, st = _check(oracle, gpu_ctx, inst, s, v, b, "strong branching")
+    assert res["nChanged"].sum() > 0
+
+
+def test_worklist_mixed_continuous_chains(oracle, gpu_ctx):
+    inst = _node(oracle, I.mixed_bigm(m=6000, n=6000, seed=44))
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 45, max_depth=12, seed=45)
+    res, _ = _check(oracle, gpu_ctx, inst, s, v, b, "mixed dives")
+    assert res["rounds"].max() >= 5 and res["nChanged"].sum() > 500
+    s, v, b = I.probe_deltas(inst, inst.lb, inst.ub, 20, seed=46)
+    _check(oracle, gpu_ctx, inst, s, v, b, "mixed probes")
+    _check(oracle, gpu_ctx, inst, s, v, b, "mixed probes maxRounds=2", max_rounds=2)
+
+
+def test_worklist_power_law_rows_of_every_length(oracle, gpu_ctx):
+    inst = _node(oracle, I.power_law(n=20000, nnz_target=150000, n_dense=3, dense_len=6000, max_len=2500, seed=46))
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 40, max_depth=20, seed=47)
+    res, _ = _check(oracle, gpu_ctx, inst, s, v, b, "power law")
+    assert res["nChanged"].sum() > 0
+
+
+def test_worklist_odd_batches(oracle, gpu_ctx):
+    """vectors without diffs, a column repeated inside a vector, a diff that crosses the other bound (R11 / R9 at the
+    diff cell), fractional diffs on integer columns, a last group that is not full"""
+    inst = _node(oracle, I.knapsack_assignment(m=1200, n=3000, seed=61, root_fixpoint=True))
+    free = np.flatnonzero(inst.ub > inst.lb)
+    start, var, bnd = [0], [], []
+    for k in range(75):
+        j = int(free[(13 * k) % free.size])
+        if k % 5 == 0:
+            pass
+        elif k % 5 == 1:
+            var += [j | I.UPPER_FLAG, j]
+            bnd += [0.0, 0.0]
+        elif k % 5 == 2:
+            var += [j, j | I.UPPER_FLAG]
+            bnd += [1.0, 0.0]  # lb above ub: infeasible before the first round
+        elif k % 5 == 3:
+            var += [j | I.UPPER_FLAG]
+            bnd += [0.6]  # rounds down to 0 (R11), counts as a round-1 change
+        else:
+            var += [j, int(free[(13 * k + 5) % free.size])]
+            bnd += [1.0, 1.0]
+        start.append(len(var))
+    s, v, b = np.array(start, np.int64), np.array(var, np.uint32), np.array(bnd, np.float64)
+    res, _ = _check(oracle, gpu_ctx, inst, s, v, b, "odd")
+    assert (res["feasible"] == 0).any() and (res["nChanged"] > 0).any()
+
+
+def test_worklist_hands_over_when_the_node_is_not_a_fixpoint(oracle, gpu_ctx):
+    inst = I.knapsack_assignment(m=1200, n=3000, seed=62)  # root bounds still tighten by themselves
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 40, max_depth=20, seed=63)
+    _check(oracle, gpu_ctx, inst, s, v, b, "not a fixpoint", want_mode=1)
+
+
+def test_worklist_then_other_batches_on_the_same_matrix(oracle, gpu_ctx):
+    """the masks a worklist run leaves are cleaned by the next run, whichever form that takes"""
+    inst = I.knapsack_assignment(m=1500, n=4000, seed=64, root_fixpoint=True)
+    mat = capi.Matrix(gpu_ctx, inst)
+    prob = oracle.Problem(inst)
+    for seed, B in ((1, 50), (2, 90), (3, 20)):
+        s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, B, max_depth=30, seed=seed)
+        res = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)[0]
+        assert gpu_ctx.stats()["lastMode"] == 2
+        ores, Lo, Uo = oracle.propagate_batch_delta(prob, inst.lb, inst.ub, s, v, b, threads=8)
+        for k in KEYS:
+            assert np.array_equal(res[k], ores[k]), (seed, k)
+        Lg, Ug = mat.batch_fetch_dense()
+        f = res["feasible"].astype(bool)
+        assert np.array_equal(Lg[f], Lo[f]) and np.array_equal(Ug[f], Uo[f])
+        if seed == 2:  # a dense batch (classic two-buffer form) in between
+            L0, U0 = I.expand_deltas(inst.lb, inst.ub, s, v, b)
+            r2, L2, U2 = mat.propagate_batch(L0, U0)
+            assert np.array_equal(r2["rounds"], ores["rounds"]) and np.array_equal(L2[f], Lo[f])
+    mat.close()
+
+
+def test_worklist_item_list_overflow_hands_over():
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "from cbc_b200 import capi, instances as I; from oracle import oracle_py as O\n"
+        "inst = I.knapsack_assignment(m=3000, n=8000, seed=41, root_fixpoint=True)\n"
+        "s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 70, max_depth=48, seed=42)\n"
+        "ctx = capi.Context(); mat = capi.Matrix(ctx, inst)\n"
+        "res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)\n"
+        "assert ctx.stats()['lastMode'] == 1, ctx.stats()\n"
+        "Lg, Ug = mat.batch_fetch_dense()\n"
+        "ores, Lo, Uo = O.propagate_batch_delta(O.Problem(inst), inst.lb, inst.ub, s, v, b, threads=8)\n"
+        "for k in ('feasible','rounds','nChanged','infeasibleRow','infeasibleCol','stopReason'):\n"
+        "    assert np.array_equal(res[k], ores[k]), k\n"
+        "f = res['feasible'].astype(bool)\n"
+        "assert np.array_equal(Lg[f], Lo[f]) and np.array_equal(Ug[f], Uo[f])\n"
+        "print('OK')\n") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),)
+    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, CBP_WL_ITEM_CAP="500"),
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
