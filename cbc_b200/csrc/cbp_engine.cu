@@ -72,6 +72,12 @@ struct BatchState {
   WlCtl *wlCtl = nullptr;
   int *wlInts = nullptr;  // vecChanged by round parity [2][Bp], active by round parity [2][G]
   unsigned wlItemCap = 0, wlCellCap = 0;
+  unsigned long long *wlHKey = nullptr;  // (vector, long row) pair table
+  double *wlHMin = nullptr, *wlHMax = nullptr;
+  int *wlHStamp = nullptr;
+  unsigned wlHSlots = 0;
+  double *wlRowBase = nullptr;  // [3][mKept] the node's sums of the long rows
+  unsigned char *wlRowExact = nullptr;
   unsigned wlPrevCells = 0;  // cells the last worklist run left in the masks
   bool wlMarksKnown = false; // dmask / ever / dirty are all zero except for those cells
 };
@@ -272,7 +278,8 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
     mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
-    mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts };
+    mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts, mat->bt.wlHKey, mat->bt.wlHMin,
+    mat->bt.wlHMax, mat->bt.wlHStamp, mat->bt.wlRowBase, mat->bt.wlRowExact };
   for (void *p : ptrs)
     if (p)
       cudaFree(p);
@@ -1074,7 +1081,10 @@ static int bt_reserve(cbp_matrix *mat, int B)
   if (cells > bt.capCells || Bp > bt.capBp) {
     void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt,
       bt.log, bt.groupFlag, bt.dmask, bt.wlItemsS[0], bt.wlItemsS[1], bt.wlItemsL[0], bt.wlItemsL[1], bt.wlK, bt.wlCells,
-      bt.wlCtl, bt.wlInts };
+      bt.wlCtl, bt.wlInts, bt.wlHKey, bt.wlHMin, bt.wlHMax, bt.wlHStamp };
+    bt.wlHKey = nullptr;
+    bt.wlHMin = bt.wlHMax = nullptr;
+    bt.wlHStamp = nullptr;
     bt.dmask = nullptr;
     bt.wlItemsS[0] = bt.wlItemsS[1] = bt.wlItemsL[0] = bt.wlItemsL[1] = nullptr;
     bt.wlK = bt.wlCells = nullptr;
@@ -1101,6 +1111,20 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.wlCellCap = static_cast<unsigned>(std::min<size_t>(1u << 25, std::max<size_t>(1u << 20, static_cast<size_t>(Bp) * 1024)));
     if (getenv("CBP_WL_ITEM_CAP"))  // tests shrink the item lists to exercise the hand-over to the full-walk path
       bt.wlItemCap = static_cast<unsigned>(std::max<long>(1, atol(getenv("CBP_WL_ITEM_CAP"))));
+    // one table slot per (vector, long row) pair that comes up; matrices without rows longer than kShortLen need none
+    bt.wlHSlots = 2;
+    if (mat->mKept > 0) {
+      // (every row's pairs go through the table when sums are exact; only the longer rows' otherwise)
+      size_t want = std::max<size_t>(1u << 18, static_cast<size_t>(Bp) * (mat->allInt ? 1024 : (mat->mKept > mat->mShort ? 64 : 0)));
+      bt.wlHSlots = 1u << 18;
+      while (bt.wlHSlots < want && bt.wlHSlots < (1u << 25))
+        bt.wlHSlots <<= 1;
+    }
+    if (dalloc(&bt.wlHKey, bt.wlHSlots) != cudaSuccess || dalloc(&bt.wlHMin, bt.wlHSlots) != cudaSuccess
+      || dalloc(&bt.wlHMax, bt.wlHSlots) != cudaSuccess || dalloc(&bt.wlHStamp, bt.wlHSlots) != cudaSuccess) {
+      ctx->err = "batch workspace (pair table)";
+      return CBP_ERR_NOMEM;
+    }
     if (dalloc(&bt.wlItemsS[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsS[1], bt.wlItemCap) != cudaSuccess
       || dalloc(&bt.wlItemsL[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsL[1], bt.wlItemCap) != cudaSuccess
       || dalloc(&bt.wlK, bt.wlCellCap) != cudaSuccess || dalloc(&bt.wlCells, bt.wlCellCap) != cudaSuccess
@@ -1125,6 +1149,13 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.dirty0Clean = bt.dmaskClean = false;
     // CBP_LOG_CAP: tests shrink the list to exercise the fall-back to the two-buffer first round
     bt.logCap = getenv("CBP_LOG_CAP") ? std::min<unsigned>(logCap, static_cast<unsigned>(atol(getenv("CBP_LOG_CAP")))) : logCap;
+  }
+  if (!bt.wlRowBase) {
+    if (dalloc(&bt.wlRowBase, 3 * static_cast<size_t>(std::max(mat->mKept, 1))) != cudaSuccess
+      || dalloc(&bt.wlRowExact, std::max(mat->mKept, 1)) != cudaSuccess) {
+      ctx->err = "batch workspace: row sums";
+      return CBP_ERR_NOMEM;
+    }
   }
   if (!bt.baseLb) {
     if (dalloc(&bt.baseLb, mat->n) != cudaSuccess || dalloc(&bt.baseUb, mat->n) != cudaSuccess
@@ -1305,6 +1336,21 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.bt = p;
   w.cscStart = mat->cscStart;
   w.cscRow = mat->cscRow;
+  w.cscVal = mat->cscVal;
+  w.hKey = bt.wlHKey;
+  w.hMin = bt.wlHMin;
+  w.hMax = bt.wlHMax;
+  w.hStamp = bt.wlHStamp;
+  w.hMask = bt.wlHSlots - 1;
+  w.rowBaseMin = bt.wlRowBase;
+  w.rowBaseMax = bt.wlRowBase + std::max(mat->mKept, 1);
+  w.rowBaseRange = bt.wlRowBase + 2 * static_cast<size_t>(std::max(mat->mKept, 1));
+  w.rowExact = bt.wlRowExact;
+  w.exactOk = (mat->allInt && !bt.hasInf) ? 1 : 0;
+  CK(cudaMemsetAsync(bt.wlHKey, 0, sizeof(unsigned long long) * bt.wlHSlots, st));
+  CK(cudaMemsetAsync(bt.wlHMin, 0, sizeof(double) * bt.wlHSlots, st));
+  CK(cudaMemsetAsync(bt.wlHMax, 0, sizeof(double) * bt.wlHSlots, st));
+  CK(cudaMemsetAsync(bt.wlHStamp, 0, sizeof(int) * bt.wlHSlots, st));
   w.dStart = bt.dStart;
   w.dVar = bt.dVar;
   w.dBnd = bt.dBnd;
@@ -1341,6 +1387,13 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   CK(cudaEventRecord(ctx->evB, st));
   CK(cudaStreamSynchronize(st));  // the one host synchronisation of the run
   *status = h.status;
+  if (getenv("CBP_WL_STAMPS")) {
+    fprintf(stderr, "worklist run: status %d rounds %d items %llu pairs %llu cells %u; phase ends (us):", h.status, h.rounds,
+      h.itemsTotal, h.pairs, h.nCells);
+    for (unsigned i = 0; i < std::min(h.nStamps, 96u); ++i)
+      fprintf(stderr, " %.1f", h.stamps[i] * 1e-3);
+    fprintf(stderr, "\n");
+  }
   float kms = 0.f, ms = 0.f;
   cudaEventElapsedTime(&kms, ctx->evPool[0], ctx->evPool[1]);
   cudaEventElapsedTime(&ms, ctx->evA, ctx->evB);

@@ -46,6 +46,7 @@ struct WlCtl {
   unsigned nS[2], nL[2];  // items of the running / next round: rows <= kShortLen nonzeros, longer rows
   unsigned nLog, nK, nCells;
   int baseBad, timeUp;
+  int inexact;     // a diff is fractional or leaves the node's bounds: long rows are walked, not updated from the node's sums
   int overflow;    // a list other than the candidate list ran out of room (written outside P1 only)
   int overflowP1;  // the candidate list did (written in P1 only): two words, so that each is read while nobody writes it
   int anyActive[2];
@@ -53,11 +54,25 @@ struct WlCtl {
   unsigned long long pairs;   // (nonzero, vector) pairs walked
   unsigned long long itemsTotal;
   unsigned long long t0;
+  // diagnostic: ns since t0 at the first phase boundaries (CBP_WL_STAMPS=1 prints them)
+  unsigned nStamps;
+  unsigned stamps[96];
 };
 
 struct WlParams {
   BtParams bt;
   const int *cscStart, *cscRow;
+  const double *cscVal;
+  // Rows longer than kShortLen: one table slot per (vector, row) pair that has come up, found by hashing.  It keeps
+  // an item from being listed twice in a round and, where sums are exact (see exactOk), the pair's activity as
+  // "the node's sums + what the vector's own cells add".
+  unsigned long long *hKey;  // ((b << 32) | row) + 1, 0 = free
+  double *hMin, *hMax;       // sum over the vector's own cells in the row of a * (own bound - node's bound)
+  int *hStamp;               // last round (+1) the pair was listed for
+  unsigned hMask;            // slots - 1 (a power of two)
+  double *rowBaseMin, *rowBaseMax, *rowBaseRange;  // [mKept] the node's sums of the long rows (written by phase 0)
+  unsigned char *rowExact;                          // [mKept] every sum over this row is exact in any order
+  int exactOk;  // host: every column is an integer column and no input bound is infinite
   // the loaded batch
   const long long *dStart;
   const unsigned *dVar;
@@ -77,6 +92,15 @@ struct WlParams {
 
 namespace cg = cooperative_groups;
 
+__device__ __forceinline__ void wl_stamp(WlCtl *ctl, unsigned gtid)
+{
+  if (gtid == 0 && ctl->nStamps < 96) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    ctl->stamps[ctl->nStamps++] = static_cast<unsigned>(t - ctl->t0);
+  }
+}
+
 // bounds of vector (g, vl) at column j in the round's source buffer: the node's unless the vector has its own cell
 __device__ __forceinline__ Bnd wl_bounds(const BtParams &p, const Bnd *__restrict__ srcCells, const unsigned *__restrict__ dm,
   int vl, int j)
@@ -93,14 +117,32 @@ __device__ __forceinline__ Bnd wl_bounds(const BtParams &p, const Bnd *__restric
 
 // candidates of a worklist round go to the list (entries past the capacity are counted and dropped: the run is
 // then repeated by the full-walk kernels)
+constexpr unsigned kWlStage = 1024;  // candidates a CTA collects in shared memory before it asks the global list for room
+
 struct WlLogSink {
   BtLogEntry *log;
   unsigned *count;
   unsigned cap;
   int *overflow;
   int b;
+  // The candidates of a phase are staged per CTA in shared memory and appended to the global list with ONE
+  // reservation per CTA when the phase ends (every candidate asking the one global counter for its slot is what the
+  // phase would otherwise spend its time on); what does not fit the stage goes to the global list directly.
+  BtLogEntry *stage;
+  unsigned *staged;
   __device__ __forceinline__ void put(unsigned var, double v)
   {
+    if (stage) {
+      const unsigned at = atomicAdd(staged, 1u);
+      if (at < kWlStage) {
+        BtLogEntry e;
+        e.var = var;
+        e.b = b;
+        e.v = v;
+        stage[at] = e;
+        return;
+      }
+    }
     const unsigned peers = __activemask();
     const int leader = __ffs(peers) - 1;
     const int laneId = threadIdx.x & 31;
@@ -130,10 +172,11 @@ struct WlFlagSink {
   __device__ __forceinline__ void lb(int, double) { *flag = 1; }
 };
 
-// reads "the node's bounds, nothing else" (base check)
-struct WlBaseReader {
+// Readers: the bounds a row walk sees.  get() for one column; get_n() for N columns at once with every load of a
+// stage issued before the first use (mask words and node bounds first, then the few own cells).
+struct WlBaseReader {  // the node's bounds, nothing else (base check)
   const Bnd *baseX;
-  __device__ __forceinline__ Bnd operator()(int j) const
+  __device__ __forceinline__ Bnd get(int j) const
   {
     const double2 v = __ldg(reinterpret_cast<const double2 *>(&baseX[j]));
     Bnd x;
@@ -141,106 +184,275 @@ struct WlBaseReader {
     x.ub = v.y;
     return x;
   }
+  template <int N>
+  __device__ __forceinline__ void get_n(const int (&j)[N], Bnd (&x)[N]) const
+  {
+#pragma unroll
+    for (int u = 0; u < N; ++u)
+      x[u] = get(j[u]);
+  }
 };
-struct WlVecReader {
+struct WlVecReader {  // one vector: the node's bounds unless it has a cell of its own
   const BtParams *p;
   const Bnd *srcCells;
   const unsigned *dm;
   int vl;
-  __device__ __forceinline__ Bnd operator()(int j) const { return wl_bounds(*p, srcCells, dm, vl, j); }
+  __device__ __forceinline__ Bnd get(int j) const { return wl_bounds(*p, srcCells, dm, vl, j); }
+  template <int N>
+  __device__ __forceinline__ void get_n(const int (&j)[N], Bnd (&x)[N]) const
+  {
+    unsigned m[N];
+#pragma unroll
+    for (int u = 0; u < N; ++u) {
+      m[u] = __ldcg(&dm[j[u]]);
+      const double2 v = __ldg(reinterpret_cast<const double2 *>(&p->baseX[j[u]]));
+      x[u].lb = v.x;
+      x[u].ub = v.y;
+    }
+#pragma unroll
+    for (int u = 0; u < N; ++u)
+      if ((m[u] >> vl) & 1u)
+        x[u] = ldcg_bnd(&srcCells[static_cast<size_t>(j[u]) * 32]);
+  }
 };
 
-// One row of at most kShortLen nonzeros by one thread, CSR order (the order of the CPU restatement).
-// Returns true if the row is violated.
-template <class Reader, class Sink>
-__device__ __forceinline__ bool wl_row_thread(const BtParams &p, int row, const Reader &rd, Sink &sink)
+constexpr int kWlChunk = 8;  // nonzeros of a thread-walked row whose loads are in flight together
+
+// One row of at most kShortLen nonzeros by one thread, CSR order (the order of the CPU restatement): its sums.
+// kCheck: also whether every sum over the row is exact in any order (integer coefficients and bounds, integer
+// columns, magnitudes far below 2^53).
+template <bool kCheck, class Reader>
+__device__ __forceinline__ RowAct wl_thread_sum(const BtParams &p, int row, const Reader &rd, bool *whole)
 {
   const int kb = __ldg(&p.rowNz[row]), cnt = __ldg(&p.rowCnt[row]);
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-  for (int k = 0; k < cnt; k += 4) {
-    double a[4];
-    int cj[4];
-    Bnd x[4];
+  double mag = 0.0;
+  bool ok = true;
+  for (int k = 0; k < cnt; k += kWlChunk) {
+    double a[kWlChunk];
+    int cj[kWlChunk], jj[kWlChunk];
+    Bnd x[kWlChunk];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < kWlChunk; ++u) {
       a[u] = 0.0;
       cj[u] = 0;
       if (k + u < cnt) {
         cj[u] = __ldg(&p.col[kb + k + u]);
         a[u] = __ldg(&p.val[kb + k + u]);
       }
+      jj[u] = col_of(cj[u]);
     }
+    rd.get_n(jj, x);
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      x[u] = rd(col_of(cj[u]));
-#pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (a[u] != 0.0)
+    for (int u = 0; u < kWlChunk; ++u)
+      if (a[u] != 0.0) {
         accumulate_fast(ra, a[u], col_is_int(cj[u]), x[u], p.s.inf);
+        if (kCheck) {
+          mag += fabs(a[u]) * fmax(fabs(x[u].lb), fabs(x[u].ub));
+          ok = ok && col_is_int(cj[u]) && a[u] == floor(a[u]) && x[u].lb == floor(x[u].lb) && x[u].ub == floor(x[u].ub);
+        }
+      }
   }
-  const RowPlan pl = plan_row(ra, __ldg(&p.rowLB[row]), __ldg(&p.rowUB[row]), p.s);
-  if (pl.infeasible)
-    return true;
-  if (pl.sideU || pl.sideL)
-    for (int k = 0; k < cnt; ++k) {
-      const int c = __ldg(&p.col[kb + k]);
-      const double a = __ldg(&p.val[kb + k]);
-      const Bnd x = rd(col_of(c));
-      tighten_nz(sink, pl, a, col_of(c), col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
-    }
-  return false;
+  if (kCheck)
+    *whole = ok && mag < 1.0e15 && ra.infMin + ra.infMax == 0;
+  return ra;
 }
 
-// One longer row by one warp: lanes stride over the row, butterfly.  Every lane returns the verdict.
 template <class Reader, class Sink>
-__device__ __forceinline__ bool wl_row_warp(const BtParams &p, int row, const Reader &rd, Sink &sink, int lane)
+__device__ __forceinline__ void wl_thread_tighten(const BtParams &p, int row, const RowPlan &pl, const Reader &rd, Sink &sink)
+{
+  const int kb = __ldg(&p.rowNz[row]), cnt = __ldg(&p.rowCnt[row]);
+  for (int k = 0; k < cnt; k += kWlChunk) {
+    double a[kWlChunk];
+    int cj[kWlChunk], jj[kWlChunk];
+    Bnd x[kWlChunk];
+#pragma unroll
+    for (int u = 0; u < kWlChunk; ++u) {
+      a[u] = 0.0;
+      cj[u] = 0;
+      if (k + u < cnt) {
+        cj[u] = __ldg(&p.col[kb + k + u]);
+        a[u] = __ldg(&p.val[kb + k + u]);
+      }
+      jj[u] = col_of(cj[u]);
+    }
+    rd.get_n(jj, x);
+#pragma unroll
+    for (int u = 0; u < kWlChunk; ++u)
+      if (a[u] != 0.0)
+        tighten_nz(sink, pl, a[u], jj[u], col_is_int(cj[u]), a[u] > 0.0 ? x[u].lb : x[u].ub,
+          a[u] > 0.0 ? x[u].ub : x[u].lb, p.s);
+  }
+}
+
+// One longer row by one warp: lanes stride over the row (four nonzeros per lane in flight), butterfly.
+template <class Reader>
+__device__ __forceinline__ RowAct wl_row_warp_sum(const BtParams &p, int row, const Reader &rd, int lane)
 {
   const int kb = __ldg(&p.rowNz[row]), ke = kb + __ldg(&p.rowCnt[row]);
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
-  for (int k = kb + lane; k < ke; k += 32) {
-    const int c = __ldg(&p.col[k]);
-    const double a = __ldg(&p.val[k]);
-    const Bnd x = rd(col_of(c));
-    accumulate(ra, a, col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s.inf);
+  for (int k0 = kb; k0 < ke; k0 += 128) {
+    double a[4];
+    int c[4], jj[4];
+    Bnd x[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int k = k0 + 32 * u + lane;
+      a[u] = 0.0;
+      c[u] = 0;
+      if (k < ke) {
+        c[u] = __ldg(&p.col[k]);
+        a[u] = __ldg(&p.val[k]);
+      }
+      jj[u] = col_of(c[u]);
+    }
+    rd.get_n(jj, x);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (a[u] != 0.0)
+        accumulate(ra, a[u], col_is_int(c[u]), a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
   }
   warp_reduce(ra);
-  const RowPlan pl = plan_row(ra, __ldg(&p.rowLB[row]), __ldg(&p.rowUB[row]), p.s);
-  if (pl.infeasible)
-    return true;
-  if (pl.sideU || pl.sideL)
-    for (int k = kb + lane; k < ke; k += 32) {
-      const int c = __ldg(&p.col[k]);
-      const double a = __ldg(&p.val[k]);
-      const Bnd x = rd(col_of(c));
-      tighten_nz(sink, pl, a, col_of(c), col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
-    }
-  return false;
+  return ra;
 }
 
-// The rows of column j become items of vector b in the lists of parity `nxt`.  One reservation per list and
-// thread (a column's rows are few), so the counters see one atomic per thread, not one per item.
-__device__ __forceinline__ void wl_emit_rows(const WlParams &w, int b, int j, int nxt)
+template <class Reader, class Sink>
+__device__ __forceinline__ void wl_row_warp_tighten(const BtParams &p, int row, const RowPlan &pl, const Reader &rd,
+  Sink &sink, int lane)
 {
-  const int cs = __ldg(&w.cscStart[j]), ce = __ldg(&w.cscStart[j + 1]);
-  int nShort = 0;
-  for (int q = cs; q < ce; ++q)
-    nShort += __ldg(&w.bt.rowCnt[__ldg(&w.cscRow[q])]) <= kShortLen ? 1 : 0;
-  const int nLong = (ce - cs) - nShort;
-  unsigned atS = nShort ? atomicAdd(&w.ctl->nS[nxt], static_cast<unsigned>(nShort)) : 0u;
-  unsigned atL = nLong ? atomicAdd(&w.ctl->nL[nxt], static_cast<unsigned>(nLong)) : 0u;
-  if ((nShort && atS + nShort > w.itemCap) || (nLong && atL + nLong > w.itemCap)) {
-    w.ctl->overflow = 1;
-    return;
+  const int kb = __ldg(&p.rowNz[row]), ke = kb + __ldg(&p.rowCnt[row]);
+  for (int k0 = kb; k0 < ke; k0 += 128) {
+    double a[4];
+    int c[4], jj[4];
+    Bnd x[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int k = k0 + 32 * u + lane;
+      a[u] = 0.0;
+      c[u] = 0;
+      if (k < ke) {
+        c[u] = __ldg(&p.col[k]);
+        a[u] = __ldg(&p.val[k]);
+      }
+      jj[u] = col_of(c[u]);
+    }
+    rd.get_n(jj, x);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (a[u] != 0.0)
+        tighten_nz(sink, pl, a[u], jj[u], col_is_int(c[u]), a[u] > 0.0 ? x[u].lb : x[u].ub,
+          a[u] > 0.0 ? x[u].ub : x[u].lb, p.s);
   }
-  for (int q = cs; q < ce; ++q) {
-    const int row = __ldg(&w.cscRow[q]);
-    WlItem it;
-    it.b = b;
-    it.row = row;
-    if (__ldg(&w.bt.rowCnt[row]) <= kShortLen)
-      w.itemsS[nxt][atS++] = it;
-    else
-      w.itemsL[nxt][atL++] = it;
+}
+
+// the slot of pair (b, row) in the table (linear probing); ~0u when the table is too full
+__device__ __forceinline__ unsigned wl_slot(const WlParams &w, int b, int row)
+{
+  const unsigned long long key = ((static_cast<unsigned long long>(static_cast<unsigned>(b)) << 32) | static_cast<unsigned>(row)) + 1ull;
+  unsigned long long z = key * 0x9E3779B97F4A7C15ull;
+  unsigned h = static_cast<unsigned>(z >> 32) & w.hMask;
+  for (int probe = 0; probe < 128; ++probe) {
+    const unsigned long long prev = atomicCAS(&w.hKey[h], 0ull, key);
+    if (prev == 0ull || prev == key)
+      return h;
+    h = (h + 1u) & w.hMask;
+  }
+  return ~0u;
+}
+
+// Room for n entries of this lane in a list: the 32 lanes of a warp (all of them call this together) share one
+// atomic on the list's counter.  Returns the lane's first slot, or ~0u when the list is full.
+__device__ __forceinline__ unsigned wl_warp_reserve(unsigned *count, unsigned cap, int *overflow, int n, int lane)
+{
+  int incl = n;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d)
+      incl += t;
+  }
+  const int total = __shfl_sync(0xffffffffu, incl, 31);
+  if (total == 0)
+    return 0u;
+  unsigned base = 0u;
+  if (lane == 31)
+    base = atomicAdd(count, static_cast<unsigned>(total));
+  base = __shfl_sync(0xffffffffu, base, 31);
+  if (base + static_cast<unsigned>(total) > cap) {
+    if (lane == 31)
+      *overflow = 1;
+    return ~0u;
+  }
+  return base + static_cast<unsigned>(incl - n);
+}
+
+// Cell (b, j) went from bounds `was` to bounds `now` (lanes with active == false have no cell): the rows of column j
+// become items of vector b in the lists of parity `nxt` (round `forRound`).  Called by all 32 lanes of a warp
+// together, each with its own cell.  Rows of at most kShortLen nonzeros go to the short list as (b, row) — unless
+// sums are exact (w.exactOk), when every row goes the way of the longer rows: the pair's table slot takes what the
+// change adds to the row's two sums, and the pair is listed (by slot) unless it already is for that round.
+__device__ __forceinline__ void wl_emit_rows(const WlParams &w, bool active, int b, int j, int nxt, int forRound,
+  const Bnd &was, const Bnd &now, int lane)
+{
+  const int cs = active ? __ldg(&w.cscStart[j]) : 0, ce = active ? __ldg(&w.cscStart[j + 1]) : 0;
+  const int trips = __reduce_max_sync(0xffffffffu, (ce - cs + 7) >> 3);
+  for (int t = 0; t < trips; ++t) {
+    const int q0 = cs + 8 * t;
+    int r[8], c[8];
+    unsigned slot[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      r[u] = q0 + u < ce ? __ldg(&w.cscRow[q0 + u]) : -1;
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      c[u] = r[u] >= 0 ? __ldg(&w.bt.rowCnt[r[u]]) : 0;
+    int nS = 0, nL = 0;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      slot[u] = ~0u;
+      if (r[u] < 0)
+        continue;
+      if (c[u] <= kShortLen && !w.exactOk) {
+        ++nS;
+        continue;
+      }
+      const unsigned sl = wl_slot(w, b, r[u]);
+      if (sl == ~0u) {
+        w.ctl->overflow = 1;
+        continue;
+      }
+      if (w.exactOk) {
+        const double a = __ldg(&w.cscVal[q0 + u]);
+        const double dLb = now.lb - was.lb, dUb = now.ub - was.ub;
+        const double dMin = a * (a > 0.0 ? dLb : dUb), dMax = a * (a > 0.0 ? dUb : dLb);
+        if (dMin != 0.0)
+          atomicAdd(&w.hMin[sl], dMin);
+        if (dMax != 0.0)
+          atomicAdd(&w.hMax[sl], dMax);
+      }
+      if (atomicMax(&w.hStamp[sl], forRound + 1) < forRound + 1) {
+        slot[u] = sl;
+        ++nL;
+      }
+    }
+    unsigned atS = wl_warp_reserve(&w.ctl->nS[nxt], w.itemCap, &w.ctl->overflow, nS, lane);
+    unsigned atL = wl_warp_reserve(&w.ctl->nL[nxt], w.itemCap, &w.ctl->overflow, nL, lane);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (r[u] < 0)
+        continue;
+      WlItem it;
+      it.row = r[u];
+      if (c[u] <= kShortLen && !w.exactOk) {
+        if (atS != ~0u) {
+          it.b = b;
+          w.itemsS[nxt][atS++] = it;
+        }
+      } else if (slot[u] != ~0u && atL != ~0u) {
+        it.b = static_cast<int>(slot[u]);
+        w.itemsL[nxt][atL++] = it;
+      }
+    }
   }
 }
 
@@ -263,14 +475,31 @@ __device__ __forceinline__ unsigned wl_append(unsigned *count, unsigned cap, int
 }
 
 #ifndef CBP_WL_BLOCKS
-#define CBP_WL_BLOCKS 3
+#define CBP_WL_BLOCKS 2
 #endif
+
+// a finished row of the base check: violated, or able to tighten something, means the node is no fixpoint
+template <class Tighten>
+__device__ __forceinline__ void wl_base_verdict(const BtParams &p, int row, const RowAct &ra, int *bad, Tighten &&walk)
+{
+  const RowPlan pl = plan_row(ra, __ldg(&p.rowLB[row]), __ldg(&p.rowUB[row]), p.s);
+  if (pl.infeasible)
+    *bad = 1;
+  else if (pl.sideU || pl.sideL)
+    walk(pl);
+}
 
 __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(const WlParams w)
 {
+  __shared__ __align__(16) BtLogEntry s_stage[kWlStage];
+  __shared__ unsigned s_staged, s_base;
+  __shared__ unsigned s_dv[kWarps][64];
   cg::grid_group grid = cg::this_grid();
   const BtParams &p = w.bt;
   WlCtl *ctl = w.ctl;
+  if (threadIdx.x == 0)
+    s_staged = 0u;
+  __syncthreads();
   const int tid = threadIdx.x, lane = tid & 31;
   const unsigned gtid = blockIdx.x * kThreads + tid, gsize = gridDim.x * kThreads;
   const unsigned gwarp = gtid >> 5, nwarps = gsize >> 5;
@@ -293,101 +522,200 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
     const WlBaseReader rd = { p.baseX };
     WlFlagSink fs = { &ctl->baseBad };
     for (unsigned j = gtid; j < static_cast<unsigned>(p.n); j += gsize) {  // R11 on the node's own bounds
-      const Bnd x = rd(j);
+      const Bnd x = rd.get(j);
       double l = x.lb, u = x.ub;
       if (prepass_col(l, u, p.colType[j] != 0, p.s) != 0)
         ctl->baseBad = 1;
     }
-    for (unsigned r = gtid; r < static_cast<unsigned>(p.mKept); r += gsize)
-      if (__ldg(&p.rowCnt[r]) <= kShortLen && wl_row_thread(p, r, rd, fs))
-        ctl->baseBad = 1;
-    for (unsigned r = gwarp; r < static_cast<unsigned>(p.mKept); r += nwarps)
-      if (__ldg(&p.rowCnt[r]) > kShortLen && wl_row_warp(p, r, rd, fs, lane))
-        ctl->baseBad = 1;
+    // the node's sums are kept for the rows whose pairs may later be evaluated as "these + the vector's own cells"
+    for (unsigned r = gtid; r < static_cast<unsigned>(p.mKept); r += gsize) {
+      if (__ldg(&p.rowCnt[r]) > kShortLen)
+        continue;
+      bool whole = false;
+      const RowAct ra = wl_thread_sum<true>(p, r, rd, &whole);
+      if (w.exactOk) {
+        w.rowBaseMin[r] = ra.minAct;
+        w.rowBaseMax[r] = ra.maxAct;
+        w.rowBaseRange[r] = ra.maxRange;
+        w.rowExact[r] = whole ? 1 : 0;
+      }
+      wl_base_verdict(p, r, ra, &ctl->baseBad, [&](const RowPlan &pl) { wl_thread_tighten(p, r, pl, rd, fs); });
+    }
+    for (unsigned r = gwarp; r < static_cast<unsigned>(p.mKept); r += nwarps) {
+      if (__ldg(&p.rowCnt[r]) <= kShortLen)
+        continue;
+      const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
+      RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+      double mag = 0.0;
+      bool whole = true;
+      for (int k0 = kb; k0 < ke; k0 += 128) {  // four nonzeros per lane in flight
+        double a[4];
+        int c[4];
+        Bnd x[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int k = k0 + 32 * u + lane;
+          a[u] = 0.0;
+          c[u] = 0;
+          if (k < ke) {
+            c[u] = __ldg(&p.col[k]);
+            a[u] = __ldg(&p.val[k]);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          x[u] = rd.get(col_of(c[u]));
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (a[u] != 0.0) {
+            accumulate(ra, a[u], col_is_int(c[u]), a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
+            mag += fabs(a[u]) * fmax(fabs(x[u].lb), fabs(x[u].ub));
+            whole = whole && col_is_int(c[u]) && a[u] == floor(a[u]) && x[u].lb == floor(x[u].lb) && x[u].ub == floor(x[u].ub);
+          }
+      }
+      warp_reduce(ra);
+#pragma unroll
+      for (int m = 16; m >= 1; m >>= 1)
+        mag += __shfl_xor_sync(0xffffffffu, mag, m);
+      whole = __all_sync(0xffffffffu, whole) && mag < 1.0e15 && ra.infMin + ra.infMax == 0;
+      if (lane == 0) {
+        w.rowBaseMin[r] = ra.minAct;
+        w.rowBaseMax[r] = ra.maxAct;
+        w.rowBaseRange[r] = ra.maxRange;
+        w.rowExact[r] = whole ? 1 : 0;
+      }
+      wl_base_verdict(p, r, ra, &ctl->baseBad, [&](const RowPlan &pl) { wl_row_warp_tighten(p, r, pl, rd, fs, lane); });
+    }
   }
   grid.sync();
+  wl_stamp(ctl, gtid);
   if (*reinterpret_cast<volatile int *>(&ctl->baseBad)) {
     if (gtid == 0)
       ctl->status = kWlBaseNotFixpoint;
     return;
   }
 
-  // ---- phase 0b: the diffs.  One thread per vector, diffs applied in order; the cells they touch are created
-  // (mask bit, both buffers), get R11, and their columns' rows are the items of the first round.
-  for (unsigned b = gtid; b < static_cast<unsigned>(w.B); b += gsize) {
+  // ---- phase 0b: the diffs.  One warp per vector, one lane per diff.  Applying the diffs in order means: a bound
+  // ends at the LAST diff that names it; so a lane writes its value unless a later diff names the same bound.  The
+  // first diff of a column creates the cell (mask bit, both buffers = the node's bounds), gives it R11 once all
+  // diffs are in, and lists the column's rows as items of the first round.
+  for (unsigned b = gwarp; b < static_cast<unsigned>(w.B); b += nwarps) {
     const long long k0 = w.dStart[b], k1 = w.dStart[b + 1];
+    // (the lanes look through the vector's other diffs several times: up to 64 of them are kept in shared memory)
+    unsigned *dv = s_dv[tid >> 5];
+    const bool stagedDiffs = k1 - k0 <= 64;
+    __syncwarp();
+    if (stagedDiffs)
+      for (int q = lane; q < static_cast<int>(k1 - k0); q += 32)
+        dv[q] = w.dVar[k0 + q];
+    __syncwarp();
+    auto var_at = [&](long long q) -> unsigned { return stagedDiffs ? dv[q - k0] : w.dVar[q]; };
     unsigned *dmaskW = const_cast<unsigned *>(p.dmask);
     const unsigned bit = 1u << (b & 31);
-    for (long long k = k0; k < k1; ++k) {
-      const unsigned v = w.dVar[k];
+    for (long long c0 = k0; c0 < k1; c0 += 32) {
+      const long long k = c0 + lane;
+      const bool have = k < k1;
+      const unsigned v = have ? var_at(k) : 0u;
       const int j = diff_col(v);
-      if (j >= p.n)
-        continue;
-      const size_t at = bt_cell(p, j, b);
-      unsigned *word = &dmaskW[bt_word(p, j, b >> 5)];
-      const bool had = (*reinterpret_cast<volatile unsigned *>(word) & bit) != 0u;  // (own bit: set by this thread only)
-      Bnd x = had ? p.X[0][at] : p.baseX[j];
-      if (!had) {
-        atomicOr(word, bit);
-        const unsigned ci = atomicAdd(&ctl->nCells, 1u);
-        if (ci < w.cellCap) {
+      const bool valid = have && j < p.n;
+      bool first = valid, last = valid;
+      if (valid) {
+        for (long long q = k0; q < k && first; ++q)
+          first = diff_col(var_at(q)) != j;
+        for (long long q = k + 1; q < k1 && last; ++q)
+          last = !(diff_col(var_at(q)) == j && ((var_at(q) ^ v) & kDiffUpper) == 0u);
+      }
+      const size_t at = valid ? bt_cell(p, j, b) : 0;
+      if (first) {
+        const Bnd nb = p.baseX[j];
+        p.X[0][at] = nb;
+        p.X[1][at] = nb;
+        atomicOr(&dmaskW[bt_word(p, j, b >> 5)], bit);
+        const unsigned ci = wl_append(&ctl->nCells, w.cellCap, &ctl->overflow);
+        if (ci != ~0u) {
           WlCell c;
           c.b = b;
           c.j = j;
           w.cells[ci] = c;
-        } else {
-          ctl->overflow = 1;
         }
       }
-      if (v & kDiffUpper)
-        x.ub = w.dBnd[k] + 0.0;
-      else
-        x.lb = w.dBnd[k] + 0.0;
-      p.X[0][at] = x;
-      p.X[1][at] = x;
-    }
-    bool dead = false;
-    for (long long k = k0; k < k1; ++k) {
-      const int j = diff_col(w.dVar[k]);
-      if (j >= p.n)
-        continue;
-      const size_t at = bt_cell(p, j, b);
-      Bnd x = p.X[0][at];
-      const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);
-      if (r == 2) {
-        atomicMin(&p.vecInfCol[b], j);
-        dead = true;
-      } else if (r == 1) {
-        p.X[0][at] = x;
-        p.X[1][at] = x;
-        const unsigned old = atomicOr(&p.dirty[0][bt_word(p, j, b >> 5)], bit);
-        if (!(old & bit)) {
-          const unsigned ki = atomicAdd(&ctl->nK, 1u);
-          if (ki < w.kCap) {
-            WlCell c;
-            c.b = b;
-            c.j = j;
-            w.K[ki] = c;
+      __syncwarp();
+      if (valid) {
+        const double nv = w.dBnd[k] + 0.0;
+        const Bnd nb = p.baseX[j];  // exact sums need every bound of the vector to be an integer inside the node's bounds
+        if (!(nv == floor(nv) && nv >= nb.lb && nv <= nb.ub))
+          ctl->inexact = 1;
+        if (last) {
+          if (v & kDiffUpper) {
+            p.X[0][at].ub = nv;
+            p.X[1][at].ub = nv;
           } else {
-            ctl->overflow = 1;
+            p.X[0][at].lb = nv;
+            p.X[1][at].lb = nv;
+          }
+        }
+      }
+      __syncwarp();
+    }
+    // R11 on the cells (one lane per cell: the lane of the column's first diff)
+    bool dead = false;
+    for (long long c0 = k0; c0 < k1; c0 += 32) {
+      const long long k = c0 + lane;
+      const int j = k < k1 ? diff_col(var_at(k)) : p.n;
+      bool first = j < p.n;
+      for (long long q = k0; q < k && first; ++q)
+        first = diff_col(var_at(q)) != j;
+      if (first) {
+        const size_t at = bt_cell(p, j, b);
+        Bnd x = p.X[0][at];
+        const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);
+        if (r == 2) {
+          atomicMin(&p.vecInfCol[b], j);
+          dead = true;
+        } else if (r == 1) {
+          p.X[0][at] = x;
+          p.X[1][at] = x;
+          const unsigned old = atomicOr(&p.dirty[0][bt_word(p, j, b >> 5)], bit);
+          if (!(old & bit)) {
+            const unsigned ki = wl_append(&ctl->nK, w.kCap, &ctl->overflow);
+            if (ki != ~0u) {
+              WlCell c;
+              c.b = b;
+              c.j = j;
+              w.K[ki] = c;
+            }
           }
         }
       }
     }
+    dead = __any_sync(0xffffffffu, dead);
     if (dead) {  // the input already crosses (R11): stops before its first round
-      p.vecStop[b] = 4;
-      p.vecRounds[b] = 1;
-      p.vecFinal[b] = 0;
-      atomicAnd(&w.active2[0][b >> 5], ~bit);
-    } else {
-      for (long long k = k0; k < k1; ++k) {
-        const int j = diff_col(w.dVar[k]);
-        if (j < p.n)
-          wl_emit_rows(w, b, j, 0);
+      if (lane == 0) {
+        p.vecStop[b] = 4;
+        p.vecRounds[b] = 1;
+        p.vecFinal[b] = 0;
+        atomicAnd(&w.active2[0][b >> 5], ~bit);
       }
+      continue;
+    }
+    __syncwarp();
+    for (long long c0 = k0; c0 < k1; c0 += 32) {
+      const long long k = c0 + lane;
+      const int j = k < k1 ? diff_col(var_at(k)) : p.n;
+      bool first = j < p.n;
+      for (long long q = k0; q < k && first; ++q)
+        first = diff_col(var_at(q)) != j;
+      Bnd was, now;
+      was.lb = was.ub = now.lb = now.ub = 0.0;
+      if (first) {
+        was = p.baseX[j];
+        now = p.X[0][bt_cell(p, j, b)];
+      }
+      wl_emit_rows(w, first, b, first ? j : 0, 0, 0, was, now, lane);
     }
   }
   grid.sync();
+  wl_stamp(ctl, gtid);
 
   // ---- the rounds
   int round = 0;
@@ -401,29 +729,121 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
     const unsigned nS = *reinterpret_cast<volatile unsigned *>(&ctl->nS[cur]);
     const unsigned nL = *reinterpret_cast<volatile unsigned *>(&ctl->nL[cur]);
     const Bnd *srcX = p.X[cur];
-    // P1: the items
+    // P1a: short-row items, one thread each
     for (unsigned i = gtid; i < nS; i += gsize) {
       const WlItem it = w.itemsS[cur][i];
       const WlVecReader rd = { &p, srcX + bt_base32(p, it.b), p.dmask + bt_word(p, 0, it.b >> 5), it.b & 31 };
-      WlLogSink sink = { p.log, &ctl->nLog, p.logCap, &ctl->overflowP1, it.b };
-      if (wl_row_thread(p, it.row, rd, sink))
+      const RowAct ra = wl_thread_sum<false>(p, it.row, rd, nullptr);
+      const RowPlan pl = plan_row(ra, __ldg(&p.rowLB[it.row]), __ldg(&p.rowUB[it.row]), p.s);
+      if (pl.infeasible) {
         atomicMin(&p.vecInfRow[it.b], __ldg(&p.rowOrig[it.row]));
+      } else if (pl.sideU || pl.sideL) {
+        WlLogSink sink = { p.log, &ctl->nLog, p.logCap, &ctl->overflowP1, it.b, s_stage, &s_staged };
+        wl_thread_tighten(p, it.row, pl, rd, sink);
+      }
       myPairs += __ldg(&p.rowCnt[it.row]);
     }
-    for (unsigned i = gwarp; i < nL; i += nwarps) {
-      const WlItem it = w.itemsL[cur][i];
-      const WlVecReader rd = { &p, srcX + bt_base32(p, it.b), p.dmask + bt_word(p, 0, it.b >> 5), it.b & 31 };
-      WlLogSink sink = { p.log, &ctl->nLog, p.logCap, &ctl->overflowP1, it.b };
-      if (wl_row_warp(p, it.row, rd, sink, lane) && lane == 0)
-        atomicMin(&p.vecInfRow[it.b], __ldg(&p.rowOrig[it.row]));
-      if (lane == 0)
-        myPairs += __ldg(&p.rowCnt[it.row]);
+    // P1b: pairs listed by table slot, one lane each; what needs a warp (a long row's walk) is done by the warp,
+    // one pair after the other
+    const bool exact = w.exactOk && !*reinterpret_cast<volatile int *>(&ctl->inexact);
+    // (neighbours in the list are one vector's rows and tend to need the same amount of work: a warp takes items that
+    // lie nwarps apart, so the expensive ones spread over all warps)
+    for (unsigned t0 = 0; t0 * nwarps < nL; t0 += 32) {
+      const unsigned i = (t0 + lane) * nwarps + gwarp;
+      const bool have = i < nL;
+      WlItem it;
+      it.b = 0;
+      it.row = 0;
+      if (have)
+        it = w.itemsL[cur][i];
+      const unsigned slot = static_cast<unsigned>(it.b);
+      const int b = have ? static_cast<int>((__ldcg(&w.hKey[slot]) - 1ull) >> 32) : 0;
+      const int row = it.row;
+      const int cnt = have ? __ldg(&p.rowCnt[row]) : 0;
+      const WlVecReader rd = { &p, srcX + bt_base32(p, b), p.dmask + bt_word(p, 0, b >> 5), b & 31 };
+      RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+      bool needSum = have;
+      if (have && exact && __ldg(&w.rowExact[row])) {
+        ra.minAct = __ldcg(&w.rowBaseMin[row]) + __ldcg(&w.hMin[slot]);
+        ra.maxAct = __ldcg(&w.rowBaseMax[row]) + __ldcg(&w.hMax[slot]);
+        ra.maxRange = __ldcg(&w.rowBaseRange[row]);  // (the node's: an upper bound of the vector's, all R6's shortcut needs)
+        needSum = false;
+      }
+      if (needSum && cnt <= kShortLen) {
+        ra = wl_thread_sum<false>(p, row, rd, nullptr);
+        myPairs += cnt;
+        needSum = false;
+      }
+      unsigned todo = __ballot_sync(0xffffffffu, needSum);
+      while (todo) {
+        const int l = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int rb = __shfl_sync(0xffffffffu, b, l), rr = __shfl_sync(0xffffffffu, row, l);
+        const WlVecReader rd2 = { &p, srcX + bt_base32(p, rb), p.dmask + bt_word(p, 0, rb >> 5), rb & 31 };
+        const RowAct r2 = wl_row_warp_sum(p, rr, rd2, lane);
+        if (lane == l) {
+          ra = r2;
+          myPairs += cnt;
+        }
+      }
+      RowPlan pl = plan_row(ra, have ? __ldg(&p.rowLB[row]) : 0.0, have ? __ldg(&p.rowUB[row]) : 0.0, p.s);
+      if (!have) {
+        pl.infeasible = false;
+        pl.sideU = false;
+        pl.sideL = false;
+      }
+      if (pl.infeasible)
+        atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[row]));
+      bool tight = !pl.infeasible && (pl.sideU || pl.sideL);
+      if (tight && cnt <= kShortLen) {
+        WlLogSink sink = { p.log, &ctl->nLog, p.logCap, &ctl->overflowP1, b, s_stage, &s_staged };
+        wl_thread_tighten(p, row, pl, rd, sink);
+        myPairs += cnt;
+        tight = false;
+      }
+      todo = __ballot_sync(0xffffffffu, tight);
+      while (todo) {
+        const int l = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int rb = __shfl_sync(0xffffffffu, b, l), rr = __shfl_sync(0xffffffffu, row, l);
+        RowPlan q;
+        q.slackU = __shfl_sync(0xffffffffu, pl.slackU, l);
+        q.slackL = __shfl_sync(0xffffffffu, pl.slackL, l);
+        q.infMin = __shfl_sync(0xffffffffu, pl.infMin, l);
+        q.infMax = __shfl_sync(0xffffffffu, pl.infMax, l);
+        q.sideU = __shfl_sync(0xffffffffu, pl.sideU ? 1 : 0, l) != 0;
+        q.sideL = __shfl_sync(0xffffffffu, pl.sideL ? 1 : 0, l) != 0;
+        q.infeasible = false;
+        const WlVecReader rd2 = { &p, srcX + bt_base32(p, rb), p.dmask + bt_word(p, 0, rb >> 5), rb & 31 };
+        WlLogSink sink = { p.log, &ctl->nLog, p.logCap, &ctl->overflowP1, rb, s_stage, &s_staged };
+        wl_row_warp_tighten(p, rr, q, rd2, sink, lane);
+        if (lane == l)
+          myPairs += cnt;
+      }
+    }
+    // the CTA's staged candidates go to the global list: one reservation
+    __syncthreads();
+    {
+      const unsigned n = min(s_staged, kWlStage);
+      if (tid == 0 && n)
+        s_base = atomicAdd(&ctl->nLog, n);
+      __syncthreads();
+      for (unsigned i = tid; i < n; i += kThreads) {
+        if (s_base + i < p.logCap)
+          p.log[s_base + i] = s_stage[i];
+        else
+          ctl->overflowP1 = 1;
+      }
+      __syncthreads();
+      if (tid == 0)
+        s_staged = 0u;
     }
     if (gtid == 0) {
       ctl->itemsTotal += nS + nL;
       ctl->anyActive[nxt] = 0;
     }
     grid.sync();
+    wl_stamp(ctl, gtid);
     if (*reinterpret_cast<volatile int *>(&ctl->overflowP1)) {  // (P1 is over: nobody writes this word now)
       status = kWlOverflow;
       break;
@@ -457,6 +877,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         }
       }
       grid.sync();
+      wl_stamp(ctl, gtid);
       // P3: the candidates, applied as the direct sink would have; whoever marks a cell first lists it
       for (unsigned i = gtid; i < nLog; i += gsize) {
         const BtLogEntry e = p.log[i];
@@ -479,6 +900,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         }
       }
       grid.sync();
+      wl_stamp(ctl, gtid);
       // P4: R9 per changed cell, counts per vector
       const unsigned nK4 = min(*reinterpret_cast<volatile unsigned *>(&ctl->nK), w.kCap);
       for (unsigned i = gtid; i < nK4; i += gsize) {
@@ -500,6 +922,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
           ctl->timeUp = 1;
       }
       grid.sync();
+      wl_stamp(ctl, gtid);
     }
     // P5: per-vector bookkeeping of src/CbcBoundPropagation.cpp:129-189; P6: carry + next round's items
     const int timeUp = *reinterpret_cast<volatile int *>(&ctl->timeUp);
@@ -530,7 +953,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         }
       }
       w.vecChanged2[nxt][b] = 0;
-      const unsigned m = __ballot_sync(0xffffffffu, on);  // (Bp is a multiple of 32 and the stride of 32: whole warps)
+      const unsigned m = __ballot_sync(0xffffffffu, on);  // (Bp and the stride are multiples of 32: whole warps)
       if (lane == 0) {
         w.active2[nxt][b >> 5] = m;
         if (m)
@@ -538,22 +961,35 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       }
     }
     const unsigned nK6 = min(*reinterpret_cast<volatile unsigned *>(&ctl->nK), w.kCap);
-    for (unsigned i = gtid; i < nK6; i += gsize) {
-      const WlCell c = w.K[i];
-      const size_t word = bt_word(p, c.j, c.b >> 5);
-      const unsigned bit = 1u << (c.b & 31);
-      atomicAnd(&p.dirty[cur][word], ~bit);
-      const bool applied = p.vecInfRow[c.b] == 0x7fffffff && p.vecInfCol[c.b] == 0x7fffffff;
-      if (!applied)
-        continue;
-      atomicOr(&p.ever[word], bit);
-      if (round + 1 >= w.limit || timeUp)
-        continue;
-      const size_t at = bt_cell(p, c.j, c.b);
-      p.X[cur][at] = p.X[nxt][at];
-      wl_emit_rows(w, c.b, c.j, nxt);
+    for (unsigned i0 = gwarp << 5; i0 < nK6; i0 += nwarps << 5) {  // (whole warps: the listing below is a warp's job)
+      const unsigned i = i0 + lane;
+      bool go = false;
+      WlCell c;
+      c.b = 0;
+      c.j = 0;
+      Bnd was, now;
+      was.lb = was.ub = now.lb = now.ub = 0.0;
+      if (i < nK6) {
+        c = w.K[i];
+        const size_t word = bt_word(p, c.j, c.b >> 5);
+        const unsigned bit = 1u << (c.b & 31);
+        atomicAnd(&p.dirty[cur][word], ~bit);
+        const bool applied = p.vecInfRow[c.b] == 0x7fffffff && p.vecInfCol[c.b] == 0x7fffffff;
+        if (applied) {
+          atomicOr(&p.ever[word], bit);
+          if (!(round + 1 >= w.limit || timeUp)) {
+            const size_t at = bt_cell(p, c.j, c.b);
+            was = p.X[cur][at];
+            now = p.X[nxt][at];
+            p.X[cur][at] = now;
+            go = true;
+          }
+        }
+      }
+      wl_emit_rows(w, go, c.b, c.j, nxt, round + 1, was, now, lane);
     }
     grid.sync();
+    wl_stamp(ctl, gtid);
     if (gtid == 0)
       ctl->nK = 0u;
     if (!*reinterpret_cast<volatile int *>(&ctl->anyActive[nxt])) {

@@ -167,3 +167,19 @@ def test_worklist_item_list_overflow_hands_over():
     out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, CBP_WL_ITEM_CAP="500"),
                          capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
+
+
+def test_worklist_long_integer_rows_exact_sums(oracle, gpu_ctx):
+    """All-integer matrix with rows of several hundred nonzeros: a (vector, row) pair's sums are the node's sums plus
+    what the vector's own cells add (exact in any order), so hardly any pair is walked; a fractional diff switches
+    the same batch to walking the rows — both must equal the oracle."""
+    inst = _node(oracle, I.knapsack_assignment(m=60, n=4000, seed=71, root_fixpoint=True, slack_max=0))
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 80, max_depth=40, seed=72, follow_xstar=0.5)
+    res, st = _check(oracle, gpu_ctx, inst, s, v, b, "long integer rows")
+    assert (res["feasible"] == 0).any() and res["nChanged"].sum() > 1000
+    exact_pairs = st["lastPairsWalked"]
+    b2 = b.copy()
+    k = int(np.flatnonzero((v & I.UPPER_FLAG) != 0)[0])
+    b2[k] = b2[k] + 0.5  # a fractional upper bound on an integer column: R11 rounds it back down
+    res2, st2 = _check(oracle, gpu_ctx, inst, s, v, b2, "long integer rows, fractional diff")
+    assert st2["lastPairsWalked"] > 2 * exact_pairs
