@@ -1337,6 +1337,11 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.cscStart = mat->cscStart;
   w.cscRow = mat->cscRow;
   w.cscVal = mat->cscVal;
+  w.sellVal = mat->sellVal;
+  w.sellCol = mat->sellCol;
+  w.sellOff = mat->sellOff;
+  w.nSlices = mat->nSlices;
+  w.mShort = mat->mShort;
   w.hKey = bt.wlHKey;
   w.hMin = bt.wlHMin;
   w.hMax = bt.wlHMax;

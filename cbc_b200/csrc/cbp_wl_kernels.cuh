@@ -63,6 +63,11 @@ struct WlParams {
   BtParams bt;
   const int *cscStart, *cscRow;
   const double *cscVal;
+  // sliced-ELL copy of the rows of at most kShortLen nonzeros (slice = 32 rows, entry k of lane l at
+  // sellOff[s] + 32 k + l): the base check reads them coalesced
+  const double *sellVal;
+  const int *sellCol, *sellOff;
+  int nSlices, mShort;
   // Rows longer than kShortLen: one table slot per (vector, row) pair that has come up, found by hashing.  It keeps
   // an item from being listed twice in a round and, where sums are exact (see exactOk), the pair's activity as
   // "the node's sums + what the vector's own cells add".
@@ -528,16 +533,45 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         ctl->baseBad = 1;
     }
     // the node's sums are kept for the rows whose pairs may later be evaluated as "these + the vector's own cells"
-    for (unsigned r = gtid; r < static_cast<unsigned>(p.mKept); r += gsize) {
-      if (__ldg(&p.rowCnt[r]) > kShortLen)
+    for (unsigned sl = gwarp; sl < static_cast<unsigned>(w.nSlices); sl += nwarps) {  // short rows: lane = row of a slice
+      const int off = __ldg(&w.sellOff[sl]), len = (__ldg(&w.sellOff[sl + 1]) - off) >> 5;
+      const int r = (sl << 5) + lane;
+      const bool valid = r < w.mShort;
+      const double *__restrict__ sv = w.sellVal + off + lane;
+      const int *__restrict__ sc = w.sellCol + off + lane;
+      RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+      double mag = 0.0;
+      bool whole = true;
+      for (int k = 0; k < len; k += kWlChunk) {
+        double a[kWlChunk];
+        int cj[kWlChunk], jj[kWlChunk];
+        Bnd x[kWlChunk];
+#pragma unroll
+        for (int u = 0; u < kWlChunk; ++u) {
+          a[u] = 0.0;
+          cj[u] = 0;
+          if (k + u < len) {
+            cj[u] = __ldg(&sc[(k + u) << 5]);
+            a[u] = __ldg(&sv[(k + u) << 5]);
+          }
+          jj[u] = col_of(cj[u]);
+        }
+        rd.get_n(jj, x);
+#pragma unroll
+        for (int u = 0; u < kWlChunk; ++u)
+          if (a[u] != 0.0) {  // (padding has a == 0)
+            accumulate_fast(ra, a[u], col_is_int(cj[u]), x[u], p.s.inf);
+            mag += fabs(a[u]) * fmax(fabs(x[u].lb), fabs(x[u].ub));
+            whole = whole && col_is_int(cj[u]) && a[u] == floor(a[u]) && x[u].lb == floor(x[u].lb) && x[u].ub == floor(x[u].ub);
+          }
+      }
+      if (!valid)
         continue;
-      bool whole = false;
-      const RowAct ra = wl_thread_sum<true>(p, r, rd, &whole);
       if (w.exactOk) {
         w.rowBaseMin[r] = ra.minAct;
         w.rowBaseMax[r] = ra.maxAct;
         w.rowBaseRange[r] = ra.maxRange;
-        w.rowExact[r] = whole ? 1 : 0;
+        w.rowExact[r] = (whole && mag < 1.0e15 && ra.infMin + ra.infMax == 0) ? 1 : 0;
       }
       wl_base_verdict(p, r, ra, &ctl->baseBad, [&](const RowPlan &pl) { wl_thread_tighten(p, r, pl, rd, fs); });
     }

@@ -1,5 +1,5 @@
-"""GPU, at BASELINE.json's full sizes: properties that do not need the CPU oracle to finish (it would take
-minutes), plus oracle checks on a bounded sample of the same inputs."""
+"""GPU, at BASELINE.json's full sizes, against the CPU oracle: whole instances for the single-vector configs, all
+vectors' verdicts plus a sample's bounds for the batches; and size-independent properties beside them."""
 import numpy as np
 import pytest
 
@@ -50,11 +50,55 @@ def test_c2_full_batch_4096_vectors(oracle, gpu_ctx):
     mat.close()
 
 
-def test_c3_full_single_vector_1m(gpu_ctx):
-    """1M x 1M, 10M nnz mixed-integer (BASELINE config 3): sound, monotone, idempotent."""
+KEYS = ("feasible", "rounds", "nChanged", "infeasibleRow", "infeasibleCol", "stopReason")
+
+
+def _batch_against_oracle(oracle, ctx, mat, inst, lb, ub, s, v, b, sample, what, want_mode=None):
+    """all vectors' verdicts, and the dense bounds of the first `sample` vectors, against the oracle"""
+    import os
+
+    res, us, uc, ul, uu = mat.propagate_batch_delta(lb, ub, s, v, b)
+    if want_mode is not None:
+        assert ctx.stats()["lastMode"] == want_mode, ctx.stats()
+    prob = oracle.Problem(inst)
+    threads = max(1, len(os.sched_getaffinity(0)))
+    ores, _, _ = oracle.propagate_batch_delta(prob, lb, ub, s, v, b, threads=threads, want_bounds=False)
+    for k in KEYS:
+        bad = np.flatnonzero(res[k] != ores[k])
+        assert bad.size == 0, f"{what}: {k} differs for vectors {bad[:8]}: {res[k][bad[:8]]} vs {ores[k][bad[:8]]}"
+    k = sample
+    _, Lo, Uo = oracle.propagate_batch_delta(prob, lb, ub, s[:k + 1], v[:s[k]], b[:s[k]], threads=threads)
+    for i in range(k):
+        if not res["feasible"][i]:
+            assert us[i + 1] == us[i]
+            continue
+        l, u = np.array(lb), np.array(ub)
+        for q in range(s[i], s[i + 1]):
+            j = int(v[q] & I.COL_MASK)
+            if v[q] & I.UPPER_FLAG:
+                u[j] = b[q]
+            else:
+                l[j] = b[q]
+        cols = uc[us[i]:us[i + 1]]
+        l_in, u_in = l.copy(), u.copy()
+        l[cols], u[cols] = ul[us[i]:us[i + 1]], uu[us[i]:us[i + 1]]
+        assert_same_bounds(inst.colType, l, u, Lo[i], Uo[i], f"{what} vector {i}")
+        assert np.array_equal(cols, np.flatnonzero((l != l_in) | (u != u_in))), f"{what} vector {i}: update list"
+
+    return res
+
+
+def test_c3_full_single_vector_1m_and_dive_batch(oracle, gpu_ctx):
+    """1M x 1M, 10M nnz mixed-integer (BASELINE config 3): the whole fixpoint run against the oracle (round by round
+    counts, every bound); sound, monotone, idempotent; then the north-star shape, a batch of dive vectors from the
+    propagated root on the same matrix (c3b), all vectors against the oracle."""
     inst = I.mixed_bigm()
     mat = capi.Matrix(gpu_ctx, inst)
     r1, l1, u1 = mat.propagate(inst.lb, inst.ub)
+    ro, lo, uo = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    assert_same_result(r1, ro, "c3")
+    assert r1["roundChanged"] == ro["roundChanged"]
+    assert_same_bounds(inst.colType, l1, u1, lo, uo, "c3")
     assert r1["feasible"] and r1["stopReason"] == 1 and r1["rounds"] > 5
     assert inst.contains(l1, u1)
     assert np.all(l1 >= inst.lb) and np.all(u1 <= inst.ub)
@@ -67,6 +111,26 @@ def test_c3_full_single_vector_1m(gpu_ctx):
     r3, l3, u3 = mat.propagate(inst.lb, inst.ub, max_rounds=3)
     assert r3["stopReason"] == 2 and r3["nChanged"] == sum(r1["roundChanged"][:3])
     assert np.all(l3 <= l1) and np.all(u3 >= u1)
+    # c3b: node bounds = the oracle's propagated root, 96 dive vectors (worklist form)
+    s, v, b = I.dive_deltas(inst, lo, uo, 96, max_depth=16, seed=I.SEED0 + 300)
+    res = _batch_against_oracle(oracle, gpu_ctx, mat, inst, lo, uo, s, v, b, 8, "c3b", want_mode=2)
+    assert res["rounds"].max() >= 5 and res["nChanged"].sum() > 1000
+    mat.close()
+
+
+def test_c4_full_knapsack_assignment_dive_batches(oracle, gpu_ctx):
+    """200k x 500k, 3M nnz (BASELINE config 4): 2,048 dive vectors from the propagated root (worklist form) and 256
+    from the unpropagated root (every row can act for every vector: the full-walk overlay kernels)."""
+    inst = I.knapsack_assignment(root_fixpoint=True)
+    r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    assert r0["feasible"] and r0["nChanged"] > 0  # (a few one-column assignment rows fix their column)
+    mat = capi.Matrix(gpu_ctx, inst)
+    s, v, b = I.dive_deltas(inst, lb0, ub0, 2048, max_depth=64, seed=I.SEED0 + 200)
+    res = _batch_against_oracle(oracle, gpu_ctx, mat, inst, lb0, ub0, s, v, b, 64, "c4 node", want_mode=2)
+    assert res["nChanged"].sum() > 10000 and res["rounds"].max() >= 3
+    s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 256, max_depth=64, seed=I.SEED0 + 201)
+    res = _batch_against_oracle(oracle, gpu_ctx, mat, inst, inst.lb, inst.ub, s, v, b, 32, "c4 root", want_mode=1)
+    assert res["nChanged"].min() > 0
     mat.close()
 
 
