@@ -562,7 +562,7 @@ class Bench:
             sm_mhz = clk.summary().get("sm_mhz") or 1965
             fp64_peak = self.props.multi_processor_count * 64 * 2 * sm_mhz * 1e6 / 1e12  # DFMA: 64 per clock and SM
             pairs = st.get("lastPairsWalked")
-            if not pairs and st.get("lastFromBase"):
+            if not pairs and st.get("lastMode", 1) == 1 and st.get("lastFromBase"):
                 # full-walk overlay rounds: every (nonzero, vector) pair of every launched round, vectors padded to the
                 # 128 a warp carries
                 pairs = float(inst.nnz) * ((work["B"] + 127) // 128 * 128) * round_launches

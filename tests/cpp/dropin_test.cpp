@@ -1,6 +1,7 @@
 // dropin_test.cpp — drives the C++ drop-ins the way Cbc's callers do, on top
 // of the COIN test double.  Usage:
-//   cbp_dropin_test <instance.bin> <out.bin> <level 1|2|3> <maxRounds> <logLevel> <timeLimit> [dive | strong <cands.bin>]
+//   cbp_dropin_test <instance.bin> <out.bin> <level 1|2|3> <maxRounds> <logLevel> <timeLimit>
+//                   [dive | strong <cands.bin> | probe <maxProbes> | divebatch <bounds.bin> | bench <reps>]
 // Prints one "RESULT {json}" line; writes the solver's final column bounds to
 // out.bin (n doubles lb, n doubles ub).  With "dive" it instead performs the
 // single-round CoinBoundPropagation step of CbcHeuristicDive
@@ -13,7 +14,11 @@
 #include <string>
 #include <vector>
 
+#include <thread>
+
 #include "CbcBoundPropagation.hpp"
+#include "CbcDiveBatch.hpp"
+#include "CbcProbePropagation.hpp"
 #include "CbcStrongPropagation.hpp"
 #include "CoinBoundPropagation.hpp"
 #include "OsiSolverInterface.hpp"
@@ -194,6 +199,140 @@ int main(int argc, char **argv)
       }
     if (o)
       fclose(o);
+    cbpReleaseThreadCache();
+    return 0;
+  }
+
+  if (argc > 8 && !strcmp(argv[7], "probe")) {
+    // the probing sweep of fixVubs (src/CbcSolverHeuristics.cpp:265-490) as one batch, consequences applied to the solver
+    CbcProbePropagation pp;
+    const bool ran = pp.run(&solver, 0, nullptr, atoi(argv[8]), maxRounds);
+    FILE *o = fopen(argv[2], "wb");
+    int nb = static_cast<int>(pp.nodeBounds().size()), np = pp.numberProbed();
+    fwrite(&np, 4, 1, o);
+    for (int k = 0; k < np; ++k) {
+      int rec[3] = { pp.column(k), pp.infeasible(k, CbcProbePropagation::Down) ? 1 : 0,
+        pp.infeasible(k, CbcProbePropagation::Up) ? 1 : 0 };
+      fwrite(rec, 4, 3, o);
+    }
+    fwrite(&nb, 4, 1, o);
+    for (const auto &e : pp.nodeBounds()) {
+      double rec[3] = { static_cast<double>(e.first), e.second.first, e.second.second };
+      fwrite(rec, 8, 3, o);
+    }
+    const int moved = pp.apply(&solver);
+    fwrite(solver.lb.data(), 8, solver.lb.size(), o);
+    fwrite(solver.ub.data(), 8, solver.ub.size(), o);
+    fclose(o);
+    printf("RESULT {\"probe\": 1, \"ran\": %d, \"numberProbed\": %d, \"failedProbes\": %d, \"nodeInfeasible\": %d, "
+           "\"nodeBounds\": %d, \"moved\": %d}\n",
+      ran ? 1 : 0, np, pp.numberFailedProbes(), pp.nodeInfeasible() ? 1 : 0, nb, moved);
+    cbpReleaseThreadCache();
+    return 0;
+  }
+  if (argc > 8 && !strcmp(argv[7], "divebatch")) {
+    // T dive threads as CbcDiveScheduler::runParallel starts them (src/CbcDiveScheduler.cpp:158-214); every thread walks
+    // through its own sequence of bound vectors (one per dive iteration) and stops at the first infeasible one.
+    // bounds.bin: int32 T, then per dive: int32 count, count x (n doubles lb, n doubles ub)
+    FILE *c = fopen(argv[8], "rb");
+    int T = 0;
+    if (!c || fread(&T, 4, 1, c) != 1 || T <= 0)
+      return 2;
+    const size_t n = solver.lb.size();
+    std::vector<std::vector<double> > seq(T);
+    std::vector<int> count(T);
+    for (int t = 0; t < T; ++t) {
+      if (fread(&count[t], 4, 1, c) != 1)
+        return 2;
+      seq[t].resize(static_cast<size_t>(count[t]) * 2 * n);
+      if (fread(seq[t].data(), 8, seq[t].size(), c) != seq[t].size())
+        return 2;
+    }
+    fclose(c);
+    CbcDiveBatch batch(&solver, T, maxRounds);
+    struct Rec {
+      int feasible, row, col;
+      CbcDiveBatch::BoundList upd;
+    };
+    std::vector<std::vector<Rec> > out(T);
+    std::vector<std::thread> threads;
+    for (int t = 0; t < T; ++t)
+      threads.emplace_back([&, t]() {
+        for (int w = 0; w < count[t]; ++w) {
+          Rec r;
+          const double *lb = seq[t].data() + static_cast<size_t>(w) * 2 * n, *ub = lb + n;
+          r.feasible = batch.propagate(t, lb, ub, r.upd, r.row, r.col) ? 1 : 0;
+          out[t].push_back(r);
+          if (!r.feasible)
+            break;  // reasonToStop = 1 in CbcHeuristicDive::solution
+        }
+        batch.finish(t);
+      });
+    for (auto &th : threads)
+      th.join();
+    FILE *o = fopen(argv[2], "wb");
+    long long total = 0;
+    for (int t = 0; t < T; ++t) {
+      const int steps = static_cast<int>(out[t].size());
+      fwrite(&steps, 4, 1, o);
+      for (const Rec &r : out[t]) {
+        int head[4] = { r.feasible, r.row, r.col, static_cast<int>(r.upd.size()) };
+        fwrite(head, 4, 4, o);
+        for (const auto &e : r.upd) {
+          double rec[3] = { static_cast<double>(e.first), e.second.first, e.second.second };
+          fwrite(rec, 8, 3, o);
+        }
+        ++total;
+      }
+    }
+    fclose(o);
+    printf("RESULT {\"divebatch\": 1, \"usable\": %d, \"dives\": %d, \"waves\": %d, \"vectors\": %lld, \"steps\": %lld}\n",
+      batch.usable() ? 1 : 0, T, batch.wavesRun(), batch.vectorsPropagated(), total);
+    return 0;
+  }
+  if (argc > 8 && !strcmp(argv[7], "bench")) {
+    // node-mode cost of the drop-in: `reps` calls of run() on the same solver (bounds reset before each), beside the
+    // same number of bare C-ABI calls with the same host buffers; the difference is what the C++ layer adds per call
+    // (finding the matrix again, copying bounds, writing changes back through setColLower / setColUpper)
+    const int reps = atoi(argv[8]);
+    const std::vector<double> lb0 = solver.lb, ub0 = solver.ub;
+    auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    CbcBoundPropagation warm;
+    warm.run(&solver, NULL, 0, static_cast<CbcBoundPropagation::Level>(level), maxRounds, true, 1e100, 0.0);
+    double tRun = 0.0, tAcq = 0.0, tCapi = 0.0;
+    int rounds = 0;
+    for (int r = 0; r < reps; ++r) {
+      solver.lb = lb0;
+      solver.ub = ub0;
+      const double t0 = now();
+      CbcBoundPropagation bp;
+      bp.run(&solver, NULL, 0, static_cast<CbcBoundPropagation::Level>(level), maxRounds, true, 1e100, 0.0);
+      tRun += now() - t0;
+      rounds = bp.nRoundsRun();
+    }
+    cbp_matrix *m = cbpAcquireMatrix(solver.view());
+    for (int r = 0; r < reps; ++r) {
+      const double t0 = now();
+      m = cbpAcquireMatrix(solver.view());
+      tAcq += now() - t0;
+    }
+    std::vector<double> l, u;
+    for (int r = 0; r < reps && m; ++r) {
+      l = lb0;
+      u = ub0;
+      const double t0 = now();
+      cbp_result res;
+      int nT = 0, nF = 0;
+      cbp_singletons(m, l.data(), u.data(), solver.tol, &nT, &nF, 0);
+      cbp_propagate(m, l.data(), u.data(), solver.tol, level == 3 ? 0 : maxRounds, 1e100, &res, nullptr, 0, 0);
+      tCapi += now() - t0;
+    }
+    const CbpCacheStats cs = cbpCacheStats();
+    printf("RESULT {\"bench\": 1, \"reps\": %d, \"rounds\": %d, \"run_us\": %.2f, \"capi_us\": %.2f, \"acquire_us\": %.2f, "
+           "\"host_share\": %.4f, \"acquire_share\": %.4f, \"cache\": {\"calls\": %lld, \"pointerHits\": %lld, "
+           "\"contentHits\": %lld, \"fullHashes\": %lld, \"uploads\": %lld}}\n",
+      reps, rounds, 1e6 * tRun / reps, 1e6 * tCapi / reps, 1e6 * tAcq / reps, tRun > 0 ? (tRun - tCapi) / tRun : 0.0,
+      tRun > 0 ? tAcq / tRun : 0.0, cs.calls, cs.pointerHits, cs.contentHits, cs.fullHashes, cs.uploads);
     cbpReleaseThreadCache();
     return 0;
   }

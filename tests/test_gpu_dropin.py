@@ -165,3 +165,141 @@ def test_strong_branching_arms_match_oracle(oracle, tmp_path):
     assert res["nInfeasibleArms"] == n_inf
     both = any((not ores["feasible"][2 * k]) and (not ores["feasible"][2 * k + 1]) for k in range(len(cols)))
     assert res["nodeInfeasible"] == (1 if both else 0)
+
+
+def _drive_mode(tmp_path, inst, mode_args, level=3, max_rounds=0, extra_env=None):
+    ip, op = str(tmp_path / "inst.bin"), str(tmp_path / "out.bin")
+    write_instance(inst, ip)
+    cmd = [DRIVER, ip, op, str(level), str(max_rounds), "0", "1e100"] + mode_args
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, **(extra_env or {})))
+    assert out.returncode == 0, out.stderr
+    res = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("RESULT ")][0][7:])
+    return res, op
+
+
+def test_dive_batch_threads_match_oracle(oracle, tmp_path):
+    """CbcDiveBatch: 8 dive threads, each walking through its own sequence of bound vectors (one more
+    fixing per step), served by one device call per wave; every step of every dive against the oracle's one round."""
+    inst = I.knapsack_assignment(m=2000, n=5000, seed=65, root_fixpoint=True)
+    r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    inst.lb, inst.ub = lb0, ub0
+    T, n = 8, inst.n
+    g = np.random.default_rng(77)
+    seqs = []
+    for t in range(T):
+        steps = int(g.integers(2, 7))
+        s, v, b = I.dive_deltas(inst, lb0, ub0, 1, max_depth=steps, seed=100 + t, follow_xstar=0.7 if t % 3 else 0.2)
+        lb, ub = lb0.copy(), ub0.copy()
+        seq = []
+        for q in range(len(v)):  # one more fixing per dive iteration, bounds carried forward with what propagation found
+            j = int(v[q] & I.COL_MASK)
+            if v[q] & I.UPPER_FLAG:
+                ub[j] = min(ub[j], b[q])
+            else:
+                lb[j] = max(lb[j], b[q])
+            if lb[j] > ub[j]:
+                break
+            seq.append((lb.copy(), ub.copy()))
+            r, lb2, ub2 = oracle.propagate(oracle.Problem(inst), lb, ub, max_rounds=1)
+            if not r["feasible"]:
+                break
+            lb, ub = lb2, ub2
+        seqs.append(seq)
+    bp = str(tmp_path / "bounds.bin")
+    with open(bp, "wb") as f:
+        f.write(struct.pack("<i", T))
+        for seq in seqs:
+            f.write(struct.pack("<i", len(seq)))
+            for lb, ub in seq:
+                f.write(lb.tobytes())
+                f.write(ub.tobytes())
+    res, op = _drive_mode(tmp_path, inst, ["divebatch", bp], level=2, max_rounds=1)
+    assert res["usable"] == 1 and res["dives"] == T
+    assert res["waves"] == max(len(s) for s in seqs)  # one device call per wave, however many dives are still running
+    assert res["vectors"] == res["steps"] == sum(len(s) for s in seqs)
+    raw = open(op, "rb").read()
+    off = 0
+    failed = 0
+    for t in range(T):
+        (steps,) = struct.unpack_from("<i", raw, off)
+        off += 4
+        assert steps == len(seqs[t])
+        for w in range(steps):
+            feas, row, col, nupd = struct.unpack_from("<4i", raw, off)
+            off += 16
+            upd = np.frombuffer(raw, np.float64, 3 * nupd, off).reshape(-1, 3)
+            off += 24 * nupd
+            lb, ub = seqs[t][w]
+            r, lo, uo = oracle.propagate(oracle.Problem(inst), lb, ub, max_rounds=1)
+            assert feas == (1 if r["feasible"] else 0), (t, w)
+            if not r["feasible"]:
+                failed += 1
+                assert (row, col) == (r["infeasibleRow"], r["infeasibleCol"]) and nupd == 0
+                continue
+            want = np.flatnonzero((lo != lb) | (uo != ub))
+            assert np.array_equal(upd[:, 0].astype(int), want), (t, w)
+            assert np.array_equal(upd[:, 1], lo[want]) and np.array_equal(upd[:, 2], uo[want])
+    assert off == len(raw)
+
+
+def test_probe_sweep_consequences(oracle, tmp_path):
+    """CbcProbePropagation: every free binary probed both ways as one batch; a failed probe fixes the
+    column the other way (src/CbcSolverHeuristics.cpp:483-486), what both probes imply holds at the node; all of it
+    recomputed here from oracle runs probe by probe."""
+    inst = I.knapsack_assignment(m=300, n=700, seed=81, root_fixpoint=True, slack_max=0)
+    r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
+    inst.lb, inst.ub = lb0, ub0
+    res, op = _drive_mode(tmp_path, inst, ["probe", "0"])
+    raw = open(op, "rb").read()
+    (np_,) = struct.unpack_from("<i", raw, 0)
+    probes = np.frombuffer(raw, np.int32, 3 * np_, 4).reshape(-1, 3)
+    off = 4 + 12 * np_
+    (nb,) = struct.unpack_from("<i", raw, off)
+    nbounds = np.frombuffer(raw, np.float64, 3 * nb, off + 4).reshape(-1, 3)
+    off += 4 + 24 * nb
+    fin = np.frombuffer(raw, np.float64, 2 * inst.n, off)
+    cols = np.flatnonzero((inst.colType != 0) & (ub0 - lb0 >= 1.0))
+    assert res["ran"] == 1 and res["numberProbed"] == np_ == cols.size and np.array_equal(probes[:, 0], cols)
+    prob = oracle.Problem(inst)
+    best_l, best_u = lb0.copy(), ub0.copy()
+    n_failed = 0
+    for k, j in enumerate(cols):
+        outs = []
+        for way in (0, 1):
+            lb, ub = lb0.copy(), ub0.copy()
+            if way == 0:
+                ub[j] = lb0[j]
+            else:
+                lb[j] = lb0[j] + 1.0
+            r, lo, uo = oracle.propagate(prob, lb, ub)
+            assert probes[k, 1 + way] == (0 if r["feasible"] else 1), (j, way)
+            outs.append((r["feasible"], lo, uo))
+        (fd, ld, ud), (fu, lu, uu) = outs
+        n_failed += (not fd) + (not fu)
+        assert fd or fu
+        if not fd:
+            best_l[j] = max(best_l[j], lb0[j] + 1.0)
+        elif not fu:
+            best_u[j] = min(best_u[j], lb0[j])
+        else:
+            both = np.minimum(ld, lu), np.maximum(ud, uu)
+            both[0][j], both[1][j] = lb0[j], ub0[j]
+            best_l, best_u = np.maximum(best_l, both[0]), np.minimum(best_u, both[1])
+    assert res["failedProbes"] == n_failed and res["nodeInfeasible"] == 0
+    want = np.flatnonzero((best_l > lb0) | (best_u < ub0))
+    assert np.array_equal(nbounds[:, 0].astype(int), want) and want.size > 0
+    assert np.array_equal(nbounds[:, 1], best_l[want]) and np.array_equal(nbounds[:, 2], best_u[want])
+    assert np.array_equal(fin[:inst.n], best_l) and np.array_equal(fin[inst.n:], best_u) and res["moved"] == want.size
+    assert inst.contains(best_l, best_u)  # the planted point survives every conclusion
+
+
+def test_node_mode_calls_are_cheap_on_the_host(tmp_path):
+    """1,000 run() calls on one solver (a B&B node re-presents its matrix every time): the C++ layer — finding the device
+    copy again, copying bounds, writing changes back — must stay a small share of the call; the matrix is uploaded once
+    and found again by address + light key every other time."""
+    inst = I.mixed_bigm(m=100_000, n=100_000, seed=91)  # ~1M nonzeros
+    res, _ = _drive_mode(tmp_path, inst, ["bench", "1000"], level=3, max_rounds=0)
+    c = res["cache"]
+    assert c["uploads"] == 1 and c["pointerHits"] >= 2000 and c["fullHashes"] == 1
+    assert res["acquire_share"] < 0.05, res
+    print("node-mode bench:", res)
