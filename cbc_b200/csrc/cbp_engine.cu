@@ -71,6 +71,10 @@ struct BatchState {
   WlCell *wlK = nullptr, *wlCells = nullptr;
   WlCtl *wlCtl = nullptr;
   int *wlInts = nullptr;  // vecChanged by round parity [2][Bp], active by round parity [2][G]
+  // device staging of the update lists for host-pointer fetches (kept between calls: no cudaMalloc per fetch)
+  int *stCol = nullptr;
+  double *stLb = nullptr, *stUb = nullptr;
+  long long stCap = 0;
   unsigned wlItemCap = 0, wlCellCap = 0;
   unsigned long long *wlHKey = nullptr;  // (vector, long row) pair table
   double *wlHMin = nullptr, *wlHMax = nullptr;
@@ -144,6 +148,27 @@ struct cbp_matrix {
   } while (0)
 
 static thread_local std::string g_createErr;
+
+// Test / A-B switches, read from the environment once per process (never inside a round loop).
+struct EnvKnobs {
+  bool noWorklist, noLazyX1, lazyX1, noBaseRound, noMultiGroup, wlStamps;
+  int overlayRounds;
+  EnvKnobs()
+    : noWorklist(getenv("CBP_NO_WORKLIST") != nullptr)
+    , noLazyX1(getenv("CBP_NO_LAZY_X1") != nullptr)
+    , lazyX1(getenv("CBP_LAZY_X1") != nullptr)
+    , noBaseRound(getenv("CBP_NO_BASE_ROUND") != nullptr)
+    , noMultiGroup(getenv("CBP_NO_MULTI_GROUP") != nullptr)
+    , wlStamps(getenv("CBP_WL_STAMPS") != nullptr)
+    , overlayRounds(getenv("CBP_OVERLAY_ROUNDS") ? atoi(getenv("CBP_OVERLAY_ROUNDS")) : INT_MAX)
+  {
+  }
+};
+static const EnvKnobs &knobs()
+{
+  static const EnvKnobs k;
+  return k;
+}
 
 static constexpr size_t kSvSmallSmem = 0;
 static constexpr unsigned kBtLogCap = 16u << 20;  // candidate list of a list round: 16M entries (256 MB)  // the short-rows-only variant needs no dynamic shared memory
@@ -278,8 +303,8 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
     mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
-    mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts, mat->bt.wlHKey, mat->bt.wlHMin,
-    mat->bt.wlHMax, mat->bt.wlHStamp, mat->bt.wlRowBase, mat->bt.wlRowExact };
+    mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts, mat->bt.wlHKey,
+    mat->bt.wlRowBase, mat->bt.wlRowExact, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb };
   for (void *p : ptrs)
     if (p)
       cudaFree(p);
@@ -1081,7 +1106,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
   if (cells > bt.capCells || Bp > bt.capBp) {
     void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt,
       bt.log, bt.groupFlag, bt.dmask, bt.wlItemsS[0], bt.wlItemsS[1], bt.wlItemsL[0], bt.wlItemsL[1], bt.wlK, bt.wlCells,
-      bt.wlCtl, bt.wlInts, bt.wlHKey, bt.wlHMin, bt.wlHMax, bt.wlHStamp };
+      bt.wlCtl, bt.wlInts, bt.wlHKey };
     bt.wlHKey = nullptr;
     bt.wlHMin = bt.wlHMax = nullptr;
     bt.wlHStamp = nullptr;
@@ -1120,10 +1145,16 @@ static int bt_reserve(cbp_matrix *mat, int B)
       while (bt.wlHSlots < want && bt.wlHSlots < (1u << 25))
         bt.wlHSlots <<= 1;
     }
-    if (dalloc(&bt.wlHKey, bt.wlHSlots) != cudaSuccess || dalloc(&bt.wlHMin, bt.wlHSlots) != cudaSuccess
-      || dalloc(&bt.wlHMax, bt.wlHSlots) != cudaSuccess || dalloc(&bt.wlHStamp, bt.wlHSlots) != cudaSuccess) {
-      ctx->err = "batch workspace (pair table)";
-      return CBP_ERR_NOMEM;
+    {  // key | min | max | stamp in one allocation: one memset clears the table
+      unsigned char *blk = nullptr;
+      if (dalloc(&blk, static_cast<size_t>(bt.wlHSlots) * 28) != cudaSuccess) {
+        ctx->err = "batch workspace (pair table)";
+        return CBP_ERR_NOMEM;
+      }
+      bt.wlHKey = reinterpret_cast<unsigned long long *>(blk);
+      bt.wlHMin = reinterpret_cast<double *>(blk + static_cast<size_t>(bt.wlHSlots) * 8);
+      bt.wlHMax = reinterpret_cast<double *>(blk + static_cast<size_t>(bt.wlHSlots) * 16);
+      bt.wlHStamp = reinterpret_cast<int *>(blk + static_cast<size_t>(bt.wlHSlots) * 24);
     }
     if (dalloc(&bt.wlItemsS[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsS[1], bt.wlItemCap) != cudaSuccess
       || dalloc(&bt.wlItemsL[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsL[1], bt.wlItemCap) != cudaSuccess
@@ -1352,10 +1383,7 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.rowBaseRange = bt.wlRowBase + 2 * static_cast<size_t>(std::max(mat->mKept, 1));
   w.rowExact = bt.wlRowExact;
   w.exactOk = (mat->allInt && !bt.hasInf) ? 1 : 0;
-  CK(cudaMemsetAsync(bt.wlHKey, 0, sizeof(unsigned long long) * bt.wlHSlots, st));
-  CK(cudaMemsetAsync(bt.wlHMin, 0, sizeof(double) * bt.wlHSlots, st));
-  CK(cudaMemsetAsync(bt.wlHMax, 0, sizeof(double) * bt.wlHSlots, st));
-  CK(cudaMemsetAsync(bt.wlHStamp, 0, sizeof(int) * bt.wlHSlots, st));
+  CK(cudaMemsetAsync(bt.wlHKey, 0, static_cast<size_t>(bt.wlHSlots) * 28, st));
   w.dStart = bt.dStart;
   w.dVar = bt.dVar;
   w.dBnd = bt.dBnd;
@@ -1392,7 +1420,7 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   CK(cudaEventRecord(ctx->evB, st));
   CK(cudaStreamSynchronize(st));  // the one host synchronisation of the run
   *status = h.status;
-  if (getenv("CBP_WL_STAMPS")) {
+  if (knobs().wlStamps) {
     fprintf(stderr, "worklist run: status %d rounds %d items %llu pairs %llu cells %u; phase ends (us):", h.status, h.rounds,
       h.itemsTotal, h.pairs, h.nCells);
     for (unsigned i = 0; i < std::min(h.nStamps, 96u); ++i)
@@ -1423,13 +1451,7 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   ctx->stats.lastPairsWalked = static_cast<int64_t>(h.pairs);
   ctx->stats.lastHostSyncs = 1;
   ctx->stats.lastItems = static_cast<int64_t>(h.itemsTotal);
-  // rounds summed over the vectors (throughput accounting)
-  std::vector<int> rounds(bt.Bp);
-  CK(cudaMemcpy(rounds.data(), p.vecRounds, sizeof(int) * bt.Bp, cudaMemcpyDeviceToHost));
-  long long tot = 0;
-  for (int b = 0; b < bt.B; ++b)
-    tot += rounds[b];
-  ctx->stats.lastRoundsTotal = tot;
+  ctx->stats.lastRoundsTotal = static_cast<long long>(h.roundsTotal);  // rounds summed over the vectors
   return CBP_OK;
 }
 
@@ -1454,8 +1476,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
   // Base + diffs batches first try the worklist form: one persistent kernel for all rounds, only the (row, vector)
   // pairs that a changed column touches.  It hands back when the node bounds are not a propagation fixpoint (then
   // every row can act for every vector) or when a list overflows.  CBP_NO_WORKLIST=1: tests and A/B runs.
-  static const bool noWorklist = getenv("CBP_NO_WORKLIST") != nullptr;
-  if (!bt.denseLoaded && !bt.consumed && bt.W == 32 && !noWorklist && !(timeLimitSec <= 0.0)) {
+  if (!bt.denseLoaded && !bt.consumed && bt.W == 32 && !knobs().noWorklist && !(timeLimitSec <= 0.0)) {
     int wlStatus = kWlOk;
     const int rcw = bt_wl_run(mat, p, limit, timeLimitSec, &wlStatus);
     if (rcw)
@@ -1509,11 +1530,11 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     // vector groups that have candidates (collected in a list) or R11 changes.
     // (worth it for shallow changes per vector — strong-branching arms, probes; deep dives tighten so much
     // in their first round that the direct two-buffer round is the cheaper one)
-    lazy = !fullPrepass && bt.W == 32 && !getenv("CBP_NO_LAZY_X1") && (bt.nDelta <= 256ll * bt.B || getenv("CBP_LAZY_X1"));
+    lazy = !fullPrepass && bt.W == 32 && !knobs().noLazyX1 && (bt.nDelta <= 256ll * bt.B || knobs().lazyX1);
     // ... and when that is so, neither buffer is built before the first round: it runs "from the base"
     // (shared base bounds + the cells the diffs touch), and the buffers are built afterwards for the
     // groups that go on
-    fromBase = lazy && !getenv("CBP_NO_BASE_ROUND");
+    fromBase = lazy && !knobs().noBaseRound;
     if (!fromBase && (rc0 = zero_rest()))
       return rc0;
     if (fromBase) {
@@ -1577,7 +1598,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     const int variant = (bt.hasInf ? 0 : 2) | (mat->allInt ? 1 : 0);
     auto launch_rows = [&](bool toList, bool base) {
       const int mode = base ? 2 : (toList ? 1 : 0);  // base implies the list
-      if (longGrid > 0 && mode == 2 && !bt.hasInf && !getenv("CBP_NO_MULTI_GROUP")) {
+      if (longGrid > 0 && mode == 2 && !bt.hasInf && !knobs().noMultiGroup) {
         // no infinite bound anywhere: four vector groups per warp share every staged matrix entry
         constexpr int V = kBaseGroups;
         const long long lg = static_cast<long long>(cdiv(bt.G, V)) * mat->nLongBt;
@@ -1602,7 +1623,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
 #undef CBP_LONG
         ++ctx->stats.kernelLaunches;
       }
-      if (warps > 0 && mode == 2 && !bt.hasInf && !getenv("CBP_NO_MULTI_GROUP")) {
+      if (warps > 0 && mode == 2 && !bt.hasInf && !knobs().noMultiGroup) {
         constexpr int V = kBaseGroups;
         const dim3 sg(cdiv(mat->nShortBt, kWarps), cdiv(bt.G, V));
         bt_rows_short_base_kernel<V><<<sg, kThreads, 0, st>>>(p, cur);
@@ -1684,7 +1705,7 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
       if ((rc0 = zero_rest()))
         return rc0;
       // CBP_OVERLAY_ROUNDS: tests leave the overlay form after that many rounds to exercise the change-over
-      static const int overlayRounds = getenv("CBP_OVERLAY_ROUNDS") ? atoi(getenv("CBP_OVERLAY_ROUNDS")) : INT_MAX;
+      const int overlayRounds = knobs().overlayRounds;
       if (count > bt.logCap || (overlay && round >= overlayRounds)) {
         // too many for the list: build the whole buffers and redo the round directly
         if (overlay) {
@@ -1856,9 +1877,26 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
   int *dCol = updCol;
   double *dLb = updLb, *dUb = updUb;
   if (!dev) {
-    CK(dalloc(&dCol, run));
-    CK(dalloc(&dLb, run));
-    CK(dalloc(&dUb, run));
+    if (run > bt.stCap) {
+      if (bt.stCol)
+        cudaFree(bt.stCol);
+      if (bt.stLb)
+        cudaFree(bt.stLb);
+      if (bt.stUb)
+        cudaFree(bt.stUb);
+      bt.stCol = nullptr;
+      bt.stLb = bt.stUb = nullptr;
+      bt.stCap = 0;
+      const long long cap = std::max<long long>(run + run / 2, 1 << 16);
+      if (dalloc(&bt.stCol, cap) != cudaSuccess || dalloc(&bt.stLb, cap) != cudaSuccess || dalloc(&bt.stUb, cap) != cudaSuccess) {
+        ctx->err = "cbp_batch_fetch: staging";
+        return CBP_ERR_NOMEM;
+      }
+      bt.stCap = cap;
+    }
+    dCol = bt.stCol;
+    dLb = bt.stLb;
+    dUb = bt.stUb;
   }
   bt_updates_kernel<true><<<updGrid, updBlock, 0, ctx->stream>>>(p, bt.B, bt.chunkCnt, bt.counts, dCol, dLb, dUb);
   ++ctx->stats.kernelLaunches;
@@ -1872,9 +1910,6 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
       e = cudaMemcpyAsync(updUb, dUb, sizeof(double) * run, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess)
       e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(dCol);
-    cudaFree(dLb);
-    cudaFree(dUb);
   } else if (e == cudaSuccess) {
     e = cudaStreamSynchronize(ctx->stream);
   }

@@ -53,6 +53,7 @@ struct WlCtl {
   int status, rounds;
   unsigned long long pairs;   // (nonzero, vector) pairs walked
   unsigned long long itemsTotal;
+  unsigned long long roundsTotal;  // rounds summed over the vectors (each adds its count when it stops)
   unsigned long long t0;
   // diagnostic: ns since t0 at the first phase boundaries (CBP_WL_STAMPS=1 prints them)
   unsigned nStamps;
@@ -321,6 +322,48 @@ __device__ __forceinline__ RowAct wl_row_warp_sum(const BtParams &p, int row, co
   return ra;
 }
 
+// the same with the exactness check of the base pass: magnitude of the row's terms, and whether they are all integers
+template <class Reader>
+__device__ __forceinline__ RowAct wl_row_warp_sum_checked(const BtParams &p, int row, const Reader &rd, int lane, double *magOut,
+  bool *wholeOut)
+{
+  const int kb = __ldg(&p.rowNz[row]), ke = kb + __ldg(&p.rowCnt[row]);
+  RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+  double mag = 0.0;
+  bool whole = true;
+  for (int k0 = kb; k0 < ke; k0 += 128) {
+    double a[4];
+    int c[4], jj[4];
+    Bnd x[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int k = k0 + 32 * u + lane;
+      a[u] = 0.0;
+      c[u] = 0;
+      if (k < ke) {
+        c[u] = __ldg(&p.col[k]);
+        a[u] = __ldg(&p.val[k]);
+      }
+      jj[u] = col_of(c[u]);
+    }
+    rd.get_n(jj, x);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (a[u] != 0.0) {
+        accumulate(ra, a[u], col_is_int(c[u]), a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
+        mag += fabs(a[u]) * fmax(fabs(x[u].lb), fabs(x[u].ub));
+        whole = whole && col_is_int(c[u]) && a[u] == floor(a[u]) && x[u].lb == floor(x[u].lb) && x[u].ub == floor(x[u].ub);
+      }
+  }
+  warp_reduce(ra);
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1)
+    mag += __shfl_xor_sync(0xffffffffu, mag, m);
+  *magOut = mag;
+  *wholeOut = __all_sync(0xffffffffu, whole);
+  return ra;
+}
+
 template <class Reader, class Sink>
 __device__ __forceinline__ void wl_row_warp_tighten(const BtParams &p, int row, const RowPlan &pl, const Reader &rd,
   Sink &sink, int lane)
@@ -499,6 +542,8 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
   __shared__ __align__(16) BtLogEntry s_stage[kWlStage];
   __shared__ unsigned s_staged, s_base;
   __shared__ unsigned s_dv[kWarps][64];
+  __shared__ RowAct s_row[kWarps];
+  __shared__ double s_mag[kWarps];
   cg::grid_group grid = cg::this_grid();
   const BtParams &p = w.bt;
   WlCtl *ctl = w.ctl;
@@ -575,43 +620,14 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       }
       wl_base_verdict(p, r, ra, &ctl->baseBad, [&](const RowPlan &pl) { wl_thread_tighten(p, r, pl, rd, fs); });
     }
-    for (unsigned r = gwarp; r < static_cast<unsigned>(p.mKept); r += nwarps) {
-      if (__ldg(&p.rowCnt[r]) <= kShortLen)
+    for (unsigned r = gwarp; r < static_cast<unsigned>(p.mKept); r += nwarps) {  // rows of 33 .. kBtLongLen nonzeros: a warp each
+      const int cnt = __ldg(&p.rowCnt[r]);
+      if (cnt <= kShortLen || cnt > kBtLongLen)
         continue;
-      const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
-      RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+      bool whole = false;
       double mag = 0.0;
-      bool whole = true;
-      for (int k0 = kb; k0 < ke; k0 += 128) {  // four nonzeros per lane in flight
-        double a[4];
-        int c[4];
-        Bnd x[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int k = k0 + 32 * u + lane;
-          a[u] = 0.0;
-          c[u] = 0;
-          if (k < ke) {
-            c[u] = __ldg(&p.col[k]);
-            a[u] = __ldg(&p.val[k]);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          x[u] = rd.get(col_of(c[u]));
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          if (a[u] != 0.0) {
-            accumulate(ra, a[u], col_is_int(c[u]), a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
-            mag += fabs(a[u]) * fmax(fabs(x[u].lb), fabs(x[u].ub));
-            whole = whole && col_is_int(c[u]) && a[u] == floor(a[u]) && x[u].lb == floor(x[u].lb) && x[u].ub == floor(x[u].ub);
-          }
-      }
-      warp_reduce(ra);
-#pragma unroll
-      for (int m = 16; m >= 1; m >>= 1)
-        mag += __shfl_xor_sync(0xffffffffu, mag, m);
-      whole = __all_sync(0xffffffffu, whole) && mag < 1.0e15 && ra.infMin + ra.infMax == 0;
+      const RowAct ra = wl_row_warp_sum_checked(p, r, rd, lane, &mag, &whole);
+      whole = whole && mag < 1.0e15 && ra.infMin + ra.infMax == 0;
       if (lane == 0) {
         w.rowBaseMin[r] = ra.minAct;
         w.rowBaseMax[r] = ra.maxAct;
@@ -619,6 +635,52 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         w.rowExact[r] = whole ? 1 : 0;
       }
       wl_base_verdict(p, r, ra, &ctl->baseBad, [&](const RowPlan &pl) { wl_row_warp_tighten(p, r, pl, rd, fs, lane); });
+    }
+    for (int i = blockIdx.x; i < p.nLongBt; i += gridDim.x) {  // longer rows: the whole CTA (a warp alone would be the phase's tail)
+      const int r = __ldg(&p.longRowsBt[i]);
+      const int kb = __ldg(&p.rowNz[r]), ke = kb + __ldg(&p.rowCnt[r]);
+      RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+      double mag = 0.0;
+      bool whole = true;
+      for (int k = kb + tid; k < ke; k += kThreads) {
+        const int c = __ldg(&p.col[k]);
+        const double a = __ldg(&p.val[k]);
+        const Bnd x = rd.get(col_of(c));
+        accumulate(ra, a, col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s.inf);
+        mag += fabs(a) * fmax(fabs(x.lb), fabs(x.ub));
+        whole = whole && col_is_int(c) && a == floor(a) && x.lb == floor(x.lb) && x.ub == floor(x.ub);
+      }
+      warp_reduce(ra);
+#pragma unroll
+      for (int m = 16; m >= 1; m >>= 1)
+        mag += __shfl_xor_sync(0xffffffffu, mag, m);
+      whole = __all_sync(0xffffffffu, whole);
+      __syncthreads();
+      if (lane == 0) {
+        s_row[tid >> 5] = ra;
+        s_mag[tid >> 5] = whole ? mag : 1.0e300;
+      }
+      __syncthreads();
+      RowAct tot = s_row[0];
+      double magTot = s_mag[0];
+      for (int q = 1; q < kWarps; ++q) {  // (every thread alike, warp order)
+        combine(tot, s_row[q]);
+        magTot += s_mag[q];
+      }
+      if (tid == 0) {
+        w.rowBaseMin[r] = tot.minAct;
+        w.rowBaseMax[r] = tot.maxAct;
+        w.rowBaseRange[r] = tot.maxRange;
+        w.rowExact[r] = (magTot < 1.0e15 && tot.infMin + tot.infMax == 0) ? 1 : 0;
+      }
+      wl_base_verdict(p, r, tot, &ctl->baseBad, [&](const RowPlan &pl) {
+        for (int k = kb + tid; k < ke; k += kThreads) {
+          const int c = __ldg(&p.col[k]);
+          const double a = __ldg(&p.val[k]);
+          const Bnd x = rd.get(col_of(c));
+          tighten_nz(fs, pl, a, col_of(c), col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+        }
+      });
     }
   }
   grid.sync();
@@ -729,6 +791,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         p.vecRounds[b] = 1;
         p.vecFinal[b] = 0;
         atomicAnd(&w.active2[0][b >> 5], ~bit);
+        atomicAdd(&ctl->roundsTotal, 1ull);
       }
       continue;
     }
@@ -962,6 +1025,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
     const int timeUp = *reinterpret_cast<volatile int *>(&ctl->timeUp);
     for (unsigned b = gtid; b < static_cast<unsigned>(p.Bp); b += gsize) {
       bool on = (w.active2[cur][b >> 5] >> (b & 31)) & 1u;
+      int stoppedRounds = 0;
       if (on) {
         const int chg = w.vecChanged2[cur][b];
         p.vecRounds[b] = round + 1;
@@ -984,8 +1048,12 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
           p.vecStop[b] = stop;
           p.vecFinal[b] = fin;
           on = false;
+          stoppedRounds = round + 1;
         }
       }
+      stoppedRounds = __reduce_add_sync(0xffffffffu, stoppedRounds);
+      if (lane == 0 && stoppedRounds)
+        atomicAdd(&ctl->roundsTotal, static_cast<unsigned long long>(stoppedRounds));
       w.vecChanged2[nxt][b] = 0;
       const unsigned m = __ballot_sync(0xffffffffu, on);  // (Bp and the stride are multiples of 32: whole warps)
       if (lane == 0) {

@@ -66,12 +66,15 @@ bool CbcBoundPropagation::run(OsiSolverInterface *solver, CoinMessageHandler * /
   const CoinPackedMatrix *byRow = solver->getMatrixByRow();
   double primalTol = 1e-7;
   solver->getDblParam(OsiPrimalTolerance, primalTol);
-  std::vector<double> lb(solver->getColLower(), solver->getColLower() + nCols);
-  std::vector<double> ub(solver->getColUpper(), solver->getColUpper() + nCols);
+  // (per-thread scratch, kept between calls: a node-level caller comes back thousands of times, and fresh
+  // megabyte-sized vectors per call cost more in page faults than the device run)
+  static thread_local std::vector<double> lb, ub;
+  static thread_local std::vector<int> perRound, touched;
+  lb.assign(solver->getColLower(), solver->getColLower() + nCols);
+  ub.assign(solver->getColUpper(), solver->getColUpper() + nCols);
 
   bool ranOnDevice = false;
   cbp_result res;
-  std::vector<int> perRound;
   const int roundLimit = (level == Fixpoint) ? INT_MAX : maxRounds;  // reference :88
   if (roundLimit > 0) {
     // the reference tests the clock before every round, the first included (:109-121)
@@ -118,7 +121,7 @@ bool CbcBoundPropagation::run(OsiSolverInterface *solver, CoinMessageHandler * /
     // write back what completed rounds changed (reference :181-187 sets both sides of a listed column)
     const double *curLb = solver->getColLower();
     const double *curUb = solver->getColUpper();
-    std::vector<int> touched;
+    touched.clear();
     for (int j = 0; j < nCols; ++j)
       if (lb[j] != curLb[j] || ub[j] != curUb[j])
         touched.push_back(j);

@@ -143,7 +143,10 @@ CBP_API int cbp_propagate_batch(cbp_matrix *mat, int B, double *lb, double *ub,
   double primalTol, int maxRounds, double timeLimitSec, cbp_result *out, int flags);
 
 /* Batch in the node bound-diff wire format of CbcPartialNodeInfo
- * (src/CbcNode.cpp:265-273: variable | 0x80000000 = upper bound): vector b is
+ * (src/CbcNode.cpp:265-273: variable | 0x80000000 = upper bound; the column is
+ * bits 0-29, bit 30 is the "can go odd way" flag of applyBounds() and is
+ * ignored, src/CbcPartialNodeInfo.cpp:139,196,208; a column >= n is refused
+ * with CBP_ERR_ARG): vector b is
  * baseLb/baseUb with deltaVar/deltaBound[deltaStart[b] .. deltaStart[b+1])
  * applied in order.  Outputs: out[B]; and, as CoinBoundPropagation's
  * updatedBounds() would list them (src/CbcBoundPropagation.cpp:166,181-186),

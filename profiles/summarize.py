@@ -27,7 +27,10 @@ def main(rep, out):
     lines = [f"# {rep}", f"kernel: {vals[hdr.index('Kernel Name')]}"]
     got = {}
     for h, u, v in zip(hdr, units, vals):
-        if h in KEYS:
+        if h in KEYS or h in ("l1tex__data_pipe_lsu_wavefronts.sum", "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed",
+                             "l1tex__t_output_wavefronts_pipe_lsu_mem_global_op_ld.sum",
+                             "l1tex__t_output_wavefronts_pipe_lsu_mem_global_op_atom.sum",
+                             "l1tex__t_output_wavefronts_pipe_lsu_mem_global_op_red.sum"):
             lines.append(f"{h:70s} {v} {u}")
             got[h] = (v, u)
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout

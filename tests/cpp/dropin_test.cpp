@@ -75,7 +75,9 @@ struct TestSolver : OsiSolverInterface {
     if (!m)
       return 0;
     int nT = 0;
-    std::vector<double> l = lb, u = ub;
+    static thread_local std::vector<double> l, u;
+    l = lb;
+    u = ub;
     if (cbp_singletons(m, l.data(), u.data(), tol, &nT, &nFixed, 0) != CBP_OK)
       return 0;
     if (nT > 0)
@@ -317,6 +319,7 @@ int main(int argc, char **argv)
       tAcq += now() - t0;
     }
     std::vector<double> l, u;
+    double tCapiSing = 0.0, tSolverSing = 0.0;
     for (int r = 0; r < reps && m; ++r) {
       l = lb0;
       u = ub0;
@@ -324,9 +327,53 @@ int main(int argc, char **argv)
       cbp_result res;
       int nT = 0, nF = 0;
       cbp_singletons(m, l.data(), u.data(), solver.tol, &nT, &nF, 0);
+      const double t1 = now();
       cbp_propagate(m, l.data(), u.data(), solver.tol, level == 3 ? 0 : maxRounds, 1e100, &res, nullptr, 0, 0);
       tCapi += now() - t0;
+      tCapiSing += t1 - t0;
     }
+    for (int r = 0; r < reps; ++r) {  // phase 1 alone, as the (test double's) solver does it
+      solver.lb = lb0;
+      solver.ub = ub0;
+      const double t0 = now();
+      int nF = 0;
+      solver.tightenBoundsFromSingletonRows(nF);
+      tSolverSing += now() - t0;
+    }
+    {  // the steps of run()'s phase 2, one by one
+      double tCopy = 0, tProp = 0, tBack = 0;
+      std::vector<double> lb2, ub2;
+      std::vector<int> perRound(1024), touched;
+      for (int r = 0; r < reps && m; ++r) {
+        solver.lb = lb0;
+        solver.ub = ub0;
+        int nF = 0;
+        solver.tightenBoundsFromSingletonRows(nF);
+        double t0 = now();
+        lb2.assign(solver.getColLower(), solver.getColLower() + solver.getNumCols());
+        ub2.assign(solver.getColUpper(), solver.getColUpper() + solver.getNumCols());
+        double t1 = now();
+        cbp_result res;
+        cbp_propagate(m, lb2.data(), ub2.data(), solver.tol, level == 3 ? 0 : maxRounds, 1e100, &res, perRound.data(), 1024, 0);
+        double t2 = now();
+        touched.clear();
+        for (int j = 0; j < solver.getNumCols(); ++j)
+          if (lb2[j] != solver.lb[j] || ub2[j] != solver.ub[j])
+            touched.push_back(j);
+        for (int j : touched) {
+          solver.setColLower(j, lb2[j]);
+          solver.setColUpper(j, ub2[j]);
+        }
+        double t3 = now();
+        tCopy += t1 - t0;
+        tProp += t2 - t1;
+        tBack += t3 - t2;
+      }
+      printf("STEPS {\"copy_us\": %.2f, \"propagate_us\": %.2f, \"write_back_us\": %.2f}\n", 1e6 * tCopy / reps,
+        1e6 * tProp / reps, 1e6 * tBack / reps);
+    }
+    printf("PHASES {\"capi_singletons_us\": %.2f, \"solver_singletons_us\": %.2f}\n", 1e6 * tCapiSing / reps,
+      1e6 * tSolverSing / reps);
     const CbpCacheStats cs = cbpCacheStats();
     printf("RESULT {\"bench\": 1, \"reps\": %d, \"rounds\": %d, \"run_us\": %.2f, \"capi_us\": %.2f, \"acquire_us\": %.2f, "
            "\"host_share\": %.4f, \"acquire_share\": %.4f, \"cache\": {\"calls\": %lld, \"pointerHits\": %lld, "

@@ -247,8 +247,25 @@ def test_probe_sweep_consequences(oracle, tmp_path):
     column the other way (src/CbcSolverHeuristics.cpp:483-486), what both probes imply holds at the node; all of it
     recomputed here from oracle runs probe by probe."""
     inst = I.knapsack_assignment(m=300, n=700, seed=81, root_fixpoint=True, slack_max=0)
+    # planted structure that only probing sees: a + b <= 1, a + c <= 1, b + c >= 1 (a = 1 cannot hold: ub(a) = 0);
+    # e + d >= 1, d - e >= 0 (both probes of e give d = 1: lb(d) = 1)
+    x0, x1 = np.flatnonzero(inst.xstar == 0), np.flatnonzero(inst.xstar == 1)
+    a, e = int(x0[3]), int(x0[11])
+    b, c, d = int(x1[2]), int(x1[5]), int(x1[9])
+    new_rows = [([a, b], [1.0, 1.0], "L", 1.0), ([a, c], [1.0, 1.0], "L", 1.0), ([b, c], [1.0, 1.0], "G", 1.0),
+                ([e, d], [1.0, 1.0], "G", 1.0), ([d, e], [1.0, -1.0], "G", 0.0)]
+    k = len(new_rows)
+    inst = I.Instance(inst.name + "+probe", inst.m + k, inst.n,
+                      np.concatenate([inst.rowStart, inst.rowStart[-1] + 2 * np.arange(1, k + 1)]),
+                      np.concatenate([inst.col, np.array([j for r in new_rows for j in r[0]], np.int32)]),
+                      np.concatenate([inst.val, np.array([v for r in new_rows for v in r[1]])]),
+                      np.concatenate([inst.sense, np.array([ord(r[2]) for r in new_rows], np.uint8)]),
+                      np.concatenate([inst.rhs, np.array([r[3] for r in new_rows])]),
+                      np.concatenate([inst.range, np.zeros(k)]), inst.colType, inst.lb, inst.ub, inst.inf, inst.xstar)
+    assert inst.is_feasible_point()
     r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
     inst.lb, inst.ub = lb0, ub0
+    assert ub0[a] == 1.0 and lb0[d] == 0.0  # propagation alone does not see either conclusion
     res, op = _drive_mode(tmp_path, inst, ["probe", "0"])
     raw = open(op, "rb").read()
     (np_,) = struct.unpack_from("<i", raw, 0)
@@ -287,7 +304,7 @@ def test_probe_sweep_consequences(oracle, tmp_path):
             best_l, best_u = np.maximum(best_l, both[0]), np.minimum(best_u, both[1])
     assert res["failedProbes"] == n_failed and res["nodeInfeasible"] == 0
     want = np.flatnonzero((best_l > lb0) | (best_u < ub0))
-    assert np.array_equal(nbounds[:, 0].astype(int), want) and want.size > 0
+    assert np.array_equal(nbounds[:, 0].astype(int), want) and best_u[a] == 0.0 and best_l[d] == 1.0
     assert np.array_equal(nbounds[:, 1], best_l[want]) and np.array_equal(nbounds[:, 2], best_u[want])
     assert np.array_equal(fin[:inst.n], best_l) and np.array_equal(fin[inst.n:], best_u) and res["moved"] == want.size
     assert inst.contains(best_l, best_u)  # the planted point survives every conclusion
