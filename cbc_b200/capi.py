@@ -311,14 +311,16 @@ class Matrix:
         B = self._B
         res = np.zeros(B, RESULT_DTYPE)
         start = np.zeros(B + 1, np.int64)
-        cap = int(upd_cap) if upd_cap is not None else max(1024, 4 * B)
+        # (the size the last fetch needed is remembered: a batch that comes back does not ask twice)
+        cap = int(upd_cap) if upd_cap is not None else max(1024, 4 * B, getattr(self, "_upd_cap_hint", 0))
         while True:
             col = np.empty(cap, np.int32)  # (only the first start[B] entries are written and returned)
             lb = np.empty(cap)
             ub = np.empty(cap)
             rc = self.ctx.lib.cbp_batch_fetch(self.h, _ptr(res), cap, _ptr(start), _ptr(col), _ptr(lb), _ptr(ub), 0)
             if rc == ERR_CAPACITY and upd_cap is None:
-                cap = int(start[B])
+                cap = int(start[B]) + int(start[B]) // 8 + 64
+                self._upd_cap_hint = cap
                 continue
             self.ctx.check(rc, "cbp_batch_fetch")
             k = int(start[B])

@@ -1145,6 +1145,11 @@ static int bt_reserve(cbp_matrix *mat, int B)
       while (bt.wlHSlots < want && bt.wlHSlots < (1u << 25))
         bt.wlHSlots <<= 1;
     }
+    if (getenv("CBP_WL_SLOTS")) {  // tests shrink the pair table to exercise the hand-over when it fills up
+      bt.wlHSlots = 2;
+      while (bt.wlHSlots < static_cast<unsigned>(std::max<long>(2, atol(getenv("CBP_WL_SLOTS")))))
+        bt.wlHSlots <<= 1;
+    }
     {  // key | min | max | stamp in one allocation: one memset clears the table
       unsigned char *blk = nullptr;
       if (dalloc(&blk, static_cast<size_t>(bt.wlHSlots) * 28) != cudaSuccess) {

@@ -61,4 +61,10 @@ def test_dropin_library_links():
     assert "_ZN20CoinBoundPropagationC1EiPKcPKdS3_PK16CoinPackedMatrixS1_S3_S3_dd" in syms
     # CbcStrongPropagation::run(OsiSolverInterface*, int, int const*, double const*, int, double)
     assert "_ZN20CbcStrongPropagation3runEP18OsiSolverInterfaceiPKiPKdid" in syms
+    # the batch front ends: CbcProbePropagation::run, CbcDiveBatch(OsiSolverInterface*, int, int) / propagate / finish,
+    # and the cache's invalidate call
+    assert "_ZN19CbcProbePropagation3runEP18OsiSolverInterfaceiPKiii" in syms
+    assert "_ZN12CbcDiveBatchC1EP18OsiSolverInterfaceii" in syms and "_ZN12CbcDiveBatch6finishEi" in syms
+    assert "_ZN12CbcDiveBatch9propagateEiPKdS1_RSt6vectorISt4pairImS3_IddEESaIS5_EERiS9_" in syms
+    assert "_Z19cbpInvalidateMatrixPKv" in syms
     assert os.path.exists(os.path.join(ROOT, "cbc_b200", "lib", "cbp_dropin_test"))

@@ -148,11 +148,16 @@ def test_worklist_then_other_batches_on_the_same_matrix(oracle, gpu_ctx):
     mat.close()
 
 
-def test_worklist_item_list_overflow_hands_over():
+@pytest.mark.parametrize("env,maker", [
+    ({"CBP_WL_ITEM_CAP": "500"}, "I.knapsack_assignment(m=3000, n=8000, seed=41, root_fixpoint=True)"),
+    ({"CBP_WL_SLOTS": "64"}, "I.knapsack_assignment(m=60, n=4000, seed=71, root_fixpoint=True, slack_max=0)"),
+], ids=["item_list_full", "pair_table_full"])
+def test_worklist_overflow_hands_over(env, maker):
     code = (
         "import sys, numpy as np; sys.path.insert(0, %r)\n"
         "from cbc_b200 import capi, instances as I; from oracle import oracle_py as O\n"
-        "inst = I.knapsack_assignment(m=3000, n=8000, seed=41, root_fixpoint=True)\n"
+        "inst = %s\n"
+        "r0, lb0, ub0 = O.propagate(O.Problem(inst), inst.lb, inst.ub); inst.lb, inst.ub = lb0, ub0\n"
         "s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, 70, max_depth=48, seed=42)\n"
         "ctx = capi.Context(); mat = capi.Matrix(ctx, inst)\n"
         "res, us, uc, ul, uu = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)\n"
@@ -163,8 +168,8 @@ def test_worklist_item_list_overflow_hands_over():
         "    assert np.array_equal(res[k], ores[k]), k\n"
         "f = res['feasible'].astype(bool)\n"
         "assert np.array_equal(Lg[f], Lo[f]) and np.array_equal(Ug[f], Uo[f])\n"
-        "print('OK')\n") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),)
-    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, CBP_WL_ITEM_CAP="500"),
+        "print('OK')\n") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), maker)
+    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env),
                          capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
 
