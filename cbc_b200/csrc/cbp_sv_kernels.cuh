@@ -16,6 +16,15 @@
 namespace cbp {
 namespace cg = cooperative_groups;
 
+#ifndef CBP_SV_P2_TRIPS
+#define CBP_SV_P2_TRIPS 1
+#endif
+#ifndef CBP_SV_P2_PACKED
+#define CBP_SV_P2_PACKED 1  // second pass of the short rows: several rows per trip, lanes grouped by row (0: two rows per trip, one after the other)
+#endif
+
+constexpr int kP2Trips = CBP_SV_P2_TRIPS;  // trips of the packed second pass whose loads are in flight together
+
 struct SvStatus {
   int rounds;
   int stopReason;
@@ -355,6 +364,56 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
     // nothing here, however many of them share the warp.
     unsigned todo = __ballot_sync(0xffffffffu, pl.sideU || pl.sideL);
     const int packed = min(pl.infMin, 2) | (min(pl.infMax, 2) << 2) | (pl.sideU ? 16 : 0) | (pl.sideL ? 32 : 0);
+#if CBP_SV_P2_PACKED
+    // Rows are short: a slice of length `len` gets 32 / len of its rows into one trip, the lanes cut into groups of
+    // `len` (lane = group * len + entry), every group working for "its" row — the group-th of the rows still to do —
+    // with that row's plan fetched by shuffle.  One copy of the tightening code serves them all.
+    if (todo) {
+      const int rowsPerTrip = 32 / len;  // (len <= kShortLen = 32, and a slice that wants anything has len >= 1)
+      const int grp = lane / len, ent = lane - grp * len;
+      while (todo) {
+        // kP2Trips trips at a time: their loads are all issued before the first use
+        int own[kP2Trips];
+        bool have[kP2Trips];
+        double a[kP2Trips];
+        int cc[kP2Trips];
+        Bnd x[kP2Trips];
+#pragma unroll
+        for (int t = 0; t < kP2Trips; ++t) {
+          const unsigned ownU = grp < rowsPerTrip ? __fns(todo, 0, grp + 1) : 0xffffffffu;
+          have[t] = ownU < 32u;
+          own[t] = have[t] ? static_cast<int>(ownU) : 0;
+          for (int r = 0; r < rowsPerTrip && todo; ++r)
+            todo &= todo - 1;
+          a[t] = 0.0;
+          cc[t] = 0;
+          if (have[t]) {
+            const int at = off + (ent << 5) + own[t];
+            cc[t] = __ldg(&p.sellCol[at]);
+            a[t] = __ldg(&p.sellVal[at]);
+          }
+        }
+#pragma unroll
+        for (int t = 0; t < kP2Trips; ++t)
+          x[t] = ldcg_bnd(&src[col_of(cc[t])]);
+#pragma unroll
+        for (int t = 0; t < kP2Trips; ++t) {
+          RowPlan q;
+          q.slackU = __shfl_sync(0xffffffffu, pl.slackU, own[t]);
+          q.slackL = __shfl_sync(0xffffffffu, pl.slackL, own[t]);
+          const int pk = __shfl_sync(0xffffffffu, packed, own[t]);
+          q.infMin = pk & 3;
+          q.infMax = (pk >> 2) & 3;
+          q.sideU = (pk & 16) != 0;
+          q.sideL = (pk & 32) != 0;
+          q.infeasible = false;
+          if (have[t] && a[t] != 0.0)
+            tighten_nz(sink, q, a[t], col_of(cc[t]), col_is_int(cc[t]), a[t] > 0.0 ? x[t].lb : x[t].ub,
+              a[t] > 0.0 ? x[t].ub : x[t].lb, p.s);
+        }
+      }
+    }
+#else
     while (todo) {
       // up to kSvPass2Rows rows per trip, all their loads issued before the first use
       int owner[kSvPass2Rows];
@@ -394,6 +453,7 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
             a4[t] > 0.0 ? x4[t].ub : x4[t].lb, p.s);
       }
     }
+#endif
     next = __shfl_sync(0xffffffffu, next, 0);
   }
 }

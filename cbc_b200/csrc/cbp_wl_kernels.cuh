@@ -291,6 +291,57 @@ __device__ __forceinline__ void wl_thread_tighten(const BtParams &p, int row, co
   }
 }
 
+// Second pass of the short-row items of one warp, nonzero-parallel: every lane may hold one (vector, row) item whose
+// row can tighten (want); the warp takes as many of those items as fit into 32 lanes at a time — an item with cnt
+// nonzeros gets cnt consecutive lanes — and each lane evaluates one nonzero of "its" item with that item's plan (fetched
+// by shuffle).  One copy of the tightening code, all lanes busy, instead of every lane walking its own row through it.
+// Called by all 32 lanes together.
+__device__ __forceinline__ void wl_tighten_packed(const BtParams &p, const Bnd *srcX, bool want, int b, int row, int cnt,
+  const RowPlan &pl, BtLogEntry *log, unsigned *nLog, int *overflow, BtLogEntry *stage, unsigned *staged, int lane)
+{
+  unsigned todo = __ballot_sync(0xffffffffu, want);
+  if (!todo)
+    return;
+  const int kb = want ? __ldg(&p.rowNz[row]) : 0;
+  const int packed = min(pl.infMin, 2) | (min(pl.infMax, 2) << 2) | (pl.sideU ? 16 : 0) | (pl.sideL ? 32 : 0);
+  while (todo) {
+    // the items of this trip: lane ranges [start, start + cnt) handed out in the order of the set bits
+    int owner = -1, ent = 0, used = 0;
+    while (todo) {
+      const int o = __ffs(todo) - 1;
+      const int c = __shfl_sync(0xffffffffu, cnt, o);
+      if (used + c > 32 && used > 0)
+        break;
+      if (lane >= used && lane < used + c) {
+        owner = o;
+        ent = lane - used;
+      }
+      used += c;
+      todo &= todo - 1;
+    }
+    const int src_l = owner >= 0 ? owner : 0;
+    const int ob = __shfl_sync(0xffffffffu, b, src_l);
+    const int okb = __shfl_sync(0xffffffffu, kb, src_l);
+    RowPlan q;
+    q.slackU = __shfl_sync(0xffffffffu, pl.slackU, src_l);
+    q.slackL = __shfl_sync(0xffffffffu, pl.slackL, src_l);
+    const int pk = __shfl_sync(0xffffffffu, packed, src_l);
+    q.infMin = pk & 3;
+    q.infMax = (pk >> 2) & 3;
+    q.sideU = (pk & 16) != 0;
+    q.sideL = (pk & 32) != 0;
+    q.infeasible = false;
+    if (owner >= 0) {
+      const int c = __ldg(&p.col[okb + ent]);
+      const double a = __ldg(&p.val[okb + ent]);
+      const Bnd x = wl_bounds(p, srcX + bt_base32(p, ob), p.dmask + bt_word(p, 0, ob >> 5), ob & 31, col_of(c));
+      WlLogSink sink = { log, nLog, p.logCap, overflow, ob, stage, staged };
+      if (a != 0.0)
+        tighten_nz(sink, q, a, col_of(c), col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+    }
+  }
+}
+
 // One longer row by one warp: lanes stride over the row (four nonzeros per lane in flight), butterfly.
 template <class Reader>
 __device__ __forceinline__ RowAct wl_row_warp_sum(const BtParams &p, int row, const Reader &rd, int lane)
@@ -606,8 +657,10 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         for (int u = 0; u < kWlChunk; ++u)
           if (a[u] != 0.0) {  // (padding has a == 0)
             accumulate_fast(ra, a[u], col_is_int(cj[u]), x[u], p.s.inf);
-            mag += fabs(a[u]) * fmax(fabs(x[u].lb), fabs(x[u].ub));
-            whole = whole && col_is_int(cj[u]) && a[u] == floor(a[u]) && x[u].lb == floor(x[u].lb) && x[u].ub == floor(x[u].ub);
+            if (w.exactOk) {  // (only then does anybody ask whether the row's sums are exact)
+              mag += fabs(a[u]) * fmax(fabs(x[u].lb), fabs(x[u].ub));
+              whole = whole && col_is_int(cj[u]) && a[u] == floor(a[u]) && x[u].lb == floor(x[u].lb) && x[u].ub == floor(x[u].ub);
+            }
           }
       }
       if (!valid)
@@ -620,7 +673,8 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       }
       wl_base_verdict(p, r, ra, &ctl->baseBad, [&](const RowPlan &pl) { wl_thread_tighten(p, r, pl, rd, fs); });
     }
-    for (unsigned r = gwarp; r < static_cast<unsigned>(p.mKept); r += nwarps) {  // rows of 33 .. kBtLongLen nonzeros: a warp each
+    // (kept order: the rows of at most kShortLen nonzeros come first)
+    for (unsigned r = w.mShort + gwarp; r < static_cast<unsigned>(p.mKept); r += nwarps) {  // rows of 33 .. kBtLongLen nonzeros: a warp each
       const int cnt = __ldg(&p.rowCnt[r]);
       if (cnt <= kShortLen || cnt > kBtLongLen)
         continue;
@@ -826,19 +880,30 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
     const unsigned nS = *reinterpret_cast<volatile unsigned *>(&ctl->nS[cur]);
     const unsigned nL = *reinterpret_cast<volatile unsigned *>(&ctl->nL[cur]);
     const Bnd *srcX = p.X[cur];
-    // P1a: short-row items, one thread each
-    for (unsigned i = gtid; i < nS; i += gsize) {
-      const WlItem it = w.itemsS[cur][i];
-      const WlVecReader rd = { &p, srcX + bt_base32(p, it.b), p.dmask + bt_word(p, 0, it.b >> 5), it.b & 31 };
-      const RowAct ra = wl_thread_sum<false>(p, it.row, rd, nullptr);
-      const RowPlan pl = plan_row(ra, __ldg(&p.rowLB[it.row]), __ldg(&p.rowUB[it.row]), p.s);
-      if (pl.infeasible) {
-        atomicMin(&p.vecInfRow[it.b], __ldg(&p.rowOrig[it.row]));
-      } else if (pl.sideU || pl.sideL) {
-        WlLogSink sink = { p.log, &ctl->nLog, p.logCap, &ctl->overflowP1, it.b, s_stage, &s_staged };
-        wl_thread_tighten(p, it.row, pl, rd, sink);
+    // P1a: short-row items: the sums one thread per item (CSR order), the tightening nonzero-parallel per warp
+    for (unsigned i0 = gwarp << 5; i0 < nS; i0 += nwarps << 5) {
+      const unsigned i = i0 + lane;
+      const bool have = i < nS;
+      WlItem it;
+      it.b = 0;
+      it.row = 0;
+      if (have)
+        it = w.itemsS[cur][i];
+      const int cnt = have ? __ldg(&p.rowCnt[it.row]) : 0;
+      RowPlan pl;
+      pl.slackU = pl.slackL = 0.0;
+      pl.infMin = pl.infMax = 0;
+      pl.sideU = pl.sideL = pl.infeasible = false;
+      if (have) {
+        const WlVecReader rd = { &p, srcX + bt_base32(p, it.b), p.dmask + bt_word(p, 0, it.b >> 5), it.b & 31 };
+        const RowAct ra = wl_thread_sum<false>(p, it.row, rd, nullptr);
+        pl = plan_row(ra, __ldg(&p.rowLB[it.row]), __ldg(&p.rowUB[it.row]), p.s);
+        if (pl.infeasible)
+          atomicMin(&p.vecInfRow[it.b], __ldg(&p.rowOrig[it.row]));
+        myPairs += cnt;
       }
-      myPairs += __ldg(&p.rowCnt[it.row]);
+      wl_tighten_packed(p, srcX, have && !pl.infeasible && (pl.sideU || pl.sideL), it.b, it.row, cnt, pl, p.log, &ctl->nLog,
+        &ctl->overflowP1, s_stage, &s_staged, lane);
     }
     // P1b: pairs listed by table slot, one lane each; what needs a warp (a long row's walk) is done by the warp,
     // one pair after the other
@@ -892,11 +957,13 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       if (pl.infeasible)
         atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[row]));
       bool tight = !pl.infeasible && (pl.sideU || pl.sideL);
-      if (tight && cnt <= kShortLen) {
-        WlLogSink sink = { p.log, &ctl->nLog, p.logCap, &ctl->overflowP1, b, s_stage, &s_staged };
-        wl_thread_tighten(p, row, pl, rd, sink);
-        myPairs += cnt;
-        tight = false;
+      {  // rows of at most kShortLen nonzeros: nonzero-parallel, several items per trip
+        const bool shortTight = tight && cnt <= kShortLen;
+        wl_tighten_packed(p, srcX, shortTight, b, row, cnt, pl, p.log, &ctl->nLog, &ctl->overflowP1, s_stage, &s_staged, lane);
+        if (shortTight) {
+          myPairs += cnt;
+          tight = false;
+        }
       }
       todo = __ballot_sync(0xffffffffu, tight);
       while (todo) {
