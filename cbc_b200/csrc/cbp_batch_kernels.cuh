@@ -999,6 +999,20 @@ __global__ void bt_base_check_kernel(const double *__restrict__ baseLb, const do
     atomicOr(flag, 1);
 }
 
+// is any bound of the loaded batch (base or diffs) infinite?
+__global__ void bt_has_inf_kernel(const double *__restrict__ baseLb, const double *__restrict__ baseUb, int n,
+  const double *__restrict__ dBnd, long long nDelta, double INF, int *flag)
+{
+  bool bad = false;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    bad = bad || is_inf(baseLb[i], INF) || is_inf(baseUb[i], INF);
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nDelta; i += stride)
+    bad = bad || is_inf(dBnd[i], INF);
+  if (bad)
+    *flag = 1;
+}
+
 // every vector starts from the base bounds; both buffers are written
 __global__ void bt_expand_kernel(const double *__restrict__ baseLb, const double *__restrict__ baseUb,
   int n, int W, size_t cells, Bnd *X0, Bnd *X1)

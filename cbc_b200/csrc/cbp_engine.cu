@@ -64,6 +64,7 @@ struct BatchState {
   long long nDelta = 0;
   bool loaded = false, denseLoaded = false, consumed = false;
   bool hasInf = true;  // some input bound may be infinite (false only when checked)
+  bool hasInfKnown = false;  // ... and whether the loaded batch has been checked (on the device, when the full-walk path needs it)
   size_t capCells = 0, capDelta = 0, capStart = 0;
   int capBp = 0;
   // worklist form (cbp_wl_kernels.cuh)
@@ -75,6 +76,10 @@ struct BatchState {
   int *stCol = nullptr;
   double *stLb = nullptr, *stUb = nullptr;
   long long stCap = 0;
+  int *st2Col = nullptr;        // second set: the unsorted lists of a worklist run's fetch
+  double *st2Lb = nullptr, *st2Ub = nullptr;
+  long long st2Cap = 0;
+  bool lastWasWorklist = false; // the last run was in worklist form and `cells` lists every cell it created
   unsigned wlItemCap = 0, wlCellCap = 0;
   unsigned long long *wlHKey = nullptr;  // (vector, long row) pair table
   double *wlHMin = nullptr, *wlHMax = nullptr;
@@ -304,7 +309,8 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
     mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts, mat->bt.wlHKey,
-    mat->bt.wlRowBase, mat->bt.wlRowExact, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb };
+    mat->bt.wlRowBase, mat->bt.wlRowExact, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
+    mat->bt.st2Col, mat->bt.st2Lb, mat->bt.st2Ub };
   for (void *p : ptrs)
     if (p)
       cudaFree(p);
@@ -1336,18 +1342,11 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
   bt.loaded = true;
   bt.denseLoaded = false;
   bt.consumed = false;
-  // Are all input bounds finite?  Then the rows kernels drop their infinity tests.
+  // Are all input bounds finite?  (Then the full-walk rows kernels drop their infinity tests.)  Found out on the device,
+  // and only if that path is taken: the worklist kernel looks for itself.
   bt.hasInf = true;
-  if (!(flags & CBP_FLAG_DEVICE_PTRS)) {
-    // (counting, not stopping at the first hit: the loops vectorise)
-    const double inf = mat->inf;
-    long long bad = 0;
-    for (int j = 0; j < mat->n; ++j)
-      bad += (!(std::fabs(baseLb[j]) < inf)) + (!(std::fabs(baseUb[j]) < inf));
-    for (long long k = 0; k < nDelta; ++k)
-      bad += !(std::fabs(deltaBound[k]) < inf);
-    bt.hasInf = bad != 0;
-  }
+  bt.hasInfKnown = false;
+  bt.lastWasWorklist = false;
   return CBP_OK;
 }
 
@@ -1387,7 +1386,7 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.rowBaseMax = bt.wlRowBase + std::max(mat->mKept, 1);
   w.rowBaseRange = bt.wlRowBase + 2 * static_cast<size_t>(std::max(mat->mKept, 1));
   w.rowExact = bt.wlRowExact;
-  w.exactOk = (mat->allInt && !bt.hasInf) ? 1 : 0;
+  w.exactOk = mat->allInt ? 1 : 0;  // (which rows' sums are exact — integer data, finite bounds — the kernel finds out)
   CK(cudaMemsetAsync(bt.wlHKey, 0, static_cast<size_t>(bt.wlHSlots) * 28, st));
   w.dStart = bt.dStart;
   w.dVar = bt.dVar;
@@ -1444,6 +1443,7 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
     return CBP_OK;
   bt.wlMarksKnown = true;
   bt.wlPrevCells = std::min(h.nCells, bt.wlCellCap);
+  bt.lastWasWorklist = true;
   bt.baseMode = true;
   bt.quiet = false;
   bt.groupBuilt.assign(bt.G, 0);
@@ -1492,6 +1492,19 @@ int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeL
     CK(cudaEventRecord(ctx->evA, st));
   }
   bt.wlMarksKnown = false;  // the full-walk path below leaves marks the worklist form knows nothing about
+  bt.lastWasWorklist = false;
+  if (!bt.denseLoaded && !bt.hasInfKnown) {  // no infinite bound in base or diffs: kernel variants without infinity tests
+    int bad = 0;
+    CK(cudaMemsetAsync(mat->dRes, 0, sizeof(int), st));
+    bt_has_inf_kernel<<<std::max(1, std::min(1024, cdiv(std::max<long long>(mat->n, bt.nDelta), 256))), 256, 0, st>>>(bt.baseLb,
+      bt.baseUb, mat->n, bt.dBnd, bt.nDelta, mat->inf, mat->dRes);
+    ++ctx->stats.kernelLaunches;
+    CK(cudaMemcpyAsync(&bad, mat->dRes, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    ++hostSyncs;
+    bt.hasInf = bad != 0;
+    bt.hasInfKnown = true;
+  }
   if (!bt.dirty0Clean)
     CK(cudaMemsetAsync(bt.dirty[0], 0, sizeof(unsigned) * words, st));
   bt.dirty0Clean = false;
@@ -1851,6 +1864,83 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
     return CBP_OK;
   }
   const BtParams p = bt_params(mat, 0.0);
+  if (bt.lastWasWorklist) {
+    // the run listed every cell it created: the update lists come from that list (count, fill, order per vector)
+    // instead of two scans over the n x B / 32 words of marks
+    const unsigned nCells = bt.wlPrevCells;
+    int *cnt32 = bt.wlInts;  // (the run is over: its per-vector ints are free)  [0, Bp) counts, [Bp, 2Bp) cursors
+    CK(cudaMemsetAsync(cnt32, 0, sizeof(int) * 2 * static_cast<size_t>(bt.Bp), ctx->stream));
+    if (nCells > 0) {
+      wl_upd_count_kernel<<<cdiv(nCells, 256), 256, 0, ctx->stream>>>(bt.wlCells, nCells, p, cnt32);
+      ++ctx->stats.kernelLaunches;
+    }
+    std::vector<int> c32(bt.Bp);
+    CK(cudaMemcpyAsync(c32.data(), cnt32, sizeof(int) * bt.Bp, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<long long> off(bt.B + 1);
+    long long run = 0;
+    for (int b = 0; b < bt.B; ++b) {
+      off[b] = run;
+      run += c32[b];
+    }
+    off[bt.B] = run;
+    if (dev)
+      CK(cudaMemcpy(updStart, off.data(), sizeof(long long) * (bt.B + 1), cudaMemcpyHostToDevice));
+    else
+      memcpy(updStart, off.data(), sizeof(long long) * (bt.B + 1));
+    if (run > updCap || (run > 0 && (!updCol || !updLb || !updUb))) {
+      ctx->err = "cbp_batch_fetch: update buffers too small";
+      return CBP_ERR_CAPACITY;
+    }
+    if (run == 0)
+      return CBP_OK;
+    auto grow = [&](int *&c, double *&l, double *&u, long long &cap) -> int {
+      if (run <= cap)
+        return CBP_OK;
+      if (c)
+        cudaFree(c);
+      if (l)
+        cudaFree(l);
+      if (u)
+        cudaFree(u);
+      c = nullptr;
+      l = u = nullptr;
+      cap = 0;
+      const long long want = std::max<long long>(run + run / 2, 1 << 16);
+      if (dalloc(&c, want) != cudaSuccess || dalloc(&l, want) != cudaSuccess || dalloc(&u, want) != cudaSuccess) {
+        ctx->err = "cbp_batch_fetch: staging";
+        return CBP_ERR_NOMEM;
+      }
+      cap = want;
+      return CBP_OK;
+    };
+    int rcg = grow(bt.st2Col, bt.st2Lb, bt.st2Ub, bt.st2Cap);
+    if (rcg)
+      return rcg;
+    int *oCol = updCol;
+    double *oLb = updLb, *oUb = updUb;
+    if (!dev) {
+      if ((rcg = grow(bt.stCol, bt.stLb, bt.stUb, bt.stCap)))
+        return rcg;
+      oCol = bt.stCol;
+      oLb = bt.stLb;
+      oUb = bt.stUb;
+    }
+    CK(cudaMemcpyAsync(bt.counts, off.data(), sizeof(long long) * (bt.B + 1), cudaMemcpyHostToDevice, ctx->stream));
+    wl_upd_fill_kernel<<<cdiv(nCells, 256), 256, 0, ctx->stream>>>(bt.wlCells, nCells, p, bt.counts, cnt32 + bt.Bp, bt.st2Col,
+      bt.st2Lb, bt.st2Ub);
+    wl_upd_sort_kernel<<<cdiv(static_cast<long long>(bt.B) * 32, 256), 256, 0, ctx->stream>>>(bt.counts, bt.B, bt.st2Col, bt.st2Lb,
+      bt.st2Ub, oCol, oLb, oUb);
+    ctx->stats.kernelLaunches += 2;
+    CK(cudaGetLastError());
+    if (!dev) {
+      CK(cudaMemcpyAsync(updCol, oCol, sizeof(int) * run, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaMemcpyAsync(updLb, oLb, sizeof(double) * run, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaMemcpyAsync(updUb, oUb, sizeof(double) * run, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    return CBP_OK;
+  }
   const int nChunks = cdiv(mat->n, kUpdChunk);
   const dim3 updGrid(bt.G, cdiv(nChunks, 4)), updBlock(128);
   bt_updates_kernel<false><<<updGrid, updBlock, 0, ctx->stream>>>(p, bt.B, bt.chunkCnt, nullptr, nullptr, nullptr,

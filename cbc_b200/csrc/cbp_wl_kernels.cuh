@@ -78,7 +78,7 @@ struct WlParams {
   unsigned hMask;            // slots - 1 (a power of two)
   double *rowBaseMin, *rowBaseMax, *rowBaseRange;  // [mKept] the node's sums of the long rows (written by phase 0)
   unsigned char *rowExact;                          // [mKept] every sum over this row is exact in any order
-  int exactOk;  // host: every column is an integer column and no input bound is infinite
+  int exactOk;  // host: every column is an integer column (rows that see an infinite bound are not exact: phase 0 finds them)
   // the loaded batch
   const long long *dStart;
   const unsigned *dVar;
@@ -1176,6 +1176,58 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
   if (gtid == 0) {
     ctl->status = status;
     ctl->rounds = round;
+  }
+}
+
+// ---- updatedBounds() of a worklist run, from the list of cells instead of a scan of the `ever` marks ----------------
+// count per vector
+__global__ void wl_upd_count_kernel(const WlCell *__restrict__ cells, unsigned nCells, const BtParams p, int *cnt)
+{
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nCells)
+    return;
+  const WlCell c = cells[i];
+  if (p.vecStop[c.b] == 4)
+    return;  // a vector proved infeasible lists nothing
+  if ((p.ever[bt_word(p, c.j, c.b >> 5)] >> (c.b & 31)) & 1u)
+    atomicAdd(&cnt[c.b], 1);
+}
+
+// (col, lb, ub) of every changed cell into its vector's segment, in the order the threads get there
+__global__ void wl_upd_fill_kernel(const WlCell *__restrict__ cells, unsigned nCells, const BtParams p,
+  const long long *__restrict__ start, int *cursor, int *col, double *lb, double *ub)
+{
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nCells)
+    return;
+  const WlCell c = cells[i];
+  if (p.vecStop[c.b] == 4 || !((p.ever[bt_word(p, c.j, c.b >> 5)] >> (c.b & 31)) & 1u))
+    return;
+  const long long at = start[c.b] + atomicAdd(&cursor[c.b], 1);
+  const Bnd x = p.X[p.vecFinal[c.b]][bt_cell(p, c.j, c.b)];
+  col[at] = c.j;
+  lb[at] = x.lb;
+  ub[at] = x.ub;
+}
+
+// a vector's segment into ascending column order (the order updatedBounds() promises): one warp per vector, every
+// entry's place = the number of entries with a smaller column (a vector's columns are distinct)
+__global__ void wl_upd_sort_kernel(const long long *__restrict__ start, int B, const int *__restrict__ colIn,
+  const double *__restrict__ lbIn, const double *__restrict__ ubIn, int *colOut, double *lbOut, double *ubOut)
+{
+  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (b >= B)
+    return;
+  const long long s0 = start[b];
+  const int k = static_cast<int>(start[b + 1] - s0);
+  for (int e = lane; e < k; e += 32) {
+    const int c = colIn[s0 + e];
+    int rank = 0;
+    for (int f = 0; f < k; ++f)
+      rank += colIn[s0 + f] < c ? 1 : 0;
+    colOut[s0 + rank] = c;
+    lbOut[s0 + rank] = lbIn[s0 + e];
+    ubOut[s0 + rank] = ubIn[s0 + e];
   }
 }
 
