@@ -70,6 +70,8 @@ struct BatchState {
   // worklist form (cbp_wl_kernels.cuh)
   WlItem *wlItemsS[2] = { nullptr, nullptr }, *wlItemsL[2] = { nullptr, nullptr };
   WlCell *wlK = nullptr, *wlCells = nullptr;
+  WlWalk *wlWalk = nullptr;
+  unsigned wlWalkCap = 0;
   WlCtl *wlCtl = nullptr;
   int *wlInts = nullptr;  // vecChanged by round parity [2][Bp], active by round parity [2][G]
   // device staging of the update lists for host-pointer fetches (kept between calls: no cudaMalloc per fetch)
@@ -309,7 +311,7 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
     mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts, mat->bt.wlHKey,
-    mat->bt.wlRowBase, mat->bt.wlRowExact, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
+    mat->bt.wlWalk, mat->bt.wlRowBase, mat->bt.wlRowExact, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
     mat->bt.st2Col, mat->bt.st2Lb, mat->bt.st2Ub };
   for (void *p : ptrs)
     if (p)
@@ -1112,7 +1114,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
   if (cells > bt.capCells || Bp > bt.capBp) {
     void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt,
       bt.log, bt.groupFlag, bt.dmask, bt.wlItemsS[0], bt.wlItemsS[1], bt.wlItemsL[0], bt.wlItemsL[1], bt.wlK, bt.wlCells,
-      bt.wlCtl, bt.wlInts, bt.wlHKey };
+      bt.wlCtl, bt.wlInts, bt.wlHKey, bt.wlWalk };
+    bt.wlWalk = nullptr;
     bt.wlHKey = nullptr;
     bt.wlHMin = bt.wlHMax = nullptr;
     bt.wlHStamp = nullptr;
@@ -1166,6 +1169,12 @@ static int bt_reserve(cbp_matrix *mat, int B)
       bt.wlHMin = reinterpret_cast<double *>(blk + static_cast<size_t>(bt.wlHSlots) * 8);
       bt.wlHMax = reinterpret_cast<double *>(blk + static_cast<size_t>(bt.wlHSlots) * 16);
       bt.wlHStamp = reinterpret_cast<int *>(blk + static_cast<size_t>(bt.wlHSlots) * 24);
+    }
+    bt.wlWalkCap = mat->nLongBt > 0
+      ? static_cast<unsigned>(std::min<size_t>(1u << 22, std::max<size_t>(1u << 16, static_cast<size_t>(Bp) * 256))) : 1u;
+    if (dalloc(&bt.wlWalk, bt.wlWalkCap) != cudaSuccess) {
+      ctx->err = "batch workspace (long-row queue)";
+      return CBP_ERR_NOMEM;
     }
     if (dalloc(&bt.wlItemsS[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsS[1], bt.wlItemCap) != cudaSuccess
       || dalloc(&bt.wlItemsL[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsL[1], bt.wlItemCap) != cudaSuccess
@@ -1400,6 +1409,8 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   }
   w.K = bt.wlK;
   w.cells = bt.wlCells;
+  w.walk = bt.wlWalk;
+  w.walkCap = bt.wlWalkCap;
   w.itemCap = bt.wlItemCap;
   w.kCap = bt.wlCellCap;
   w.cellCap = bt.wlCellCap;

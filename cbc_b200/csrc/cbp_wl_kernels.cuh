@@ -41,10 +41,21 @@ struct WlCell {
 
 enum { kWlOk = 0, kWlBaseNotFixpoint = 1, kWlOverflow = 2 };
 
+// A (vector, row) pair whose row is too long for one warp (more than kBtLongLen nonzeros) and has to be walked — for
+// its sums (needSum) or, sums known, for the tightening with the plan kept here: done after the items by a whole CTA
+// per entry, so that one 4,000-nonzero row walked by one warp is not the tail of the phase.
+struct __align__(16) WlWalk {
+  int b, row;
+  int needSum;
+  int packed;  // plan: infMin | infMax << 2 | sideU << 4 | sideL << 5
+  double slackU, slackL;
+};
+
 // control block (device); zeroed by the host before every launch
 struct WlCtl {
   unsigned nS[2], nL[2];  // items of the running / next round: rows <= kShortLen nonzeros, longer rows
   unsigned nLog, nK, nCells;
+  unsigned nWalk;  // entries of the long-row walk queue of the running round
   int baseBad, timeUp;
   int inexact;     // a diff is fractional or leaves the node's bounds: long rows are walked, not updated from the node's sums
   int overflow;    // a list other than the candidate list ran out of room (written outside P1 only)
@@ -87,6 +98,8 @@ struct WlParams {
   // lists
   WlItem *itemsS[2], *itemsL[2];
   WlCell *K, *cells;
+  WlWalk *walk;
+  unsigned walkCap;
   unsigned itemCap, kCap, cellCap;
   unsigned prevCells;  // cells the previous worklist run left behind (their mask / ever bits are taken out first)
   WlCtl *ctl;
@@ -925,6 +938,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       const WlVecReader rd = { &p, srcX + bt_base32(p, b), p.dmask + bt_word(p, 0, b >> 5), b & 31 };
       RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
       bool needSum = have;
+      bool have_plan = have;  // (false once the pair has gone to the long-row queue)
       if (have && exact && __ldg(&w.rowExact[row])) {
         ra.minAct = __ldcg(&w.rowBaseMin[row]) + __ldcg(&w.hMin[slot]);
         ra.maxAct = __ldcg(&w.rowBaseMax[row]) + __ldcg(&w.hMax[slot]);
@@ -935,6 +949,20 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         ra = wl_thread_sum<false>(p, row, rd, nullptr);
         myPairs += cnt;
         needSum = false;
+      }
+      if (needSum && cnt > kBtLongLen) {  // too long for a warp: a CTA walks it after the items (sums, then the rest)
+        const unsigned qi = wl_append(&ctl->nWalk, w.walkCap, &ctl->overflowP1);
+        if (qi != ~0u) {
+          WlWalk e;
+          e.b = b;
+          e.row = row;
+          e.needSum = 1;
+          e.packed = 0;
+          e.slackU = e.slackL = 0.0;
+          w.walk[qi] = e;
+        }
+        needSum = false;
+        have_plan = false;
       }
       unsigned todo = __ballot_sync(0xffffffffu, needSum);
       while (todo) {
@@ -949,7 +977,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         }
       }
       RowPlan pl = plan_row(ra, have ? __ldg(&p.rowLB[row]) : 0.0, have ? __ldg(&p.rowUB[row]) : 0.0, p.s);
-      if (!have) {
+      if (!have_plan) {
         pl.infeasible = false;
         pl.sideU = false;
         pl.sideL = false;
@@ -957,6 +985,20 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       if (pl.infeasible)
         atomicMin(&p.vecInfRow[b], __ldg(&p.rowOrig[row]));
       bool tight = !pl.infeasible && (pl.sideU || pl.sideL);
+      if (tight && cnt > kBtLongLen) {  // the sums were exact and cheap, the tightening walk is not: queue it with its plan
+        const unsigned qi = wl_append(&ctl->nWalk, w.walkCap, &ctl->overflowP1);
+        if (qi != ~0u) {
+          WlWalk e;
+          e.b = b;
+          e.row = row;
+          e.needSum = 0;
+          e.packed = min(pl.infMin, 2) | (min(pl.infMax, 2) << 2) | (pl.sideU ? 16 : 0) | (pl.sideL ? 32 : 0);
+          e.slackU = pl.slackU;
+          e.slackL = pl.slackL;
+          w.walk[qi] = e;
+        }
+        tight = false;
+      }
       {  // rows of at most kShortLen nonzeros: nonzero-parallel, several items per trip
         const bool shortTight = tight && cnt <= kShortLen;
         wl_tighten_packed(p, srcX, shortTight, b, row, cnt, pl, p.log, &ctl->nLog, &ctl->overflowP1, s_stage, &s_staged, lane);
@@ -1011,6 +1053,96 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
     if (*reinterpret_cast<volatile int *>(&ctl->overflowP1)) {  // (P1 is over: nobody writes this word now)
       status = kWlOverflow;
       break;
+    }
+    const unsigned nWalk = *reinterpret_cast<volatile unsigned *>(&ctl->nWalk);
+    if (nWalk > 0) {
+      // P1c: the long rows that have to be walked, a CTA per (vector, row) pair
+      for (unsigned e = blockIdx.x; e < nWalk; e += gridDim.x) {
+        const WlWalk q = w.walk[e];
+        const WlVecReader rd = { &p, srcX + bt_base32(p, q.b), p.dmask + bt_word(p, 0, q.b >> 5), q.b & 31 };
+        const int kb = __ldg(&p.rowNz[q.row]), ke = kb + __ldg(&p.rowCnt[q.row]);
+        RowPlan pl;
+        pl.slackU = q.slackU;
+        pl.slackL = q.slackL;
+        pl.infMin = q.packed & 3;
+        pl.infMax = (q.packed >> 2) & 3;
+        pl.sideU = (q.packed & 16) != 0;
+        pl.sideL = (q.packed & 32) != 0;
+        pl.infeasible = false;
+        if (q.needSum) {
+          RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
+          for (int k0 = kb; k0 < ke; k0 += 2 * kThreads) {  // two nonzeros per thread in flight
+            double a[2];
+            int c[2], jj[2];
+            Bnd x[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int k = k0 + u * kThreads + tid;
+              a[u] = 0.0;
+              c[u] = 0;
+              if (k < ke) {
+                c[u] = __ldg(&p.col[k]);
+                a[u] = __ldg(&p.val[k]);
+              }
+              jj[u] = col_of(c[u]);
+            }
+            rd.get_n(jj, x);
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+              if (a[u] != 0.0)
+                accumulate(ra, a[u], col_is_int(c[u]), a[u] > 0.0 ? x[u].lb : x[u].ub, a[u] > 0.0 ? x[u].ub : x[u].lb, p.s.inf);
+          }
+          warp_reduce(ra);
+          __syncthreads();
+          if (lane == 0)
+            s_row[tid >> 5] = ra;
+          __syncthreads();
+          RowAct tot = s_row[0];
+          for (int q2 = 1; q2 < kWarps; ++q2)  // (every thread alike, warp order)
+            combine(tot, s_row[q2]);
+          pl = plan_row(tot, __ldg(&p.rowLB[q.row]), __ldg(&p.rowUB[q.row]), p.s);
+          if (pl.infeasible && tid == 0)
+            atomicMin(&p.vecInfRow[q.b], __ldg(&p.rowOrig[q.row]));
+          if (tid == 0)
+            myPairs += ke - kb;
+        }
+        if (!pl.infeasible && (pl.sideU || pl.sideL)) {
+          WlLogSink sink = { p.log, &ctl->nLog, p.logCap, &ctl->overflowP1, q.b, s_stage, &s_staged };
+          for (int k = kb + tid; k < ke; k += kThreads) {
+            const int c = __ldg(&p.col[k]);
+            const double a = __ldg(&p.val[k]);
+            const Bnd x = rd.get(col_of(c));
+            tighten_nz(sink, pl, a, col_of(c), col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+          }
+          if (tid == 0)
+            myPairs += ke - kb;
+        }
+        __syncthreads();
+      }
+      __syncthreads();
+      {
+        const unsigned n = min(s_staged, kWlStage);
+        if (tid == 0 && n)
+          s_base = atomicAdd(&ctl->nLog, n);
+        __syncthreads();
+        for (unsigned i = tid; i < n; i += kThreads) {
+          if (s_base + i < p.logCap)
+            p.log[s_base + i] = s_stage[i];
+          else
+            ctl->overflow = 1;
+        }
+        __syncthreads();
+        if (tid == 0)
+          s_staged = 0u;
+      }
+      grid.sync();
+      wl_stamp(ctl, gtid);
+      if (gtid == 0)
+        ctl->nWalk = 0u;  // (every thread has read it: the barrier above lies in between)
+      if (*reinterpret_cast<volatile int *>(&ctl->overflowP1) || *reinterpret_cast<volatile int *>(&ctl->overflow)) {
+        status = kWlOverflow;
+        break;
+      }
     }
     const unsigned nLog = min(*reinterpret_cast<volatile unsigned *>(&ctl->nLog), p.logCap);
     if (gtid == 0) {  // (the consumed item lists; nobody touches these counters before P6)

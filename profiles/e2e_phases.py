@@ -18,7 +18,7 @@ def root(inst):
     return lb, ub
 
 
-w = bench.make_workload(name, 0, 1.0, root)
+w = bench.make_workload(name, 0, float(sys.argv[2]) if len(sys.argv) > 2 else 1.0, root)
 inst = w["inst"]
 s, v, b = w["deltas"]
 mat = capi.Matrix(ctx, inst)
@@ -37,4 +37,4 @@ for _ in range(N):
     tl += t1 - t0
     tr += t2 - t1
     tf += t3 - t2
-print("%s: load %.3f ms  run %.3f ms  fetch %.3f ms  (updates %d)" % (name, tl / N * 1e3, tr / N * 1e3, tf / N * 1e3, r[2].size))
+print("%s B=%d %s: load %.3f ms  run %.3f ms  fetch %.3f ms  (updates %d)" % (name, len(s) - 1, "full-walk" if os.environ.get("CBP_NO_WORKLIST") else "worklist", tl / N * 1e3, tr / N * 1e3, tf / N * 1e3, r[2].size))
