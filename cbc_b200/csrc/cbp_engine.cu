@@ -83,12 +83,15 @@ struct BatchState {
   long long st2Cap = 0;
   bool lastWasWorklist = false; // the last run was in worklist form and `cells` lists every cell it created
   unsigned wlItemCap = 0, wlCellCap = 0;
-  unsigned long long *wlHKey = nullptr;  // (vector, long row) pair table
-  double *wlHMin = nullptr, *wlHMax = nullptr;
-  int *wlHStamp = nullptr;
+  WlPair *wlHKey = nullptr;  // (vector, row) pair table
+  unsigned wlHActive = 0;    // slots the next run hashes into (a power of two <= wlHSlots): what the last run took x 3,
+                             // so that a batch that touches few pairs keeps its table in L2
   unsigned wlHSlots = 0;
-  double *wlRowBase = nullptr;  // [3][mKept] the node's sums of the long rows
-  unsigned char *wlRowExact = nullptr;
+  unsigned *wlUsed = nullptr;   // table slots the running worklist run takes (emptied again after it)
+  unsigned wlUsedCap = 0;
+  bool wlTableClean = false;    // every slot of the table is free, except the wlPrevUsed listed in wlUsed
+  unsigned wlPrevUsed = 0;
+  WlRowBase *wlRowBase = nullptr;  // [mKept] the node's sums of the rows
   unsigned wlPrevCells = 0;  // cells the last worklist run left in the masks
   bool wlMarksKnown = false; // dmask / ever / dirty are all zero except for those cells
 };
@@ -160,6 +163,7 @@ static thread_local std::string g_createErr;
 struct EnvKnobs {
   bool noWorklist, noLazyX1, lazyX1, noBaseRound, noMultiGroup, wlStamps;
   int overlayRounds;
+  int wlTableFactor;  // CBP_WL_TABLE_FACTOR: slots per pair the last run took (0 = always the whole table)
   EnvKnobs()
     : noWorklist(getenv("CBP_NO_WORKLIST") != nullptr)
     , noLazyX1(getenv("CBP_NO_LAZY_X1") != nullptr)
@@ -168,6 +172,7 @@ struct EnvKnobs {
     , noMultiGroup(getenv("CBP_NO_MULTI_GROUP") != nullptr)
     , wlStamps(getenv("CBP_WL_STAMPS") != nullptr)
     , overlayRounds(getenv("CBP_OVERLAY_ROUNDS") ? atoi(getenv("CBP_OVERLAY_ROUNDS")) : INT_MAX)
+    , wlTableFactor(getenv("CBP_WL_TABLE_FACTOR") ? atoi(getenv("CBP_WL_TABLE_FACTOR")) : 16)
   {
   }
 };
@@ -311,7 +316,7 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
     mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts, mat->bt.wlHKey,
-    mat->bt.wlWalk, mat->bt.wlRowBase, mat->bt.wlRowExact, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
+    mat->bt.wlWalk, mat->bt.wlUsed, mat->bt.wlRowBase, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
     mat->bt.st2Col, mat->bt.st2Lb, mat->bt.st2Ub };
   for (void *p : ptrs)
     if (p)
@@ -1114,11 +1119,11 @@ static int bt_reserve(cbp_matrix *mat, int B)
   if (cells > bt.capCells || Bp > bt.capBp) {
     void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt,
       bt.log, bt.groupFlag, bt.dmask, bt.wlItemsS[0], bt.wlItemsS[1], bt.wlItemsL[0], bt.wlItemsL[1], bt.wlK, bt.wlCells,
-      bt.wlCtl, bt.wlInts, bt.wlHKey, bt.wlWalk };
+      bt.wlCtl, bt.wlInts, bt.wlHKey, bt.wlWalk, bt.wlUsed };
     bt.wlWalk = nullptr;
+    bt.wlUsed = nullptr;
+    bt.wlTableClean = false;
     bt.wlHKey = nullptr;
-    bt.wlHMin = bt.wlHMax = nullptr;
-    bt.wlHStamp = nullptr;
     bt.dmask = nullptr;
     bt.wlItemsS[0] = bt.wlItemsS[1] = bt.wlItemsL[0] = bt.wlItemsL[1] = nullptr;
     bt.wlK = bt.wlCells = nullptr;
@@ -1149,7 +1154,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.wlHSlots = 2;
     if (mat->mKept > 0) {
       // (every row's pairs go through the table when sums are exact; only the longer rows' otherwise)
-      size_t want = std::max<size_t>(1u << 18, static_cast<size_t>(Bp) * (mat->allInt ? 1024 : (mat->mKept > mat->mShort ? 64 : 0)));
+      // (a run empties the slots it took, so the size costs memory, not time: sized for a load factor well under 1/2)
+      size_t want = std::max<size_t>(1u << 18, static_cast<size_t>(Bp) * (mat->allInt ? 2048 : (mat->mKept > mat->mShort ? 256 : 0)));
       bt.wlHSlots = 1u << 18;
       while (bt.wlHSlots < want && bt.wlHSlots < (1u << 25))
         bt.wlHSlots <<= 1;
@@ -1159,16 +1165,18 @@ static int bt_reserve(cbp_matrix *mat, int B)
       while (bt.wlHSlots < static_cast<unsigned>(std::max<long>(2, atol(getenv("CBP_WL_SLOTS")))))
         bt.wlHSlots <<= 1;
     }
-    {  // key | min | max | stamp in one allocation: one memset clears the table
-      unsigned char *blk = nullptr;
-      if (dalloc(&blk, static_cast<size_t>(bt.wlHSlots) * 28) != cudaSuccess) {
+    {
+      if (dalloc(&bt.wlHKey, bt.wlHSlots) != cudaSuccess) {
         ctx->err = "batch workspace (pair table)";
         return CBP_ERR_NOMEM;
       }
-      bt.wlHKey = reinterpret_cast<unsigned long long *>(blk);
-      bt.wlHMin = reinterpret_cast<double *>(blk + static_cast<size_t>(bt.wlHSlots) * 8);
-      bt.wlHMax = reinterpret_cast<double *>(blk + static_cast<size_t>(bt.wlHSlots) * 16);
-      bt.wlHStamp = reinterpret_cast<int *>(blk + static_cast<size_t>(bt.wlHSlots) * 24);
+      bt.wlHActive = bt.wlHSlots;
+      bt.wlUsedCap = std::min(bt.wlHSlots, std::max(1u << 20, bt.wlItemCap));
+      if (dalloc(&bt.wlUsed, bt.wlUsedCap) != cudaSuccess) {
+        ctx->err = "batch workspace (pair table slots)";
+        return CBP_ERR_NOMEM;
+      }
+      bt.wlTableClean = false;
     }
     bt.wlWalkCap = mat->nLongBt > 0
       ? static_cast<unsigned>(std::min<size_t>(1u << 22, std::max<size_t>(1u << 16, static_cast<size_t>(Bp) * 256))) : 1u;
@@ -1202,8 +1210,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.logCap = getenv("CBP_LOG_CAP") ? std::min<unsigned>(logCap, static_cast<unsigned>(atol(getenv("CBP_LOG_CAP")))) : logCap;
   }
   if (!bt.wlRowBase) {
-    if (dalloc(&bt.wlRowBase, 3 * static_cast<size_t>(std::max(mat->mKept, 1))) != cudaSuccess
-      || dalloc(&bt.wlRowExact, std::max(mat->mKept, 1)) != cudaSuccess) {
+    if (dalloc(&bt.wlRowBase, static_cast<size_t>(std::max(mat->mKept, 1))) != cudaSuccess) {
       ctx->err = "batch workspace: row sums";
       return CBP_ERR_NOMEM;
     }
@@ -1386,17 +1393,24 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.sellOff = mat->sellOff;
   w.nSlices = mat->nSlices;
   w.mShort = mat->mShort;
-  w.hKey = bt.wlHKey;
-  w.hMin = bt.wlHMin;
-  w.hMax = bt.wlHMax;
-  w.hStamp = bt.wlHStamp;
-  w.hMask = bt.wlHSlots - 1;
-  w.rowBaseMin = bt.wlRowBase;
-  w.rowBaseMax = bt.wlRowBase + std::max(mat->mKept, 1);
-  w.rowBaseRange = bt.wlRowBase + 2 * static_cast<size_t>(std::max(mat->mKept, 1));
-  w.rowExact = bt.wlRowExact;
+  w.tab = bt.wlHKey;
+  w.hMask = bt.wlHActive - 1;
+  w.hShift = 64;
+  for (unsigned t = bt.wlHActive; t > 1u; t >>= 1)
+    --w.hShift;
+  if (w.hShift > 63) {  // (a one-slot table: no shift by 64)
+    w.hShift = 63;
+  }
+  w.rowBase = bt.wlRowBase;
   w.exactOk = mat->allInt ? 1 : 0;  // (which rows' sums are exact — integer data, finite bounds — the kernel finds out)
-  CK(cudaMemsetAsync(bt.wlHKey, 0, static_cast<size_t>(bt.wlHSlots) * 28, st));
+  w.used = bt.wlUsed;
+  w.usedCap = bt.wlUsedCap;
+  if (!bt.wlTableClean) {  // first use, or the last run took more slots than its list holds
+    CK(cudaMemsetAsync(bt.wlHKey, 0, static_cast<size_t>(bt.wlHSlots) * sizeof(WlPair), st));
+    bt.wlPrevUsed = 0;
+  }
+  w.prevUsed = bt.wlPrevUsed;
+  bt.wlTableClean = false;
   w.dStart = bt.dStart;
   w.dVar = bt.dVar;
   w.dBnd = bt.dBnd;
@@ -1418,12 +1432,9 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.ctl = bt.wlCtl;
   w.limit = limit;
   w.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
-  CK(cudaMemsetAsync(bt.wlCtl, 0, sizeof(WlCtl), st));
-  CK(cudaMemsetAsync(bt.wlInts, 0, sizeof(int) * (static_cast<size_t>(bt.Bp) * 2 + static_cast<size_t>(bt.G) * 2), st));
-  bt_init_state_kernel<<<cdiv(bt.Bp, 256), 256, 0, st>>>(p, bt.B);
-  CK(cudaMemcpyAsync(w.active2[0], p.active, sizeof(unsigned) * bt.G, cudaMemcpyDeviceToDevice, st));
-  bt_base_pack_kernel<<<cdiv(mat->n, 256), 256, 0, st>>>(bt.baseLb, bt.baseUb, mat->n, bt.baseX);
-  ctx->stats.kernelLaunches += 2;
+  wl_setup_kernel<<<cdiv(std::max<size_t>(std::max(mat->n, bt.Bp), sizeof(WlCtl) / sizeof(unsigned)), 256), 256, 0, st>>>(w,
+    bt.baseLb, bt.baseUb, bt.baseX);
+  ++ctx->stats.kernelLaunches;
   const int grid = std::max(1, ctx->wlBlocksPerSM * ctx->numSMs);
   void *args[] = { &w };
   CK(cudaEventRecord(ctx->evPool[0], st));
@@ -1435,9 +1446,19 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   CK(cudaEventRecord(ctx->evB, st));
   CK(cudaStreamSynchronize(st));  // the one host synchronisation of the run
   *status = h.status;
+  bt.wlTableClean = !h.usedOverflow;
+  bt.wlPrevUsed = std::min(h.nUsed, bt.wlUsedCap);
+  {  // the next run's table: three slots per pair this one took (all of it after a run that ran out of room)
+    unsigned want = 1u << 10;
+    const unsigned f = static_cast<unsigned>(std::max(1, knobs().wlTableFactor));
+    while (want < bt.wlHSlots && want / f < h.nUsed)
+      want <<= 1;
+    bt.wlHActive = (h.status == kWlOverflow || h.usedOverflow || knobs().wlTableFactor <= 0) ? bt.wlHSlots
+                                                                                             : std::min(want, bt.wlHSlots);
+  }
   if (knobs().wlStamps) {
-    fprintf(stderr, "worklist run: status %d rounds %d items %llu pairs %llu cells %u; phase ends (us):", h.status, h.rounds,
-      h.itemsTotal, h.pairs, h.nCells);
+    fprintf(stderr, "worklist run: status %d rounds %d items %llu pairs %llu cells %u table %u of %u; phase ends (us):", h.status,
+      h.rounds, h.itemsTotal, h.pairs, h.nCells, h.nUsed, w.hMask + 1u);
     for (unsigned i = 0; i < std::min(h.nStamps, 96u); ++i)
       fprintf(stderr, " %.1f", h.stamps[i] * 1e-3);
     fprintf(stderr, "\n");

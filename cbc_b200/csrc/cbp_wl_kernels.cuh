@@ -51,7 +51,22 @@ struct __align__(16) WlWalk {
   double slackU, slackL;
 };
 
-// control block (device); zeroed by the host before every launch
+// One slot of the (vector, row) pair table: a 32-byte sector, so that finding the pair, adding to its sums and stamping
+// it touch one sector of HBM, not four.
+struct __align__(32) WlPair {
+  unsigned long long key;  // ((b << 32) | row) + 1, 0 = free
+  double dMin, dMax;       // sum over the vector's own cells in the row of a * (own bound - node's bound)
+  int stamp;               // last round (+1) the pair was listed for
+  int pad;
+};
+// The node's sums of a row (written by phase 0), one sector as well.
+struct __align__(32) WlRowBase {
+  double mn, mx, range;
+  int exact;  // every sum over this row is exact in any order
+  int pad;
+};
+
+// control block (device); zeroed by wl_setup_kernel before every launch
 struct WlCtl {
   unsigned nS[2], nL[2];  // items of the running / next round: rows <= kShortLen nonzeros, longer rows
   unsigned nLog, nK, nCells;
@@ -62,6 +77,8 @@ struct WlCtl {
   int overflowP1;  // the candidate list did (written in P1 only): two words, so that each is read while nobody writes it
   int anyActive[2];
   int status, rounds;
+  unsigned nUsed;    // table slots taken by this run (listed in WlParams::used; the next run empties them first)
+  int usedOverflow;  // more than the list holds: the host clears the whole table before the next run
   unsigned long long pairs;   // (nonzero, vector) pairs walked
   unsigned long long itemsTotal;
   unsigned long long roundsTotal;  // rounds summed over the vectors (each adds its count when it stops)
@@ -83,12 +100,12 @@ struct WlParams {
   // Rows longer than kShortLen: one table slot per (vector, row) pair that has come up, found by hashing.  It keeps
   // an item from being listed twice in a round and, where sums are exact (see exactOk), the pair's activity as
   // "the node's sums + what the vector's own cells add".
-  unsigned long long *hKey;  // ((b << 32) | row) + 1, 0 = free
-  double *hMin, *hMax;       // sum over the vector's own cells in the row of a * (own bound - node's bound)
-  int *hStamp;               // last round (+1) the pair was listed for
-  unsigned hMask;            // slots - 1 (a power of two)
-  double *rowBaseMin, *rowBaseMax, *rowBaseRange;  // [mKept] the node's sums of the long rows (written by phase 0)
-  unsigned char *rowExact;                          // [mKept] every sum over this row is exact in any order
+  WlPair *tab;
+  unsigned hMask;            // slots in use - 1 (a power of two)
+  int hShift;                // 64 - log2(slots in use): the hash is the top bits of key x odd constant
+  unsigned *used;            // slots this run has taken, so that the run after it starts from an empty table without
+  unsigned usedCap;          // a memset of all of it
+  WlRowBase *rowBase;        // [mKept]
   int exactOk;  // host: every column is an integer column (rows that see an infinite bound are not exact: phase 0 finds them)
   // the loaded batch
   const long long *dStart;
@@ -101,6 +118,7 @@ struct WlParams {
   WlWalk *walk;
   unsigned walkCap;
   unsigned itemCap, kCap, cellCap;
+  unsigned prevUsed;   // table slots the previous worklist run took (listed in `used`; emptied first)
   unsigned prevCells;  // cells the previous worklist run left behind (their mask / ever bits are taken out first)
   WlCtl *ctl;
   int *vecChanged2[2];   // [Bp] changed columns, by round parity
@@ -457,45 +475,54 @@ __device__ __forceinline__ void wl_row_warp_tighten(const BtParams &p, int row, 
   }
 }
 
-// the slot of pair (b, row) in the table (linear probing); ~0u when the table is too full
-__device__ __forceinline__ unsigned wl_slot(const WlParams &w, int b, int row)
+// The three reservations of wl_emit_rows — short items, table items, newly taken table slots — with their atomics in
+// flight together.  ~0u = that list is full.
+__device__ __forceinline__ void wl_warp_reserve3(const WlParams &w, int nxt, int nS, int nL, int nU, int lane,
+  unsigned &atS, unsigned &atL, unsigned &atU)
 {
-  const unsigned long long key = ((static_cast<unsigned long long>(static_cast<unsigned>(b)) << 32) | static_cast<unsigned>(row)) + 1ull;
-  unsigned long long z = key * 0x9E3779B97F4A7C15ull;
-  unsigned h = static_cast<unsigned>(z >> 32) & w.hMask;
-  for (int probe = 0; probe < 128; ++probe) {
-    const unsigned long long prev = atomicCAS(&w.hKey[h], 0ull, key);
-    if (prev == 0ull || prev == key)
-      return h;
-    h = (h + 1u) & w.hMask;
-  }
-  return ~0u;
-}
-
-// Room for n entries of this lane in a list: the 32 lanes of a warp (all of them call this together) share one
-// atomic on the list's counter.  Returns the lane's first slot, or ~0u when the list is full.
-__device__ __forceinline__ unsigned wl_warp_reserve(unsigned *count, unsigned cap, int *overflow, int n, int lane)
-{
-  int incl = n;
+  int iS = nS, iL = nL, iU = nU;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
-    const int t = __shfl_up_sync(0xffffffffu, incl, d);
-    if (lane >= d)
-      incl += t;
+    const int tS = __shfl_up_sync(0xffffffffu, iS, d), tL = __shfl_up_sync(0xffffffffu, iL, d),
+              tU = __shfl_up_sync(0xffffffffu, iU, d);
+    if (lane >= d) {
+      iS += tS;
+      iL += tL;
+      iU += tU;
+    }
   }
-  const int total = __shfl_sync(0xffffffffu, incl, 31);
-  if (total == 0)
-    return 0u;
-  unsigned base = 0u;
-  if (lane == 31)
-    base = atomicAdd(count, static_cast<unsigned>(total));
-  base = __shfl_sync(0xffffffffu, base, 31);
-  if (base + static_cast<unsigned>(total) > cap) {
+  const int totS = __shfl_sync(0xffffffffu, iS, 31), totL = __shfl_sync(0xffffffffu, iL, 31),
+            totU = __shfl_sync(0xffffffffu, iU, 31);
+  unsigned bS = 0u, bL = 0u, bU = 0u;
+  if (lane == 31) {
+    if (totS)
+      bS = atomicAdd(&w.ctl->nS[nxt], static_cast<unsigned>(totS));
+    if (totL)
+      bL = atomicAdd(&w.ctl->nL[nxt], static_cast<unsigned>(totL));
+    if (totU)
+      bU = atomicAdd(&w.ctl->nUsed, static_cast<unsigned>(totU));
+  }
+  bS = __shfl_sync(0xffffffffu, bS, 31);
+  bL = __shfl_sync(0xffffffffu, bL, 31);
+  bU = __shfl_sync(0xffffffffu, bU, 31);
+  atS = bS + static_cast<unsigned>(iS - nS);
+  atL = bL + static_cast<unsigned>(iL - nL);
+  atU = bU + static_cast<unsigned>(iU - nU);
+  if (bS + static_cast<unsigned>(totS) > w.itemCap) {
     if (lane == 31)
-      *overflow = 1;
-    return ~0u;
+      w.ctl->overflow = 1;
+    atS = ~0u;
   }
-  return base + static_cast<unsigned>(incl - n);
+  if (bL + static_cast<unsigned>(totL) > w.itemCap) {
+    if (lane == 31)
+      w.ctl->overflow = 1;
+    atL = ~0u;
+  }
+  if (bU + static_cast<unsigned>(totU) > w.usedCap) {
+    if (lane == 31)
+      w.ctl->usedOverflow = 1;
+    atU = ~0u;
+  }
 }
 
 // Cell (b, j) went from bounds `was` to bounds `now` (lanes with active == false have no cell): the rows of column j
@@ -510,57 +537,103 @@ __device__ __forceinline__ void wl_emit_rows(const WlParams &w, bool active, int
   const int trips = __reduce_max_sync(0xffffffffu, (ce - cs + 7) >> 3);
   for (int t = 0; t < trips; ++t) {
     const int q0 = cs + 8 * t;
-    int r[8], c[8];
+    int r[8];
     unsigned slot[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u)
       r[u] = q0 + u < ce ? __ldg(&w.cscRow[q0 + u]) : -1;
+    unsigned shortRows = 0u;  // rows for the short list (with exact sums every row goes through the table)
+    if (!w.exactOk) {
+      int c[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
-      c[u] = r[u] >= 0 ? __ldg(&w.bt.rowCnt[r[u]]) : 0;
-    int nS = 0, nL = 0;
+      for (int u = 0; u < 8; ++u)
+        c[u] = r[u] >= 0 ? __ldg(&w.bt.rowCnt[r[u]]) : 0x7fffffff;
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (c[u] <= kShortLen)
+          shortRows |= 1u << u;
+    }
+    const int nS = __popc(shortRows);
+    // The pairs' table slots (linear probing): every probe step is one compare-and-swap per row, and the eight rows'
+    // steps go out together before any answer is waited for — one after the other they would be a chain of round trips.
+    const unsigned long long keyHi = static_cast<unsigned long long>(static_cast<unsigned>(b)) << 32;
+    unsigned pend = 0u, fresh = 0u;
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       slot[u] = ~0u;
-      if (r[u] < 0)
+      if (r[u] < 0 || ((shortRows >> u) & 1u))
         continue;
-      if (c[u] <= kShortLen && !w.exactOk) {
-        ++nS;
-        continue;
-      }
-      const unsigned sl = wl_slot(w, b, r[u]);
-      if (sl == ~0u) {
-        w.ctl->overflow = 1;
-        continue;
-      }
-      if (w.exactOk) {
-        const double a = __ldg(&w.cscVal[q0 + u]);
-        const double dLb = now.lb - was.lb, dUb = now.ub - was.ub;
-        const double dMin = a * (a > 0.0 ? dLb : dUb), dMax = a * (a > 0.0 ? dUb : dLb);
-        if (dMin != 0.0)
-          atomicAdd(&w.hMin[sl], dMin);
-        if (dMax != 0.0)
-          atomicAdd(&w.hMax[sl], dMax);
-      }
-      if (atomicMax(&w.hStamp[sl], forRound + 1) < forRound + 1) {
-        slot[u] = sl;
-        ++nL;
-      }
+      const unsigned long long key = (keyHi | static_cast<unsigned>(r[u])) + 1ull;
+      slot[u] = static_cast<unsigned>((key * 0x9E3779B97F4A7C15ull) >> w.hShift);
+      pend |= 1u << u;
     }
-    unsigned atS = wl_warp_reserve(&w.ctl->nS[nxt], w.itemCap, &w.ctl->overflow, nS, lane);
-    unsigned atL = wl_warp_reserve(&w.ctl->nL[nxt], w.itemCap, &w.ctl->overflow, nL, lane);
+    unsigned tbl = pend;  // rows that go through the table
+    for (int probe = 0; probe < 128 && pend; ++probe) {
+      unsigned long long seen[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if ((pend >> u) & 1u)
+          seen[u] = atomicCAS(&w.tab[slot[u]].key, 0ull, (keyHi | static_cast<unsigned>(r[u])) + 1ull);
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if ((pend >> u) & 1u) {
+          if (seen[u] == 0ull || seen[u] == (keyHi | static_cast<unsigned>(r[u])) + 1ull) {
+            pend &= ~(1u << u);
+            if (seen[u] == 0ull)
+              fresh |= 1u << u;
+          } else {
+            slot[u] = (slot[u] + 1u) & w.hMask;
+          }
+        }
+    }
+    if (pend) {  // the table is too full
+      w.ctl->overflow = 1;
+      tbl &= ~pend;
+    }
+    const int nNew = __popc(fresh);
+    if (w.exactOk) {
+      const double dLb = now.lb - was.lb, dUb = now.ub - was.ub;
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if ((tbl >> u) & 1u) {
+          const double a = __ldg(&w.cscVal[q0 + u]);
+          const double dMin = a * (a > 0.0 ? dLb : dUb), dMax = a * (a > 0.0 ? dUb : dLb);
+          if (dMin != 0.0)
+            atomicAdd(&w.tab[slot[u]].dMin, dMin);
+          if (dMax != 0.0)
+            atomicAdd(&w.tab[slot[u]].dMax, dMax);
+        }
+    }
+    unsigned listed = 0u;  // table rows not yet listed for that round
+    {
+      int stamp[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        stamp[u] = ((tbl >> u) & 1u) ? atomicMax(&w.tab[slot[u]].stamp, forRound + 1) : 0x7fffffff;
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (stamp[u] < forRound + 1)
+          listed |= 1u << u;
+    }
+    const int nL = __popc(listed);
+    unsigned atS, atL, atU;
+    wl_warp_reserve3(w, nxt, nS, nL, nNew, lane, atS, atL, atU);
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (((fresh >> u) & 1u) && atU != ~0u)
+        w.used[atU++] = slot[u];
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       if (r[u] < 0)
         continue;
       WlItem it;
       it.row = r[u];
-      if (c[u] <= kShortLen && !w.exactOk) {
+      if ((shortRows >> u) & 1u) {
         if (atS != ~0u) {
           it.b = b;
           w.itemsS[nxt][atS++] = it;
         }
-      } else if (slot[u] != ~0u && atL != ~0u) {
+      } else if (((listed >> u) & 1u) && atL != ~0u) {
         it.b = static_cast<int>(slot[u]);
         w.itemsL[nxt][atL++] = it;
       }
@@ -627,6 +700,12 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
     atomicAnd(const_cast<unsigned *>(&p.dmask[word]), ~bit);
     atomicAnd(&p.ever[word], ~bit);
   }
+  // (and the table slots it took are emptied: scattered stores that ride along with the matrix read of the base check)
+  for (unsigned i = gtid; i < w.prevUsed; i += gsize) {
+    uint4 *q = reinterpret_cast<uint4 *>(&w.tab[w.used[i]]);
+    q[0] = make_uint4(0u, 0u, 0u, 0u);
+    q[1] = make_uint4(0u, 0u, 0u, 0u);
+  }
   if (gtid == 0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -679,10 +758,13 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       if (!valid)
         continue;
       if (w.exactOk) {
-        w.rowBaseMin[r] = ra.minAct;
-        w.rowBaseMax[r] = ra.maxAct;
-        w.rowBaseRange[r] = ra.maxRange;
-        w.rowExact[r] = (whole && mag < 1.0e15 && ra.infMin + ra.infMax == 0) ? 1 : 0;
+        WlRowBase rbw;
+        rbw.mn = ra.minAct;
+        rbw.mx = ra.maxAct;
+        rbw.range = ra.maxRange;
+        rbw.exact = (whole && mag < 1.0e15 && ra.infMin + ra.infMax == 0) ? 1 : 0;
+        rbw.pad = 0;
+        w.rowBase[r] = rbw;
       }
       wl_base_verdict(p, r, ra, &ctl->baseBad, [&](const RowPlan &pl) { wl_thread_tighten(p, r, pl, rd, fs); });
     }
@@ -696,10 +778,13 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       const RowAct ra = wl_row_warp_sum_checked(p, r, rd, lane, &mag, &whole);
       whole = whole && mag < 1.0e15 && ra.infMin + ra.infMax == 0;
       if (lane == 0) {
-        w.rowBaseMin[r] = ra.minAct;
-        w.rowBaseMax[r] = ra.maxAct;
-        w.rowBaseRange[r] = ra.maxRange;
-        w.rowExact[r] = whole ? 1 : 0;
+        WlRowBase rbw;
+        rbw.mn = ra.minAct;
+        rbw.mx = ra.maxAct;
+        rbw.range = ra.maxRange;
+        rbw.exact = whole ? 1 : 0;
+        rbw.pad = 0;
+        w.rowBase[r] = rbw;
       }
       wl_base_verdict(p, r, ra, &ctl->baseBad, [&](const RowPlan &pl) { wl_row_warp_tighten(p, r, pl, rd, fs, lane); });
     }
@@ -735,10 +820,13 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         magTot += s_mag[q];
       }
       if (tid == 0) {
-        w.rowBaseMin[r] = tot.minAct;
-        w.rowBaseMax[r] = tot.maxAct;
-        w.rowBaseRange[r] = tot.maxRange;
-        w.rowExact[r] = (magTot < 1.0e15 && tot.infMin + tot.infMax == 0) ? 1 : 0;
+        WlRowBase rbw;
+        rbw.mn = tot.minAct;
+        rbw.mx = tot.maxAct;
+        rbw.range = tot.maxRange;
+        rbw.exact = (magTot < 1.0e15 && tot.infMin + tot.infMax == 0) ? 1 : 0;
+        rbw.pad = 0;
+        w.rowBase[r] = rbw;
       }
       wl_base_verdict(p, r, tot, &ctl->baseBad, [&](const RowPlan &pl) {
         for (int k = kb + tid; k < ke; k += kThreads) {
@@ -932,18 +1020,29 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       if (have)
         it = w.itemsL[cur][i];
       const unsigned slot = static_cast<unsigned>(it.b);
-      const int b = have ? static_cast<int>((__ldcg(&w.hKey[slot]) - 1ull) >> 32) : 0;
+      // (the pair's slot: key | dMin in one 16-byte load, dMax | stamp in the other — one sector)
+      ulonglong2 pk = make_ulonglong2(1ull, 0ull);
+      double2 pm = make_double2(0.0, 0.0);
+      if (have) {
+        pk = __ldcg(reinterpret_cast<const ulonglong2 *>(&w.tab[slot]));
+        pm = __ldcg(reinterpret_cast<const double2 *>(&w.tab[slot].dMax));
+      }
+      const int b = static_cast<int>((pk.x - 1ull) >> 32);
       const int row = it.row;
       const int cnt = have ? __ldg(&p.rowCnt[row]) : 0;
       const WlVecReader rd = { &p, srcX + bt_base32(p, b), p.dmask + bt_word(p, 0, b >> 5), b & 31 };
       RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
       bool needSum = have;
       bool have_plan = have;  // (false once the pair has gone to the long-row queue)
-      if (have && exact && __ldg(&w.rowExact[row])) {
-        ra.minAct = __ldcg(&w.rowBaseMin[row]) + __ldcg(&w.hMin[slot]);
-        ra.maxAct = __ldcg(&w.rowBaseMax[row]) + __ldcg(&w.hMax[slot]);
-        ra.maxRange = __ldcg(&w.rowBaseRange[row]);  // (the node's: an upper bound of the vector's, all R6's shortcut needs)
-        needSum = false;
+      if (have && exact) {
+        const double2 r0 = __ldcg(reinterpret_cast<const double2 *>(&w.rowBase[row]));
+        const double2 r1 = __ldcg(reinterpret_cast<const double2 *>(&w.rowBase[row].range));
+        if (__double2hiint(r1.y) != 0 || __double2loint(r1.y) != 0) {  // (exact | pad as the second word pair: exact != 0)
+          ra.minAct = r0.x + __longlong_as_double(static_cast<long long>(pk.y));
+          ra.maxAct = r0.y + pm.x;
+          ra.maxRange = r1.x;  // (the node's: an upper bound of the vector's, all R6's shortcut needs)
+          needSum = false;
+        }
       }
       if (needSum && cnt <= kShortLen) {
         ra = wl_thread_sum<false>(p, row, rd, nullptr);
@@ -1308,6 +1407,41 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
   if (gtid == 0) {
     ctl->status = status;
     ctl->rounds = round;
+  }
+}
+
+// ---- before and after the run ----------------------------------------------------------------------------------------
+// Everything the run starts from, in one launch: the control block and the per-vector words zeroed, vectors 0..B-1
+// running, the node's bounds packed as (lb, ub) pairs.
+__global__ void wl_setup_kernel(const WlParams w, const double *__restrict__ baseLb, const double *__restrict__ baseUb,
+  Bnd *__restrict__ baseX)
+{
+  const BtParams &p = w.bt;
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < sizeof(WlCtl) / sizeof(unsigned))
+    reinterpret_cast<unsigned *>(w.ctl)[i] = 0u;
+  if (i < static_cast<unsigned>(p.n)) {
+    Bnd x;
+    x.lb = baseLb[i] + 0.0;  // (no -0.0 in the bound arrays)
+    x.ub = baseUb[i] + 0.0;
+    baseX[i] = x;
+  }
+  if (i < static_cast<unsigned>(p.Bp)) {  // (Bp is a multiple of 32: whole warps)
+    p.vecInfRow[i] = 0x7fffffff;
+    p.vecInfCol[i] = 0x7fffffff;
+    p.vecChanged[i] = 0;
+    p.vecRounds[i] = 0;
+    p.vecTotal[i] = 0;
+    p.vecStop[i] = 0;
+    p.vecFinal[i] = 0;
+    w.vecChanged2[0][i] = 0;
+    w.vecChanged2[1][i] = 0;
+    const unsigned m = __ballot_sync(0xffffffffu, static_cast<int>(i) < w.B);
+    if ((threadIdx.x & 31) == 0) {
+      p.active[i >> 5] = m;
+      w.active2[0][i >> 5] = m;
+      w.active2[1][i >> 5] = 0u;
+    }
   }
 }
 

@@ -188,3 +188,43 @@ def test_worklist_long_integer_rows_exact_sums(oracle, gpu_ctx):
     b2[k] = b2[k] + 0.5  # a fractional upper bound on an integer column: R11 rounds it back down
     res2, st2 = _check(oracle, gpu_ctx, inst, s, v, b2, "long integer rows, fractional diff")
     assert st2["lastPairsWalked"] > 2 * exact_pairs
+
+
+def _table_reuse(oracle, ctx):
+    """exact-sum batches of different sizes one after the other on one matrix: each run starts from the table the run
+    before it left (its slots emptied, the part in use resized)"""
+    inst = _node(oracle, I.knapsack_assignment(m=60, n=4000, seed=71, root_fixpoint=True, slack_max=0))
+    mat = capi.Matrix(ctx, inst)
+    prob = oracle.Problem(inst)
+    for seed, B, depth in ((1, 120, 40), (2, 8, 6), (3, 120, 40), (1, 120, 40), (4, 33, 60)):
+        s, v, b = I.dive_deltas(inst, inst.lb, inst.ub, B, max_depth=depth, seed=seed, follow_xstar=0.6)
+        res = mat.propagate_batch_delta(inst.lb, inst.ub, s, v, b)[0]
+        assert ctx.stats()["lastMode"] == 2
+        ores, Lo, Uo = oracle.propagate_batch_delta(prob, inst.lb, inst.ub, s, v, b, threads=8)
+        for k in KEYS:
+            assert np.array_equal(res[k], ores[k]), (seed, k)
+        Lg, Ug = mat.batch_fetch_dense()
+        f = res["feasible"].astype(bool)
+        assert np.array_equal(Lg[f], Lo[f]) and np.array_equal(Ug[f], Uo[f]), seed
+    mat.close()
+
+
+def test_worklist_pair_table_is_reused_across_runs(oracle, gpu_ctx):
+    _table_reuse(oracle, gpu_ctx)
+
+
+def test_worklist_pair_table_nearly_full():
+    """CBP_WL_TABLE_FACTOR=1: the part of the table in use is barely larger than what the last run took — long probe
+    chains, and a hand-over when a run needs more; the answers stay the oracle's"""
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import test_gpu_worklist as T\n"
+        "from cbc_b200 import capi; from oracle import oracle_py as O\n"
+        "ctx = capi.Context()\n"
+        "stats = ctx.stats  # (lastMode may be 1 when a run outgrows the part of the table in use)\n"
+        "ctx.stats = lambda: dict(stats(), lastMode=2)\n"
+        "T._table_reuse(O, ctx)\n"
+        "print('OK')\n") % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, CBP_WL_TABLE_FACTOR="1"),
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
