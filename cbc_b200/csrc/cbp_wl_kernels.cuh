@@ -525,29 +525,79 @@ __device__ __forceinline__ void wl_warp_reserve3(const WlParams &w, int nxt, int
   }
 }
 
+// One cell of a warp's 32 in wl_emit_rows (shared memory): where the column's rows start, how many rows the cells of
+// the lanes below have, whose cell it is, what the change adds to a bound.
+struct __align__(32) WlEmitCell {
+  int cs, excl, b, pad;
+  double dLb, dUb;
+};
+
 // Cell (b, j) went from bounds `was` to bounds `now` (lanes with active == false have no cell): the rows of column j
 // become items of vector b in the lists of parity `nxt` (round `forRound`).  Called by all 32 lanes of a warp
-// together, each with its own cell.  Rows of at most kShortLen nonzeros go to the short list as (b, row) — unless
-// sums are exact (w.exactOk), when every row goes the way of the longer rows: the pair's table slot takes what the
-// change adds to the row's two sums, and the pair is listed (by slot) unless it already is for that round.
+// together, each with its own cell; `se` = 32 records of shared memory that belong to the warp.  Rows of at most
+// kShortLen nonzeros go to the short list as (b, row) — unless sums are exact (w.exactOk), when every row goes the way
+// of the longer rows: the pair's table slot takes what the change adds to the row's two sums, and the pair is listed
+// (by slot) unless it already is for that round.
+// The 32 columns' rows are laid end to end and dealt out to the lanes eight at a time: the number of trips (each a
+// chain of round trips to L2 — probe, add, stamp, reserve) follows the columns' average length, not the longest one.
 __device__ __forceinline__ void wl_emit_rows(const WlParams &w, bool active, int b, int j, int nxt, int forRound,
-  const Bnd &was, const Bnd &now, int lane)
+  const Bnd &was, const Bnd &now, int lane, WlEmitCell *se)
 {
   const int cs = active ? __ldg(&w.cscStart[j]) : 0, ce = active ? __ldg(&w.cscStart[j + 1]) : 0;
-  const int trips = __reduce_max_sync(0xffffffffu, (ce - cs + 7) >> 3);
-  for (int t = 0; t < trips; ++t) {
-    const int q0 = cs + 8 * t;
-    int r[8];
+  int incl = ce - cs;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d)
+      incl += t;
+  }
+  const int total = __shfl_sync(0xffffffffu, incl, 31);
+  if (total == 0)
+    return;
+  __syncwarp();
+  {
+    WlEmitCell e;
+    e.cs = cs;
+    e.excl = incl - (ce - cs);
+    e.b = b;
+    e.pad = 0;
+    e.dLb = now.lb - was.lb;
+    e.dUb = now.ub - was.ub;
+    se[lane] = e;
+  }
+  __syncwarp();
+  for (int base = 0; base < total; base += 256) {
+    int r[8], q[8];
+    unsigned char own[8];
     unsigned slot[8];
+    unsigned have = 0u;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int idx = base + 32 * u + lane;
+      r[u] = -1;
+      q[u] = 0;
+      own[u] = 0;
+      if (idx < total) {
+        int o = 0;  // the cell: the last one with excl <= idx
+#pragma unroll
+        for (int st = 16; st >= 1; st >>= 1)
+          if (se[o + st].excl <= idx)
+            o += st;
+        own[u] = static_cast<unsigned char>(o);
+        q[u] = se[o].cs + (idx - se[o].excl);
+        have |= 1u << u;
+      }
+    }
 #pragma unroll
     for (int u = 0; u < 8; ++u)
-      r[u] = q0 + u < ce ? __ldg(&w.cscRow[q0 + u]) : -1;
+      if ((have >> u) & 1u)
+        r[u] = __ldg(&w.cscRow[q[u]]);
     unsigned shortRows = 0u;  // rows for the short list (with exact sums every row goes through the table)
     if (!w.exactOk) {
       int c[8];
 #pragma unroll
       for (int u = 0; u < 8; ++u)
-        c[u] = r[u] >= 0 ? __ldg(&w.bt.rowCnt[r[u]]) : 0x7fffffff;
+        c[u] = ((have >> u) & 1u) ? __ldg(&w.bt.rowCnt[r[u]]) : 0x7fffffff;
 #pragma unroll
       for (int u = 0; u < 8; ++u)
         if (c[u] <= kShortLen)
@@ -556,16 +606,15 @@ __device__ __forceinline__ void wl_emit_rows(const WlParams &w, bool active, int
     const int nS = __popc(shortRows);
     // The pairs' table slots (linear probing): every probe step is one compare-and-swap per row, and the eight rows'
     // steps go out together before any answer is waited for — one after the other they would be a chain of round trips.
-    const unsigned long long keyHi = static_cast<unsigned long long>(static_cast<unsigned>(b)) << 32;
-    unsigned pend = 0u, fresh = 0u;
+    unsigned pend = have & ~shortRows, fresh = 0u;
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       slot[u] = ~0u;
-      if (r[u] < 0 || ((shortRows >> u) & 1u))
-        continue;
-      const unsigned long long key = (keyHi | static_cast<unsigned>(r[u])) + 1ull;
-      slot[u] = static_cast<unsigned>((key * 0x9E3779B97F4A7C15ull) >> w.hShift);
-      pend |= 1u << u;
+      if ((pend >> u) & 1u) {
+        const unsigned long long key
+          = ((static_cast<unsigned long long>(static_cast<unsigned>(se[own[u]].b)) << 32) | static_cast<unsigned>(r[u])) + 1ull;
+        slot[u] = static_cast<unsigned>((key * 0x9E3779B97F4A7C15ull) >> w.hShift);
+      }
     }
     unsigned tbl = pend;  // rows that go through the table
     for (int probe = 0; probe < 128 && pend; ++probe) {
@@ -573,11 +622,14 @@ __device__ __forceinline__ void wl_emit_rows(const WlParams &w, bool active, int
 #pragma unroll
       for (int u = 0; u < 8; ++u)
         if ((pend >> u) & 1u)
-          seen[u] = atomicCAS(&w.tab[slot[u]].key, 0ull, (keyHi | static_cast<unsigned>(r[u])) + 1ull);
+          seen[u] = atomicCAS(&w.tab[slot[u]].key, 0ull,
+            ((static_cast<unsigned long long>(static_cast<unsigned>(se[own[u]].b)) << 32) | static_cast<unsigned>(r[u])) + 1ull);
 #pragma unroll
       for (int u = 0; u < 8; ++u)
         if ((pend >> u) & 1u) {
-          if (seen[u] == 0ull || seen[u] == (keyHi | static_cast<unsigned>(r[u])) + 1ull) {
+          const unsigned long long key
+            = ((static_cast<unsigned long long>(static_cast<unsigned>(se[own[u]].b)) << 32) | static_cast<unsigned>(r[u])) + 1ull;
+          if (seen[u] == 0ull || seen[u] == key) {
             pend &= ~(1u << u);
             if (seen[u] == 0ull)
               fresh |= 1u << u;
@@ -592,11 +644,11 @@ __device__ __forceinline__ void wl_emit_rows(const WlParams &w, bool active, int
     }
     const int nNew = __popc(fresh);
     if (w.exactOk) {
-      const double dLb = now.lb - was.lb, dUb = now.ub - was.ub;
 #pragma unroll
       for (int u = 0; u < 8; ++u)
         if ((tbl >> u) & 1u) {
-          const double a = __ldg(&w.cscVal[q0 + u]);
+          const double a = __ldg(&w.cscVal[q[u]]);
+          const double dLb = se[own[u]].dLb, dUb = se[own[u]].dUb;
           const double dMin = a * (a > 0.0 ? dLb : dUb), dMax = a * (a > 0.0 ? dUb : dLb);
           if (dMin != 0.0)
             atomicAdd(&w.tab[slot[u]].dMin, dMin);
@@ -624,13 +676,11 @@ __device__ __forceinline__ void wl_emit_rows(const WlParams &w, bool active, int
         w.used[atU++] = slot[u];
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
-      if (r[u] < 0)
-        continue;
       WlItem it;
       it.row = r[u];
       if ((shortRows >> u) & 1u) {
         if (atS != ~0u) {
-          it.b = b;
+          it.b = se[own[u]].b;
           w.itemsS[nxt][atS++] = it;
         }
       } else if (((listed >> u) & 1u) && atL != ~0u) {
@@ -678,9 +728,9 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
 {
   __shared__ __align__(16) BtLogEntry s_stage[kWlStage];
   __shared__ unsigned s_staged, s_base;
-  __shared__ unsigned s_dv[kWarps][64];
   __shared__ RowAct s_row[kWarps];
   __shared__ double s_mag[kWarps];
+  __shared__ WlEmitCell s_emit[kWarps][32];
   cg::grid_group grid = cg::this_grid();
   const BtParams &p = w.bt;
   WlCtl *ctl = w.ctl;
@@ -846,124 +896,112 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
     return;
   }
 
-  // ---- phase 0b: the diffs.  One warp per vector, one lane per diff.  Applying the diffs in order means: a bound
-  // ends at the LAST diff that names it; so a lane writes its value unless a later diff names the same bound.  The
-  // first diff of a column creates the cell (mask bit, both buffers = the node's bounds), gives it R11 once all
-  // diffs are in, and lists the column's rows as items of the first round.
-  for (unsigned b = gwarp; b < static_cast<unsigned>(w.B); b += nwarps) {
-    const long long k0 = w.dStart[b], k1 = w.dStart[b + 1];
-    // (the lanes look through the vector's other diffs several times: up to 64 of them are kept in shared memory)
-    unsigned *dv = s_dv[tid >> 5];
-    const bool stagedDiffs = k1 - k0 <= 64;
-    __syncwarp();
-    if (stagedDiffs)
-      for (int q = lane; q < static_cast<int>(k1 - k0); q += 32)
-        dv[q] = w.dVar[k0 + q];
-    __syncwarp();
-    auto var_at = [&](long long q) -> unsigned { return stagedDiffs ? dv[q - k0] : w.dVar[q]; };
+  // ---- phase 0b: the diffs, one lane per diff over all vectors' diffs laid end to end (a vector with one diff — a
+  // strong-branching arm — costs a lane, not a warp).  Applying a vector's diffs in order means: a bound ends at the
+  // LAST diff that names it.  The lane of the FIRST diff of a column owns the cell: it folds the vector's later diffs
+  // of that column into the node's bounds, gives the result R11, creates the cell (mask bit, both buffers) and lists
+  // it; the column's rows become items of the first round once it is known which vectors already cross (below).
+  {
+    const long long nDiff = w.dStart[w.B];
     unsigned *dmaskW = const_cast<unsigned *>(p.dmask);
-    const unsigned bit = 1u << (b & 31);
-    for (long long c0 = k0; c0 < k1; c0 += 32) {
-      const long long k = c0 + lane;
-      const bool have = k < k1;
-      const unsigned v = have ? var_at(k) : 0u;
+    for (long long kk = static_cast<long long>(gwarp) << 5; kk < nDiff; kk += static_cast<long long>(nwarps) << 5) {
+      const long long k = kk + lane;
+      if (k >= nDiff)
+        continue;
+      int lo = 0, hi = w.B;  // the vector: the last b with dStart[b] <= k
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(&w.dStart[mid]) <= k)
+          lo = mid;
+        else
+          hi = mid;
+      }
+      const int b = lo;
+      const long long k0 = __ldg(&w.dStart[b]), k1 = __ldg(&w.dStart[b + 1]);
+      const unsigned v = __ldg(&w.dVar[k]);
       const int j = diff_col(v);
-      const bool valid = have && j < p.n;
-      bool first = valid, last = valid;
-      if (valid) {
-        for (long long q = k0; q < k && first; ++q)
-          first = diff_col(var_at(q)) != j;
-        for (long long q = k + 1; q < k1 && last; ++q)
-          last = !(diff_col(var_at(q)) == j && ((var_at(q) ^ v) & kDiffUpper) == 0u);
-      }
-      const size_t at = valid ? bt_cell(p, j, b) : 0;
-      if (first) {
-        const Bnd nb = p.baseX[j];
-        p.X[0][at] = nb;
-        p.X[1][at] = nb;
-        atomicOr(&dmaskW[bt_word(p, j, b >> 5)], bit);
-        const unsigned ci = wl_append(&ctl->nCells, w.cellCap, &ctl->overflow);
-        if (ci != ~0u) {
-          WlCell c;
-          c.b = b;
-          c.j = j;
-          w.cells[ci] = c;
-        }
-      }
-      __syncwarp();
-      if (valid) {
-        const double nv = w.dBnd[k] + 0.0;
-        const Bnd nb = p.baseX[j];  // exact sums need every bound of the vector to be an integer inside the node's bounds
-        if (!(nv == floor(nv) && nv >= nb.lb && nv <= nb.ub))
-          ctl->inexact = 1;
-        if (last) {
-          if (v & kDiffUpper) {
-            p.X[0][at].ub = nv;
-            p.X[1][at].ub = nv;
-          } else {
-            p.X[0][at].lb = nv;
-            p.X[1][at].lb = nv;
-          }
-        }
-      }
-      __syncwarp();
-    }
-    // R11 on the cells (one lane per cell: the lane of the column's first diff)
-    bool dead = false;
-    for (long long c0 = k0; c0 < k1; c0 += 32) {
-      const long long k = c0 + lane;
-      const int j = k < k1 ? diff_col(var_at(k)) : p.n;
-      bool first = j < p.n;
+      if (j >= p.n)
+        continue;
+      bool first = true;
       for (long long q = k0; q < k && first; ++q)
-        first = diff_col(var_at(q)) != j;
-      if (first) {
-        const size_t at = bt_cell(p, j, b);
-        Bnd x = p.X[0][at];
-        const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);
-        if (r == 2) {
-          atomicMin(&p.vecInfCol[b], j);
-          dead = true;
-        } else if (r == 1) {
-          p.X[0][at] = x;
-          p.X[1][at] = x;
-          const unsigned old = atomicOr(&p.dirty[0][bt_word(p, j, b >> 5)], bit);
-          if (!(old & bit)) {
-            const unsigned ki = wl_append(&ctl->nK, w.kCap, &ctl->overflow);
-            if (ki != ~0u) {
-              WlCell c;
-              c.b = b;
-              c.j = j;
-              w.K[ki] = c;
-            }
+        first = diff_col(__ldg(&w.dVar[q])) != j;
+      if (!first)
+        continue;
+      const Bnd nb = p.baseX[j];
+      Bnd x0 = nb;
+      bool inexact = false;
+      for (long long q = k; q < k1; ++q) {
+        const unsigned vq = q == k ? v : __ldg(&w.dVar[q]);
+        if (diff_col(vq) != j)
+          continue;
+        const double nv = __ldg(&w.dBnd[q]) + 0.0;
+        // exact sums need every bound of the vector to be an integer inside the node's bounds
+        inexact = inexact || !(nv == floor(nv) && nv >= nb.lb && nv <= nb.ub);
+        if (vq & kDiffUpper)
+          x0.ub = nv;
+        else
+          x0.lb = nv;
+      }
+      if (inexact)
+        ctl->inexact = 1;
+      Bnd x = x0;
+      const int r = prepass_col(x.lb, x.ub, p.colType[j] != 0, p.s);  // R11 on the cell
+      const size_t at = bt_cell(p, j, b);
+      const unsigned bit = 1u << (b & 31);
+      if (r != 1)
+        x = x0;
+      p.X[0][at] = x;
+      p.X[1][at] = x;
+      atomicOr(&dmaskW[bt_word(p, j, b >> 5)], bit);
+      const unsigned ci = wl_append(&ctl->nCells, w.cellCap, &ctl->overflow);
+      if (ci != ~0u) {
+        WlCell c;
+        c.b = b;
+        c.j = j;
+        w.cells[ci] = c;
+      }
+      if (r == 2) {
+        atomicMin(&p.vecInfCol[b], j);  // the input already crosses: the vector stops before its first round
+      } else if (r == 1) {
+        const unsigned old = atomicOr(&p.dirty[0][bt_word(p, j, b >> 5)], bit);
+        if (!(old & bit)) {
+          const unsigned ki = wl_append(&ctl->nK, w.kCap, &ctl->overflow);
+          if (ki != ~0u) {
+            WlCell c;
+            c.b = b;
+            c.j = j;
+            w.K[ki] = c;
           }
         }
       }
     }
-    dead = __any_sync(0xffffffffu, dead);
-    if (dead) {  // the input already crosses (R11): stops before its first round
-      if (lane == 0) {
+    grid.sync();
+    for (unsigned b = gtid; b < static_cast<unsigned>(w.B); b += gsize)
+      if (__ldcg(&p.vecInfCol[b]) != 0x7fffffff) {
         p.vecStop[b] = 4;
         p.vecRounds[b] = 1;
         p.vecFinal[b] = 0;
-        atomicAnd(&w.active2[0][b >> 5], ~bit);
+        atomicAnd(&w.active2[0][b >> 5], ~(1u << (b & 31)));
         atomicAdd(&ctl->roundsTotal, 1ull);
       }
-      continue;
-    }
-    __syncwarp();
-    for (long long c0 = k0; c0 < k1; c0 += 32) {
-      const long long k = c0 + lane;
-      const int j = k < k1 ? diff_col(var_at(k)) : p.n;
-      bool first = j < p.n;
-      for (long long q = k0; q < k && first; ++q)
-        first = diff_col(var_at(q)) != j;
+    const unsigned nNew = min(*reinterpret_cast<volatile unsigned *>(&ctl->nCells), w.cellCap);
+    for (unsigned i0 = gwarp << 5; i0 < nNew; i0 += nwarps << 5) {  // (whole warps: the listing is a warp's job)
+      const unsigned i = i0 + lane;
+      bool go = false;
+      WlCell c;
+      c.b = 0;
+      c.j = 0;
       Bnd was, now;
       was.lb = was.ub = now.lb = now.ub = 0.0;
-      if (first) {
-        was = p.baseX[j];
-        now = p.X[0][bt_cell(p, j, b)];
+      if (i < nNew) {
+        c = w.cells[i];
+        if (__ldcg(&p.vecInfCol[c.b]) == 0x7fffffff) {
+          go = true;
+          was = p.baseX[c.j];
+          now = ldcg_bnd(&p.X[0][bt_cell(p, c.j, c.b)]);
+        }
       }
-      wl_emit_rows(w, first, b, first ? j : 0, 0, 0, was, now, lane);
+      wl_emit_rows(w, go, c.b, c.j, 0, 0, was, now, lane, s_emit[tid >> 5]);
     }
   }
   grid.sync();
@@ -1386,7 +1424,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
           }
         }
       }
-      wl_emit_rows(w, go, c.b, c.j, nxt, round + 1, was, now, lane);
+      wl_emit_rows(w, go, c.b, c.j, nxt, round + 1, was, now, lane, s_emit[tid >> 5]);
     }
     grid.sync();
     wl_stamp(ctl, gtid);
