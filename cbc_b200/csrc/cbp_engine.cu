@@ -89,6 +89,15 @@ struct BatchState {
   unsigned wlHSlots = 0;
   unsigned *wlUsed = nullptr;   // table slots the running worklist run takes (emptied again after it)
   unsigned wlUsedCap = 0;
+  // a worklist run leaves the vectors' update lists in stCol/stLb/stUb and copies what a fetch reads first into
+  // pinned host memory before its one synchronisation
+  bool updReady = false;        // the last run wrote the lists itself
+  long long updTotal = 0;
+  // control block | per-vector results | list offsets | head of the lists: one device block (wlCtl, ints and counts
+  // point into it), so that ONE copy brings all a fetch needs to its pinned mirror
+  unsigned char *blob = nullptr, *hBlob = nullptr;
+  size_t blobOffInts = 0, blobOffCounts = 0, blobOffHead = 0, blobBytes = 0;
+  long long headCopied = 0;     // list entries of the last run that are in the mirror
   bool wlTableClean = false;    // every slot of the table is free, except the wlPrevUsed listed in wlUsed
   unsigned wlPrevUsed = 0;
   WlRowBase *wlRowBase = nullptr;  // [mKept] the node's sums of the rows
@@ -182,6 +191,7 @@ static const EnvKnobs &knobs()
   return k;
 }
 
+static constexpr long long kUpdPrefetch = 32768;  // update-list entries a worklist run copies to the host unasked
 static constexpr size_t kSvSmallSmem = 0;
 static constexpr unsigned kBtLogCap = 16u << 20;  // candidate list of a list round: 16M entries (256 MB)  // the short-rows-only variant needs no dynamic shared memory
 
@@ -313,14 +323,16 @@ void cbp_matrix_free(cbp_matrix *mat)
     mat->longPart, mat->X[0],
     mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
     mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
-    mat->bt.ints, mat->bt.counts, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
+    mat->bt.blob, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
-    mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlCtl, mat->bt.wlInts, mat->bt.wlHKey,
+    mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlInts, mat->bt.wlHKey,
     mat->bt.wlWalk, mat->bt.wlUsed, mat->bt.wlRowBase, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
     mat->bt.st2Col, mat->bt.st2Lb, mat->bt.st2Ub };
   for (void *p : ptrs)
     if (p)
       cudaFree(p);
+  if (mat->bt.hBlob)
+    cudaFreeHost(mat->bt.hBlob);
   for (int r = 0; r < mat->p2p.world; ++r)
     if (mat->p2p.attached && r != mat->p2p.rank && mat->p2p.peer[r])
       cudaIpcCloseMemHandle(mat->p2p.peer[r]);
@@ -1117,9 +1129,13 @@ static int bt_reserve(cbp_matrix *mat, int B)
   const int Bp = (B + 31) / 32 * 32;
   const size_t cells = static_cast<size_t>(mat->n) * Bp;
   if (cells > bt.capCells || Bp > bt.capBp) {
-    void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.ints, bt.counts, bt.chunkCnt,
+    void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.blob, bt.chunkCnt,
       bt.log, bt.groupFlag, bt.dmask, bt.wlItemsS[0], bt.wlItemsS[1], bt.wlItemsL[0], bt.wlItemsL[1], bt.wlK, bt.wlCells,
-      bt.wlCtl, bt.wlInts, bt.wlHKey, bt.wlWalk, bt.wlUsed };
+      bt.wlInts, bt.wlHKey, bt.wlWalk, bt.wlUsed };
+    bt.blob = nullptr;
+    if (bt.hBlob)
+      cudaFreeHost(bt.hBlob);
+    bt.hBlob = nullptr;
     bt.wlWalk = nullptr;
     bt.wlUsed = nullptr;
     bt.wlTableClean = false;
@@ -1187,7 +1203,7 @@ static int bt_reserve(cbp_matrix *mat, int B)
     if (dalloc(&bt.wlItemsS[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsS[1], bt.wlItemCap) != cudaSuccess
       || dalloc(&bt.wlItemsL[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsL[1], bt.wlItemCap) != cudaSuccess
       || dalloc(&bt.wlK, bt.wlCellCap) != cudaSuccess || dalloc(&bt.wlCells, bt.wlCellCap) != cudaSuccess
-      || dalloc(&bt.wlCtl, 1) != cudaSuccess || dalloc(&bt.wlInts, static_cast<size_t>(Bp) * 2 + static_cast<size_t>(Bp / 32) * 2 + 8) != cudaSuccess) {
+      || dalloc(&bt.wlInts, static_cast<size_t>(Bp) * 4 + static_cast<size_t>(Bp / 32) * 2 + 8) != cudaSuccess) {
       ctx->err = std::string("batch workspace (worklists): ") + cudaGetErrorString(cudaGetLastError());
       return CBP_ERR_NOMEM;
     }
@@ -1195,13 +1211,26 @@ static int bt_reserve(cbp_matrix *mat, int B)
       || dalloc(&bt.dirty[0], words) != cudaSuccess || dalloc(&bt.dirty[1], words) != cudaSuccess
       || dalloc(&bt.ever, words) != cudaSuccess || dalloc(&bt.active, Bp / 32) != cudaSuccess
       || dalloc(&bt.dmask, words) != cudaSuccess
-      || dalloc(&bt.ints, static_cast<size_t>(Bp) * 7 + 8) != cudaSuccess
-      || dalloc(&bt.counts, static_cast<size_t>(Bp) + 1) != cudaSuccess
       || dalloc(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp) != cudaSuccess
       || dalloc(&bt.groupFlag, static_cast<size_t>(Bp / 32) + 2) != cudaSuccess
       || dalloc(&bt.log, logCap) != cudaSuccess) {
       ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
       return CBP_ERR_NOMEM;
+    }
+    {
+      auto up256 = [](size_t x) { return (x + 255) & ~static_cast<size_t>(255); };
+      bt.blobOffInts = up256(sizeof(WlCtl));
+      bt.blobOffCounts = bt.blobOffInts + up256(sizeof(int) * (static_cast<size_t>(Bp) * 7 + 8));
+      bt.blobOffHead = bt.blobOffCounts + up256(sizeof(long long) * (static_cast<size_t>(Bp) + 1));
+      bt.blobBytes = bt.blobOffHead + sizeof(WlUpdHead) * static_cast<size_t>(kUpdPrefetch);
+      if (dalloc(&bt.blob, bt.blobBytes) != cudaSuccess
+        || cudaHostAlloc(reinterpret_cast<void **>(&bt.hBlob), bt.blobBytes, cudaHostAllocDefault) != cudaSuccess) {
+        ctx->err = std::string("batch workspace (result block): ") + cudaGetErrorString(cudaGetLastError());
+        return CBP_ERR_NOMEM;
+      }
+      bt.wlCtl = reinterpret_cast<WlCtl *>(bt.blob);
+      bt.ints = reinterpret_cast<int *>(bt.blob + bt.blobOffInts);
+      bt.counts = reinterpret_cast<long long *>(bt.blob + bt.blobOffCounts);
     }
     bt.capCells = cells;
     bt.capBp = Bp;
@@ -1430,6 +1459,36 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.cellCap = bt.wlCellCap;
   w.prevCells = bt.wlPrevCells;
   w.ctl = bt.wlCtl;
+  // the update lists (P7): unsorted into st2*, sorted into st*; buffers sized by an earlier fetch (none yet: the
+  // first fetch takes the stand-alone path and sizes them)
+  if (bt.stCap == 0 || bt.st2Cap == 0) {  // (a fetch grows them when a run needs more)
+    void *oldp[] = { bt.stCol, bt.stLb, bt.stUb, bt.st2Col, bt.st2Lb, bt.st2Ub };
+    for (void *q : oldp)
+      if (q)
+        cudaFree(q);
+    bt.stCol = bt.st2Col = nullptr;
+    bt.stLb = bt.stUb = bt.st2Lb = bt.st2Ub = nullptr;
+    bt.stCap = bt.st2Cap = 0;
+    const long long want = 1 << 16;
+    if (dalloc(&bt.stCol, want) != cudaSuccess || dalloc(&bt.stLb, want) != cudaSuccess || dalloc(&bt.stUb, want) != cudaSuccess
+      || dalloc(&bt.st2Col, want) != cudaSuccess || dalloc(&bt.st2Lb, want) != cudaSuccess || dalloc(&bt.st2Ub, want) != cudaSuccess) {
+      ctx->err = "batch workspace (update lists)";
+      return CBP_ERR_NOMEM;
+    }
+    bt.stCap = bt.st2Cap = want;
+  }
+  bt.updReady = false;
+  w.updStart = bt.counts;
+  w.updCnt = bt.wlInts + 2 * static_cast<size_t>(bt.Bp) + 2 * static_cast<size_t>(bt.G) + 8;  // (its own 2 Bp ints)
+  w.updColTmp = bt.st2Col;
+  w.updLbTmp = bt.st2Lb;
+  w.updUbTmp = bt.st2Ub;
+  w.updCol = bt.stCol;
+  w.updLb = bt.stLb;
+  w.updUb = bt.stUb;
+  w.updCap = std::min(bt.stCap, bt.st2Cap);
+  w.updHead = reinterpret_cast<WlUpdHead *>(bt.blob + bt.blobOffHead);
+  w.updHeadCap = kUpdPrefetch;
   w.limit = limit;
   w.budgetNs = timeLimitSec >= 1.0e9 ? ~0ull : static_cast<unsigned long long>(timeLimitSec * 1.0e9);
   wl_setup_kernel<<<cdiv(std::max<size_t>(std::max(mat->n, bt.Bp), sizeof(WlCtl) / sizeof(unsigned)), 256), 256, 0, st>>>(w,
@@ -1441,10 +1500,14 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   CK(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(bt_worklist_kernel), dim3(grid), dim3(kThreads), args, 0, st));
   CK(cudaEventRecord(ctx->evPool[1], st));
   ++ctx->stats.kernelLaunches;
-  WlCtl h;
-  CK(cudaMemcpyAsync(&h, bt.wlCtl, sizeof(h), cudaMemcpyDeviceToHost, st));
   CK(cudaEventRecord(ctx->evB, st));
+  // the control block, and with it what a fetch reads first: the per-vector results, the lists' offsets and as much of
+  // the lists' head as the last run would have needed (and a quarter more)
+  const long long pre = w.updCap > 0 ? std::min<long long>(kUpdPrefetch, std::max<long long>(256, bt.updTotal + bt.updTotal / 4 + 64)) : 0;
+  CK(cudaMemcpyAsync(bt.hBlob, bt.blob, bt.blobOffHead + sizeof(WlUpdHead) * static_cast<size_t>(pre), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));  // the one host synchronisation of the run
+  const WlCtl &h = *reinterpret_cast<const WlCtl *>(bt.hBlob);
+  bt.headCopied = pre;
   *status = h.status;
   bt.wlTableClean = !h.usedOverflow;
   bt.wlPrevUsed = std::min(h.nUsed, bt.wlUsedCap);
@@ -1476,6 +1539,8 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   bt.wlMarksKnown = true;
   bt.wlPrevCells = std::min(h.nCells, bt.wlCellCap);
   bt.lastWasWorklist = true;
+  bt.updReady = h.updDone != 0;
+  bt.updTotal = static_cast<long long>(h.nUpd);
   bt.baseMode = true;
   bt.quiet = false;
   bt.groupBuilt.assign(bt.G, 0);
@@ -1838,9 +1903,14 @@ static int bt_fetch_results(cbp_matrix *mat, cbp_result *out, bool devOut)
 {
   cbp_ctx *ctx = mat->ctx;
   BatchState &bt = mat->bt;
-  std::vector<int> h(static_cast<size_t>(bt.Bp) * 7);
-  CK(cudaMemcpyAsync(h.data(), bt.ints, sizeof(int) * h.size(), cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
+  std::vector<int> hv;
+  const int *h = reinterpret_cast<const int *>(bt.hBlob + bt.blobOffInts);  // (a worklist run has brought them over already)
+  if (!bt.lastWasWorklist) {
+    hv.resize(static_cast<size_t>(bt.Bp) * 7);
+    CK(cudaMemcpyAsync(hv.data(), bt.ints, sizeof(int) * hv.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    h = hv.data();
+  }
   std::vector<cbp_result> tmp;
   cbp_result *dstp = out;
   if (devOut) {
@@ -1896,6 +1966,39 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
     return CBP_OK;
   }
   const BtParams p = bt_params(mat, 0.0);
+  if (bt.lastWasWorklist && bt.updReady) {  // the run wrote the lists itself: copies only
+    const long long run = bt.updTotal;
+    if (dev)
+      CK(cudaMemcpyAsync(updStart, bt.counts, sizeof(long long) * (bt.B + 1), cudaMemcpyDeviceToDevice, ctx->stream));
+    else
+      memcpy(updStart, bt.hBlob + bt.blobOffCounts, sizeof(long long) * (bt.B + 1));
+    if (run > updCap || (run > 0 && (!updCol || !updLb || !updUb))) {
+      ctx->err = "cbp_batch_fetch: update buffers too small";
+      return CBP_ERR_CAPACITY;
+    }
+    if (dev) {
+      if (run > 0) {
+        CK(cudaMemcpyAsync(updCol, bt.stCol, sizeof(int) * run, cudaMemcpyDeviceToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(updLb, bt.stLb, sizeof(double) * run, cudaMemcpyDeviceToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(updUb, bt.stUb, sizeof(double) * run, cudaMemcpyDeviceToDevice, ctx->stream));
+      }
+      CK(cudaStreamSynchronize(ctx->stream));
+    } else if (run == 0) {
+    } else if (run <= bt.headCopied) {
+      const WlUpdHead *hd = reinterpret_cast<const WlUpdHead *>(bt.hBlob + bt.blobOffHead);
+      for (long long i = 0; i < run; ++i) {
+        updCol[i] = hd[i].col;
+        updLb[i] = hd[i].lb;
+        updUb[i] = hd[i].ub;
+      }
+    } else {
+      CK(cudaMemcpyAsync(updCol, bt.stCol, sizeof(int) * run, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaMemcpyAsync(updLb, bt.stLb, sizeof(double) * run, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaMemcpyAsync(updUb, bt.stUb, sizeof(double) * run, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+    }
+    return CBP_OK;
+  }
   if (bt.lastWasWorklist) {
     // the run listed every cell it created: the update lists come from that list (count, fill, order per vector)
     // instead of two scans over the n x B / 32 words of marks
@@ -1961,7 +2064,7 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
     CK(cudaMemcpyAsync(bt.counts, off.data(), sizeof(long long) * (bt.B + 1), cudaMemcpyHostToDevice, ctx->stream));
     wl_upd_fill_kernel<<<cdiv(nCells, 256), 256, 0, ctx->stream>>>(bt.wlCells, nCells, p, bt.counts, cnt32 + bt.Bp, bt.st2Col,
       bt.st2Lb, bt.st2Ub);
-    wl_upd_sort_kernel<<<cdiv(static_cast<long long>(bt.B) * 32, 256), 256, 0, ctx->stream>>>(bt.counts, bt.B, bt.st2Col, bt.st2Lb,
+    wl_upd_sort_kernel<<<bt.B, kThreads, 0, ctx->stream>>>(bt.counts, bt.B, bt.st2Col, bt.st2Lb,
       bt.st2Ub, oCol, oLb, oUb);
     ctx->stats.kernelLaunches += 2;
     CK(cudaGetLastError());

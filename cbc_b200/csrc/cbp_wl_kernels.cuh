@@ -66,6 +66,12 @@ struct __align__(32) WlRowBase {
   int pad;
 };
 
+// One entry of the head of the update lists, as it travels to the host with the control block.
+struct WlUpdHead {
+  int col, pad;
+  double lb, ub;
+};
+
 // control block (device); zeroed by wl_setup_kernel before every launch
 struct WlCtl {
   unsigned nS[2], nL[2];  // items of the running / next round: rows <= kShortLen nonzeros, longer rows
@@ -77,6 +83,8 @@ struct WlCtl {
   int overflowP1;  // the candidate list did (written in P1 only): two words, so that each is read while nobody writes it
   int anyActive[2];
   int status, rounds;
+  int updDone;       // the update lists of the vectors were written by the kernel itself (nUpd entries)
+  unsigned long long nUpd;
   unsigned nUsed;    // table slots taken by this run (listed in WlParams::used; the next run empties them first)
   int usedOverflow;  // more than the list holds: the host clears the whole table before the next run
   unsigned long long pairs;   // (nonzero, vector) pairs walked
@@ -125,6 +133,15 @@ struct WlParams {
   unsigned *active2[2];  // [G] running vectors, by round parity
   int limit;             // round limit (INT_MAX: none)
   unsigned long long budgetNs;
+  // updatedBounds() of every vector, written at the end of the run when the buffers are large enough: per vector
+  // the changed columns in ascending order with their final bounds (updTmp*: the same entries in arrival order)
+  long long *updStart;  // [B + 1]
+  int *updCnt;          // [2 Bp] counts, cursors
+  int *updColTmp, *updCol;
+  double *updLbTmp, *updUbTmp, *updLb, *updUb;
+  long long updCap;
+  WlUpdHead *updHead;  // the first updHeadCap entries of the ordered lists once more, next to the control block
+  long long updHeadCap;
 };
 
 namespace cg = cooperative_groups;
@@ -724,9 +741,135 @@ __device__ __forceinline__ void wl_base_verdict(const BtParams &p, int row, cons
     walk(pl);
 }
 
+// ---- updatedBounds() of a worklist run, from the list of cells instead of a scan of the `ever` marks ----------------
+// count per vector
+__device__ __forceinline__ void wl_upd_count(const WlCell c, const BtParams &p, int *cnt)
+{
+  if (__ldcg(&p.vecStop[c.b]) == 4)
+    return;  // a vector proved infeasible lists nothing
+  if ((__ldcg(&p.ever[bt_word(p, c.j, c.b >> 5)]) >> (c.b & 31)) & 1u)
+    atomicAdd(&cnt[c.b], 1);
+}
+
+// (col, lb, ub) of a changed cell into its vector's segment, in the order the threads get there
+__device__ __forceinline__ void wl_upd_fill(const WlCell c, const BtParams &p, const long long *start, int *cursor, int *col,
+  double *lb, double *ub)
+{
+  if (__ldcg(&p.vecStop[c.b]) == 4 || !((__ldcg(&p.ever[bt_word(p, c.j, c.b >> 5)]) >> (c.b & 31)) & 1u))
+    return;
+  const long long at = __ldcg(&start[c.b]) + atomicAdd(&cursor[c.b], 1);
+  const Bnd x = ldcg_bnd(&p.X[__ldcg(&p.vecFinal[c.b])][bt_cell(p, c.j, c.b)]);
+  col[at] = c.j;
+  lb[at] = x.lb;
+  ub[at] = x.ub;
+}
+
+// A vector's segment into ascending column order (the order updatedBounds() promises); a vector's columns are
+// distinct.  Up to 32 entries: one warp, an entry per lane, every entry's place = the number of smaller columns (by
+// shuffle).  Longer segments are a CTA's job (wl_upd_sort_cta).
+__device__ __forceinline__ void wl_upd_emit(long long at, int c, double l, double u, int *colOut, double *lbOut, double *ubOut,
+  WlUpdHead *head, long long headCap)
+{
+  colOut[at] = c;
+  lbOut[at] = l;
+  ubOut[at] = u;
+  if (at < headCap) {
+    WlUpdHead hd;
+    hd.col = c;
+    hd.pad = 0;
+    hd.lb = l;
+    hd.ub = u;
+    head[at] = hd;
+  }
+}
+
+constexpr int kWlSortWarp = 256;   // segments up to this length: a warp
+constexpr int kWlSortSmem = 2048;  // ... up to this length: a CTA, bitonic in shared memory; longer: a CTA, by counting
+
+// cols: kWlSortWarp ints of shared memory that belong to the warp
+__device__ __forceinline__ void wl_upd_sort_warp(const long long *start, int b, int lane, int *cols, const int *colIn,
+  const double *lbIn, const double *ubIn, int *colOut, double *lbOut, double *ubOut, WlUpdHead *head, long long headCap)
+{
+  const long long s0 = start[b];
+  const int k = static_cast<int>(start[b + 1] - s0);
+  if (k <= 0 || k > kWlSortWarp)
+    return;
+  if (k <= 32) {
+    const int c = lane < k ? colIn[s0 + lane] : 0x7fffffff;
+    int rank = 0;
+#pragma unroll
+    for (int f = 0; f < 32; ++f)
+      rank += __shfl_sync(0xffffffffu, c, f) < c ? 1 : 0;
+    if (lane < k)
+      wl_upd_emit(s0 + rank, c, lbIn[s0 + lane], ubIn[s0 + lane], colOut, lbOut, ubOut, head, headCap);
+    return;
+  }
+  __syncwarp();
+  for (int e = lane; e < k; e += 32)
+    cols[e] = colIn[s0 + e];
+  __syncwarp();
+  for (int e = lane; e < k; e += 32) {
+    const int c = cols[e];
+    int rank = 0;
+    for (int f = 0; f < k; ++f)  // (all lanes read the same word: a broadcast)
+      rank += cols[f] < c ? 1 : 0;
+    wl_upd_emit(s0 + rank, c, lbIn[s0 + e], ubIn[s0 + e], colOut, lbOut, ubOut, head, headCap);
+  }
+  __syncwarp();
+}
+
+// keys: kWlSortSmem 64-bit words of shared memory; all kThreads threads of the CTA call this together
+__device__ __forceinline__ void wl_upd_sort_cta(const long long *start, int b, int tid, unsigned long long *keys,
+  const int *colIn, const double *lbIn, const double *ubIn, int *colOut, double *lbOut, double *ubOut, WlUpdHead *head,
+  long long headCap)
+{
+  const long long s0 = start[b];
+  const int k = static_cast<int>(start[b + 1] - s0);
+  if (k <= kWlSortWarp)
+    return;
+  if (k <= kWlSortSmem) {
+    int n2 = 64;
+    while (n2 < k)
+      n2 <<= 1;
+    __syncthreads();
+    for (int e = tid; e < n2; e += kThreads)  // (column << 32) | position: the order of the columns, the entry to fetch
+      keys[e] = e < k ? (static_cast<unsigned long long>(static_cast<unsigned>(colIn[s0 + e])) << 32) | static_cast<unsigned>(e)
+                      : ~0ull;
+    __syncthreads();
+    for (int span = 2; span <= n2; span <<= 1)
+      for (int half = span >> 1; half >= 1; half >>= 1) {
+        for (int t = tid; t < (n2 >> 1); t += kThreads) {
+          const int lo = ((t / half) * (half << 1)) + (t % half), hi = lo + half;
+          const bool up = (lo & span) == 0;
+          const unsigned long long x = keys[lo], y = keys[hi];
+          if ((x > y) == up) {
+            keys[lo] = y;
+            keys[hi] = x;
+          }
+        }
+        __syncthreads();
+      }
+    for (int e = tid; e < k; e += kThreads) {
+      const unsigned long long key = keys[e];
+      const int from = static_cast<int>(key & 0xffffffffu);
+      wl_upd_emit(s0 + e, static_cast<int>(key >> 32), lbIn[s0 + from], ubIn[s0 + from], colOut, lbOut, ubOut, head, headCap);
+    }
+    __syncthreads();
+    return;
+  }
+  for (int e = tid; e < k; e += kThreads) {  // by counting (the loads hit L1)
+    const int c = colIn[s0 + e];
+    int rank = 0;
+    for (int f = 0; f < k; ++f)
+      rank += colIn[s0 + f] < c ? 1 : 0;
+    wl_upd_emit(s0 + rank, c, lbIn[s0 + e], ubIn[s0 + e], colOut, lbOut, ubOut, head, headCap);
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(const WlParams w)
 {
   __shared__ __align__(16) BtLogEntry s_stage[kWlStage];
+  static_assert(sizeof(BtLogEntry) * kWlStage >= sizeof(unsigned long long) * kWlSortSmem, "P7 sorts in the staging buffer");
   __shared__ unsigned s_staged, s_base;
   __shared__ RowAct s_row[kWarps];
   __shared__ double s_mag[kWarps];
@@ -1442,10 +1585,101 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
     myPairs += __shfl_xor_sync(0xffffffffu, myPairs, m);
   if (lane == 0 && myPairs)
     atomicAdd(&ctl->pairs, myPairs);
+  // (every way out of the loop passes a grid barrier after the last write to these flags)
+  if (status == kWlOk
+    && (*reinterpret_cast<volatile int *>(&ctl->overflow) || *reinterpret_cast<volatile int *>(&ctl->overflowP1)))
+    status = kWlOverflow;  // a list filled up in the last round
   if (gtid == 0) {
     ctl->status = status;
     ctl->rounds = round;
   }
+  if (status != kWlOk || w.updCap <= 0)
+    return;
+  // ---- P7: the vectors' update lists, so that fetching them is a copy: count per vector, offsets, fill, order
+  // (the counters were zeroed by wl_setup_kernel)
+  const unsigned nAll = min(*reinterpret_cast<volatile unsigned *>(&ctl->nCells), w.cellCap);
+  for (unsigned i = gtid; i < nAll; i += gsize)
+    wl_upd_count(w.cells[i], p, w.updCnt);
+  grid.sync();
+  wl_stamp(ctl, gtid);
+  if (blockIdx.x == 0) {  // offsets: one CTA; a warp takes a run of consecutive vectors: its total first, then the scan
+    __shared__ long long s_tot[kWarps];
+    const int wq = tid >> 5;
+    const int per = ((w.B + kWarps * 32 - 1) / (kWarps * 32)) * 32;
+    const int b0 = min(wq * per, w.B), b1 = min(b0 + per, w.B);
+    long long sum = 0;
+    for (int b = b0 + lane; b < b1; b += 256) {  // (eight loads in flight)
+      int v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        v[u] = b + 32 * u < b1 ? w.updCnt[b + 32 * u] : 0;
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        sum += v[u];
+    }
+#pragma unroll
+    for (int m = 16; m >= 1; m >>= 1)
+      sum += __shfl_xor_sync(0xffffffffu, sum, m);
+    if (lane == 0)
+      s_tot[wq] = sum;
+    __syncthreads();
+    long long run = 0;
+    for (int q = 0; q < wq; ++q)
+      run += s_tot[q];
+    int nextv = b0 + lane < b1 ? w.updCnt[b0 + lane] : 0;
+    for (int b = b0; b < b1; b += 32) {
+      const int v = nextv;
+      nextv = b + 32 + lane < b1 ? w.updCnt[b + 32 + lane] : 0;
+      long long incl = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const long long t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d)
+          incl += t;
+      }
+      if (b + lane < b1)
+        w.updStart[b + lane] = run + incl - v;
+      run += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (wq == kWarps - 1 && lane == 0) {
+      w.updStart[w.B] = run;
+      ctl->nUpd = static_cast<unsigned long long>(run);
+    }
+  }
+  grid.sync();
+  wl_stamp(ctl, gtid);
+  const long long nUpd = static_cast<long long>(*reinterpret_cast<volatile unsigned long long *>(&ctl->nUpd));
+  if (nUpd > w.updCap)
+    return;  // (the host grows the buffers and takes the lists with the stand-alone kernels)
+  for (unsigned i = gtid; i < nAll; i += gsize)
+    wl_upd_fill(w.cells[i], p, w.updStart, w.updCnt + p.Bp, w.updColTmp, w.updLbTmp, w.updUbTmp);
+  grid.sync();
+  wl_stamp(ctl, gtid);
+  // (what the fill wrote is read with plain loads: the barrier's fence has invalidated L1, and nobody writes it now)
+  for (unsigned b = gwarp; b < static_cast<unsigned>(w.B); b += nwarps)
+    wl_upd_sort_warp(w.updStart, b, lane, reinterpret_cast<int *>(s_emit[tid >> 5]), w.updColTmp, w.updLbTmp, w.updUbTmp,
+      w.updCol, w.updLb, w.updUb, w.updHead, w.updHeadCap);
+  {  // the long segments: a CTA each; every CTA looks through its share of the vectors at once
+    const int perCta = (w.B + gridDim.x - 1) / gridDim.x;
+    const int c0 = min(static_cast<int>(blockIdx.x) * perCta, w.B), c1 = min(c0 + perCta, w.B);
+    for (int base = c0; base < c1; base += kThreads) {
+      const int b = base + tid;
+      const bool big = b < c1 && w.updStart[b + 1] - w.updStart[b] > kWlSortWarp;
+      __syncthreads();
+      if (tid == 0)
+        s_base = 0u;
+      __syncthreads();
+      if (big)
+        reinterpret_cast<int *>(s_emit)[atomicAdd(&s_base, 1u)] = b;  // (at most kThreads ints; the warps are done with s_emit)
+      __syncthreads();
+      const unsigned nBig = s_base;
+      for (unsigned q = 0; q < nBig; ++q)
+        wl_upd_sort_cta(w.updStart, reinterpret_cast<int *>(s_emit)[q], tid, reinterpret_cast<unsigned long long *>(s_stage),
+          w.updColTmp, w.updLbTmp, w.updUbTmp, w.updCol, w.updLb, w.updUb, w.updHead, w.updHeadCap);
+    }
+  }
+  if (gtid == 0)
+    ctl->updDone = 1;
 }
 
 // ---- before and after the run ----------------------------------------------------------------------------------------
@@ -1474,6 +1708,8 @@ __global__ void wl_setup_kernel(const WlParams w, const double *__restrict__ bas
     p.vecFinal[i] = 0;
     w.vecChanged2[0][i] = 0;
     w.vecChanged2[1][i] = 0;
+    w.updCnt[i] = 0;
+    w.updCnt[p.Bp + i] = 0;
     const unsigned m = __ballot_sync(0xffffffffu, static_cast<int>(i) < w.B);
     if ((threadIdx.x & 31) == 0) {
       p.active[i >> 5] = m;
@@ -1483,56 +1719,34 @@ __global__ void wl_setup_kernel(const WlParams w, const double *__restrict__ bas
   }
 }
 
-// ---- updatedBounds() of a worklist run, from the list of cells instead of a scan of the `ever` marks ----------------
-// count per vector
+// ---- updatedBounds() of a worklist run, stand-alone (the run's own P7 did not have the room) ------------------------
 __global__ void wl_upd_count_kernel(const WlCell *__restrict__ cells, unsigned nCells, const BtParams p, int *cnt)
 {
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nCells)
-    return;
-  const WlCell c = cells[i];
-  if (p.vecStop[c.b] == 4)
-    return;  // a vector proved infeasible lists nothing
-  if ((p.ever[bt_word(p, c.j, c.b >> 5)] >> (c.b & 31)) & 1u)
-    atomicAdd(&cnt[c.b], 1);
+  if (i < nCells)
+    wl_upd_count(cells[i], p, cnt);
 }
 
-// (col, lb, ub) of every changed cell into its vector's segment, in the order the threads get there
 __global__ void wl_upd_fill_kernel(const WlCell *__restrict__ cells, unsigned nCells, const BtParams p,
   const long long *__restrict__ start, int *cursor, int *col, double *lb, double *ub)
 {
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nCells)
-    return;
-  const WlCell c = cells[i];
-  if (p.vecStop[c.b] == 4 || !((p.ever[bt_word(p, c.j, c.b >> 5)] >> (c.b & 31)) & 1u))
-    return;
-  const long long at = start[c.b] + atomicAdd(&cursor[c.b], 1);
-  const Bnd x = p.X[p.vecFinal[c.b]][bt_cell(p, c.j, c.b)];
-  col[at] = c.j;
-  lb[at] = x.lb;
-  ub[at] = x.ub;
+  if (i < nCells)
+    wl_upd_fill(cells[i], p, start, cursor, col, lb, ub);
 }
 
-// a vector's segment into ascending column order (the order updatedBounds() promises): one warp per vector, every
-// entry's place = the number of entries with a smaller column (a vector's columns are distinct)
-__global__ void wl_upd_sort_kernel(const long long *__restrict__ start, int B, const int *__restrict__ colIn,
-  const double *__restrict__ lbIn, const double *__restrict__ ubIn, int *colOut, double *lbOut, double *ubOut)
+// one CTA of kThreads threads per vector
+__global__ void __launch_bounds__(kThreads) wl_upd_sort_kernel(const long long *__restrict__ start, int B, const int *colIn,
+  const double *lbIn, const double *ubIn, int *colOut, double *lbOut, double *ubOut)
 {
-  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  __shared__ unsigned long long keys[kWlSortSmem];
+  const int b = blockIdx.x;
   if (b >= B)
     return;
-  const long long s0 = start[b];
-  const int k = static_cast<int>(start[b + 1] - s0);
-  for (int e = lane; e < k; e += 32) {
-    const int c = colIn[s0 + e];
-    int rank = 0;
-    for (int f = 0; f < k; ++f)
-      rank += colIn[s0 + f] < c ? 1 : 0;
-    colOut[s0 + rank] = c;
-    lbOut[s0 + rank] = lbIn[s0 + e];
-    ubOut[s0 + rank] = ubIn[s0 + e];
-  }
+  __shared__ int cols[kWlSortWarp];
+  if ((threadIdx.x >> 5) == 0)
+    wl_upd_sort_warp(start, b, threadIdx.x & 31, cols, colIn, lbIn, ubIn, colOut, lbOut, ubOut, nullptr, 0);
+  wl_upd_sort_cta(start, b, threadIdx.x, keys, colIn, lbIn, ubIn, colOut, lbOut, ubOut, nullptr, 0);
 }
 
 }  // namespace cbp

@@ -228,3 +228,51 @@ def test_worklist_pair_table_nearly_full():
     out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, CBP_WL_TABLE_FACTOR="1"),
                          capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "OK" in out.stdout, out.stderr[-2000:]
+
+
+def _stars(sizes, col_type):
+    """hubs h with leaves x_i <= x_h (rows x_i - x_h <= 0), all columns in [0, 10]: the node is a fixpoint, and lowering
+    a hub's upper bound changes exactly its leaves in one round"""
+    n = len(sizes) + int(sum(sizes))
+    rows, cols, vals = [], [], []
+    leaf = len(sizes)
+    hub_leaves = []
+    for h, k in enumerate(sizes):
+        mine = np.arange(leaf, leaf + k)
+        hub_leaves.append(mine)
+        for i in mine:
+            r = len(rows) // 2
+            rows += [r, r]
+            cols += [int(i), h]
+            vals += [1.0, -1.0]
+        leaf += k
+    m = len(rows) // 2
+    # scatter the leaves over the column range so that a hub's update list does not arrive in column order
+    perm = np.random.Generator(np.random.Philox(7)).permutation(n)
+    cols = perm[np.asarray(cols)]
+    rowStart, col, val, _ = I._csr_from_pairs(m, n, np.asarray(rows), cols, np.asarray(vals))
+    inst = I.Instance(name="stars", m=m, n=n, rowStart=rowStart, col=col, val=val,
+                      sense=np.full(m, ord("L"), np.uint8), rhs=np.zeros(m), range=np.zeros(m),
+                      colType=np.full(n, col_type, np.int8), lb=np.zeros(n), ub=np.full(n, 10.0))
+    return inst, perm, hub_leaves
+
+
+@pytest.mark.parametrize("col_type", [2, 0], ids=["integer_exact_sums", "continuous"])
+def test_worklist_update_lists_of_every_length(oracle, gpu_ctx, col_type):
+    """update lists of 0, 1, 20, 33, 200, 257, 1500, 2049 and 5000 entries: every ordering path of the run's last phase
+    (warp by shuffles, warp counting, CTA bitonic, CTA counting), lists longer than the head the run copies unasked,
+    and — second batch — more entries than the list buffers hold (the stand-alone kernels size them)"""
+    sizes = [0, 1, 20, 33, 200, 257, 1500, 2049, 5000]
+    inst, perm, leaves = _stars(sizes, col_type)
+    s = np.arange(len(sizes) + 1, dtype=np.int64)
+    v = (perm[np.arange(len(sizes))].astype(np.uint32) | np.uint32(I.UPPER_FLAG))
+    b = np.full(len(sizes), 5.0)
+    res, st = _check(oracle, gpu_ctx, inst, s, v, b, "stars")
+    assert np.array_equal(res["nChanged"], np.asarray(sizes))
+    # every hub in every vector: 9 x 9,060 entries > the 65,536 the buffers start with
+    B = 9
+    s2 = np.arange(B + 1, dtype=np.int64) * len(sizes)
+    v2 = np.tile(v, B)
+    b2 = np.repeat(np.arange(1.0, B + 1.0), len(sizes))
+    res2, _ = _check(oracle, gpu_ctx, inst, s2, v2, b2, "stars, all hubs per vector")
+    assert np.all(res2["nChanged"] == sum(sizes))
