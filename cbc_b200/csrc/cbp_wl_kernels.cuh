@@ -1557,7 +1557,8 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         atomicAnd(&p.dirty[cur][word], ~bit);
         const bool applied = p.vecInfRow[c.b] == 0x7fffffff && p.vecInfCol[c.b] == 0x7fffffff;
         if (applied) {
-          atomicOr(&p.ever[word], bit);
+          if (!(atomicOr(&p.ever[word], bit) & bit))
+            atomicAdd(&w.updCnt[c.b], 1);  // (the cell's first change: one more entry of the vector's update list)
           if (!(round + 1 >= w.limit || timeUp)) {
             const size_t at = bt_cell(p, c.j, c.b);
             was = p.X[cur][at];
@@ -1595,55 +1596,58 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
   }
   if (status != kWlOk || w.updCap <= 0)
     return;
-  // ---- P7: the vectors' update lists, so that fetching them is a copy: count per vector, offsets, fill, order
-  // (the counters were zeroed by wl_setup_kernel)
+  // ---- P7: the vectors' update lists, so that fetching them is a copy: offsets, fill, order
+  // (the counts: P6 adds one when it sets a cell's `ever` bit; a vector proved infeasible lists nothing)
   const unsigned nAll = min(*reinterpret_cast<volatile unsigned *>(&ctl->nCells), w.cellCap);
-  for (unsigned i = gtid; i < nAll; i += gsize)
-    wl_upd_count(w.cells[i], p, w.updCnt);
-  grid.sync();
-  wl_stamp(ctl, gtid);
-  if (blockIdx.x == 0) {  // offsets: one CTA; a warp takes a run of consecutive vectors: its total first, then the scan
-    __shared__ long long s_tot[kWarps];
+  if (blockIdx.x == 0) {  // offsets: one CTA, 8,192 vectors at a time: a warp takes 1,024 consecutive ones, 32 per lane
+    __shared__ long long s_tot[kWarps];  // in registers (all loads in flight at once), and scans them by shuffles
     const int wq = tid >> 5;
-    const int per = ((w.B + kWarps * 32 - 1) / (kWarps * 32)) * 32;
-    const int b0 = min(wq * per, w.B), b1 = min(b0 + per, w.B);
-    long long sum = 0;
-    for (int b = b0 + lane; b < b1; b += 256) {  // (eight loads in flight)
-      int v[8];
+    long long done = 0;  // entries of the vectors before this piece
+    for (int base = 0; base < w.B; base += kWarps * 1024) {
+      const int b0 = base + wq * 1024;
+      int v[32];
+      int sum = 0;
 #pragma unroll
-      for (int u = 0; u < 8; ++u)
-        v[u] = b + 32 * u < b1 ? w.updCnt[b + 32 * u] : 0;
-#pragma unroll
-      for (int u = 0; u < 8; ++u)
-        sum += v[u];
-    }
-#pragma unroll
-    for (int m = 16; m >= 1; m >>= 1)
-      sum += __shfl_xor_sync(0xffffffffu, sum, m);
-    if (lane == 0)
-      s_tot[wq] = sum;
-    __syncthreads();
-    long long run = 0;
-    for (int q = 0; q < wq; ++q)
-      run += s_tot[q];
-    int nextv = b0 + lane < b1 ? w.updCnt[b0 + lane] : 0;
-    for (int b = b0; b < b1; b += 32) {
-      const int v = nextv;
-      nextv = b + 32 + lane < b1 ? w.updCnt[b + 32 + lane] : 0;
-      long long incl = v;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const long long t = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d)
-          incl += t;
+      for (int u = 0; u < 32; ++u) {
+        const int b = b0 + 32 * u + lane;
+        v[u] = (b < w.B && p.vecStop[b] != 4) ? w.updCnt[b] : 0;
       }
-      if (b + lane < b1)
-        w.updStart[b + lane] = run + incl - v;
-      run += __shfl_sync(0xffffffffu, incl, 31);
+#pragma unroll
+      for (int u = 0; u < 32; ++u)
+        sum += v[u];
+#pragma unroll
+      for (int m = 16; m >= 1; m >>= 1)
+        sum += __shfl_xor_sync(0xffffffffu, sum, m);
+      __syncthreads();
+      if (lane == 0)
+        s_tot[wq] = sum;
+      __syncthreads();
+      long long run = done;
+      long long all = done;
+      for (int q = 0; q < kWarps; ++q) {
+        if (q < wq)
+          run += s_tot[q];
+        all += s_tot[q];
+      }
+#pragma unroll
+      for (int u = 0; u < 32; ++u) {
+        int incl = v[u];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, incl, d);
+          if (lane >= d)
+            incl += t;
+        }
+        const int b = b0 + 32 * u + lane;
+        if (b < w.B)
+          w.updStart[b] = run + (incl - v[u]);
+        run += __shfl_sync(0xffffffffu, incl, 31);
+      }
+      done = all;
     }
-    if (wq == kWarps - 1 && lane == 0) {
-      w.updStart[w.B] = run;
-      ctl->nUpd = static_cast<unsigned long long>(run);
+    if (tid == 0) {
+      w.updStart[w.B] = done;
+      ctl->nUpd = static_cast<unsigned long long>(done);
     }
   }
   grid.sync();
