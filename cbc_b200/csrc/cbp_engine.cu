@@ -92,6 +92,7 @@ struct BatchState {
   // a worklist run leaves the vectors' update lists in stCol/stLb/stUb and copies what a fetch reads first into
   // pinned host memory before its one synchronisation
   bool updReady = false;        // the last run wrote the lists itself
+  bool listsWanted = false;     // a fetch on this matrix has asked for update lists: runs write them from now on
   long long updTotal = 0;
   // control block | per-vector results | list offsets | head of the lists: one device block (wlCtl, ints and counts
   // point into it), so that ONE copy brings all a fetch needs to its pinned mirror
@@ -1395,6 +1396,29 @@ int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *ba
   return CBP_OK;
 }
 
+// the buffers a worklist run writes the vectors' update lists into (a fetch grows them when a run needs more)
+static int bt_list_buffers(cbp_matrix *mat)
+{
+  BatchState &bt = mat->bt;
+  if (bt.stCap > 0 && bt.st2Cap > 0)
+    return CBP_OK;
+  void *oldp[] = { bt.stCol, bt.stLb, bt.stUb, bt.st2Col, bt.st2Lb, bt.st2Ub };
+  for (void *q : oldp)
+    if (q)
+      cudaFree(q);
+  bt.stCol = bt.st2Col = nullptr;
+  bt.stLb = bt.stUb = bt.st2Lb = bt.st2Ub = nullptr;
+  bt.stCap = bt.st2Cap = 0;
+  const long long want = 1 << 16;
+  if (dalloc(&bt.stCol, want) != cudaSuccess || dalloc(&bt.stLb, want) != cudaSuccess || dalloc(&bt.stUb, want) != cudaSuccess
+    || dalloc(&bt.st2Col, want) != cudaSuccess || dalloc(&bt.st2Lb, want) != cudaSuccess || dalloc(&bt.st2Ub, want) != cudaSuccess) {
+    mat->ctx->err = "batch workspace (update lists)";
+    return CBP_ERR_NOMEM;
+  }
+  bt.stCap = bt.st2Cap = want;
+  return CBP_OK;
+}
+
 // A base + diffs batch in worklist form (cbp_wl_kernels.cuh): a few set-up launches, ONE cooperative launch for all
 // rounds, one read-back of the control block.  *status: kWlOk, or why the caller must run the full-walk path instead.
 static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeLimitSec, int *status)
@@ -1461,21 +1485,10 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.ctl = bt.wlCtl;
   // the update lists (P7): unsorted into st2*, sorted into st*; buffers sized by an earlier fetch (none yet: the
   // first fetch takes the stand-alone path and sizes them)
-  if (bt.stCap == 0 || bt.st2Cap == 0) {  // (a fetch grows them when a run needs more)
-    void *oldp[] = { bt.stCol, bt.stLb, bt.stUb, bt.st2Col, bt.st2Lb, bt.st2Ub };
-    for (void *q : oldp)
-      if (q)
-        cudaFree(q);
-    bt.stCol = bt.st2Col = nullptr;
-    bt.stLb = bt.stUb = bt.st2Lb = bt.st2Ub = nullptr;
-    bt.stCap = bt.st2Cap = 0;
-    const long long want = 1 << 16;
-    if (dalloc(&bt.stCol, want) != cudaSuccess || dalloc(&bt.stLb, want) != cudaSuccess || dalloc(&bt.stUb, want) != cudaSuccess
-      || dalloc(&bt.st2Col, want) != cudaSuccess || dalloc(&bt.st2Lb, want) != cudaSuccess || dalloc(&bt.st2Ub, want) != cudaSuccess) {
-      ctx->err = "batch workspace (update lists)";
-      return CBP_ERR_NOMEM;
-    }
-    bt.stCap = bt.st2Cap = want;
+  if (bt.listsWanted) {
+    const int rcl = bt_list_buffers(mat);
+    if (rcl)
+      return rcl;
   }
   bt.updReady = false;
   w.updStart = bt.counts;
@@ -1486,7 +1499,7 @@ static int bt_wl_run(cbp_matrix *mat, const BtParams &p, int limit, double timeL
   w.updCol = bt.stCol;
   w.updLb = bt.stLb;
   w.updUb = bt.stUb;
-  w.updCap = std::min(bt.stCap, bt.st2Cap);
+  w.updCap = bt.listsWanted ? std::min(bt.stCap, bt.st2Cap) : 0;  // (a caller that never fetches lists does not pay for them)
   w.updHead = reinterpret_cast<WlUpdHead *>(bt.blob + bt.blobOffHead);
   w.updHeadCap = kUpdPrefetch;
   w.limit = limit;
@@ -1958,6 +1971,12 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
     return rc;
   if (!updStart)
     return CBP_OK;
+  if (!bt.listsWanted) {  // from now on the runs on this matrix write the lists themselves
+    bt.listsWanted = true;
+    const int rcl = bt_list_buffers(mat);
+    if (rcl)
+      return rcl;
+  }
   if (bt.quiet) {  // the run set no mark at all: no vector has an update
     if (dev)
       CK(cudaMemsetAsync(updStart, 0, sizeof(long long) * (bt.B + 1), ctx->stream));

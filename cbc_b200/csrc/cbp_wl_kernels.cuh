@@ -492,54 +492,17 @@ __device__ __forceinline__ void wl_row_warp_tighten(const BtParams &p, int row, 
   }
 }
 
-// The three reservations of wl_emit_rows — short items, table items, newly taken table slots — with their atomics in
-// flight together.  ~0u = that list is full.
-__device__ __forceinline__ void wl_warp_reserve3(const WlParams &w, int nxt, int nS, int nL, int nU, int lane,
-  unsigned &atS, unsigned &atL, unsigned &atU)
+// Cells a warp takes per trip when n cells are to be listed: few enough that every warp of the grid gets some (the
+// rows of a warp's cells are dealt out to all 32 lanes anyway, and a trip's cost is its chain of round trips to L2,
+// not its width), a power of two, at most 32.
+__device__ __forceinline__ unsigned wl_cells_per_warp(unsigned n, unsigned nwarps)
 {
-  int iS = nS, iL = nL, iU = nU;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const int tS = __shfl_up_sync(0xffffffffu, iS, d), tL = __shfl_up_sync(0xffffffffu, iL, d),
-              tU = __shfl_up_sync(0xffffffffu, iU, d);
-    if (lane >= d) {
-      iS += tS;
-      iL += tL;
-      iU += tU;
-    }
-  }
-  const int totS = __shfl_sync(0xffffffffu, iS, 31), totL = __shfl_sync(0xffffffffu, iL, 31),
-            totU = __shfl_sync(0xffffffffu, iU, 31);
-  unsigned bS = 0u, bL = 0u, bU = 0u;
-  if (lane == 31) {
-    if (totS)
-      bS = atomicAdd(&w.ctl->nS[nxt], static_cast<unsigned>(totS));
-    if (totL)
-      bL = atomicAdd(&w.ctl->nL[nxt], static_cast<unsigned>(totL));
-    if (totU)
-      bU = atomicAdd(&w.ctl->nUsed, static_cast<unsigned>(totU));
-  }
-  bS = __shfl_sync(0xffffffffu, bS, 31);
-  bL = __shfl_sync(0xffffffffu, bL, 31);
-  bU = __shfl_sync(0xffffffffu, bU, 31);
-  atS = bS + static_cast<unsigned>(iS - nS);
-  atL = bL + static_cast<unsigned>(iL - nL);
-  atU = bU + static_cast<unsigned>(iU - nU);
-  if (bS + static_cast<unsigned>(totS) > w.itemCap) {
-    if (lane == 31)
-      w.ctl->overflow = 1;
-    atS = ~0u;
-  }
-  if (bL + static_cast<unsigned>(totL) > w.itemCap) {
-    if (lane == 31)
-      w.ctl->overflow = 1;
-    atL = ~0u;
-  }
-  if (bU + static_cast<unsigned>(totU) > w.usedCap) {
-    if (lane == 31)
-      w.ctl->usedOverflow = 1;
-    atU = ~0u;
-  }
+  const unsigned c = (n + nwarps - 1u) / nwarps;
+  if (c <= 1u)
+    return 1u;
+  if (c >= 32u)
+    return 32u;
+  return 1u << (32 - __clz(c - 1u));
 }
 
 // One cell of a warp's 32 in wl_emit_rows (shared memory): where the column's rows start, how many rows the cells of
@@ -685,25 +648,59 @@ __device__ __forceinline__ void wl_emit_rows(const WlParams &w, bool active, int
           listed |= 1u << u;
     }
     const int nL = __popc(listed);
-    unsigned atS, atL, atU;
-    wl_warp_reserve3(w, nxt, nS, nL, nNew, lane, atS, atL, atU);
-#pragma unroll
-    for (int u = 0; u < 8; ++u)
-      if (((fresh >> u) & 1u) && atU != ~0u)
-        w.used[atU++] = slot[u];
+    // Room in the three lists — short items, table items, newly taken table slots — with one atomic per list and warp;
+    // an entry's place follows its place among the warp's rows (row 32 u + lane of this trip), so the lists keep a
+    // vector's rows together, which is what the next round's item phase reads fastest.
+    int totS = 0, totL = 0, totU = 0;
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
+      totS += __popc(__ballot_sync(0xffffffffu, (shortRows >> u) & 1u));
+      totL += __popc(__ballot_sync(0xffffffffu, (listed >> u) & 1u));
+      totU += __popc(__ballot_sync(0xffffffffu, (fresh >> u) & 1u));
+    }
+    unsigned bS = 0u, bL = 0u, bU = 0u;
+    if (lane == 0) {
+      if (totS)
+        bS = atomicAdd(&w.ctl->nS[nxt], static_cast<unsigned>(totS));
+      if (totL)
+        bL = atomicAdd(&w.ctl->nL[nxt], static_cast<unsigned>(totL));
+      if (totU)
+        bU = atomicAdd(&w.ctl->nUsed, static_cast<unsigned>(totU));
+    }
+    bS = __shfl_sync(0xffffffffu, bS, 0);
+    bL = __shfl_sync(0xffffffffu, bL, 0);
+    bU = __shfl_sync(0xffffffffu, bU, 0);
+    const bool okS = bS + static_cast<unsigned>(totS) <= w.itemCap, okL = bL + static_cast<unsigned>(totL) <= w.itemCap,
+               okU = bU + static_cast<unsigned>(totU) <= w.usedCap;
+    if (lane == 0) {
+      if (!okS || !okL)
+        w.ctl->overflow = 1;
+      if (!okU)
+        w.ctl->usedOverflow = 1;
+    }
+    const unsigned below = (1u << lane) - 1u;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const unsigned mS = __ballot_sync(0xffffffffu, (shortRows >> u) & 1u), mL = __ballot_sync(0xffffffffu, (listed >> u) & 1u),
+                     mU = __ballot_sync(0xffffffffu, (fresh >> u) & 1u);
       WlItem it;
       it.row = r[u];
       if ((shortRows >> u) & 1u) {
-        if (atS != ~0u) {
+        if (okS) {
           it.b = se[own[u]].b;
-          w.itemsS[nxt][atS++] = it;
+          w.itemsS[nxt][bS + __popc(mS & below)] = it;
         }
-      } else if (((listed >> u) & 1u) && atL != ~0u) {
-        it.b = static_cast<int>(slot[u]);
-        w.itemsL[nxt][atL++] = it;
+      } else if ((listed >> u) & 1u) {
+        if (okL) {
+          it.b = static_cast<int>(slot[u]);
+          w.itemsL[nxt][bL + __popc(mL & below)] = it;
+        }
       }
+      if (((fresh >> u) & 1u) && okU)
+        w.used[bU + __popc(mU & below)] = slot[u];
+      bS += __popc(mS);
+      bL += __popc(mL);
+      bU += __popc(mU);
     }
   }
 }
@@ -1128,8 +1125,9 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
         atomicAdd(&ctl->roundsTotal, 1ull);
       }
     const unsigned nNew = min(*reinterpret_cast<volatile unsigned *>(&ctl->nCells), w.cellCap);
-    for (unsigned i0 = gwarp << 5; i0 < nNew; i0 += nwarps << 5) {  // (whole warps: the listing is a warp's job)
-      const unsigned i = i0 + lane;
+    const unsigned cpwNew = wl_cells_per_warp(nNew, nwarps);
+    for (unsigned i0 = gwarp * cpwNew; i0 < nNew; i0 += nwarps * cpwNew) {  // (whole warps: the listing is a warp's job)
+      const unsigned i = lane < cpwNew ? i0 + lane : nNew;
       bool go = false;
       WlCell c;
       c.b = 0;
@@ -1542,8 +1540,9 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       }
     }
     const unsigned nK6 = min(*reinterpret_cast<volatile unsigned *>(&ctl->nK), w.kCap);
-    for (unsigned i0 = gwarp << 5; i0 < nK6; i0 += nwarps << 5) {  // (whole warps: the listing below is a warp's job)
-      const unsigned i = i0 + lane;
+    const unsigned cpw6 = wl_cells_per_warp(nK6, nwarps);
+    for (unsigned i0 = gwarp * cpw6; i0 < nK6; i0 += nwarps * cpw6) {  // (whole warps: the listing below is a warp's job)
+      const unsigned i = lane < cpw6 ? i0 + lane : nK6;
       bool go = false;
       WlCell c;
       c.b = 0;
