@@ -601,9 +601,17 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     up(&mat->cscRow, hCscRow);
     up(&mat->cscVal, hCscVal);
     // Event-driven rounds pay off while (changed columns) x (rows per column) x (nonzeros per row) stays a small
-    // part of the matrix: changed <= n m / (64 nnz) (measured on the 1M x 1M mixed instance: below ~1,500 changed
-    // columns the event-driven round beats the full scan).  CBP_EVENT_DIV replaces the 64 (0: never event-driven).
-    static const double evDiv = getenv("CBP_EVENT_DIV") ? atof(getenv("CBP_EVENT_DIV")) : 64.0;
+    // part of the matrix.  Matrices of short rows and short columns only (no row over kShortLen nonzeros, no column
+    // over 128 rows): changed <= n m / (8 nnz) — measured on the 1M x 1M mixed instance: an event-driven round costs
+    // 13 us + 3.7 us per 1,000 changed columns against 63-75 us for the full scan, so it wins below ~13,000 changed
+    // columns.  Otherwise n m / (64 nnz): a medium row is a warp's job of its own in such a round, and a long column is
+    // walked by one warp, 32 rows at a time.  CBP_EVENT_DIV replaces the 8 / 64 (0: never event-driven).
+    int maxColLen = 0;
+    for (int j = 0; j < n; ++j)
+      maxColLen = std::max(maxColLen, hCscStart[static_cast<size_t>(j) + 1] - hCscStart[j]);
+    const bool lightweight = mat->mShort == static_cast<int>(mKept) && maxColLen <= 128;
+    static const double evDivEnv = getenv("CBP_EVENT_DIV") ? atof(getenv("CBP_EVENT_DIV")) : -1.0;
+    const double evDiv = evDivEnv >= 0.0 ? evDivEnv : (lightweight ? 8.0 : 64.0);
     mat->eventMaxChanged = (evDiv > 0.0 && nnzKept > 0)
       ? static_cast<int>(std::min<double>(static_cast<double>(n) * static_cast<double>(mKept) / (evDiv * static_cast<double>(nnzKept)), 1.0e9))
       : 0;

@@ -460,7 +460,7 @@ __device__ __forceinline__ void sv_short_rows(const SvParams &p, const Bnd *__re
 
 // One short row (<= kShortLen nonzeros) by one thread from the packed CSR copy: the same sums in the same order as
 // the sliced-ELL pass (entries in CSR order, accumulate_fast), so a row gives the same plan whichever pass visits it.
-__device__ __forceinline__ void sv_event_short_row(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink, int row)
+__device__ __forceinline__ RowPlan sv_event_short_plan(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink, int row)
 {
   const int kb = __ldg(&p.rowNz[row]), cnt = __ldg(&p.rowCnt[row]);
   RowAct ra = { 0.0, 0.0, 0.0, 0, 0 };
@@ -488,29 +488,54 @@ __device__ __forceinline__ void sv_event_short_row(const SvParams &p, const Bnd 
   const RowPlan pl = plan_row(ra, __ldg(&p.rowLB[row]), __ldg(&p.rowUB[row]), p.s);
   if (pl.infeasible)
     sink.flag_row(p.rowOrig[row] + p.rowOffset);
-  if (pl.sideU || pl.sideL)
-    for (int k = 0; k < cnt; k += 8) {  // (all loads of a chunk are issued before the first use)
-      double a[8];
-      int cj[8];
-      Bnd x[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        a[u] = 0.0;
-        cj[u] = 0;
-        if (k + u < cnt) {
-          cj[u] = __ldg(&p.col[kb + k + u]);
-          a[u] = __ldg(&p.val[kb + k + u]);
-        }
+  return pl;
+}
+
+// The short rows of a warp's lanes that can tighten (want), nonzero-parallel: as many of them as fit into 32 lanes at
+// a time — a row with cnt nonzeros gets cnt consecutive lanes — and each lane evaluates one nonzero of "its" row
+// with that row's plan (fetched by shuffle).  One copy of the tightening code with all lanes busy, instead of every
+// lane walking its own row through it.  Called by all 32 lanes together.
+__device__ __forceinline__ void sv_tighten_packed(const SvParams &p, const Bnd *__restrict__ src, SvSink &sink, bool want,
+  int row, const RowPlan &pl, int lane)
+{
+  unsigned todo = __ballot_sync(0xffffffffu, want);
+  if (!todo)
+    return;
+  const int kb = want ? __ldg(&p.rowNz[row]) : 0, cnt = want ? __ldg(&p.rowCnt[row]) : 0;
+  const int packed = min(pl.infMin, 2) | (min(pl.infMax, 2) << 2) | (pl.sideU ? 16 : 0) | (pl.sideL ? 32 : 0);
+  while (todo) {
+    int owner = -1, ent = 0, used = 0;
+    while (todo) {
+      const int o = __ffs(todo) - 1;
+      const int c = __shfl_sync(0xffffffffu, cnt, o);
+      if (used + c > 32 && used > 0)
+        break;
+      if (lane >= used && lane < used + c) {
+        owner = o;
+        ent = lane - used;
       }
-#pragma unroll
-      for (int u = 0; u < 8; ++u)
-        x[u] = ldcg_bnd(&src[col_of(cj[u])]);
-#pragma unroll
-      for (int u = 0; u < 8; ++u)
-        if (a[u] != 0.0)
-          tighten_nz(sink, pl, a[u], col_of(cj[u]), col_is_int(cj[u]), a[u] > 0.0 ? x[u].lb : x[u].ub,
-            a[u] > 0.0 ? x[u].ub : x[u].lb, p.s);
+      used += c;
+      todo &= todo - 1;
     }
+    const int from = owner >= 0 ? owner : 0;
+    const int okb = __shfl_sync(0xffffffffu, kb, from);
+    RowPlan q;
+    q.slackU = __shfl_sync(0xffffffffu, pl.slackU, from);
+    q.slackL = __shfl_sync(0xffffffffu, pl.slackL, from);
+    const int pk = __shfl_sync(0xffffffffu, packed, from);
+    q.infMin = pk & 3;
+    q.infMax = (pk >> 2) & 3;
+    q.sideU = (pk & 16) != 0;
+    q.sideL = (pk & 32) != 0;
+    q.infeasible = false;
+    if (owner >= 0) {
+      const int c = __ldg(&p.col[okb + ent]);
+      const double a = __ldg(&p.val[okb + ent]);
+      const Bnd x = ldcg_bnd(&src[col_of(c)]);
+      if (a != 0.0)
+        tighten_nz(sink, q, a, col_of(c), col_is_int(c), a > 0.0 ? x.lb : x.ub, a > 0.0 ? x.ub : x.lb, p.s);
+    }
+  }
 }
 
 // One medium row (kShortLen < nonzeros <= kTileNnz) by one warp: lanes stride over the row, butterfly — the
@@ -541,19 +566,46 @@ __device__ __forceinline__ void sv_event_medium_row(const SvParams &p, const Bnd
 
 // Event-driven row phase: the previous round changed few columns, and a row none of whose columns moved would
 // only repeat what it did last round (same bounds, same candidates, all of them already rejected or applied), so only
-// the rows that hold a changed column are evaluated.  A warp takes one word of the previous round's marks; for each
-// marked column it brings the target buffer up to date (step A1) and walks the column's rows in the column-major
-// copy: short rows one per lane, medium rows one after the other by the whole warp.  A row that holds two changed
-// columns is evaluated twice; its candidates are max/min reductions, so that is harmless.  Rows longer than a tile
-// are not handled here: the caller scans them in full.
+// the rows that hold a changed column are evaluated.  A warp takes a few words of the previous round's marks (as few
+// as leaves every warp of the grid some: the phase is a chain of dependent loads per warp, not a throughput), brings
+// the target buffer up to date for their marked columns (step A1), and then lays its marked columns end to end, 32
+// at a time (lane = column: its range in the column-major copy), and those columns' rows end to end, 32 at a time
+// (lane = row): short rows one per lane, medium rows one after the other by the whole warp.  So the number of trips
+// follows the number of rows to visit, not the number of marked columns.  A row that holds two changed columns is
+// evaluated twice; its candidates are max/min reductions, so that is harmless.  Rows longer than a tile are not
+// handled here: the caller scans them in full.
+__device__ __forceinline__ int sv_owner_of(int incl, int idx)
+{
+  // the first lane whose inclusive count exceeds idx (idx < the warp's total)
+  int o = 0;
+#pragma unroll
+  for (int st = 16; st >= 1; st >>= 1)
+    if (__shfl_sync(0xffffffffu, incl, o + st - 1) <= idx)
+      o += st;
+  return o;
+}
+
+__device__ __forceinline__ int sv_warp_incl(int v, int lane)
+{
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, v, d);
+    if (lane >= d)
+      v += t;
+  }
+  return v;
+}
+
 __device__ __forceinline__ void sv_event_rows(const SvParams &p, const Bnd *__restrict__ src, Bnd *dst, unsigned *prev,
   SvSink &sink)
 {
   const int lane = threadIdx.x & 31;
   const int gwarp = (blockIdx.x * kThreads + threadIdx.x) >> 5, nwarps = (gridDim.x * kThreads) >> 5;
-  for (int w0 = gwarp << 5; w0 < p.nWords; w0 += nwarps << 5) {  // 32 mark words per warp and trip, one per lane
+  const int per = (p.nWords + nwarps - 1) / nwarps;
+  const int wpw = per <= 1 ? 1 : (per >= 32 ? 32 : 1 << (32 - __clz(per - 1)));  // mark words per warp and trip
+  for (int w0 = gwarp * wpw; w0 < p.nWords; w0 += nwarps * wpw) {
     const int wl = w0 + lane;
-    const unsigned mine = wl < p.nWords ? __ldcg(&prev[wl]) : 0u;
+    const unsigned mine = (lane < wpw && wl < p.nWords) ? __ldcg(&prev[wl]) : 0u;
     if (mine) {
       prev[wl] = 0u;
       unsigned bits = mine;  // A1 for this lane's marked columns
@@ -565,27 +617,40 @@ __device__ __forceinline__ void sv_event_rows(const SvParams &p, const Bnd *__re
         atomic_min_f64(&dst[j].ub, b.ub);
       }
     }
-    unsigned live = __ballot_sync(0xffffffffu, mine != 0u);
-    while (live) {
-      const int sl = __ffs(live) - 1;
-      live &= live - 1;
-      unsigned bits = __shfl_sync(0xffffffffu, mine, sl);
-      const int w = w0 + sl;
-      while (bits) {
-        const int j = (w << 5) + __ffs(bits) - 1;
-        bits &= bits - 1;
-        const int cs = __ldg(&p.cscStart[j]), ce = __ldg(&p.cscStart[j + 1]);
-        for (int q0 = cs; q0 < ce; q0 += 32) {
-          const int q = q0 + lane;
-          const int row = q < ce ? __ldg(&p.cscRow[q]) : -1;
-          if (row >= 0 && row < p.mShort)
-            sv_event_short_row(p, src, sink, row);
-          unsigned med = __ballot_sync(0xffffffffu, row >= p.mShort && row < p.firstLongRow);
-          while (med) {
-            const int l = __ffs(med) - 1;
-            med &= med - 1;
-            sv_event_medium_row(p, src, sink, __shfl_sync(0xffffffffu, row, l), lane);
-          }
+    const int inclC = sv_warp_incl(__popc(mine), lane);
+    const int nCols = __shfl_sync(0xffffffffu, inclC, 31);
+    for (int cb = 0; cb < nCols; cb += 32) {  // (uniform)
+      const int ci = cb + lane;
+      const int o = sv_owner_of(inclC, min(ci, nCols - 1));
+      const unsigned obits = __shfl_sync(0xffffffffu, mine, o);
+      const int oexcl = __shfl_sync(0xffffffffu, inclC, o) - __popc(obits);
+      int cs = 0, len = 0;
+      if (ci < nCols) {
+        const int j = ((w0 + o) << 5) + static_cast<int>(__fns(obits, 0, ci - oexcl + 1));
+        cs = __ldg(&p.cscStart[j]);
+        len = __ldg(&p.cscStart[j + 1]) - cs;
+      }
+      const int inclR = sv_warp_incl(len, lane);
+      const int nRows = __shfl_sync(0xffffffffu, inclR, 31);
+      for (int rb = 0; rb < nRows; rb += 32) {  // (uniform)
+        const int ri = rb + lane;
+        const int o2 = sv_owner_of(inclR, min(ri, nRows - 1));
+        const int cs2 = __shfl_sync(0xffffffffu, cs, o2);
+        const int ex2 = __shfl_sync(0xffffffffu, inclR, o2) - __shfl_sync(0xffffffffu, len, o2);
+        const int row = ri < nRows ? __ldg(&p.cscRow[cs2 + (ri - ex2)]) : -1;
+        RowPlan pl;
+        pl.slackU = pl.slackL = 0.0;
+        pl.infMin = pl.infMax = 0;
+        pl.sideU = pl.sideL = pl.infeasible = false;
+        const bool isShort = row >= 0 && row < p.mShort;
+        if (isShort)
+          pl = sv_event_short_plan(p, src, sink, row);
+        sv_tighten_packed(p, src, sink, isShort && (pl.sideU || pl.sideL), row, pl, lane);
+        unsigned med = __ballot_sync(0xffffffffu, row >= p.mShort && row < p.firstLongRow);
+        while (med) {
+          const int l = __ffs(med) - 1;
+          med &= med - 1;
+          sv_event_medium_row(p, src, sink, __shfl_sync(0xffffffffu, row, l), lane);
         }
       }
     }
