@@ -2091,7 +2091,7 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
     CK(cudaMemcpyAsync(bt.counts, off.data(), sizeof(long long) * (bt.B + 1), cudaMemcpyHostToDevice, ctx->stream));
     wl_upd_fill_kernel<<<cdiv(nCells, 256), 256, 0, ctx->stream>>>(bt.wlCells, nCells, p, bt.counts, cnt32 + bt.Bp, bt.st2Col,
       bt.st2Lb, bt.st2Ub);
-    wl_upd_sort_kernel<<<bt.B, kThreads, 0, ctx->stream>>>(bt.counts, bt.B, bt.st2Col, bt.st2Lb,
+    wl_upd_sort_kernel<<<bt.B, kThreads, 0, ctx->stream>>>(p, bt.counts, bt.B, bt.st2Col, bt.st2Lb,
       bt.st2Ub, oCol, oLb, oUb);
     ctx->stats.kernelLaunches += 2;
     CK(cudaGetLastError());

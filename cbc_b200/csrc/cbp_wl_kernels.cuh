@@ -781,7 +781,7 @@ __device__ __forceinline__ void wl_upd_emit(long long at, int c, double l, doubl
 }
 
 constexpr int kWlSortWarp = 256;   // segments up to this length: a warp
-constexpr int kWlSortSmem = 2048;  // ... up to this length: a CTA, bitonic in shared memory; longer: a CTA, by counting
+constexpr int kWlSortSmem = 2048;  // ... up to this length: a CTA, bitonic in shared memory; longer: a CTA reads the marks in column order
 
 // cols: kWlSortWarp ints of shared memory that belong to the warp
 __device__ __forceinline__ void wl_upd_sort_warp(const long long *start, int b, int lane, int *cols, const int *colIn,
@@ -816,9 +816,9 @@ __device__ __forceinline__ void wl_upd_sort_warp(const long long *start, int b, 
 }
 
 // keys: kWlSortSmem 64-bit words of shared memory; all kThreads threads of the CTA call this together
-__device__ __forceinline__ void wl_upd_sort_cta(const long long *start, int b, int tid, unsigned long long *keys,
-  const int *colIn, const double *lbIn, const double *ubIn, int *colOut, double *lbOut, double *ubOut, WlUpdHead *head,
-  long long headCap)
+__device__ __forceinline__ void wl_upd_sort_cta(const BtParams &p, const long long *start, int b, int tid,
+  unsigned long long *keys, const int *colIn, const double *lbIn, const double *ubIn, int *colOut, double *lbOut,
+  double *ubOut, WlUpdHead *head, long long headCap)
 {
   const long long s0 = start[b];
   const int k = static_cast<int>(start[b + 1] - s0);
@@ -854,12 +854,39 @@ __device__ __forceinline__ void wl_upd_sort_cta(const long long *start, int b, i
     __syncthreads();
     return;
   }
-  for (int e = tid; e < k; e += kThreads) {  // by counting (the loads hit L1)
-    const int c = colIn[s0 + e];
-    int rank = 0;
-    for (int f = 0; f < k; ++f)
-      rank += colIn[s0 + f] < c ? 1 : 0;
-    wl_upd_emit(s0 + rank, c, lbIn[s0 + e], ubIn[s0 + e], colOut, lbOut, ubOut, head, headCap);
+  // Longer still: not ordered at all but read off the vector's `ever` marks column by column (the marks of a
+  // 32-vector group are one word per column, consecutive columns adjacent): n / kThreads steps whatever the segment's
+  // length, where counting places would take length^2 / kThreads.
+  {
+    unsigned *cnt = reinterpret_cast<unsigned *>(keys);  // [kWarps] warp totals, [kWarps] = the running place
+    const unsigned *words = p.ever + bt_word(p, 0, b >> 5);
+    const unsigned bit = 1u << (b & 31);
+    const Bnd *fin = p.X[p.vecFinal[b]];
+    const int lane = tid & 31, warp = tid >> 5;
+    __syncthreads();
+    if (tid == 0)
+      cnt[kWarps] = 0u;
+    __syncthreads();
+    for (int j0 = 0; j0 < p.n; j0 += kThreads) {
+      const int j = j0 + tid;
+      const bool has = j < p.n && (words[j] & bit) != 0u;
+      const unsigned m = __ballot_sync(0xffffffffu, has);
+      if (lane == 0)
+        cnt[warp] = __popc(m);
+      __syncthreads();
+      unsigned at = cnt[kWarps];
+      for (int q = 0; q < warp; ++q)
+        at += cnt[q];
+      if (has) {
+        const Bnd x = fin[bt_cell(p, j, b)];
+        wl_upd_emit(s0 + at + __popc(m & ((1u << lane) - 1u)), j, x.lb, x.ub, colOut, lbOut, ubOut, head, headCap);
+      }
+      __syncthreads();
+      if (tid == kThreads - 1)
+        cnt[kWarps] = at + __popc(m);
+      // (the next step's first barrier orders this write before the reads that follow it)
+    }
+    __syncthreads();
   }
 }
 
@@ -1677,7 +1704,7 @@ __global__ void __launch_bounds__(kThreads, CBP_WL_BLOCKS) bt_worklist_kernel(co
       __syncthreads();
       const unsigned nBig = s_base;
       for (unsigned q = 0; q < nBig; ++q)
-        wl_upd_sort_cta(w.updStart, reinterpret_cast<int *>(s_emit)[q], tid, reinterpret_cast<unsigned long long *>(s_stage),
+        wl_upd_sort_cta(p, w.updStart, reinterpret_cast<int *>(s_emit)[q], tid, reinterpret_cast<unsigned long long *>(s_stage),
           w.updColTmp, w.updLbTmp, w.updUbTmp, w.updCol, w.updLb, w.updUb, w.updHead, w.updHeadCap);
     }
   }
@@ -1739,8 +1766,8 @@ __global__ void wl_upd_fill_kernel(const WlCell *__restrict__ cells, unsigned nC
 }
 
 // one CTA of kThreads threads per vector
-__global__ void __launch_bounds__(kThreads) wl_upd_sort_kernel(const long long *__restrict__ start, int B, const int *colIn,
-  const double *lbIn, const double *ubIn, int *colOut, double *lbOut, double *ubOut)
+__global__ void __launch_bounds__(kThreads) wl_upd_sort_kernel(const BtParams p, const long long *__restrict__ start, int B,
+  const int *colIn, const double *lbIn, const double *ubIn, int *colOut, double *lbOut, double *ubOut)
 {
   __shared__ unsigned long long keys[kWlSortSmem];
   const int b = blockIdx.x;
@@ -1749,7 +1776,7 @@ __global__ void __launch_bounds__(kThreads) wl_upd_sort_kernel(const long long *
   __shared__ int cols[kWlSortWarp];
   if ((threadIdx.x >> 5) == 0)
     wl_upd_sort_warp(start, b, threadIdx.x & 31, cols, colIn, lbIn, ubIn, colOut, lbOut, ubOut, nullptr, 0);
-  wl_upd_sort_cta(start, b, threadIdx.x, keys, colIn, lbIn, ubIn, colOut, lbOut, ubOut, nullptr, 0);
+  wl_upd_sort_cta(p, start, b, threadIdx.x, keys, colIn, lbIn, ubIn, colOut, lbOut, ubOut, nullptr, 0);
 }
 
 }  // namespace cbp
