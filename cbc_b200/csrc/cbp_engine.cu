@@ -8,10 +8,15 @@
 #include <algorithm>
 #include <climits>
 #include <cmath>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <memory>
 #include <string>
+#include <thread>
+#include <utility>
 #include <vector>
 
 #include "../../include/cbp_capi.h"
@@ -213,6 +218,38 @@ static Scal make_scal(const cbp_matrix *mat, double tol)
 
 static inline int cdiv(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
 
+// std::vector whose resize() does not zero: the big host arrays of an upload are written in full by the threads that
+// fill them (who then also take their page faults), a zero fill by one thread first would cost as much as the fill.
+template <class T> struct NoInitAlloc : std::allocator<T> {
+  template <class U> struct rebind {
+    using other = NoInitAlloc<U>;
+  };
+  NoInitAlloc() = default;
+  template <class U> NoInitAlloc(const NoInitAlloc<U> &) {}
+  template <class U> void construct(U *p) { ::new (static_cast<void *>(p)) U; }
+  template <class U, class... A> void construct(U *p, A &&...a) { ::new (static_cast<void *>(p)) U(std::forward<A>(a)...); }
+};
+template <class T> using RawVec = std::vector<T, NoInitAlloc<T>>;
+
+// Host side of an upload in parallel: f(begin, end, thread) over [0, n) cut into one piece per thread (the pieces are
+// multiples of `grain`).  Small jobs run on the caller's thread.
+template <class F> static void par_for(size_t n, int threads, size_t grain, F f)
+{
+  if (threads <= 1 || n <= grain) {
+    f(static_cast<size_t>(0), n, 0);
+    return;
+  }
+  size_t chunk = (n + threads - 1) / threads;
+  chunk = (chunk + grain - 1) / grain * grain;
+  std::vector<std::thread> th;
+  int t = 0;
+  for (size_t b = 0; b < n; b += chunk, ++t)
+    th.emplace_back(f, b, std::min(n, b + chunk), t);
+  for (std::thread &x : th)
+    x.join();
+}
+
+
 // ----------------------------------------------------------------------------
 extern "C" {
 
@@ -353,13 +390,55 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     return nullptr;
   }
   cudaSetDevice(ctx->device);
+  const bool upTimes = getenv("CBP_UPLOAD_TIMES") != nullptr;  // tuning aid: where an upload spends its time
+  auto upT0 = std::chrono::steady_clock::now();
+  auto lap = [&](const char *what) {
+    if (!upTimes)
+      return;
+    const auto t = std::chrono::steady_clock::now();
+    fprintf(stderr, "  upload %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t - upT0).count());
+    upT0 = t;
+  };
   const double INF = infinity;
   struct KRow {
     int orig, cnt;
     double rl, ru;
   };
+  // (re-tiling a matrix is host work proportional to its nonzeros: the passes over them run on several threads —
+  // CBP_UPLOAD_THREADS, default min(cores, 16) — and give the same arrays whatever the number of threads)
+  long long nnzIn = 0;
+  if (m > 0)
+    nnzIn = rowLen ? 0 : rowStart[m] - rowStart[0];
+  if (rowLen)
+    for (int i = 0; i < m; ++i)
+      nnzIn += rowLen[i];
+  static const int upThreadsEnv = getenv("CBP_UPLOAD_THREADS") ? atoi(getenv("CBP_UPLOAD_THREADS")) : 0;
+  const int upThreads = nnzIn < 200000 ? 1
+    : std::max(1, upThreadsEnv > 0 ? upThreadsEnv : std::min(16, static_cast<int>(std::thread::hardware_concurrency())));
   std::vector<KRow> cls[3];
   long long nnzKept = 0;
+  std::vector<int> rawCnt(static_cast<size_t>(std::max(m, 0)), 0);
+  std::atomic<int> badCol(0);
+  par_for(static_cast<size_t>(m), upThreads, 1024, [&](size_t b, size_t e2, int) {
+    for (size_t i = b; i < e2; ++i) {
+      const char sn = rowSense[i];
+      if (sn != 'L' && sn != 'G' && sn != 'E' && sn != 'R')
+        continue;
+      const int64_t s = rowStart[i], e = rowLen ? s + rowLen[i] : rowStart[i + 1];
+      int cnt = 0;
+      for (int64_t k = s; k < e; ++k)
+        if (val[k] != 0.0) {
+          if (colIdx[k] < 0 || colIdx[k] >= n)
+            badCol.store(1, std::memory_order_relaxed);
+          ++cnt;
+        }
+      rawCnt[i] = cnt;
+    }
+  });
+  if (badCol.load()) {
+    ctx->err = "cbp_matrix_upload: column index out of range";
+    return nullptr;
+  }
   for (int i = 0; i < m; ++i) {
     double rl, ru;
     const double r = rhs[i];
@@ -370,17 +449,7 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     case 'R': rl = r - std::fabs(range ? range[i] : 0.0); ru = r; break;
     default: continue;
     }
-    const int64_t s = rowStart[i], e = rowLen ? s + rowLen[i] : rowStart[i + 1];
-    int cnt = 0;
-    for (int64_t k = s; k < e; ++k) {
-      if (val[k] != 0.0) {
-        if (colIdx[k] < 0 || colIdx[k] >= n) {
-          ctx->err = "cbp_matrix_upload: column index out of range";
-          return nullptr;
-        }
-        ++cnt;
-      }
-    }
+    const int cnt = rawCnt[i];
     // a row without nonzeros says rl <= 0 <= ru; keep it only if that can fail (R4)
     if (cnt == 0 && !(ru < 0.0 || rl > 0.0))
       continue;
@@ -388,13 +457,16 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     cls[c].push_back({ i, cnt, rl, ru });
     nnzKept += cnt;
   }
+  lap("classify rows");
   const size_t mKept = cls[0].size() + cls[1].size() + cls[2].size();
   if (nnzKept + static_cast<long long>(kAlign) * (static_cast<long long>(mKept) + 8) > INT_MAX) {
     ctx->err = "cbp_matrix_upload: more than 2^31 nonzeros are not supported";
     return nullptr;
   }
-  std::vector<double> hVal, hRl(mKept), hRu(mKept);
-  std::vector<int> hCol, hRp, hOrig(mKept), hNz(mKept), hCnt(mKept), hPos(mKept, 0), hSing;
+  RawVec<double> hVal;
+  RawVec<int> hCol;
+  std::vector<double> hRl(mKept), hRu(mKept);
+  std::vector<int> hRp, hOrig(mKept), hNz(mKept), hCnt(mKept), hPos(mKept, 0), hSing;
   std::vector<Tile> hTiles;
   std::vector<LongRow> hLong;
   hVal.reserve(nnzKept + nnzKept / 64 + 64);
@@ -433,36 +505,87 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   // short rows: sorted by length inside windows (little padding in the slices,
   // the caller's order survives at window scale), stored once in packed CSR
   // form (batch kernels, phase 1) and once as sliced-ELL (single-vector loop)
-  std::vector<double> hSellVal;
-  std::vector<int> hSellCol, hSellOff;
+  RawVec<double> hSellVal;
+  RawVec<int> hSellCol;
+  std::vector<int> hSellOff;
   {
     std::vector<KRow> &rows = cls[kShort];
-    for (size_t w = 0; w < rows.size(); w += kSellWindow) {
-      const size_t e = std::min(rows.size(), w + kSellWindow);
-      std::stable_sort(rows.begin() + w, rows.begin() + e,
-        [](const KRow &a, const KRow &b) { return a.cnt > b.cnt; });
-    }
-    for (const KRow &kr : rows)
-      emit_row(kr, kept++);
+    par_for((rows.size() + kSellWindow - 1) / kSellWindow, upThreads, 1, [&](size_t wb, size_t we, int) {
+      for (size_t wi = wb; wi < we; ++wi) {
+        const size_t w = wi * kSellWindow, e = std::min(rows.size(), w + kSellWindow);
+        std::stable_sort(rows.begin() + w, rows.begin() + e, [](const KRow &a, const KRow &b) { return a.cnt > b.cnt; });
+      }
+    });
     const int mS = static_cast<int>(rows.size());
+    {  // where every short row's entries go in the packed arrays (no padding between short rows)
+      int at = 0;
+      for (int r = 0; r < mS; ++r) {
+        hNz[r] = at;
+        at += rows[r].cnt;
+      }
+      hVal.resize(static_cast<size_t>(at));
+      hCol.resize(static_cast<size_t>(at));
+    }
     const int nSlices = (mS + 31) / 32;
     hSellOff.assign(nSlices + 1, 0);
     for (int sl = 0; sl < nSlices; ++sl) {
       int len = 0;
       for (int r = sl * 32; r < std::min(mS, sl * 32 + 32); ++r)
-        len = std::max(len, hCnt[r]);
+        len = std::max(len, rows[r].cnt);
       hSellOff[sl + 1] = hSellOff[sl] + 32 * len;
     }
-    hSellVal.assign(static_cast<size_t>(hSellOff[nSlices]) + 32, 0.0);
-    hSellCol.assign(static_cast<size_t>(hSellOff[nSlices]) + 32, 0);
-    for (int r = 0; r < mS; ++r) {
-      const size_t base = static_cast<size_t>(hSellOff[r >> 5]) + (r & 31);
-      for (int k = 0; k < hCnt[r]; ++k) {
-        hSellVal[base + 32 * static_cast<size_t>(k)] = hVal[hNz[r] + k];
-        hSellCol[base + 32 * static_cast<size_t>(k)] = hCol[hNz[r] + k];
-      }
+    hSellVal.resize(static_cast<size_t>(hSellOff[nSlices]) + 32);  // (not zeroed: every entry is written below)
+    hSellCol.resize(static_cast<size_t>(hSellOff[nSlices]) + 32);
+    for (size_t i = static_cast<size_t>(hSellOff[nSlices]); i < hSellVal.size(); ++i) {
+      hSellVal[i] = 0.0;
+      hSellCol[i] = 0;
     }
+    std::vector<std::vector<int>> singOf(static_cast<size_t>(std::max(upThreads, 1)));
+    par_for(static_cast<size_t>(mS), upThreads, 32, [&](size_t rb, size_t re, int t) {  // (whole slices per thread)
+      for (size_t r = rb; r < re; ++r) {
+        const KRow &kr = rows[r];
+        hOrig[r] = kr.orig;
+        hRl[r] = kr.rl;
+        hRu[r] = kr.ru;
+        hCnt[r] = kr.cnt;
+        const int64_t s = rowStart[kr.orig], e = rowLen ? s + rowLen[kr.orig] : rowStart[kr.orig + 1];
+        size_t at = static_cast<size_t>(hNz[r]);
+        const size_t base = static_cast<size_t>(hSellOff[r >> 5]) + (r & 31);
+        int k2 = 0;
+        for (int64_t k = s; k < e; ++k) {
+          if (val[k] == 0.0)
+            continue;
+          const bool isInt = colType && colType[colIdx[k]] != 0;
+          const int c = isInt ? (colIdx[k] | INT_MIN) : colIdx[k];  // bit 31 = integer column
+          hVal[at] = val[k];
+          hCol[at] = c;
+          ++at;
+          hSellVal[base + 32 * static_cast<size_t>(k2)] = val[k];
+          hSellCol[base + 32 * static_cast<size_t>(k2)] = c;
+          ++k2;
+        }
+        const int len = (hSellOff[(r >> 5) + 1] - hSellOff[r >> 5]) >> 5;
+        for (; k2 < len; ++k2) {  // the slice's padding behind this row
+          hSellVal[base + 32 * static_cast<size_t>(k2)] = 0.0;
+          hSellCol[base + 32 * static_cast<size_t>(k2)] = 0;
+        }
+        if (kr.cnt == 1)
+          singOf[static_cast<size_t>(t)].push_back(static_cast<int>(r));
+      }
+      if (re == static_cast<size_t>(mS) && (mS & 31)) {  // the lanes of the last slice that have no row
+        const int sl = mS >> 5, len = (hSellOff[sl + 1] - hSellOff[sl]) >> 5;
+        for (int l = mS & 31; l < 32; ++l)
+          for (int k2 = 0; k2 < len; ++k2) {
+            hSellVal[static_cast<size_t>(hSellOff[sl]) + 32 * static_cast<size_t>(k2) + l] = 0.0;
+            hSellCol[static_cast<size_t>(hSellOff[sl]) + 32 * static_cast<size_t>(k2) + l] = 0;
+          }
+      }
+    });
+    for (const std::vector<int> &v : singOf)  // (thread pieces are ascending row ranges: ascending in all)
+      hSing.insert(hSing.end(), v.begin(), v.end());
+    kept = mS;
   }
+  lap("short rows: packed + SELL");
   {  // medium rows: greedy tiles of whole rows, staged through shared memory
     const int c = kMedium;
     size_t i = 0;
@@ -520,6 +643,7 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     hCol.push_back(0);
   }
 
+  lap("medium / long rows");
   cbp_matrix *mat = new cbp_matrix();
   mat->ctx = ctx;
   mat->m = m;
@@ -572,6 +696,7 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   up(&mat->sellVal, hSellVal);
   up(&mat->sellCol, hSellCol);
   up(&mat->sellOff, hSellOff);
+  lap("allocate + copy (CSR, SELL)");
   std::vector<int> hOrder(hSellOff.size() - 1);
   for (size_t i = 0; i < hOrder.size(); ++i)
     hOrder[i] = static_cast<int>(i);
@@ -583,23 +708,78 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   mat->mShort = static_cast<int>(cls[kShort].size());
   mat->firstLongRow = static_cast<int>(cls[kShort].size() + cls[kMedium].size());
   {  // column-major copy of the kept rows (the CSC of north_star's "CSR and CSC copies in HBM")
-    std::vector<int> hCscStart(static_cast<size_t>(n) + 1, 0);
-    for (size_t r = 0; r < mKept; ++r)
-      for (int k = hNz[r]; k < hNz[r] + hCnt[r]; ++k)
-        ++hCscStart[static_cast<size_t>(hCol[k] & kColMask) + 1];
-    for (int j = 0; j < n; ++j)
-      hCscStart[j + 1] += hCscStart[j];
-    std::vector<int> hCscRow(static_cast<size_t>(hCscStart[n]) + 1), fill(hCscStart.begin(), hCscStart.end() - 1);
-    std::vector<double> hCscVal(static_cast<size_t>(hCscStart[n]) + 1);
-    for (size_t r = 0; r < mKept; ++r)
-      for (int k = hNz[r]; k < hNz[r] + hCnt[r]; ++k) {
-        const int at = fill[hCol[k] & kColMask]++;
-        hCscRow[at] = static_cast<int>(r);
-        hCscVal[at] = hVal[k];
+    // Every thread takes a range of kept rows: its own count per column, then — columns in parallel — where each
+    // thread's entries of a column start (thread ranges ascend, so a column's rows end up in ascending order whatever
+    // the number of threads), then the fill through the thread's own cursors.  No atomics, no sorting.
+    const int cscT = static_cast<int>(std::max<size_t>(1, std::min<size_t>(static_cast<size_t>(upThreads),
+      (static_cast<size_t>(256) << 20) / (sizeof(int) * (static_cast<size_t>(n) + 1)))));
+    const size_t rowsPer = (mKept + cscT - 1) / std::max(cscT, 1) + 1;
+    std::vector<std::vector<int>> cur(static_cast<size_t>(cscT));
+    par_for(static_cast<size_t>(cscT), cscT, 1, [&](size_t tb, size_t te, int) {
+      for (size_t t = tb; t < te; ++t) {
+        std::vector<int> &h = cur[t];
+        h.assign(static_cast<size_t>(n), 0);
+        const size_t rb = std::min(mKept, t * rowsPer), re = std::min(mKept, rb + rowsPer);
+        for (size_t r = rb; r < re; ++r)
+          for (int k = hNz[r]; k < hNz[r] + hCnt[r]; ++k)
+            ++h[static_cast<size_t>(hCol[k] & kColMask)];
       }
+    });
+    std::vector<int> hCscStart(static_cast<size_t>(n) + 1, 0);
+    {
+      // per column chunk: the chunk's total; then the chunks' bases; then every (thread, column) cursor
+      const size_t colChunk = 8192;
+      const size_t nChunks = (static_cast<size_t>(n) + colChunk - 1) / colChunk;
+      std::vector<long long> chunkSum(nChunks + 1, 0);
+      par_for(nChunks, upThreads, 1, [&](size_t cb, size_t ce, int) {
+        for (size_t c = cb; c < ce; ++c) {
+          long long tot = 0;
+          for (size_t j = c * colChunk; j < std::min(static_cast<size_t>(n), (c + 1) * colChunk); ++j)
+            for (int t = 0; t < cscT; ++t)
+              tot += cur[static_cast<size_t>(t)][j];
+          chunkSum[c + 1] = tot;
+        }
+      });
+      for (size_t c = 0; c < nChunks; ++c)
+        chunkSum[c + 1] += chunkSum[c];
+      par_for(nChunks, upThreads, 1, [&](size_t cb, size_t ce, int) {
+        for (size_t c = cb; c < ce; ++c) {
+          int at = static_cast<int>(chunkSum[c]);
+          for (size_t j = c * colChunk; j < std::min(static_cast<size_t>(n), (c + 1) * colChunk); ++j) {
+            hCscStart[j] = at;
+            for (int t = 0; t < cscT; ++t) {
+              const int cntTj = cur[static_cast<size_t>(t)][j];
+              cur[static_cast<size_t>(t)][j] = at;
+              at += cntTj;
+            }
+          }
+        }
+      });
+      hCscStart[static_cast<size_t>(n)] = static_cast<int>(chunkSum[nChunks]);
+    }
+    RawVec<int> hCscRow;
+    RawVec<double> hCscVal;
+    hCscRow.resize(static_cast<size_t>(hCscStart[n]) + 1);  // (not zeroed: the fill writes every entry but the spare one)
+    hCscVal.resize(static_cast<size_t>(hCscStart[n]) + 1);
+    hCscRow[static_cast<size_t>(hCscStart[n])] = 0;
+    hCscVal[static_cast<size_t>(hCscStart[n])] = 0.0;
+    par_for(static_cast<size_t>(cscT), cscT, 1, [&](size_t tb, size_t te, int) {
+      for (size_t t = tb; t < te; ++t) {
+        std::vector<int> &h = cur[t];
+        const size_t rb = std::min(mKept, t * rowsPer), re = std::min(mKept, rb + rowsPer);
+        for (size_t r = rb; r < re; ++r)
+          for (int k = hNz[r]; k < hNz[r] + hCnt[r]; ++k) {
+            const int at = h[static_cast<size_t>(hCol[k] & kColMask)]++;
+            hCscRow[at] = static_cast<int>(r);
+            hCscVal[at] = hVal[k];
+          }
+      }
+    });
+    lap("column-major copy: build");
     up(&mat->cscStart, hCscStart);
     up(&mat->cscRow, hCscRow);
     up(&mat->cscVal, hCscVal);
+    lap("column-major copy: upload");
     // Event-driven rounds pay off while (changed columns) x (rows per column) x (nonzeros per row) stays a small
     // part of the matrix.  Matrices of short rows and short columns only (no row over kShortLen nonzeros, no column
     // over 128 rows): changed <= n m / (8 nnz) — measured on the 1M x 1M mixed instance: an event-driven round costs
@@ -632,6 +812,7 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   ok = ok && dalloc(&mat->dRes, 16) == cudaSuccess;
   ok = ok && dalloc(&mat->dAct, 3 * static_cast<size_t>(std::max(m, 1))) == cudaSuccess;
   ok = ok && cudaStreamSynchronize(ctx->stream) == cudaSuccess;
+  lap("state buffers + sync");
   if (!ok) {
     ctx->err = std::string("cbp_matrix_upload: ") + cudaGetErrorString(cudaGetLastError());
     cbp_matrix_free(mat);
