@@ -140,6 +140,11 @@ struct cbp_matrix {
   int eventMaxChanged = 0;  // single vector: rounds after a round that changed at most this many columns are event-driven
   // device, single-vector workspace
   RowAct *longPart = nullptr;
+  // everything an upload allocates comes out of one device allocation (a second one only if the estimate fell short):
+  // thirty cudaMallocs were a quarter of a small upload
+  std::vector<void *> arenaChunks;
+  unsigned char *arenaCur = nullptr;
+  size_t arenaLeft = 0, arenaHint = 0;
   Bnd *X[2] = { nullptr, nullptr };
   unsigned *dirty[2] = { nullptr, nullptr };
   int nWords = 0;
@@ -205,6 +210,27 @@ template <class T>
 static cudaError_t dalloc(T **p, size_t count)
 {
   return cudaMalloc(reinterpret_cast<void **>(p), std::max<size_t>(count, 1) * sizeof(T));
+}
+
+template <class T>
+static cudaError_t mat_alloc(cbp_matrix *mat, T **p, size_t count)
+{
+  const size_t bytes = (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~static_cast<size_t>(255);
+  if (bytes > mat->arenaLeft) {
+    const size_t sz = std::max(bytes, std::max<size_t>(mat->arenaHint, static_cast<size_t>(1) << 20));
+    void *q = nullptr;
+    const cudaError_t e = cudaMalloc(&q, sz);
+    if (e != cudaSuccess)
+      return e;
+    mat->arenaChunks.push_back(q);
+    mat->arenaCur = static_cast<unsigned char *>(q);
+    mat->arenaLeft = sz;
+    mat->arenaHint = sz / 4;  // (should the estimate have been short: a quarter as much again)
+  }
+  *p = reinterpret_cast<T *>(mat->arenaCur);
+  mat->arenaCur += bytes;
+  mat->arenaLeft -= bytes;
+  return cudaSuccess;
 }
 
 static Scal make_scal(const cbp_matrix *mat, double tol)
@@ -355,12 +381,9 @@ void cbp_matrix_free(cbp_matrix *mat)
   if (!mat)
     return;
   cudaSetDevice(mat->ctx->device);
-  void *ptrs[] = { mat->val, mat->col, mat->tiles, mat->rp, mat->rowLB, mat->rowUB, mat->rowOrig,
-    mat->rowNz, mat->rowCnt, mat->rowPos, mat->longRows, mat->colType, mat->singRows, mat->shortRowsBt,
-    mat->longRowsBt, mat->sellVal, mat->sellCol, mat->sellOff, mat->sliceOrder, mat->cscStart, mat->cscRow, mat->cscVal,
-    mat->longPart, mat->X[0],
-    mat->X[1], mat->dirty[0], mat->dirty[1], mat->st, mat->dLb, mat->dUb, mat->dRes, mat->dAct,
-    mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
+  for (void *q : mat->arenaChunks)  // (the matrix's own arrays and single-vector state)
+    cudaFree(q);
+  void *ptrs[] = { mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
     mat->bt.blob, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
     mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
     mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlInts, mat->bt.wlHKey,
@@ -666,12 +689,17 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
     for (int j = 0; j < n; ++j)
       hType[j] = static_cast<signed char>(colType[j]);
 
+  // (what the arrays below will take, within a per cent: packed CSR, sliced-ELL, column-major copy, per-row and
+  // per-column arrays, the single-vector state)
+  mat->arenaHint = 12 * (hVal.size() + hSellVal.size() + static_cast<size_t>(nnzKept)) + 64 * (mKept + 64)
+    + 80 * (static_cast<size_t>(n) + 64) + 32 * (static_cast<size_t>(std::max(m, 1)) + 64) + sizeof(Tile) * (hTiles.size() + 8)
+    + 4 * hRp.size() + sizeof(RowAct) * (static_cast<size_t>(nParts) + 8) + sizeof(SvStatus) + 48 * 256 + (64 << 10);
   bool ok = true;
   auto up = [&](auto **dptr, const auto &h) {
     using T = typename std::remove_reference<decltype(h)>::type::value_type;
     if (!ok)
       return;
-    if (dalloc(reinterpret_cast<T **>(dptr), h.size()) != cudaSuccess) {
+    if (mat_alloc(mat, reinterpret_cast<T **>(dptr), h.size()) != cudaSuccess) {
       ok = false;
       return;
     }
@@ -803,14 +831,14 @@ cbp_matrix *cbp_matrix_upload(cbp_ctx *ctx, int m, int n, const int64_t *rowStar
   mat->nLongBt = static_cast<int>(hLongBt.size());
   up(&mat->shortRowsBt, hShortBt);
   up(&mat->longRowsBt, hLongBt);
-  ok = ok && dalloc(&mat->longPart, nParts) == cudaSuccess;
-  ok = ok && dalloc(&mat->X[0], n) == cudaSuccess && dalloc(&mat->X[1], n) == cudaSuccess;
-  ok = ok && dalloc(&mat->dirty[0], mat->nWords) == cudaSuccess
-    && dalloc(&mat->dirty[1], mat->nWords) == cudaSuccess;
-  ok = ok && dalloc(&mat->st, 1) == cudaSuccess;
-  ok = ok && dalloc(&mat->dLb, n) == cudaSuccess && dalloc(&mat->dUb, n) == cudaSuccess;
-  ok = ok && dalloc(&mat->dRes, 16) == cudaSuccess;
-  ok = ok && dalloc(&mat->dAct, 3 * static_cast<size_t>(std::max(m, 1))) == cudaSuccess;
+  ok = ok && mat_alloc(mat, &mat->longPart, nParts) == cudaSuccess;
+  ok = ok && mat_alloc(mat, &mat->X[0], n) == cudaSuccess && mat_alloc(mat, &mat->X[1], n) == cudaSuccess;
+  ok = ok && mat_alloc(mat, &mat->dirty[0], mat->nWords) == cudaSuccess
+    && mat_alloc(mat, &mat->dirty[1], mat->nWords) == cudaSuccess;
+  ok = ok && mat_alloc(mat, &mat->st, 1) == cudaSuccess;
+  ok = ok && mat_alloc(mat, &mat->dLb, n) == cudaSuccess && mat_alloc(mat, &mat->dUb, n) == cudaSuccess;
+  ok = ok && mat_alloc(mat, &mat->dRes, 16) == cudaSuccess;
+  ok = ok && mat_alloc(mat, &mat->dAct, 3 * static_cast<size_t>(std::max(m, 1))) == cudaSuccess;
   ok = ok && cudaStreamSynchronize(ctx->stream) == cudaSuccess;
   lap("state buffers + sync");
   if (!ok) {
