@@ -101,6 +101,7 @@ struct BatchState {
   long long updTotal = 0;
   // control block | per-vector results | list offsets | head of the lists: one device block (wlCtl, ints and counts
   // point into it), so that ONE copy brings all a fetch needs to its pinned mirror
+  unsigned char *arena = nullptr;  // the batch workspace below is one device allocation (bt_reserve)
   unsigned char *blob = nullptr, *hBlob = nullptr;
   size_t blobOffInts = 0, blobOffCounts = 0, blobOffHead = 0, blobBytes = 0;
   long long headCopied = 0;     // list entries of the last run that are in the mirror
@@ -383,11 +384,8 @@ void cbp_matrix_free(cbp_matrix *mat)
   cudaSetDevice(mat->ctx->device);
   for (void *q : mat->arenaChunks)  // (the matrix's own arrays and single-vector state)
     cudaFree(q);
-  void *ptrs[] = { mat->bt.X[0], mat->bt.X[1], mat->bt.dirty[0], mat->bt.dirty[1], mat->bt.ever, mat->bt.active,
-    mat->bt.blob, mat->bt.chunkCnt, mat->bt.log, mat->bt.groupFlag, mat->bt.baseLb, mat->bt.baseUb, mat->bt.dStart, mat->bt.dVar,
-    mat->bt.dBnd, mat->bt.dmask, mat->bt.baseX, mat->bt.wlItemsS[0], mat->bt.wlItemsS[1], mat->bt.wlItemsL[0],
-    mat->bt.wlItemsL[1], mat->bt.wlK, mat->bt.wlCells, mat->bt.wlInts, mat->bt.wlHKey,
-    mat->bt.wlWalk, mat->bt.wlUsed, mat->bt.wlRowBase, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
+  void *ptrs[] = { mat->bt.arena, mat->bt.dStart, mat->bt.dVar,
+    mat->bt.dBnd, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
     mat->bt.st2Col, mat->bt.st2Lb, mat->bt.st2Ub };
   for (void *p : ptrs)
     if (p)
@@ -1347,9 +1345,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
   const int Bp = (B + 31) / 32 * 32;
   const size_t cells = static_cast<size_t>(mat->n) * Bp;
   if (cells > bt.capCells || Bp > bt.capBp) {
-    void *old[] = { bt.X[0], bt.X[1], bt.dirty[0], bt.dirty[1], bt.ever, bt.active, bt.blob, bt.chunkCnt,
-      bt.log, bt.groupFlag, bt.dmask, bt.wlItemsS[0], bt.wlItemsS[1], bt.wlItemsL[0], bt.wlItemsL[1], bt.wlK, bt.wlCells,
-      bt.wlInts, bt.wlHKey, bt.wlWalk, bt.wlUsed };
+    void *old[] = { bt.arena };
+    bt.arena = nullptr;
     bt.blob = nullptr;
     if (bt.hBlob)
       cudaFreeHost(bt.hBlob);
@@ -1399,52 +1396,50 @@ static int bt_reserve(cbp_matrix *mat, int B)
       while (bt.wlHSlots < static_cast<unsigned>(std::max<long>(2, atol(getenv("CBP_WL_SLOTS")))))
         bt.wlHSlots <<= 1;
     }
-    {
-      if (dalloc(&bt.wlHKey, bt.wlHSlots) != cudaSuccess) {
-        ctx->err = "batch workspace (pair table)";
-        return CBP_ERR_NOMEM;
-      }
-      bt.wlHActive = bt.wlHSlots;
-      bt.wlUsedCap = std::min(bt.wlHSlots, std::max(1u << 20, bt.wlItemCap));
-      if (dalloc(&bt.wlUsed, bt.wlUsedCap) != cudaSuccess) {
-        ctx->err = "batch workspace (pair table slots)";
-        return CBP_ERR_NOMEM;
-      }
-      bt.wlTableClean = false;
-    }
+    bt.wlHActive = bt.wlHSlots;
+    bt.wlUsedCap = std::min(bt.wlHSlots, std::max(1u << 20, bt.wlItemCap));
+    bt.wlTableClean = false;
     bt.wlWalkCap = mat->nLongBt > 0
       ? static_cast<unsigned>(std::min<size_t>(1u << 22, std::max<size_t>(1u << 16, static_cast<size_t>(Bp) * 256))) : 1u;
-    if (dalloc(&bt.wlWalk, bt.wlWalkCap) != cudaSuccess) {
-      ctx->err = "batch workspace (long-row queue)";
-      return CBP_ERR_NOMEM;
-    }
-    if (dalloc(&bt.wlItemsS[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsS[1], bt.wlItemCap) != cudaSuccess
-      || dalloc(&bt.wlItemsL[0], bt.wlItemCap) != cudaSuccess || dalloc(&bt.wlItemsL[1], bt.wlItemCap) != cudaSuccess
-      || dalloc(&bt.wlK, bt.wlCellCap) != cudaSuccess || dalloc(&bt.wlCells, bt.wlCellCap) != cudaSuccess
-      || dalloc(&bt.wlInts, static_cast<size_t>(Bp) * 4 + static_cast<size_t>(Bp / 32) * 2 + 8) != cudaSuccess) {
-      ctx->err = std::string("batch workspace (worklists): ") + cudaGetErrorString(cudaGetLastError());
-      return CBP_ERR_NOMEM;
-    }
-    if (dalloc(&bt.X[0], cells) != cudaSuccess || dalloc(&bt.X[1], cells) != cudaSuccess
-      || dalloc(&bt.dirty[0], words) != cudaSuccess || dalloc(&bt.dirty[1], words) != cudaSuccess
-      || dalloc(&bt.ever, words) != cudaSuccess || dalloc(&bt.active, Bp / 32) != cudaSuccess
-      || dalloc(&bt.dmask, words) != cudaSuccess
-      || dalloc(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp) != cudaSuccess
-      || dalloc(&bt.groupFlag, static_cast<size_t>(Bp / 32) + 2) != cudaSuccess
-      || dalloc(&bt.log, logCap) != cudaSuccess) {
-      ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
-      return CBP_ERR_NOMEM;
-    }
     {
       auto up256 = [](size_t x) { return (x + 255) & ~static_cast<size_t>(255); };
       bt.blobOffInts = up256(sizeof(WlCtl));
       bt.blobOffCounts = bt.blobOffInts + up256(sizeof(int) * (static_cast<size_t>(Bp) * 7 + 8));
       bt.blobOffHead = bt.blobOffCounts + up256(sizeof(long long) * (static_cast<size_t>(Bp) + 1));
       bt.blobBytes = bt.blobOffHead + sizeof(WlUpdHead) * static_cast<size_t>(kUpdPrefetch);
-      if (dalloc(&bt.blob, bt.blobBytes) != cudaSuccess
+      // one device allocation for the whole workspace (a first batch on a new matrix paid some twenty cudaMallocs)
+      struct Piece {
+        void **ptr;
+        size_t bytes;
+      };
+      auto piece = [](auto **p, size_t count) {
+        using T = typename std::remove_pointer<typename std::remove_pointer<decltype(p)>::type>::type;
+        return Piece { reinterpret_cast<void **>(p), std::max<size_t>(count, 1) * sizeof(T) };
+      };
+      const Piece pieces[] = { piece(&bt.wlHKey, bt.wlHSlots), piece(&bt.wlUsed, bt.wlUsedCap), piece(&bt.wlWalk, bt.wlWalkCap),
+        piece(&bt.wlItemsS[0], bt.wlItemCap), piece(&bt.wlItemsS[1], bt.wlItemCap), piece(&bt.wlItemsL[0], bt.wlItemCap),
+        piece(&bt.wlItemsL[1], bt.wlItemCap), piece(&bt.wlK, bt.wlCellCap), piece(&bt.wlCells, bt.wlCellCap),
+        piece(&bt.wlInts, static_cast<size_t>(Bp) * 4 + static_cast<size_t>(Bp / 32) * 2 + 8), piece(&bt.X[0], cells),
+        piece(&bt.X[1], cells), piece(&bt.dirty[0], words), piece(&bt.dirty[1], words), piece(&bt.ever, words),
+        piece(&bt.active, Bp / 32), piece(&bt.dmask, words),
+        piece(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp), piece(&bt.groupFlag, static_cast<size_t>(Bp / 32) + 2),
+        piece(&bt.log, logCap), piece(&bt.blob, bt.blobBytes), piece(&bt.wlRowBase, static_cast<size_t>(std::max(mat->mKept, 1))),
+        piece(&bt.baseLb, mat->n), piece(&bt.baseUb, mat->n), piece(&bt.baseX, mat->n) };
+      size_t total = 0;
+      for (const Piece &q : pieces)
+        total += up256(q.bytes);
+      if (cudaMalloc(reinterpret_cast<void **>(&bt.arena), total) != cudaSuccess
         || cudaHostAlloc(reinterpret_cast<void **>(&bt.hBlob), bt.blobBytes, cudaHostAllocDefault) != cudaSuccess) {
-        ctx->err = std::string("batch workspace (result block): ") + cudaGetErrorString(cudaGetLastError());
+        ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
+        if (bt.arena)
+          cudaFree(bt.arena);
+        bt.arena = nullptr;
         return CBP_ERR_NOMEM;
+      }
+      size_t at = 0;
+      for (const Piece &q : pieces) {
+        *q.ptr = bt.arena + at;
+        at += up256(q.bytes);
       }
       bt.wlCtl = reinterpret_cast<WlCtl *>(bt.blob);
       bt.ints = reinterpret_cast<int *>(bt.blob + bt.blobOffInts);
@@ -1455,19 +1450,6 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.dirty0Clean = bt.dmaskClean = false;
     // CBP_LOG_CAP: tests shrink the list to exercise the fall-back to the two-buffer first round
     bt.logCap = getenv("CBP_LOG_CAP") ? std::min<unsigned>(logCap, static_cast<unsigned>(atol(getenv("CBP_LOG_CAP")))) : logCap;
-  }
-  if (!bt.wlRowBase) {
-    if (dalloc(&bt.wlRowBase, static_cast<size_t>(std::max(mat->mKept, 1))) != cudaSuccess) {
-      ctx->err = "batch workspace: row sums";
-      return CBP_ERR_NOMEM;
-    }
-  }
-  if (!bt.baseLb) {
-    if (dalloc(&bt.baseLb, mat->n) != cudaSuccess || dalloc(&bt.baseUb, mat->n) != cudaSuccess
-      || dalloc(&bt.baseX, mat->n) != cudaSuccess) {
-      ctx->err = "batch workspace: base bounds";
-      return CBP_ERR_NOMEM;
-    }
   }
   bt.B = B;
   bt.Bp = Bp;
