@@ -163,7 +163,11 @@ CBP_API int cbp_propagate_batch_delta(cbp_matrix *mat, const double *baseLb, con
  * benchmark) can keep the inputs in HBM: load = upload base + deltas; run =
  * expand them into the per-vector bound arrays and do the round loop (may be
  * repeated: every run starts again from base + deltas); fetch = results and
- * changed bounds of the last run. */
+ * changed bounds of the last run.  A run in worklist form (cbp_stats.lastMode
+ * == 2) leaves every vector's result in pinned host memory when it returns,
+ * and — once a fetch on this matrix has asked for update lists (updStart !=
+ * NULL) — the lists too, ordered by column; fetching them is then a host-side
+ * copy. */
 CBP_API int cbp_batch_load_delta(cbp_matrix *mat, const double *baseLb, const double *baseUb,
   int B, const int64_t *deltaStart, const uint32_t *deltaVar, const double *deltaBound, int flags);
 CBP_API int cbp_batch_run(cbp_matrix *mat, double primalTol, int maxRounds, double timeLimitSec);
