@@ -5,6 +5,8 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <algorithm>
 
 #include "CbpDeviceCache.hpp"
 #include "OsiSolverInterface.hpp"
@@ -70,29 +72,48 @@ bool CbcStrongPropagation::run(OsiSolverInterface *solver, int numberToDo, const
   for (int b = 0; b <= B; ++b)
     start[b] = b;
 
+  // The device keeps a batch's bounds as [column][vector] cells (two buffers of 16 bytes): a sweep over every integer
+  // column of a large model (CbcNode::analyze, fixVubs) does not fit as one batch, so the arms go in pieces of at most
+  // CBP_BATCH_BYTES (default 16 GB) of cells — whole candidates, a multiple of 32 arms.
+  static const double batchBytes = getenv("CBP_BATCH_BYTES") ? atof(getenv("CBP_BATCH_BYTES")) : 16.0e9;
+  long long perCall = static_cast<long long>(batchBytes / (33.0 * static_cast<double>(nCols)));
+  perCall = std::max<long long>(64, perCall / 32 * 32);
   std::vector<cbp_result> res(B);
   std::vector<int64_t> updStart(B + 1, 0);
-  int64_t cap = 64 * static_cast<int64_t>(B) + 1024;
-  for (int attempt = 0; attempt < 2; ++attempt) {
-    updCol_.resize(cap);
-    updLb_.resize(cap);
-    updUb_.resize(cap);
-    const int rc = attempt == 0
-      ? cbp_propagate_batch_delta(mat, solver->getColLower(), solver->getColUpper(), B, start.data(), var.data(),
-          bnd.data(), primalTol, maxRounds, timeLimit, res.data(), cap, updStart.data(), updCol_.data(),
-          updLb_.data(), updUb_.data(), 0)
-      : cbp_batch_fetch(mat, res.data(), cap, updStart.data(), updCol_.data(), updLb_.data(), updUb_.data(), 0);
-    if (rc == CBP_OK)
-      break;
-    if (rc == CBP_ERR_CAPACITY && attempt == 0) {  // the offsets are valid: ask again with room for everything
-      cap = updStart[B];
-      continue;
+  std::vector<int64_t> pieceStart;
+  std::vector<int> pieceCol;
+  std::vector<double> pieceLb, pieceUb;
+  for (long long o = 0; o < B; o += perCall) {
+    const int Bc = static_cast<int>(std::min<long long>(perCall, B - o));
+    pieceStart.assign(static_cast<size_t>(Bc) + 1, 0);
+    int64_t cap = 64 * static_cast<int64_t>(Bc) + 1024;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+      pieceCol.resize(cap);
+      pieceLb.resize(cap);
+      pieceUb.resize(cap);
+      const int rc = attempt == 0
+        ? cbp_propagate_batch_delta(mat, solver->getColLower(), solver->getColUpper(), Bc, start.data(), var.data() + o,
+            bnd.data() + o, primalTol, maxRounds, timeLimit, res.data() + o, cap, pieceStart.data(), pieceCol.data(),
+            pieceLb.data(), pieceUb.data(), 0)
+        : cbp_batch_fetch(mat, res.data() + o, cap, pieceStart.data(), pieceCol.data(), pieceLb.data(), pieceUb.data(), 0);
+      if (rc == CBP_OK)
+        break;
+      if (rc == CBP_ERR_CAPACITY && attempt == 0) {  // the offsets are valid: ask again with room for everything
+        cap = pieceStart[Bc];
+        continue;
+      }
+      fprintf(stderr, "CbcStrongPropagation: device run failed (%d); no arm filtered\n", rc);
+      updCol_.clear();
+      updLb_.clear();
+      updUb_.clear();
+      return false;
     }
-    fprintf(stderr, "CbcStrongPropagation: device run failed (%d); no arm filtered\n", rc);
-    updCol_.clear();
-    updLb_.clear();
-    updUb_.clear();
-    return false;
+    const int64_t base = updStart[o];
+    for (int i = 0; i < Bc; ++i)
+      updStart[o + i + 1] = base + pieceStart[i + 1];
+    updCol_.insert(updCol_.end(), pieceCol.begin(), pieceCol.begin() + pieceStart[Bc]);
+    updLb_.insert(updLb_.end(), pieceLb.begin(), pieceLb.begin() + pieceStart[Bc]);
+    updUb_.insert(updUb_.end(), pieceUb.begin(), pieceUb.begin() + pieceStart[Bc]);
   }
   arm_.resize(B);
   for (int b = 0; b < B; ++b) {

@@ -113,9 +113,11 @@ def test_dive_step(oracle, tmp_path):
             assert res["infeasibleRow"] == r["infeasibleRow"] and res["reasonToStop"] == 1
 
 
-def test_strong_branching_arms_match_oracle(oracle, tmp_path):
-    """CbcStrongPropagation: the 2 x numberToDo arms of a strong-branching step as one batch,
-    against the oracle run arm by arm: verdicts, rounds, implied bounds, forced fixings."""
+@pytest.mark.parametrize("env", [{}, {"CBP_BATCH_BYTES": "1"}], ids=["one_batch", "pieces_of_64_arms"])
+def test_strong_branching_arms_match_oracle(oracle, tmp_path, env):
+    """CbcStrongPropagation: the 2 x numberToDo arms of a strong-branching step as one batch (or, when
+    they would not fit the device as one, in pieces: CBP_BATCH_BYTES), against the oracle run arm by arm: verdicts,
+    rounds, implied bounds, forced fixings."""
     inst = I.fast0507_shaped(m=101, n=9000, fix_frac=0.996, seed=22)
     r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
     inst.lb, inst.ub = lb0, ub0  # node bounds = propagated root
@@ -129,7 +131,7 @@ def test_strong_branching_arms_match_oracle(oracle, tmp_path):
         f.write(cols.tobytes())
         f.write(np.ascontiguousarray(vals, np.float64).tobytes())
     out = subprocess.run([DRIVER, ip, op, "3", "0", "0", "1e100", "strong", cp], capture_output=True, text=True,
-                         timeout=300)
+                         timeout=300, env=dict(os.environ, **env))
     assert out.returncode == 0, out.stderr
     res = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("RESULT ")][0][7:])
     assert res["ran"] == 1
@@ -242,7 +244,8 @@ def test_dive_batch_threads_match_oracle(oracle, tmp_path):
     assert off == len(raw)
 
 
-def test_probe_sweep_consequences(oracle, tmp_path):
+@pytest.mark.parametrize("env", [None, {"CBP_BATCH_BYTES": "1"}], ids=["one_batch", "pieces_of_64_arms"])
+def test_probe_sweep_consequences(oracle, tmp_path, env):
     """CbcProbePropagation: every free binary probed both ways as one batch; a failed probe fixes the
     column the other way (src/CbcSolverHeuristics.cpp:483-486), what both probes imply holds at the node; all of it
     recomputed here from oracle runs probe by probe."""
@@ -266,7 +269,7 @@ def test_probe_sweep_consequences(oracle, tmp_path):
     r0, lb0, ub0 = oracle.propagate(oracle.Problem(inst), inst.lb, inst.ub)
     inst.lb, inst.ub = lb0, ub0
     assert ub0[a] == 1.0 and lb0[d] == 0.0  # propagation alone does not see either conclusion
-    res, op = _drive_mode(tmp_path, inst, ["probe", "0"])
+    res, op = _drive_mode(tmp_path, inst, ["probe", "0"], extra_env=env)
     raw = open(op, "rb").read()
     (np_,) = struct.unpack_from("<i", raw, 0)
     probes = np.frombuffer(raw, np.int32, 3 * np_, 4).reshape(-1, 3)
