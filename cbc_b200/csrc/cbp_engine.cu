@@ -38,7 +38,55 @@ struct cbp_ctx {
   cbp_stats stats {};
   cudaEvent_t evA = nullptr, evB = nullptr;
   std::vector<cudaEvent_t> evPool;  // pairs, batch rounds
+  // Blocks of freed matrices (their arrays, their batch workspace, its pinned mirror) wait here for the next matrix
+  // of about the same size: a branch-and-cut run that gets a new matrix per node (the cuts changed) would otherwise
+  // pay cudaMalloc / cudaHostAlloc / cudaFree of the same sizes at every node.  All work on a block is on this
+  // context's stream, so the next owner's work is ordered behind the last owner's.
+  struct PoolBlock {
+    void *p;
+    size_t bytes;
+    bool host;
+  };
+  std::vector<PoolBlock> pool;
 };
+
+static void *pool_take(cbp_ctx *ctx, size_t bytes, bool host, size_t *got)
+{
+  int best = -1;
+  for (int i = 0; i < static_cast<int>(ctx->pool.size()); ++i) {
+    const cbp_ctx::PoolBlock &b = ctx->pool[i];
+    if (b.host == host && b.bytes >= bytes && b.bytes <= 2 * bytes + (static_cast<size_t>(64) << 20)
+      && (best < 0 || b.bytes < ctx->pool[best].bytes))
+      best = i;
+  }
+  if (best < 0)
+    return nullptr;
+  void *p = ctx->pool[best].p;
+  *got = ctx->pool[best].bytes;
+  ctx->pool.erase(ctx->pool.begin() + best);
+  return p;
+}
+
+static void pool_give(cbp_ctx *ctx, void *p, size_t bytes, bool host)
+{
+  if (!p)
+    return;
+  size_t held = 0;
+  int same = 0;
+  for (const cbp_ctx::PoolBlock &b : ctx->pool)
+    if (b.host == host) {
+      held += b.bytes;
+      ++same;
+    }
+  if (same >= 6 || held + bytes > (host ? (static_cast<size_t>(64) << 20) : (static_cast<size_t>(48) << 30))) {
+    if (host)
+      cudaFreeHost(p);
+    else
+      cudaFree(p);
+    return;
+  }
+  ctx->pool.push_back({ p, bytes, host });
+}
 
 struct BatchState {
   int B = 0, Bp = 0, G = 0;
@@ -102,6 +150,8 @@ struct BatchState {
   // control block | per-vector results | list offsets | head of the lists: one device block (wlCtl, ints and counts
   // point into it), so that ONE copy brings all a fetch needs to its pinned mirror
   unsigned char *arena = nullptr;  // the batch workspace below is one device allocation (bt_reserve)
+  size_t arenaBytes = 0, hBlobBytes = 0;
+  bool stInArena = false, st2InArena = false;  // the two sets of update-list buffers still are the arena's default ones
   unsigned char *blob = nullptr, *hBlob = nullptr;
   size_t blobOffInts = 0, blobOffCounts = 0, blobOffHead = 0, blobBytes = 0;
   long long headCopied = 0;     // list entries of the last run that are in the mirror
@@ -111,6 +161,35 @@ struct BatchState {
   unsigned wlPrevCells = 0;  // cells the last worklist run left in the masks
   bool wlMarksKnown = false; // dmask / ever / dirty are all zero except for those cells
 };
+
+// (the default-sized list buffers are part of the batch arena; grown ones are allocations of their own)
+static void bt_free_lists(BatchState &bt, bool first, bool second)
+{
+  if (first) {
+    if (!bt.stInArena) {
+      void *q[] = { bt.stCol, bt.stLb, bt.stUb };
+      for (void *x : q)
+        if (x)
+          cudaFree(x);
+    }
+    bt.stCol = nullptr;
+    bt.stLb = bt.stUb = nullptr;
+    bt.stCap = 0;
+    bt.stInArena = false;
+  }
+  if (second) {
+    if (!bt.st2InArena) {
+      void *q[] = { bt.st2Col, bt.st2Lb, bt.st2Ub };
+      for (void *x : q)
+        if (x)
+          cudaFree(x);
+    }
+    bt.st2Col = nullptr;
+    bt.st2Lb = bt.st2Ub = nullptr;
+    bt.st2Cap = 0;
+    bt.st2InArena = false;
+  }
+}
 
 struct cbp_matrix {
   cbp_ctx *ctx = nullptr;
@@ -143,7 +222,7 @@ struct cbp_matrix {
   RowAct *longPart = nullptr;
   // everything an upload allocates comes out of one device allocation (a second one only if the estimate fell short):
   // thirty cudaMallocs were a quarter of a small upload
-  std::vector<void *> arenaChunks;
+  std::vector<std::pair<void *, size_t>> arenaChunks;
   unsigned char *arenaCur = nullptr;
   size_t arenaLeft = 0, arenaHint = 0;
   Bnd *X[2] = { nullptr, nullptr };
@@ -203,6 +282,7 @@ static const EnvKnobs &knobs()
   return k;
 }
 
+static constexpr long long kListDefault = 1 << 16;  // update-list entries the batch arena has room for (a fetch grows beyond)
 static constexpr long long kUpdPrefetch = 32768;  // update-list entries a worklist run copies to the host unasked
 static constexpr size_t kSvSmallSmem = 0;
 static constexpr unsigned kBtLogCap = 16u << 20;  // candidate list of a list round: 16M entries (256 MB)  // the short-rows-only variant needs no dynamic shared memory
@@ -218,12 +298,14 @@ static cudaError_t mat_alloc(cbp_matrix *mat, T **p, size_t count)
 {
   const size_t bytes = (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~static_cast<size_t>(255);
   if (bytes > mat->arenaLeft) {
-    const size_t sz = std::max(bytes, std::max<size_t>(mat->arenaHint, static_cast<size_t>(1) << 20));
-    void *q = nullptr;
-    const cudaError_t e = cudaMalloc(&q, sz);
-    if (e != cudaSuccess)
-      return e;
-    mat->arenaChunks.push_back(q);
+    size_t sz = std::max(bytes, std::max<size_t>(mat->arenaHint, static_cast<size_t>(1) << 20));
+    void *q = pool_take(mat->ctx, sz, false, &sz);
+    if (!q) {
+      const cudaError_t e = cudaMalloc(&q, sz);
+      if (e != cudaSuccess)
+        return e;
+    }
+    mat->arenaChunks.push_back(std::make_pair(q, sz));
     mat->arenaCur = static_cast<unsigned char *>(q);
     mat->arenaLeft = sz;
     mat->arenaHint = sz / 4;  // (should the estimate have been short: a quarter as much again)
@@ -338,6 +420,14 @@ void cbp_destroy(cbp_ctx *ctx)
     cudaEventDestroy(ctx->evB);
   for (cudaEvent_t e : ctx->evPool)
     cudaEventDestroy(e);
+  cudaDeviceSynchronize();
+  for (const cbp_ctx::PoolBlock &b : ctx->pool) {
+    if (b.host)
+      cudaFreeHost(b.p);
+    else
+      cudaFree(b.p);
+  }
+  ctx->pool.clear();
   if (ctx->ownsStream && ctx->stream)
     cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -382,16 +472,16 @@ void cbp_matrix_free(cbp_matrix *mat)
   if (!mat)
     return;
   cudaSetDevice(mat->ctx->device);
-  for (void *q : mat->arenaChunks)  // (the matrix's own arrays and single-vector state)
-    cudaFree(q);
-  void *ptrs[] = { mat->bt.arena, mat->bt.dStart, mat->bt.dVar,
-    mat->bt.dBnd, mat->bt.stCol, mat->bt.stLb, mat->bt.stUb,
-    mat->bt.st2Col, mat->bt.st2Lb, mat->bt.st2Ub };
+  for (const std::pair<void *, size_t> &q : mat->arenaChunks)  // (the matrix's own arrays and single-vector state)
+    pool_give(mat->ctx, q.first, q.second, false);
+  pool_give(mat->ctx, mat->bt.arena, mat->bt.arenaBytes, false);
+  mat->bt.arena = nullptr;
+  bt_free_lists(mat->bt, true, true);
+  void *ptrs[] = { mat->bt.dStart, mat->bt.dVar, mat->bt.dBnd };
   for (void *p : ptrs)
     if (p)
       cudaFree(p);
-  if (mat->bt.hBlob)
-    cudaFreeHost(mat->bt.hBlob);
+  pool_give(mat->ctx, mat->bt.hBlob, mat->bt.hBlobBytes, true);
   for (int r = 0; r < mat->p2p.world; ++r)
     if (mat->p2p.attached && r != mat->p2p.rank && mat->p2p.peer[r])
       cudaIpcCloseMemHandle(mat->p2p.peer[r]);
@@ -1345,11 +1435,11 @@ static int bt_reserve(cbp_matrix *mat, int B)
   const int Bp = (B + 31) / 32 * 32;
   const size_t cells = static_cast<size_t>(mat->n) * Bp;
   if (cells > bt.capCells || Bp > bt.capBp) {
-    void *old[] = { bt.arena };
+    bt_free_lists(bt, true, true);
+    pool_give(ctx, bt.arena, bt.arenaBytes, false);
+    pool_give(ctx, bt.hBlob, bt.hBlobBytes, true);
     bt.arena = nullptr;
     bt.blob = nullptr;
-    if (bt.hBlob)
-      cudaFreeHost(bt.hBlob);
     bt.hBlob = nullptr;
     bt.wlWalk = nullptr;
     bt.wlUsed = nullptr;
@@ -1362,9 +1452,6 @@ static int bt_reserve(cbp_matrix *mat, int B)
     bt.wlInts = nullptr;
     bt.wlMarksKnown = false;
     bt.wlPrevCells = 0;
-    for (void *p : old)
-      if (p)
-        cudaFree(p);
     bt.X[0] = bt.X[1] = nullptr;
     bt.dirty[0] = bt.dirty[1] = bt.ever = bt.active = nullptr;
     bt.ints = nullptr;
@@ -1424,16 +1511,25 @@ static int bt_reserve(cbp_matrix *mat, int B)
         piece(&bt.active, Bp / 32), piece(&bt.dmask, words),
         piece(&bt.chunkCnt, static_cast<size_t>(cdiv(mat->n, kUpdChunk)) * Bp), piece(&bt.groupFlag, static_cast<size_t>(Bp / 32) + 2),
         piece(&bt.log, logCap), piece(&bt.blob, bt.blobBytes), piece(&bt.wlRowBase, static_cast<size_t>(std::max(mat->mKept, 1))),
-        piece(&bt.baseLb, mat->n), piece(&bt.baseUb, mat->n), piece(&bt.baseX, mat->n) };
+        piece(&bt.baseLb, mat->n), piece(&bt.baseUb, mat->n), piece(&bt.baseX, mat->n), piece(&bt.stCol, kListDefault),
+        piece(&bt.stLb, kListDefault), piece(&bt.stUb, kListDefault), piece(&bt.st2Col, kListDefault),
+        piece(&bt.st2Lb, kListDefault), piece(&bt.st2Ub, kListDefault) };
       size_t total = 0;
       for (const Piece &q : pieces)
         total += up256(q.bytes);
-      if (cudaMalloc(reinterpret_cast<void **>(&bt.arena), total) != cudaSuccess
-        || cudaHostAlloc(reinterpret_cast<void **>(&bt.hBlob), bt.blobBytes, cudaHostAllocDefault) != cudaSuccess) {
+      bt.arenaBytes = total;
+      bt.arena = static_cast<unsigned char *>(pool_take(ctx, total, false, &bt.arenaBytes));
+      bt.hBlobBytes = bt.blobBytes;
+      bt.hBlob = static_cast<unsigned char *>(pool_take(ctx, bt.blobBytes, true, &bt.hBlobBytes));
+      if ((!bt.arena && cudaMalloc(reinterpret_cast<void **>(&bt.arena), total) != cudaSuccess)
+        || (!bt.hBlob && cudaHostAlloc(reinterpret_cast<void **>(&bt.hBlob), bt.blobBytes, cudaHostAllocDefault) != cudaSuccess)) {
         ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
         if (bt.arena)
           cudaFree(bt.arena);
+        if (bt.hBlob)
+          cudaFreeHost(bt.hBlob);
         bt.arena = nullptr;
+        bt.hBlob = nullptr;
         return CBP_ERR_NOMEM;
       }
       size_t at = 0;
@@ -1441,6 +1537,8 @@ static int bt_reserve(cbp_matrix *mat, int B)
         *q.ptr = bt.arena + at;
         at += up256(q.bytes);
       }
+      bt.stCap = bt.st2Cap = kListDefault;
+      bt.stInArena = bt.st2InArena = true;
       bt.wlCtl = reinterpret_cast<WlCtl *>(bt.blob);
       bt.ints = reinterpret_cast<int *>(bt.blob + bt.blobOffInts);
       bt.counts = reinterpret_cast<long long *>(bt.blob + bt.blobOffCounts);
@@ -1601,14 +1699,8 @@ static int bt_list_buffers(cbp_matrix *mat)
   BatchState &bt = mat->bt;
   if (bt.stCap > 0 && bt.st2Cap > 0)
     return CBP_OK;
-  void *oldp[] = { bt.stCol, bt.stLb, bt.stUb, bt.st2Col, bt.st2Lb, bt.st2Ub };
-  for (void *q : oldp)
-    if (q)
-      cudaFree(q);
-  bt.stCol = bt.st2Col = nullptr;
-  bt.stLb = bt.stUb = bt.st2Lb = bt.st2Ub = nullptr;
-  bt.stCap = bt.st2Cap = 0;
-  const long long want = 1 << 16;
+  bt_free_lists(bt, true, true);
+  const long long want = kListDefault;
   if (dalloc(&bt.stCol, want) != cudaSuccess || dalloc(&bt.stLb, want) != cudaSuccess || dalloc(&bt.stUb, want) != cudaSuccess
     || dalloc(&bt.st2Col, want) != cudaSuccess || dalloc(&bt.st2Lb, want) != cudaSuccess || dalloc(&bt.st2Ub, want) != cudaSuccess) {
     mat->ctx->err = "batch workspace (update lists)";
@@ -2250,15 +2342,7 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
     auto grow = [&](int *&c, double *&l, double *&u, long long &cap) -> int {
       if (run <= cap)
         return CBP_OK;
-      if (c)
-        cudaFree(c);
-      if (l)
-        cudaFree(l);
-      if (u)
-        cudaFree(u);
-      c = nullptr;
-      l = u = nullptr;
-      cap = 0;
+      bt_free_lists(bt, &c == &bt.stCol, &c == &bt.st2Col);
       const long long want = std::max<long long>(run + run / 2, 1 << 16);
       if (dalloc(&c, want) != cudaSuccess || dalloc(&l, want) != cudaSuccess || dalloc(&u, want) != cudaSuccess) {
         ctx->err = "cbp_batch_fetch: staging";
@@ -2326,15 +2410,7 @@ int cbp_batch_fetch(cbp_matrix *mat, cbp_result *out, int64_t updCap, int64_t *u
   double *dLb = updLb, *dUb = updUb;
   if (!dev) {
     if (run > bt.stCap) {
-      if (bt.stCol)
-        cudaFree(bt.stCol);
-      if (bt.stLb)
-        cudaFree(bt.stLb);
-      if (bt.stUb)
-        cudaFree(bt.stUb);
-      bt.stCol = nullptr;
-      bt.stLb = bt.stUb = nullptr;
-      bt.stCap = 0;
+      bt_free_lists(bt, true, false);
       const long long cap = std::max<long long>(run + run / 2, 1 << 16);
       if (dalloc(&bt.stCol, cap) != cudaSuccess || dalloc(&bt.stLb, cap) != cudaSuccess || dalloc(&bt.stUb, cap) != cudaSuccess) {
         ctx->err = "cbp_batch_fetch: staging";
@@ -2485,6 +2561,8 @@ int cbp_propagate_batch_delta(cbp_matrix *mat, const double *baseLb, const doubl
   int rc = cbp_batch_load_delta(mat, baseLb, baseUb, B, deltaStart, deltaVar, deltaBound, flags);
   if (rc)
     return rc;
+  if (updStart)  // (the run then writes the lists itself: fetching them is a copy)
+    mat->bt.listsWanted = true;
   if ((rc = cbp_batch_run(mat, primalTol, maxRounds, timeLimitSec)))
     return rc;
   return cbp_batch_fetch(mat, out, updCap, updStart, updCol, updLb, updUb, flags);
