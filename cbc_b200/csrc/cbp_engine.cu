@@ -67,6 +67,19 @@ static void *pool_take(cbp_ctx *ctx, size_t bytes, bool host, size_t *got)
   return p;
 }
 
+// (before an allocation is given up for lack of memory: what this context holds back goes first)
+static void pool_flush(cbp_ctx *ctx)
+{
+  for (const cbp_ctx::PoolBlock &b : ctx->pool) {
+    if (b.host)
+      cudaFreeHost(b.p);
+    else
+      cudaFree(b.p);
+  }
+  ctx->pool.clear();
+  cudaGetLastError();
+}
+
 static void pool_give(cbp_ctx *ctx, void *p, size_t bytes, bool host)
 {
   if (!p)
@@ -78,7 +91,7 @@ static void pool_give(cbp_ctx *ctx, void *p, size_t bytes, bool host)
       held += b.bytes;
       ++same;
     }
-  if (same >= 6 || held + bytes > (host ? (static_cast<size_t>(64) << 20) : (static_cast<size_t>(48) << 30))) {
+  if (same >= 6 || held + bytes > (host ? (static_cast<size_t>(64) << 20) : (static_cast<size_t>(16) << 30))) {
     if (host)
       cudaFreeHost(p);
     else
@@ -301,7 +314,11 @@ static cudaError_t mat_alloc(cbp_matrix *mat, T **p, size_t count)
     size_t sz = std::max(bytes, std::max<size_t>(mat->arenaHint, static_cast<size_t>(1) << 20));
     void *q = pool_take(mat->ctx, sz, false, &sz);
     if (!q) {
-      const cudaError_t e = cudaMalloc(&q, sz);
+      cudaError_t e = cudaMalloc(&q, sz);
+      if (e != cudaSuccess) {
+        pool_flush(mat->ctx);
+        e = cudaMalloc(&q, sz);
+      }
       if (e != cudaSuccess)
         return e;
     }
@@ -1521,6 +1538,10 @@ static int bt_reserve(cbp_matrix *mat, int B)
       bt.arena = static_cast<unsigned char *>(pool_take(ctx, total, false, &bt.arenaBytes));
       bt.hBlobBytes = bt.blobBytes;
       bt.hBlob = static_cast<unsigned char *>(pool_take(ctx, bt.blobBytes, true, &bt.hBlobBytes));
+      if (!bt.arena && cudaMalloc(reinterpret_cast<void **>(&bt.arena), total) != cudaSuccess) {
+        bt.arena = nullptr;
+        pool_flush(ctx);
+      }
       if ((!bt.arena && cudaMalloc(reinterpret_cast<void **>(&bt.arena), total) != cudaSuccess)
         || (!bt.hBlob && cudaHostAlloc(reinterpret_cast<void **>(&bt.hBlob), bt.blobBytes, cudaHostAllocDefault) != cudaSuccess)) {
         ctx->err = std::string("batch workspace: ") + cudaGetErrorString(cudaGetLastError());
